@@ -1,0 +1,80 @@
+"""Seeded parity cases shared by the golden generator, the oracle tests and the GPU parity tests.
+
+Each case is (reads spec, overlapper flags).  Sizes are chosen so the CPU oracle finishes in
+seconds; the BASELINE.json shapes (C1..C5) are represented at reduced genome size.
+"""
+import helpers as H
+
+# name -> dict(gen=kwargs for gen_reads, erate="string as passed to --maxerate", params=overrides, threads=T, skip=bool)
+CASES = {
+    # C1 shape: corrected long reads, one hash block vs one query block
+    "c1_small": dict(gen=dict(genome_len=50000, coverage=20, len_min=1000, len_max=3000, err=0.02, seed=7),
+                     erate="0.06", params=dict(hash_bits=18, hash_load=0.75), threads=4),
+    # C2 shape: raw-noise reads, wide-band extension, hopeless check auto-off
+    "c2_noisy": dict(gen=dict(genome_len=30000, coverage=15, len_min=1500, len_max=3500, err=0.06, seed=1002),
+                     erate="0.15", params=dict(hash_bits=18, hash_load=0.75, kmer_len=17), threads=3),
+    # C4 shape: short reads, partial overlaps (-G), min length 40
+    "c4_short": dict(gen=dict(genome_len=20000, coverage=25, len_min=150, len_max=150, err=0.005, seed=1004, sub_only=True),
+                     erate="0.06", params=dict(hash_bits=16, hash_load=0.75, partial=1, min_olap_len=40), threads=2),
+    # several hash sub-blocks in one invocation (--hashstrings smaller than the -h range) + a -r sub-range
+    "multiblock": dict(gen=dict(genome_len=30000, coverage=12, len_min=800, len_max=2000, err=0.015, seed=21),
+                       erate="0.045", params=dict(hash_bits=17, hash_load=0.75, max_hash_strings=100,
+                                                  bgn_hash_id=20, end_hash_id=230, bgn_ref_id=5, end_ref_id=200), threads=1),
+    # hash-load cutoff trips (tiny table) -> Build_Hash_Index loads fewer reads than asked, several times
+    "loadlimit": dict(gen=dict(genome_len=20000, coverage=10, len_min=800, len_max=1500, err=0.01, seed=33),
+                      erate="0.06", params=dict(hash_bits=10, hash_load=0.8), threads=2),
+    # scheduler quirk: (end-bgn) % perThread == 0 drops the last query read; -m keeps multiple overlaps per pair
+    "quirk_m": dict(gen=dict(genome_len=15000, coverage=16, len_min=700, len_max=1600, err=0.02, seed=5),
+                    erate="0.06", params=dict(hash_bits=16, hash_load=0.75, unique_olap=0, bgn_ref_id=1, end_ref_id=161),
+                    threads=2),
+    # repeat-rich genome with a frequent-k-mer skip list (C5 shape)
+    "repeats_skip": dict(gen=dict(genome_len=60000, coverage=12, len_min=1000, len_max=2500, err=0.015, seed=1005,
+                                  repeat_frac=0.3, repeat_families=4, repeat_min=300, repeat_max=900, repeat_div=0.02),
+                         erate="0.06", params=dict(hash_bits=18, hash_load=0.75), threads=4, skip=True),
+    # -z: hopeless check off at low error rate
+    "nohopeless": dict(gen=dict(genome_len=20000, coverage=12, len_min=900, len_max=2000, err=0.025, seed=77),
+                       erate="0.06", params=dict(hash_bits=16, hash_load=0.75, use_hopeless_check=0), threads=2),
+}
+
+
+def build_case(name):
+    """-> (reads, params dict for the oracle, erate string, threads, skip k-mer list or None)"""
+    c = CASES[name]
+    reads = H.gen_reads(**c["gen"])
+    over = dict(c["params"])
+    over.setdefault("max_hash_strings", reads.n)
+    over.setdefault("max_hash_data_len", 100000000)
+    over.setdefault("end_hash_id", reads.n)
+    over.setdefault("end_ref_id", reads.n)
+    P = H.default_params(max_erate=H.strtof(c["erate"]), num_threads=c["threads"], **over)
+    skip = None
+    if c.get("skip"):
+        skip = frequent_kmers(reads, P["kmer_len"], 40)
+    return reads, P, c["erate"], c["threads"], skip
+
+
+def frequent_kmers(reads, K, threshold):
+    """Canonical-agnostic frequent k-mer list (what `meryl -Dt -n T` would feed `-k file`)."""
+    from collections import Counter
+    cnt = Counter()
+    for rid in range(1, reads.n + 1):
+        s = reads.seq(rid).lower()
+        for i in range(0, len(s) - K + 1):
+            cnt[s[i:i + K]] += 1
+    comp = str.maketrans("acgt", "tgca")
+    out = []
+    seen = set()
+    for k, v in sorted(cnt.items()):
+        rc = k.translate(comp)[::-1]
+        tot = v + (cnt.get(rc, 0) if rc != k else 0)
+        canon = min(k, rc)
+        if tot >= threshold and canon not in seen:
+            seen.add(canon)
+            out.append(canon)
+    return out
+
+
+def write_skip_file(kmers, path):
+    with open(path, "w") as f:
+        for k in kmers:
+            f.write(">1\n%s\n" % k)

@@ -1,0 +1,295 @@
+"""Test/bench harness helpers: seeded read generator, reference-tool wrappers, oracle bindings.
+
+Nothing here is on the product path.  The oracle (oracle/liboic_oracle.so) and the reference
+binaries (oracle/_ref/*) are only ever used as checkers / CPU baselines.
+"""
+import ctypes as C
+import os
+import subprocess
+import struct
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+TOOLS_DIR = os.path.join(ROOT, "tools")
+
+
+def _newer(src, dst):
+    return (not os.path.exists(dst)) or os.path.getmtime(src) > os.path.getmtime(dst)
+
+
+def build_harness_libs():
+    """Compile the generator and the oracle restatement (gcc/g++, seconds)."""
+    gen_src = os.path.join(TOOLS_DIR, "gen_reads.c")
+    gen_so = os.path.join(TOOLS_DIR, "libgenreads.so")
+    if _newer(gen_src, gen_so):
+        subprocess.check_call(["gcc", "-O2", "-fopenmp", "-shared", "-fPIC", gen_src, "-o", gen_so])
+    gen_bin = os.path.join(TOOLS_DIR, "gen_reads")
+    if _newer(gen_src, gen_bin):
+        subprocess.check_call(["gcc", "-O2", "-fopenmp", "-DGEN_MAIN", gen_src, "-o", gen_bin])
+    o_src = os.path.join(ORACLE_DIR, "oic_oracle.cpp")
+    o_so = os.path.join(ORACLE_DIR, "liboic_oracle.so")
+    if _newer(o_src, o_so) or _newer(os.path.join(ORACLE_DIR, "oic_oracle.h"), o_so):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", o_src, "-o", o_so])
+    return gen_so, o_so
+
+
+def have_ref():
+    return all(os.access(os.path.join(REF_DIR, t), os.X_OK)
+               for t in ("overlapInCore", "gatekeeperCreate", "overlapConvert"))
+
+
+# ----------------------------------------------------------------------------- generator
+
+class GenParams(C.Structure):
+    _fields_ = [("genome_len", C.c_uint64), ("coverage", C.c_double), ("len_min", C.c_uint32),
+                ("len_max", C.c_uint32), ("err", C.c_double), ("sub_only", C.c_int), ("seed", C.c_uint64),
+                ("repeat_frac", C.c_double), ("repeat_families", C.c_uint32), ("repeat_min", C.c_uint32),
+                ("repeat_max", C.c_uint32), ("repeat_div", C.c_double)]
+
+
+class Reads:
+    """Reads in memory: ASCII bases concatenated (uint8), offsets[n+1], lengths[n]. IDs are 1-based."""
+
+    def __init__(self, bases, offsets, lengths):
+        self.bases, self.offsets, self.lengths = bases, offsets, lengths
+        self.n = len(lengths)
+
+    def seq(self, rid):
+        o = int(self.offsets[rid - 1])
+        return self.bases[o:o + int(self.lengths[rid - 1])].tobytes().decode()
+
+    def write_fasta(self, path):
+        with open(path, "wb") as f:
+            for i in range(self.n):
+                f.write(b">read%d\n" % (i + 1))
+                o = int(self.offsets[i])
+                f.write(self.bases[o:o + int(self.lengths[i])].tobytes())
+                f.write(b"\n")
+
+
+def gen_reads(genome_len, coverage, len_min, len_max, err, seed, sub_only=False,
+              repeat_frac=0.0, repeat_families=0, repeat_min=1000, repeat_max=6000, repeat_div=0.02):
+    gen_so, _ = build_harness_libs()
+    lib = C.CDLL(gen_so)
+    lib.oic_gen_genome.restype = C.c_void_p
+    lib.oic_gen_genome.argtypes = [C.POINTER(GenParams)]
+    lib.oic_gen_num_reads.restype = C.c_uint64
+    lib.oic_gen_num_reads.argtypes = [C.POINTER(GenParams)]
+    lib.oic_gen_lengths.restype = C.c_uint64
+    lib.oic_gen_lengths.argtypes = [C.POINTER(GenParams), C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.oic_gen_fill.argtypes = [C.POINTER(GenParams), C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.oic_gen_free.argtypes = [C.c_void_p]
+    p = GenParams(genome_len, coverage, len_min, len_max, err, int(sub_only), seed,
+                  repeat_frac, repeat_families, repeat_min, repeat_max, repeat_div)
+    g = lib.oic_gen_genome(C.byref(p))
+    n = lib.oic_gen_num_reads(C.byref(p))
+    lengths = np.zeros(n, dtype=np.uint32)
+    total = lib.oic_gen_lengths(C.byref(p), g, n, lengths.ctypes.data)
+    offsets = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum(lengths, out=offsets[1:])
+    bases = np.zeros(total + 1, dtype=np.uint8)
+    lib.oic_gen_fill(C.byref(p), g, n, offsets.ctypes.data, bases.ctypes.data)
+    lib.oic_gen_free(g)
+    return Reads(bases[:total], offsets, lengths)
+
+
+# ----------------------------------------------------------------------------- reference tools
+
+def make_store(reads, workdir, minlength=0):
+    """reads -> FASTA -> reference gatekeeperCreate -> <workdir>/t.gkpStore"""
+    os.makedirs(workdir, exist_ok=True)
+    fa = os.path.join(workdir, "reads.fasta")
+    reads.write_fasta(fa)
+    gkp = os.path.join(workdir, "in.gkp")
+    with open(gkp, "w") as f:
+        f.write("name reads\npreset pacbio-corrected\n%s\n" % fa)
+    store = os.path.join(workdir, "t.gkpStore")
+    subprocess.check_call(["rm", "-rf", store])
+    subprocess.check_call([os.path.join(REF_DIR, "gatekeeperCreate"), "-minlength", str(minlength), "-o", store, gkp],
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return store
+
+
+def run_overlapper(binary, store, out_prefix, args, threads=4):
+    """Run an overlapInCore-compatible binary; returns (ovb path, stats path)."""
+    ovb = out_prefix + ".ovb"
+    stats = out_prefix + ".stats"
+    cmd = [binary, "-t", str(threads)] + list(args) + ["-o", ovb, "-s", stats, store]
+    with open(out_prefix + ".err", "w") as ef:
+        subprocess.check_call(cmd, stderr=ef, stdout=ef)
+    return ovb, stats
+
+
+def dump_ovb_sorted(store, ovb):
+    """reference overlapConvert -raw | sort  (the parity comparator of SURVEY.md 8(c))"""
+    out = subprocess.check_output([os.path.join(REF_DIR, "overlapConvert"), "-G", store, "-raw", ovb],
+                                  stderr=subprocess.DEVNULL)
+    lines = out.decode().splitlines()
+    lines.sort()
+    return lines
+
+
+def format_raw(o):
+    """Render decoded overlap fields the way ovOverlap::toString(ovOverlapAsRaw) does (ST/ovOverlap.C:67-79)."""
+    return "%10u %10u  %c  %6d  %6u %6u  %6u %6u  %7.6f %s %s %s" % (
+        o["a_iid"], o["b_iid"], "I" if o["flipped"] else "N", o["span"],
+        o["ahg5"], o["ahg3"], o["bhg5"], o["bhg3"], o["evalue"] / 10000.0,
+        "OBT" if o["for_obt"] else "   ", "DUP" if o["for_dup"] else "   ", "UTG" if o["for_utg"] else "   ")
+
+
+def parse_stats(path):
+    d = {}
+    for line in open(path):
+        if "=" in line:
+            k, v = line.split("=")
+            d[k.strip()] = int(v)
+    return d
+
+
+def decode_ovb(path):
+    """Native .ovb decoder (no reference tool): needs a snappy decompressor -> provided by canu_b200.ovb"""
+    from canu_b200 import ovb
+    return ovb.read_ovb(path)
+
+
+# ----------------------------------------------------------------------------- oracle
+
+class OracleParams(C.Structure):
+    _fields_ = [("kmer_len", C.c_int32), ("max_erate", C.c_double), ("min_olap_len", C.c_int32),
+                ("partial", C.c_int32), ("unique_olap", C.c_int32), ("use_hopeless_check", C.c_int32),
+                ("hash_bits", C.c_uint32), ("hash_load", C.c_double), ("max_hash_strings", C.c_uint32),
+                ("max_hash_data_len", C.c_uint64), ("frag_olap_limit", C.c_uint64),
+                ("filter_by_kmer_count", C.c_uint64), ("num_threads", C.c_uint32),
+                ("bgn_hash_id", C.c_uint32), ("end_hash_id", C.c_uint32),
+                ("bgn_ref_id", C.c_uint32), ("end_ref_id", C.c_uint32)]
+
+
+OVERLAP_DT = np.dtype([(n, np.uint32) for n in
+                       ("a_iid", "b_iid", "ahg5", "ahg3", "bhg5", "bhg3", "span", "evalue",
+                        "flipped", "for_obt", "for_dup", "for_utg")])
+MATCH_DT = np.dtype([("offset", np.int32), ("len", np.int32), ("start", np.int32)])
+PAIR_DT = np.dtype([("q_id", np.uint32), ("h_id", np.uint32), ("strand", np.uint32), ("consistent", np.uint32),
+                    ("diag_ct", np.int32), ("diag_bgn", np.int32), ("diag_end", np.int32), ("n_matches", np.uint32),
+                    ("first_match", np.uint64)])
+EXT_DT = np.dtype([("q_id", np.uint32), ("h_id", np.uint32), ("strand", np.uint32),
+                   ("m_offset", np.int32), ("m_len", np.int32), ("m_start", np.int32),
+                   ("s_lo", np.int32), ("s_hi", np.int32), ("t_lo", np.int32), ("t_hi", np.int32),
+                   ("errors", np.int32), ("kind", np.int32), ("delta_len", np.int32), ("delta_hash", np.int32)])
+STATS_FIELDS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skipped", "multi_overlap",
+                "total_overlaps", "contained", "dovetail", "n_hash_bases", "n_inserts", "n_distinct",
+                "n_query_bases", "n_windows", "n_found", "n_refs", "n_add_ref", "ext_calls", "ext_cells",
+                "ext_words"]
+
+
+class OracleStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in STATS_FIELDS] + [("n_hash_blocks", C.c_uint32), ("last_end_hash_id", C.c_uint32)]
+
+
+def strtof(s):
+    """--maxerate is parsed with strtof and widened to double (OIC/overlapInCore.C:395)."""
+    return float(np.float32(float(s)))
+
+
+def oracle_lib():
+    _, o_so = build_harness_libs()
+    lib = C.CDLL(o_so)
+    lib.oracle_create.restype = C.c_void_p
+    lib.oracle_create.argtypes = [C.POINTER(OracleParams), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p]
+    lib.oracle_set_skip_kmers.argtypes = [C.c_void_p, C.c_uint64, C.c_char_p]
+    lib.oracle_set_dump.argtypes = [C.c_void_p, C.c_uint32]
+    lib.oracle_run.argtypes = [C.c_void_p]
+    for name in ("overlaps", "pairs", "matches", "exts"):
+        getattr(lib, "oracle_num_" + name).restype = C.c_uint64
+        getattr(lib, "oracle_num_" + name).argtypes = [C.c_void_p]
+        getattr(lib, "oracle_" + name).restype = C.c_void_p
+        getattr(lib, "oracle_" + name).argtypes = [C.c_void_p]
+    lib.oracle_stats.restype = C.POINTER(OracleStats)
+    lib.oracle_stats.argtypes = [C.c_void_p]
+    lib.oracle_index_num_keys.restype = C.c_uint64
+    lib.oracle_index_num_keys.argtypes = [C.c_void_p]
+    for name in ("keys", "occ_start", "occ", "flags"):
+        getattr(lib, "oracle_index_" + name).restype = C.c_void_p
+        getattr(lib, "oracle_index_" + name).argtypes = [C.c_void_p]
+    lib.oracle_destroy.argtypes = [C.c_void_p]
+    lib.oracle_max_errors.restype = C.c_int32
+    lib.oracle_max_errors.argtypes = [C.c_double]
+    lib.oracle_match_limit.argtypes = [C.c_double, C.c_int32, C.c_void_p]
+    lib.oracle_error_bound.restype = C.c_int32
+    lib.oracle_error_bound.argtypes = [C.c_double, C.c_int32]
+    lib.oracle_extend.restype = C.c_int32
+    lib.oracle_extend.argtypes = [C.c_double, C.c_int32, C.c_char_p, C.c_int32, C.c_char_p, C.c_int32, C.c_int32,
+                                  C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                  C.c_void_p, C.c_void_p]
+    return lib
+
+
+def _copy(ptr, n, dt):
+    if n == 0:
+        return np.zeros(0, dtype=dt)
+    buf = (C.c_char * (n * dt.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dt).copy()
+
+
+def default_params(**kw):
+    d = dict(kmer_len=22, max_erate=strtof("0.06"), min_olap_len=500, partial=0, unique_olap=1,
+             use_hopeless_check=1, hash_bits=22, hash_load=0.6, max_hash_strings=10000,
+             max_hash_data_len=100000000, frag_olap_limit=2 ** 64 - 1, filter_by_kmer_count=0,
+             num_threads=1, bgn_hash_id=1, end_hash_id=2 ** 32 - 1, bgn_ref_id=1, end_ref_id=2 ** 32 - 1)
+    d.update(kw)
+    if d["max_erate"] > 0.06:
+        d["use_hopeless_check"] = 0
+    return d
+
+
+def run_oracle(reads, params, dump=0, skip_kmers=None):
+    """Run the CPU restatement. Returns dict(overlaps, stats, pairs, matches, exts, index)."""
+    lib = oracle_lib()
+    p = OracleParams(**params)
+    offs = np.ascontiguousarray(reads.offsets[:-1], dtype=np.uint64)
+    lens = np.ascontiguousarray(reads.lengths, dtype=np.uint32)
+    bases = np.ascontiguousarray(reads.bases)
+    ctx = lib.oracle_create(C.byref(p), reads.n, offs.ctypes.data, lens.ctypes.data, bases.ctypes.data, None, None)
+    if skip_kmers:
+        lib.oracle_set_skip_kmers(ctx, len(skip_kmers), "".join(skip_kmers).encode())
+    lib.oracle_set_dump(ctx, dump)
+    lib.oracle_run(ctx)
+    res = {}
+    res["overlaps"] = _copy(lib.oracle_overlaps(ctx), lib.oracle_num_overlaps(ctx), OVERLAP_DT)
+    st = lib.oracle_stats(ctx).contents
+    res["stats"] = {n: getattr(st, n) for n in STATS_FIELDS + ["n_hash_blocks", "last_end_hash_id"]}
+    res["pairs"] = _copy(lib.oracle_pairs(ctx), lib.oracle_num_pairs(ctx), PAIR_DT)
+    res["matches"] = _copy(lib.oracle_matches(ctx), lib.oracle_num_matches(ctx), MATCH_DT)
+    res["exts"] = _copy(lib.oracle_exts(ctx), lib.oracle_num_exts(ctx), EXT_DT)
+    nk = lib.oracle_index_num_keys(ctx)
+    if nk:
+        u64 = np.dtype(np.uint64)
+        res["index"] = dict(keys=_copy(lib.oracle_index_keys(ctx), nk, u64),
+                            occ_start=_copy(lib.oracle_index_occ_start(ctx), nk + 1, u64),
+                            flags=_copy(lib.oracle_index_flags(ctx), nk, np.dtype(np.uint8)))
+        res["index"]["occ"] = _copy(lib.oracle_index_occ(ctx), int(res["index"]["occ_start"][-1]), u64)
+    lib.oracle_destroy(ctx)
+    return res
+
+
+def oic_args(params, erate_str):
+    """argv (minus -t/-o/-s/store) for an overlapInCore-compatible binary equivalent to an oracle param dict."""
+    a = []
+    if params["partial"]:
+        a.append("-G")
+    if not params["unique_olap"]:
+        a.append("-m")
+    if not params["use_hopeless_check"] and float(erate_str) <= 0.06:
+        a.append("-z")
+    a += ["-k", str(params["kmer_len"]), "--hashbits", str(params["hash_bits"]),
+          "--hashload", repr(params["hash_load"]), "--maxerate", erate_str,
+          "--minlength", str(params["min_olap_len"]),
+          "--hashstrings", str(params["max_hash_strings"]), "--hashdatalen", str(params["max_hash_data_len"])]
+    if params["end_hash_id"] != 2 ** 32 - 1 or params["bgn_hash_id"] != 1:
+        a += ["-h", "%d-%d" % (params["bgn_hash_id"], params["end_hash_id"])]
+    if params["end_ref_id"] != 2 ** 32 - 1 or params["bgn_ref_id"] != 1:
+        a += ["-r", "%d-%d" % (params["bgn_ref_id"], params["end_ref_id"])]
+    return a

@@ -113,7 +113,8 @@ static uint32_t gen_one(const gen_params_t *p, const uint8_t *g, uint64_t i, cha
         if (out) out[n] = ACGT[b];
         n++;
       } else if (t < 0.8) { /* insertion: extra random base, then the true base */
-        if (out) out[n] = ACGT[splitmix64(&s) & 3];
+        uint8_t ib = splitmix64(&s) & 3; /* drawn in both passes: the length pass must consume the same stream */
+        if (out) out[n] = ACGT[ib];
         n++;
         if (out) out[n] = ACGT[b];
         n++;
