@@ -1,0 +1,902 @@
+/*
+ * oic_b200.cu -- context, host orchestration and the C ABI (include/oic_b200.h) of the B200-native
+ * overlapInCore path.  Kernels live in oic_build.cuh (pack + k-mer index), oic_search.cuh (seed scan, run
+ * grouping, Add_Match replay) and oic_extend.cuh (banded prefix edit distance + overlap output).
+ *
+ * Reference call stack replaced: OverlapDriver -> Build_Hash_Index -> Process_Overlaps ->
+ * Find_Overlaps -> Process_String_Olaps -> Process_Matches -> Extend_Alignment -> Output_Overlap.
+ * There is no CPU implementation of any stage in this library: every entry point needs a CUDA device.
+ */
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/oic_b200.h"
+#include "oic_extend.cuh"
+
+using namespace oic;
+
+namespace {
+
+std::string g_create_error;
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { e = cudaMalloc(&p, bytes); want = bytes; }
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// ---- host tables: Edit_Match_Limit (LIBO/Binomial_Bound.C:47-107,119-194, BITS == 21 slope) ------------------
+// Smallest n >= start such that more than e errors in n bases at rate p is not "improbable" (1e-4).
+int binomial_bound(int e, double p, int start) {
+  const double PROB_BOUND = 1e-4, NORMAL_THOLD = 3.62;
+  const double q = 1.0 - p;
+  if (start < e) start = e;
+  for (int n = start; n < MAX_READLEN; n++) {
+    if (n <= 35) {   // exact binomial tail
+      double sum = 0.0, p_power = 1.0, q_power = pow(q, n);
+      int binom = 1, ct = 0;
+      for (int k = 0; k < e && 1.0 - sum > PROB_BOUND; k++) {
+        sum += binom * p_power * q_power;
+        binom *= n - ct;
+        binom /= ++ct;
+        p_power *= p;
+        q_power /= q;
+      }
+      if (1.0 - sum > PROB_BOUND) return n;
+    } else {         // normal test first, then the Poisson sum
+      const double np = n * p;
+      const double z = (e - 0.5 - np) / sqrt(np * q);
+      if (z <= NORMAL_THOLD) return n;
+      double sum = 0.0, mu_power = 1.0, factorial = 1.0;
+      const double poisson_coeff = exp(-np);
+      for (int k = 0; k < e; k++) {
+        sum += mu_power * poisson_coeff / factorial;
+        mu_power *= np;
+        factorial *= k + 1;
+      }
+      if (1.0 - sum > PROB_BOUND) return n;
+    }
+  }
+  return MAX_READLEN;
+}
+
+void build_match_limit(double erate, int n_entries, std::vector<int32_t> &ml) {
+  const int max_errors = 1 + (int)ceil(erate * MAX_READLEN);   // LIBO/prefixEditDistance.C:39
+  ml.assign(std::max(n_entries, 2), 0);
+  const int exact = std::min(max_errors, 2000);
+  int e = 2, start = 1;
+  for (; e < exact && e < n_entries; e++) {
+    start = binomial_bound(e - 1, erate, start);
+    ml[e] = start - 1;
+  }
+  if (e < n_entries) {
+    // the reference fills the rest linearly from the last exact entry (which we must have computed)
+    const double sl = 0.982064188397525 / erate + 0.067835741959926;
+    double vl = ml[e - 1] + sl;
+    for (; e < n_entries; e++) {
+      ml[e] = (int32_t)ceil(vl);
+      vl += sl;
+    }
+  }
+}
+
+}  // namespace
+
+struct oic_ctx {
+  oic_params_t P;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint32_t debug = 0;
+
+  // reads
+  uint32_t first_id = 0, n_reads = 0;
+  std::vector<int64_t> h_pos;
+  std::vector<uint32_t> h_len;
+  std::vector<uint8_t> h_hash_ok, h_ref_ok;
+  uint64_t stream_words = 0;
+  uint32_t max_read_len = 0;
+  DevBuf d_fwd, d_rc, d_pos, d_len;
+
+  // host tables on device
+  int max_rows = 0;
+  DevBuf d_match_limit;
+
+  // skip k-mers (both orientations, as keys)
+  std::vector<uint64_t> skip_keys;
+  DevBuf d_skip_keys;
+
+  // hash block
+  bool hash_ready = false;
+  oic_hash_meta_t hb = {};
+  DevBuf d_table, d_occ, d_str_flags, d_str_use, d_win_slot, d_blk, d_big_list, d_occ_tmp, d_hist;
+
+  // search buffers
+  DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
+      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas;
+  DevBuf d_ctr, d_flag;
+  uint64_t rec_cap = 0;       // run records per batch
+  uint64_t batch_bases = 0;
+
+  std::vector<oic_ovb_record_t> overlaps;
+  oic_stats_t stats = {};
+  oic_timings_t tm = {};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+
+  // debug dumps of the last oic_process_overlaps call
+  std::vector<int64_t> dbg_pairs;
+  std::vector<int32_t> dbg_matches;
+
+  int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    err = buf;
+    return code;
+  }
+};
+
+#define CK(call)                                                                                             \
+  do {                                                                                                       \
+    cudaError_t e_ = (call);                                                                                 \
+    if (e_ != cudaSuccess) return c->fail(OIC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+namespace {
+
+inline unsigned nblocks(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+
+struct StageTimer {
+  oic_ctx *c;
+  float *acc;
+  StageTimer(oic_ctx *c_, float *acc_) : c(c_), acc(acc_) { cudaEventRecord(c->ev[0], c->stream); }
+  void stop() {
+    cudaEventRecord(c->ev[1], c->stream);
+    cudaEventSynchronize(c->ev[1]);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+    *acc += ms;
+  }
+};
+
+int read_counters(oic_ctx *c, DevCounters &h) {
+  CK(cudaMemcpyAsync(&h, c->d_ctr.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->tm.d2h_bytes += sizeof(h);
+  return 0;
+}
+int zero_counters(oic_ctx *c) {
+  CK(cudaMemsetAsync(c->d_ctr.p, 0, sizeof(DevCounters), c->stream));
+  return 0;
+}
+
+__global__ void k_table_init(Slot *t, uint64_t n) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) reinterpret_cast<uint4 *>(t)[i] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
+}
+
+// ---- hash build ------------------------------------------------------------------------------------------
+// Builds the index over string slots [0, n_strings) starting at read index ri_bgn; use[] says which are loaded.
+int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vector<uint8_t> &use, DevCounters &hc) {
+  const oic_params_t &P = c->P;
+  const int K = P.kmer_len;
+  uint64_t n_windows = 0;
+  for (uint32_t s = 0; s < n_strings; s++)
+    if (use[s] && c->h_len[ri_bgn + s] >= (uint32_t)K) n_windows += c->h_len[ri_bgn + s] - K + 1;
+  if (n_windows >= (1ull << 31)) return c->fail(OIC_ERR_CAPACITY, "hash block has %llu k-mers (limit 2^31)", (unsigned long long)n_windows);
+  uint64_t want = 2 * (n_windows + c->skip_keys.size()) + 16;
+  uint64_t slots = 1024;
+  while (slots < want) slots <<= 1;
+
+  CK(c->d_table.ensure(slots * sizeof(Slot)));
+  CK(c->d_str_flags.ensure(((size_t)n_strings + 8) & ~(size_t)3));
+  CK(c->d_str_use.ensure((size_t)n_strings + 4));
+  const int64_t region_pos = c->h_pos[ri_bgn];
+  const uint32_t ri_last = ri_bgn + n_strings - 1;
+  const int64_t region_end = c->h_pos[ri_last] + c->h_len[ri_last];
+  const uint64_t region_words = (uint64_t)((region_end - region_pos + 31) >> 5);
+  CK(c->d_win_slot.ensure(region_words * 32 * sizeof(uint32_t)));
+  const uint64_t n_scan_blocks = (slots + SCAN_ITEMS - 1) / SCAN_ITEMS;
+  CK(c->d_blk.ensure((n_scan_blocks + 2) * sizeof(uint32_t)));
+
+  if (zero_counters(c)) return OIC_ERR_CUDA;
+  k_table_init<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots);
+  CK(cudaMemsetAsync(c->d_str_flags.p, 0, ((size_t)n_strings + 8) & ~(size_t)3, c->stream));
+  CK(cudaMemcpyAsync(c->d_str_use.p, use.data(), n_strings, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += n_strings;
+  CK(cudaMemsetAsync(c->d_win_slot.p, 0xff, region_words * 32 * sizeof(uint32_t), c->stream));
+
+  BuildArgs a;
+  a.fwd = c->d_fwd.as<uint64_t>();
+  a.rd_pos = c->d_pos.as<int64_t>();
+  a.rd_len = c->d_len.as<uint32_t>();
+  a.str_use = c->d_str_use.as<uint8_t>();
+  a.ri_bgn = ri_bgn;
+  a.n_strings = n_strings;
+  a.region_pos = region_pos;
+  a.region_words = region_words;
+  a.K = K;
+  a.table = c->d_table.as<Slot>();
+  a.slot_mask = slots - 1;
+  a.win_slot = c->d_win_slot.as<uint32_t>();
+  a.occ = nullptr;
+  a.ctr = c->d_ctr.as<DevCounters>();
+
+  k_insert<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
+  k_scan_slots_reduce<<<(unsigned)n_scan_blocks, SCAN_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_blk.as<uint32_t>());
+  k_scan_u32_single<<<1, SCAN_THREADS, 0, c->stream>>>(c->d_blk.as<uint32_t>(), (uint32_t)n_scan_blocks);
+  k_scan_slots_apply<<<(unsigned)n_scan_blocks, SCAN_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_blk.as<uint32_t>());
+  c->tm.launches += 5;
+  uint32_t n_occ = 0;
+  CK(cudaMemcpyAsync(&n_occ, c->d_blk.as<uint32_t>() + n_scan_blocks, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->tm.d2h_bytes += 4;
+  if (n_occ != n_windows) return c->fail(OIC_ERR_STATE, "internal: %u occurrences counted, %llu expected", n_occ, (unsigned long long)n_windows);
+
+  CK(c->d_occ.ensure(((size_t)n_occ + 32) * sizeof(uint64_t)));
+  CK(c->d_big_list.ensure(((size_t)n_occ / 33 + 2) * sizeof(uint32_t)));
+  a.occ = c->d_occ.as<uint64_t>();
+  k_fill<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
+  k_sort_small<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_occ.as<uint64_t>(), c->d_big_list.as<uint32_t>(),
+                                                             c->d_ctr.as<DevCounters>());
+  c->tm.launches += 2;
+  if (read_counters(c, hc)) return OIC_ERR_CUDA;
+  if (hc.n_big_lists) {
+    CK(c->d_occ_tmp.ensure(((size_t)n_occ + 32) * sizeof(uint64_t)));
+    unsigned grid = std::min<unsigned>(hc.n_big_lists, 148 * 8);
+    k_sort_big<<<grid, BIG_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), c->d_big_list.as<uint32_t>(), hc.n_big_lists, c->d_occ.as<uint64_t>(),
+                                                    c->d_occ_tmp.as<uint64_t>());
+    c->tm.launches += 1;
+  }
+  c->hb.table_slots = slots;
+  c->hb.n_occ = n_occ;
+  c->hb.n_strings = n_strings;
+  c->hb.n_distinct = hc.n_distinct;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// ================================================================================================ C ABI
+extern "C" {
+
+const char *oic_last_error(const oic_ctx_t *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
+  if (!p || !out) { g_create_error = "null argument"; return OIC_ERR_ARG; }
+  *out = nullptr;
+  if (p->kmer_len < 2 || p->kmer_len > 31) { g_create_error = "k-mer length must be 2..31 in this build"; return OIC_ERR_UNSUPPORTED; }
+  if (p->frag_olap_limit != UINT64_MAX) { g_create_error = "-l (per-end overlap limit) is not supported in this build"; return OIC_ERR_UNSUPPORTED; }
+  if (!(p->max_erate > 0.0) || p->max_erate >= 1.0) { g_create_error = "bad --maxerate"; return OIC_ERR_ARG; }
+  if (p->max_hash_strings == 0 || p->num_threads == 0) { g_create_error = "bad --hashstrings / -t"; return OIC_ERR_ARG; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU path)";
+    return OIC_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) { g_create_error = "bad device index"; return OIC_ERR_ARG; }
+  if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OIC_ERR_CUDA; }
+  oic_ctx *c = new oic_ctx();
+  c->P = *p;
+  if (c->P.max_erate > 0.06) c->P.use_hopeless_check = 0;   // OIC/overlapInCore.C:416-421
+  c->device = device;
+  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess ||
+      (e = c->d_ctr.ensure(sizeof(DevCounters))) != cudaSuccess) {
+    g_create_error = cudaGetErrorString(e);
+    delete c;
+    return OIC_ERR_CUDA;
+  }
+  cudaMemset(c->d_ctr.p, 0, sizeof(DevCounters));
+  const char *rc = getenv("OIC_REC_CAP"), *bb = getenv("OIC_BATCH_BASES");
+  c->rec_cap = rc ? strtoull(rc, nullptr, 10) : (48ull << 20);
+  c->batch_bases = bb ? strtoull(bb, nullptr, 10) : (24ull << 20);
+  *out = c;
+  return OIC_OK;
+}
+
+void oic_destroy(oic_ctx_t *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  DevBuf *bufs[] = {&c->d_fwd, &c->d_rc, &c->d_pos, &c->d_len, &c->d_match_limit, &c->d_skip_keys, &c->d_table, &c->d_occ,
+                    &c->d_str_flags, &c->d_str_use, &c->d_win_slot, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
+                    &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
+                    &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
+                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas,
+                    &c->d_ctr, &c->d_flag};
+  for (DevBuf *b : bufs) b->release();
+  if (c->ev[0]) cudaEventDestroy(c->ev[0]);
+  if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+void oic_set_debug(oic_ctx_t *c, uint32_t mask) { c->debug = mask; }
+
+int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *offsets, const uint32_t *lengths,
+                   const char *bases, const uint8_t *hash_ok, const uint8_t *ref_ok) {
+  if (!c || (n && (!offsets || !lengths || !bases)) || first_id < 1) return c ? c->fail(OIC_ERR_ARG, "oic_load_reads: bad argument") : OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  c->hash_ready = false;
+  c->first_id = first_id;
+  c->n_reads = n;
+  c->h_pos.resize(n + 1);
+  c->h_len.assign(lengths, lengths + n);
+  c->h_hash_ok.assign(n, 1);
+  c->h_ref_ok.assign(n, 1);
+  if (hash_ok) c->h_hash_ok.assign(hash_ok, hash_ok + n);
+  if (ref_ok) c->h_ref_ok.assign(ref_ok, ref_ok + n);
+  int64_t pos = READ_LEAD_BASES;
+  uint64_t asc_lo = UINT64_MAX, asc_hi = 0;
+  c->max_read_len = 0;
+  for (uint32_t i = 0; i < n; i++) {
+    if (lengths[i] > (uint32_t)MAX_READLEN) return c->fail(OIC_ERR_ARG, "read %u longer than AS_MAX_READLEN", first_id + i);
+    c->h_pos[i] = pos;
+    pos = (pos + lengths[i] + READ_PAD_BASES + 31) & ~(int64_t)31;
+    asc_lo = std::min(asc_lo, offsets[i]);
+    asc_hi = std::max(asc_hi, offsets[i] + lengths[i]);
+    c->max_read_len = std::max(c->max_read_len, lengths[i]);
+  }
+  c->h_pos[n] = pos;
+  c->stream_words = (uint64_t)(pos >> 5) + 4;
+  if (n == 0) return OIC_OK;
+
+  StageTimer t(c, &c->tm.ms_pack);
+  CK(c->d_fwd.ensure(c->stream_words * 8));
+  CK(c->d_rc.ensure(c->stream_words * 8));
+  CK(c->d_pos.ensure((size_t)(n + 1) * 8));
+  CK(c->d_len.ensure((size_t)(n + 1) * 4));
+  DevBuf d_ascii, d_off;
+  const uint64_t asc_bytes = asc_hi - asc_lo;
+  CK(d_ascii.ensure(asc_bytes + 64));
+  CK(d_off.ensure((size_t)n * 8));
+  std::vector<uint64_t> rel(n);
+  for (uint32_t i = 0; i < n; i++) rel[i] = offsets[i] - asc_lo;
+  CK(cudaMemcpyAsync(d_ascii.p, bases + asc_lo, asc_bytes, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d_off.p, rel.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_pos.p, c->h_pos.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_len.p, c->h_len.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += asc_bytes + (uint64_t)n * 20 + 8;
+  if (zero_counters(c)) return OIC_ERR_CUDA;
+  k_pack_reads<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<char>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
+                                                                     c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
+                                                                     c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>());
+  c->tm.launches += 1;
+  DevCounters hc;
+  int rcode = read_counters(c, hc);
+  d_ascii.release();
+  d_off.release();
+  if (rcode) return rcode;
+  CK(cudaGetLastError());
+  t.stop();
+  if (hc.bad_base) return c->fail(OIC_ERR_BASES, "a loaded read contains a non-ACGT base; not supported in this build");
+
+  // Edit_Match_Limit for every row an extension can reach: error limit <= ceil(erate * longest read)
+  c->max_rows = (int)ceil(c->P.max_erate * (double)c->max_read_len) + 3;
+  std::vector<int32_t> ml;
+  build_match_limit(c->P.max_erate, c->max_rows + 1, ml);
+  CK(c->d_match_limit.ensure(ml.size() * 4));
+  CK(cudaMemcpyAsync(c->d_match_limit.p, ml.data(), ml.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->tm.h2d_bytes += ml.size() * 4;
+  return OIC_OK;
+}
+
+int oic_set_skip_kmers(oic_ctx_t *c, uint64_t n, const char *kmers) {
+  if (!c || (n && !kmers)) return OIC_ERR_ARG;
+  const int K = c->P.kmer_len;
+  c->skip_keys.clear();
+  c->skip_keys.reserve(2 * n);
+  auto code = [](char ch) -> int {
+    switch (ch) { case 'c': case 'C': return 1; case 'g': case 'G': return 2; case 't': case 'T': return 3; default: return 0; }
+  };
+  auto rc_code = [](char ch) -> int {   // AS_UTL_reverseComplement table: non-ACGT -> NUL, which codes as 0
+    switch (ch) { case 'a': case 'A': return 3; case 'c': case 'C': return 2; case 'g': case 'G': return 1; default: return 0; }
+  };
+  for (uint64_t i = 0; i < n; i++) {
+    const char *s = kmers + i * K;
+    uint64_t kf = 0, kr = 0;
+    for (int j = 0; j < K; j++) {
+      kf |= (uint64_t)code(s[j]) << (2 * j);
+      kr |= (uint64_t)rc_code(s[K - 1 - j]) << (2 * j);
+    }
+    c->skip_keys.push_back(kf);
+    c->skip_keys.push_back(kr);
+  }
+  return OIC_OK;
+}
+
+int oic_build_hash_index(oic_ctx_t *c, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id) {
+  if (!c) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  const oic_params_t &P = c->P;
+  c->hash_ready = false;
+  if (bgn_id < c->first_id || end_id >= c->first_id + c->n_reads || c->n_reads == 0)
+    return c->fail(OIC_ERR_ARG, "hash range %u-%u outside the loaded reads %u-%u", bgn_id, end_id, c->first_id, c->first_id + c->n_reads - 1);
+  StageTimer t(c, &c->tm.ms_build);
+  // which reads the reference's load loop would take, ignoring the hash-load limit (Build_Hash_Index.C:538-616)
+  std::vector<uint8_t> use;
+  uint64_t total_len = 0;
+  uint32_t cur = bgn_id;
+  while (use.size() < P.max_hash_strings && total_len < P.max_hash_data_len && cur <= end_id) {
+    const uint32_t ri = cur - c->first_id;
+    uint8_t u = c->h_hash_ok[ri] && (int64_t)c->h_len[ri] >= (int64_t)P.min_olap_len;
+    if (u) total_len += c->h_len[ri] + 1;
+    use.push_back(u);
+    cur++;
+  }
+  uint32_t n_strings = (uint32_t)use.size();
+  if (n_strings == 0) { if (last_id) *last_id = end_id; t.stop(); return c->fail(OIC_ERR_ARG, "empty hash range"); }
+  const uint64_t hash_entry_limit = (uint64_t)(P.hash_load * (double)((uint64_t)1 << P.hash_bits) * 21);   // Build_Hash_Index.C:474
+  const uint32_t ri_bgn = bgn_id - c->first_id;
+
+  DevCounters hc;
+  int rcode = build_block(c, ri_bgn, n_strings, use, hc);
+  if (rcode) return rcode;
+  if (hc.n_distinct >= hash_entry_limit) {
+    // the load loop stops taking reads once Hash_Entries >= limit: find the read at which that happens
+    CK(c->d_hist.ensure((size_t)n_strings * 4));
+    CK(cudaMemsetAsync(c->d_hist.p, 0, (size_t)n_strings * 4, c->stream));
+    k_first_occ<<<nblocks(c->hb.table_slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), c->hb.table_slots, c->d_occ.as<uint64_t>(),
+                                                                        c->d_hist.as<uint32_t>());
+    c->tm.launches += 1;
+    std::vector<uint32_t> hist(n_strings);
+    CK(cudaMemcpyAsync(hist.data(), c->d_hist.p, (size_t)n_strings * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->tm.d2h_bytes += (uint64_t)n_strings * 4;
+    uint64_t cum = 0;
+    uint32_t cut = n_strings;
+    for (uint32_t s = 0; s < n_strings; s++) {
+      cum += hist[s];
+      if (cum >= hash_entry_limit) { cut = s + 1; break; }
+    }
+    if (cut < n_strings) {
+      n_strings = cut;
+      use.resize(n_strings);
+      rcode = build_block(c, ri_bgn, n_strings, use, hc);
+      if (rcode) return rcode;
+    }
+  }
+  // screened k-mers
+  unsigned int has_empty = 0;
+  if (!c->skip_keys.empty()) {
+    CK(c->d_skip_keys.ensure(c->skip_keys.size() * 8));
+    CK(c->d_flag.ensure(16));
+    CK(cudaMemsetAsync(c->d_flag.p, 0, 16, c->stream));
+    CK(cudaMemcpyAsync(c->d_skip_keys.p, c->skip_keys.data(), c->skip_keys.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    c->tm.h2d_bytes += c->skip_keys.size() * 8;
+    k_mark_skip<<<nblocks(c->skip_keys.size(), 128), 128, 0, c->stream>>>(
+        c->d_table.as<Slot>(), c->hb.table_slots - 1, c->d_skip_keys.as<uint64_t>(), c->skip_keys.size(), c->d_occ.as<uint64_t>(),
+        c->d_len.as<uint32_t>(), ri_bgn, n_strings, c->d_str_flags.as<uint8_t>(), P.kmer_len, P.use_hopeless_check, c->d_flag.as<unsigned int>());
+    c->tm.launches += 1;
+    CK(cudaMemcpyAsync(&has_empty, c->d_flag.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  t.stop();
+  c->hb.bgn_id = bgn_id;
+  c->hb.last_id = bgn_id + n_strings - 1;
+  c->hb.has_empty = has_empty;
+  c->hash_ready = true;
+  for (uint32_t s = 0; s < n_strings; s++)
+    if (use[s]) c->stats.n_hash_bases += c->h_len[ri_bgn + s];
+  c->stats.n_inserts += hc.n_inserts;
+  c->stats.n_distinct += hc.n_distinct;
+  c->stats.n_hash_blocks++;
+  c->stats.last_end_hash_id = c->hb.last_id;
+  if (last_id) *last_id = c->hb.last_id;
+  return OIC_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int ensure_pair_scratch(oic_ctx *c, unsigned n_warps, unsigned long long rowcap) {
+  CK(c->d_vals.ensure((size_t)n_warps * rowcap * 4));
+  CK(c->d_rowmeta.ensure((size_t)n_warps * c->max_rows * sizeof(int4)));
+  CK(c->d_deltas.ensure((size_t)n_warps * (4ull * c->max_rows + 8) * 4));
+  return 0;
+}
+
+// returns 0 ok, 1 = run buffer overflow (caller retries with a smaller batch), <0 error
+int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or ~0 per query */) {
+  const oic_params_t &P = c->P;
+  const uint32_t nq = (uint32_t)qs_read.size();
+  const uint32_t nqs = 2 * nq;
+  if (nq == 0) return 0;
+  const uint32_t max_chunks = (uint32_t)(c->rec_cap / CHUNK);
+
+  CK(c->d_qs_read.ensure((size_t)nq * 4));
+  CK(cudaMemcpyAsync(c->d_qs_read.p, qs_read.data(), (size_t)nq * 4, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += (uint64_t)nq * 4;
+  CK(c->d_recs.ensure((size_t)max_chunks * CHUNK * sizeof(Seed)));
+  CK(c->d_chunk_next.ensure((size_t)max_chunks * 4));
+  CK(c->d_chunk_cnt.ensure((size_t)max_chunks * 4));
+  CK(c->d_chunk_qs.ensure((size_t)max_chunks * 4));
+  CK(c->d_qs_first.ensure((size_t)nqs * 4));
+  CK(c->d_qs_nrec.ensure((size_t)nqs * 4));
+  CK(c->d_qs_base.ensure((size_t)nqs * 4 + 16));
+  CK(c->d_qs_screen.ensure((size_t)nqs + 16));
+  if (c->hb.has_empty) {
+    std::vector<uint32_t> tb(nqs);
+    uint64_t tot = 0;
+    for (uint32_t q = 0; q < nq; q++) {
+      uint32_t tiles = qs_read[q] == 0xffffffffu ? 0 : (c->h_len[qs_read[q]] + 31) / 32 + 1;
+      tb[2 * q] = (uint32_t)tot; tot += tiles;
+      tb[2 * q + 1] = (uint32_t)tot; tot += tiles;
+    }
+    CK(c->d_qs_tile_base.ensure((size_t)nqs * 4));
+    CK(c->d_tile_empty.ensure((size_t)tot * 4 + 16));
+    CK(cudaMemcpyAsync(c->d_qs_tile_base.p, tb.data(), (size_t)nqs * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemsetAsync(c->d_tile_empty.p, 0, (size_t)tot * 4 + 16, c->stream));
+    c->tm.h2d_bytes += (uint64_t)nqs * 4;
+  }
+  if (zero_counters(c)) return OIC_ERR_CUDA;
+
+  // ---- K2a seed scan
+  ScanArgs sa;
+  sa.fwd = c->d_fwd.as<uint64_t>(); sa.rc = c->d_rc.as<uint64_t>();
+  sa.rd_pos = c->d_pos.as<int64_t>(); sa.rd_len = c->d_len.as<uint32_t>();
+  sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.n_queries = nq;
+  sa.first_id = c->first_id; sa.hash_bgn_id = c->hb.bgn_id; sa.K = P.kmer_len;
+  sa.table = c->d_table.as<Slot>(); sa.slot_mask = c->hb.table_slots - 1; sa.occ = c->d_occ.as<uint64_t>();
+  sa.has_empty = (int)c->hb.has_empty;
+  sa.recs = c->d_recs.as<Seed>(); sa.max_chunks = max_chunks;
+  sa.chunk_next = c->d_chunk_next.as<uint32_t>(); sa.chunk_cnt = c->d_chunk_cnt.as<uint32_t>(); sa.chunk_qs = c->d_chunk_qs.as<uint32_t>();
+  sa.qs_first_chunk = c->d_qs_first.as<uint32_t>(); sa.qs_nrec = c->d_qs_nrec.as<uint32_t>();
+  sa.qs_screen = c->d_qs_screen.as<uint8_t>();
+  sa.qs_tile_base = c->d_qs_tile_base.as<uint32_t>(); sa.tile_empty = c->d_tile_empty.as<uint32_t>();
+  sa.ctr = c->d_ctr.as<DevCounters>();
+  DevCounters hc;
+  {
+    StageTimer t(c, &c->tm.ms_scan);
+    k_seed_scan<<<nblocks(nqs, SCAN_WARPS), SCAN_WARPS * 32, 0, c->stream>>>(sa);
+    c->tm.launches += 1;
+    if (read_counters(c, hc)) return OIC_ERR_CUDA;
+    CK(cudaGetLastError());
+    t.stop();
+  }
+  if (hc.rec_overflow) return 1;
+  const uint32_t n_chunks = hc.rec_chunks;
+  const uint64_t n_runs = hc.n_runs;
+
+  uint32_t n_pairs = 0;
+  if (n_runs > 0) {
+    StageTimer t(c, &c->tm.ms_group);
+    // ---- K2b run lengths
+    RunLenArgs ra;
+    ra.fwd = sa.fwd; ra.rc = sa.rc; ra.rd_pos = sa.rd_pos; ra.rd_len = sa.rd_len; ra.qs_read = sa.qs_read;
+    ra.hash_ri_bgn = c->hb.bgn_id - c->first_id; ra.K = P.kmer_len; ra.recs = sa.recs; ra.n_chunks = n_chunks;
+    ra.chunk_cnt = sa.chunk_cnt; ra.chunk_qs = sa.chunk_qs; ra.has_empty = sa.has_empty;
+    ra.qs_tile_base = sa.qs_tile_base; ra.tile_empty = sa.tile_empty;
+    k_run_length<<<nblocks((uint64_t)n_chunks * CHUNK, 256), 256, 0, c->stream>>>(ra);
+    // ---- exclusive scan of the per-strand run counts
+    const uint64_t nb = (nqs + SCAN_ITEMS - 1) / SCAN_ITEMS;
+    CK(c->d_blk.ensure((nb + 2) * 4));
+    k_scan_u32_reduce<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(c->d_qs_nrec.as<uint32_t>(), nqs, c->d_blk.as<uint32_t>());
+    k_scan_u32_single<<<1, SCAN_THREADS, 0, c->stream>>>(c->d_blk.as<uint32_t>(), (uint32_t)nb);
+    k_scan_u32_apply<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(c->d_qs_nrec.as<uint32_t>(), c->d_qs_base.as<uint32_t>(), nqs, c->d_blk.as<uint32_t>());
+    // ---- K2c group by hash read
+    CK(c->d_bufA.ensure((size_t)n_runs * sizeof(Seed)));
+    CK(c->d_bufB.ensure((size_t)n_runs * sizeof(Seed)));
+    CK(c->d_scratch.ensure((size_t)n_runs * 16));
+    CK(c->d_pairs.ensure((size_t)n_runs * sizeof(Pair)));
+    CK(c->d_info.ensure((size_t)n_runs * sizeof(PairInfo)));
+    int bits = 1;
+    while ((1ull << bits) < c->hb.n_strings) bits++;
+    GroupArgs ga;
+    ga.recs = sa.recs; ga.chunk_next = sa.chunk_next; ga.chunk_cnt = sa.chunk_cnt;
+    ga.qs_first_chunk = sa.qs_first_chunk; ga.qs_nrec = sa.qs_nrec; ga.qs_base = c->d_qs_base.as<uint32_t>(); ga.n_qs = nqs;
+    ga.bufA = c->d_bufA.as<Seed>(); ga.bufB = c->d_bufB.as<Seed>(); ga.passes = (bits + 7) / 8;
+    ga.pairs = c->d_pairs.as<Pair>(); ga.ctr = c->d_ctr.as<DevCounters>();
+    k_group_runs<<<nblocks(nqs, GROUP_WARPS), GROUP_WARPS * 32, 0, c->stream>>>(ga);
+    c->tm.launches += 5;
+    if (read_counters(c, hc)) return OIC_ERR_CUDA;
+    n_pairs = (uint32_t)hc.n_pairs;
+    // ---- K2d Add_Match replay
+    ReplayArgs rp;
+    rp.src = (ga.passes & 1) ? ga.bufB : ga.bufA;
+    rp.dst = (ga.passes & 1) ? ga.bufA : ga.bufB;
+    rp.scratch = c->d_scratch.as<int32_t>(); rp.pairs = ga.pairs; rp.info = c->d_info.as<PairInfo>(); rp.n_pairs = n_pairs;
+    rp.qs_base = ga.qs_base; rp.qs_nrec = ga.qs_nrec; rp.K = P.kmer_len;
+    if (n_pairs) k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
+    c->tm.launches += 1;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    t.stop();
+
+    if ((c->debug & 1) && n_pairs) {
+      std::vector<Pair> hp(n_pairs);
+      std::vector<PairInfo> hi(n_pairs);
+      std::vector<Seed> hs(n_runs);
+      CK(cudaMemcpy(hp.data(), c->d_pairs.p, (size_t)n_pairs * sizeof(Pair), cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(hi.data(), c->d_info.p, (size_t)n_pairs * sizeof(PairInfo), cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(hs.data(), rp.dst, (size_t)n_runs * sizeof(Seed), cudaMemcpyDeviceToHost));
+      for (uint32_t i = 0; i < n_pairs; i++) {
+        int64_t rec[9] = {(int64_t)c->first_id + qs_read[hp[i].qs >> 1], (int64_t)c->hb.bgn_id + hp[i].str, (int64_t)(hp[i].qs & 1),
+                          hi[i].consistent, hi[i].diag_ct, hi[i].diag_bgn, hi[i].diag_end, (int64_t)hp[i].n,
+                          (int64_t)(c->dbg_matches.size() / 3)};
+        c->dbg_pairs.insert(c->dbg_pairs.end(), rec, rec + 9);
+        for (uint32_t j = 0; j < hp[i].n; j++) {
+          const Seed &s = hs[hp[i].first + j];
+          c->dbg_matches.push_back(s.offset); c->dbg_matches.push_back(s.len); c->dbg_matches.push_back(s.start);
+        }
+      }
+    }
+
+    // ---- K3 pairs
+    if (n_pairs) {
+      StageTimer t3(c, &c->tm.ms_extend);
+      const unsigned grid = 148 * 4;
+      const unsigned n_warps = grid * EXT_WARPS;
+      const unsigned long long rowcap = (unsigned long long)c->max_rows * 160 + 1024;
+      if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
+      const uint32_t out_cap = n_pairs * (P.unique_olap ? 1u : (uint32_t)MAX_DISTINCT_OLAPS);
+      CK(c->d_out.ensure((size_t)out_cap * 24 + 24));
+      CK(c->d_retry.ensure((size_t)n_pairs * 4 + 4));
+      ExtArgs ea;
+      ea.fwd = sa.fwd; ea.rc = sa.rc; ea.rd_pos = sa.rd_pos; ea.rd_len = sa.rd_len; ea.qs_read = sa.qs_read;
+      ea.first_id = c->first_id; ea.hash_ri_bgn = c->hb.bgn_id - c->first_id; ea.hash_bgn_id = c->hb.bgn_id;
+      ea.str_flags = c->d_str_flags.as<uint8_t>(); ea.qs_screen = c->d_qs_screen.as<uint8_t>();
+      ea.seeds = rp.dst; ea.pairs = ga.pairs; ea.info = rp.info; ea.n_pairs = n_pairs;
+      ea.task_list = nullptr; ea.n_tasks = n_pairs;
+      ea.K = P.kmer_len; ea.partial = P.partial; ea.unique_olap = P.unique_olap; ea.use_hopeless = P.use_hopeless_check;
+      ea.min_olap_len = P.min_olap_len; ea.filter_by_kmer_count = P.filter_by_kmer_count;
+      ea.erate = P.max_erate; ea.minkmer_factor = exp(-1.0 * (double)P.kmer_len * P.max_erate);
+      ea.branch_match_value = P.max_erate / (1 + P.max_erate);               // LIBO/prefixEditDistance.C:95
+      ea.min_branch_tail_slope = (P.max_erate > 0.06) ? 1.0 : 0.20;          // LIBO/prefixEditDistance.C:41
+      ea.match_limit = c->d_match_limit.as<int32_t>(); ea.max_rows = c->max_rows;
+      ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
+      ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
+      ea.ctr = sa.ctr;
+      k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+      c->tm.launches += 1;
+      if (read_counters(c, hc)) return OIC_ERR_CUDA;
+      CK(cudaGetLastError());
+      if (hc.n_retry) {
+        // pairs whose rows did not fit the per-warp scratch: regenerate the seed lists (the pruning above edits them
+        // in place; finished pairs are not read again) and rerun just those pairs with worst-case scratch
+        const uint32_t nr = hc.n_retry;
+        k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
+        const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) + 1024;
+        const unsigned grid2 = 37;
+        DevBuf keep_retry;
+        CK(keep_retry.ensure((size_t)nr * 4));
+        CK(cudaMemcpyAsync(keep_retry.p, c->d_retry.p, (size_t)nr * 4, cudaMemcpyDeviceToDevice, c->stream));
+        if (ensure_pair_scratch(c, grid2 * EXT_WARPS, big)) { keep_retry.release(); return OIC_ERR_CUDA; }
+        ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = big; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
+        ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
+        CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->pair_cursor, 0, 4, c->stream));
+        CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));
+        k_process_pairs<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        c->tm.launches += 2;
+        int r2 = read_counters(c, hc);
+        keep_retry.release();
+        if (r2) return OIC_ERR_CUDA;
+        CK(cudaGetLastError());
+        if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch (internal)");
+      }
+      if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
+      if (hc.n_out) {
+        size_t old = c->overlaps.size();
+        c->overlaps.resize(old + hc.n_out);
+        CK(cudaMemcpyAsync(c->overlaps.data() + old, c->d_out.p, (size_t)hc.n_out * 24, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        c->tm.d2h_bytes += (uint64_t)hc.n_out * 24;
+      }
+      t3.stop();
+    }
+  }
+
+  oic_stats_t &s = c->stats;
+  s.n_query_bases += hc.n_query_bases; s.n_windows += hc.n_windows; s.n_found += hc.n_found; s.n_refs += hc.n_refs;
+  s.n_add_ref += hc.n_add_ref; s.n_runs += hc.n_runs; s.n_pairs += n_pairs;
+  s.ext_calls += hc.ext_calls; s.ext_cells += hc.ext_cells; s.ext_words += hc.ext_words;
+  s.kmer_hits_without_olap += hc.kmer_hits_without_olap; s.kmer_hits_with_olap += hc.kmer_hits_with_olap;
+  s.kmer_hits_skipped += hc.kmer_hits_skipped; s.multi_overlap += hc.multi_overlap;
+  s.total_overlaps += hc.total_overlaps; s.contained += hc.contained; s.dovetail += hc.dovetail;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int oic_process_overlaps(oic_ctx_t *c, uint32_t bgn_ref_id, uint32_t end_ref_id) {
+  if (!c) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  if (!c->hash_ready) return c->fail(OIC_ERR_STATE, "oic_process_overlaps before oic_build_hash_index");
+  c->dbg_pairs.clear();
+  c->dbg_matches.clear();
+  if (end_ref_id < bgn_ref_id) return OIC_OK;
+  if (bgn_ref_id < c->first_id || end_ref_id >= c->first_id + c->n_reads)
+    return c->fail(OIC_ERR_ARG, "query range %u-%u outside the loaded reads", bgn_ref_id, end_ref_id);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, c->stream);
+  const oic_params_t &P = c->P;
+  uint32_t id = bgn_ref_id;
+  uint64_t batch_bases = c->batch_bases;
+  int rc = 0;
+  while (id <= end_ref_id) {
+    std::vector<uint32_t> qs;
+    uint64_t bases = 0;
+    uint32_t j = id;
+    while (j <= end_ref_id && (qs.empty() || bases < batch_bases)) {
+      const uint32_t ri = j - c->first_id;
+      const bool act = c->h_ref_ok[ri] && (int64_t)c->h_len[ri] >= (int64_t)P.min_olap_len;   // Process_Overlaps.C:108-115
+      qs.push_back(act ? ri : 0xffffffffu);
+      if (act) bases += c->h_len[ri];
+      j++;
+    }
+    rc = run_batch(c, qs);
+    if (rc < 0) break;
+    if (rc == 1) {   // run buffer too small for this batch
+      if (qs.size() == 1) c->rec_cap *= 2; else batch_bases = std::max<uint64_t>(bases / 2, 1);
+      rc = 0;
+      continue;
+    }
+    id = j;
+  }
+  cudaEventRecord(e1, c->stream);
+  cudaEventSynchronize(e1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  c->tm.ms_total_search += ms;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return rc;
+}
+
+uint32_t oic_last_processed_ref(uint32_t bgn_ref, uint32_t end_ref, uint32_t num_threads) {
+  if (end_ref < bgn_ref || num_threads == 0) return 0;
+  const uint32_t per_thread = 1 + (end_ref - bgn_ref) / num_threads / 8;   // OIC/overlapInCore.C:249
+  // a block that would START at end_ref is dropped by `bgnID < endRefID` (Process_Overlaps.C:86)
+  if ((end_ref - bgn_ref) % per_thread == 0) return end_ref - 1 >= bgn_ref ? end_ref - 1 : 0;
+  return end_ref;
+}
+
+int oic_overlap_driver(oic_ctx_t *c) {
+  if (!c) return OIC_ERR_ARG;
+  const oic_params_t &P = c->P;
+  if (c->n_reads == 0) return c->fail(OIC_ERR_STATE, "no reads loaded");
+  const uint32_t num_reads = c->first_id + c->n_reads - 1;
+  uint32_t g_bgn = P.bgn_hash_id < 1 ? 1 : P.bgn_hash_id;
+  uint32_t g_end = P.end_hash_id > num_reads ? num_reads : P.end_hash_id;
+  uint64_t bgn = g_bgn, end = (uint64_t)g_bgn + P.max_hash_strings - 1;
+  while (bgn < g_end) {   // strict '<' (OIC/overlapInCore.C:222)
+    if (end > g_end) end = g_end;
+    uint32_t last = 0;
+    int rc = oic_build_hash_index(c, (uint32_t)bgn, (uint32_t)end, &last);
+    if (rc) return rc;
+    uint32_t bgn_ref = P.bgn_ref_id < 1 ? 1 : P.bgn_ref_id;
+    uint32_t end_ref = P.end_ref_id > num_reads ? num_reads : P.end_ref_id;
+    uint32_t last_ref = oic_last_processed_ref(bgn_ref, end_ref, P.num_threads);
+    if (last_ref >= bgn_ref) {
+      rc = oic_process_overlaps(c, bgn_ref, last_ref);
+      if (rc) return rc;
+    }
+    bgn = (uint64_t)last + 1;
+    end = bgn + P.max_hash_strings - 1;
+  }
+  return OIC_OK;
+}
+
+uint64_t oic_num_overlaps(const oic_ctx_t *c) { return c ? c->overlaps.size() : 0; }
+
+int oic_copy_overlaps(oic_ctx_t *c, oic_ovb_record_t *dst, uint64_t capacity, uint64_t *n_copied) {
+  if (!c || (!dst && capacity)) return OIC_ERR_ARG;
+  uint64_t n = std::min<uint64_t>(capacity, c->overlaps.size());
+  if (n) memcpy(dst, c->overlaps.data(), n * sizeof(oic_ovb_record_t));
+  if (n_copied) *n_copied = n;
+  return OIC_OK;
+}
+void oic_clear_overlaps(oic_ctx_t *c) { if (c) c->overlaps.clear(); }
+
+int oic_get_stats(const oic_ctx_t *c, oic_stats_t *out) {
+  if (!c || !out) return OIC_ERR_ARG;
+  *out = c->stats;
+  return OIC_OK;
+}
+int oic_get_timings(oic_ctx_t *c, oic_timings_t *out) {
+  if (!c || !out) return OIC_ERR_ARG;
+  *out = c->tm;
+  return OIC_OK;
+}
+void oic_reset_timings(oic_ctx_t *c) { if (c) memset(&c->tm, 0, sizeof(c->tm)); }
+
+// ---- multi-GPU replication of the hash block -----------------------------------------------------------
+int oic_hash_block_meta(const oic_ctx_t *c, oic_hash_meta_t *m) {
+  if (!c || !m || !c->hash_ready) return OIC_ERR_STATE;
+  *m = c->hb;
+  return OIC_OK;
+}
+int oic_hash_block_reserve(oic_ctx_t *c, const oic_hash_meta_t *m) {
+  if (!c || !m) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  c->hash_ready = false;
+  CK(c->d_table.ensure(m->table_slots * sizeof(Slot)));
+  CK(c->d_occ.ensure(((size_t)m->n_occ + 32) * 8));
+  CK(c->d_str_flags.ensure(((size_t)m->n_strings + 8) & ~(size_t)3));
+  return OIC_OK;
+}
+int oic_hash_block_buffers(const oic_ctx_t *c, oic_dev_buffer_t b[OIC_HASH_BLOCK_NBUF]) {
+  if (!c || !b) return OIC_ERR_ARG;
+  b[0].ptr = c->d_table.p; b[0].bytes = c->hb.table_slots * sizeof(Slot);
+  b[1].ptr = c->d_occ.p; b[1].bytes = ((uint64_t)c->hb.n_occ + 32) * 8;
+  b[2].ptr = c->d_str_flags.p; b[2].bytes = ((uint64_t)c->hb.n_strings + 8) & ~(uint64_t)3;
+  return OIC_OK;
+}
+int oic_hash_block_commit(oic_ctx_t *c, const oic_hash_meta_t *m) {
+  if (!c || !m) return OIC_ERR_ARG;
+  c->hb = *m;
+  c->hash_ready = true;
+  c->stats.n_hash_blocks++;
+  c->stats.last_end_hash_id = m->last_id;
+  return OIC_OK;
+}
+
+// ---- stage dumps ---------------------------------------------------------------------------------------
+int oic_dump_index(oic_ctx_t *c, uint64_t *n_keys, uint64_t *n_occ, uint64_t *keys, uint64_t *occ_start, uint64_t *occ, uint8_t *flags) {
+  if (!c || !c->hash_ready) return OIC_ERR_STATE;
+  cudaSetDevice(c->device);
+  std::vector<Slot> t(c->hb.table_slots);
+  std::vector<uint64_t> o(c->hb.n_occ);
+  CK(cudaMemcpy(t.data(), c->d_table.p, t.size() * sizeof(Slot), cudaMemcpyDeviceToHost));
+  if (!o.empty()) CK(cudaMemcpy(o.data(), c->d_occ.p, o.size() * 8, cudaMemcpyDeviceToHost));
+  std::vector<uint32_t> idx;
+  for (uint64_t i = 0; i < t.size(); i++)
+    if (t[i].key != EMPTY_KEY) idx.push_back((uint32_t)i);
+  std::sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return t[a].key < t[b].key; });
+  if (n_keys) *n_keys = idx.size();
+  if (n_occ) *n_occ = c->hb.n_occ;
+  if (!keys) return OIC_OK;
+  uint64_t w = 0;
+  for (size_t k = 0; k < idx.size(); k++) {
+    const Slot &s = t[idx[k]];
+    keys[k] = s.key;
+    occ_start[k] = w;
+    flags[k] = (s.lenflags & EMPTY_FLAG) ? 1 : 0;
+    uint32_t n = s.lenflags & LEN_MASK;
+    for (uint32_t j = 0; j < n; j++) {
+      uint64_t e = o[s.start + j];
+      occ[w++] = ((uint64_t)occ_str(e) << 32) | occ_off(e);
+    }
+  }
+  occ_start[idx.size()] = w;
+  return OIC_OK;
+}
+
+int oic_dump_pairs(oic_ctx_t *c, uint64_t *n_pairs, uint64_t *n_matches, int64_t *pairs, int32_t *matches) {
+  if (!c) return OIC_ERR_ARG;
+  if (n_pairs) *n_pairs = c->dbg_pairs.size() / 9;
+  if (n_matches) *n_matches = c->dbg_matches.size() / 3;
+  if (pairs && !c->dbg_pairs.empty()) memcpy(pairs, c->dbg_pairs.data(), c->dbg_pairs.size() * 8);
+  if (matches && !c->dbg_matches.empty()) memcpy(matches, c->dbg_matches.data(), c->dbg_matches.size() * 4);
+  return OIC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,120 @@
+/*
+ * oic_dev_common.cuh -- device-side data layout shared by the build / scan / extend kernels.
+ *
+ * HBM layout:
+ *   reads     2-bit packed, 32 bases per uint64 word, base i of the stream at bits [2i, 2i+2) of word i/32
+ *             (first base in the LOW bits, the same convention as the reference's rolling k-mer key,
+ *             OIC/overlapInCore-Build_Hash_Index.C:374-379).  Every read starts on a word boundary and is
+ *             followed by >= 64 zero bases, so unaligned 32-base extractions never leave the buffer.
+ *             Two streams with identical read positions: forward strand and reverse complement.
+ *   table     open-addressing k-mer table, 16-byte slots {key, start, len|Empty}; one 16-byte load answers a probe.
+ *   occ       occurrence array (CSR payload), 8 bytes per k-mer occurrence, DESCENDING (string, offset) per key:
+ *             the order the reference's chain has after pushing at the head (Build_Hash_Index.C:317-323).
+ */
+#ifndef OIC_DEV_COMMON_CUH
+#define OIC_DEV_COMMON_CUH
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "oic_core.cuh"
+
+namespace oic {
+
+struct __align__(16) Slot {
+  unsigned long long key;
+  uint32_t start;
+  uint32_t lenflags;  // bits 0..30 occurrence count, bit 31 = Empty (screened k-mer)
+};
+constexpr unsigned long long EMPTY_KEY = ~0ULL;
+constexpr uint32_t EMPTY_FLAG = 0x80000000u;
+constexpr uint32_t LEN_MASK = 0x7fffffffu;
+constexpr uint32_t NO_SLOT = 0xffffffffu;
+
+constexpr int READ_PAD_BASES = 64;   // zero bases after every read
+constexpr int READ_LEAD_BASES = 64;  // zero bases before the first read
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+/* 32 bases starting at stream position p (p >= 0) */
+__device__ __forceinline__ uint64_t ext32(const uint64_t *__restrict__ W, int64_t p) {
+  int64_t w = p >> 5;
+  int s = (int)(p & 31) * 2;
+  uint64_t lo = W[w];
+  if (s == 0) return lo;
+  uint64_t hi = W[w + 1];
+  return (lo >> s) | (hi << (64 - s));
+}
+
+__device__ __forceinline__ uint32_t base_at(const uint64_t *__restrict__ W, int64_t p) {
+  return (uint32_t)(W[p >> 5] >> ((p & 31) * 2)) & 3u;
+}
+
+/* number of equal bases comparing A[pa + i] with T[pt + i], i = 0.. , at most `limit` */
+__device__ __forceinline__ int match_fwd(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T,
+                                         int64_t pt, int limit) {
+  int r = 0;
+  while (r < limit) {
+    uint64_t x = ext32(A, pa + r) ^ ext32(T, pt + r);
+    if (x) { r += (__ffsll((long long)x) - 1) >> 1; break; }
+    r += 32;
+  }
+  return r < limit ? r : limit;
+}
+
+/* number of equal bases comparing A[pa - i] with T[pt - i], i = 0.. , at most `limit` (pa - limit + 1 >= -31 is safe:
+ * the stream has READ_LEAD_BASES of padding in front) */
+__device__ __forceinline__ int match_rev(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T,
+                                         int64_t pt, int limit) {
+  int r = 0;
+  while (r < limit) {
+    uint64_t x = ext32(A, pa - r - 31) ^ ext32(T, pt - r - 31);
+    if (x) { r += __clzll((long long)x) >> 1; break; }
+    r += 32;
+  }
+  return r < limit ? r : limit;
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+/* inclusive scan */
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+  int l = lane_id();
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(FULL, v, o);
+    if (l >= o) v += t;
+  }
+  return v;
+}
+
+/* counters shared by all kernels of a context (one cudaMemcpy to read them) */
+struct DevCounters {
+  unsigned long long n_inserts, n_distinct;
+  unsigned long long n_query_bases, n_windows, n_found, n_refs, n_add_ref;
+  unsigned long long n_runs, n_pairs;
+  unsigned long long ext_calls, ext_cells, ext_words;
+  unsigned long long kmer_hits_without_olap, kmer_hits_with_olap, kmer_hits_skipped, multi_overlap;
+  unsigned long long total_overlaps, contained, dovetail;
+  // transient
+  unsigned int rec_chunks;     // bump allocator of seed-run chunks
+  unsigned int rec_overflow;   // set when the run buffer was too small
+  unsigned int n_big_lists;
+  unsigned int pair_cursor;    // work queue of the pair kernel
+  unsigned int n_retry;        // pairs whose edit rows did not fit the per-warp scratch
+  unsigned int n_out;          // overlap records written
+  unsigned int bad_base;       // a non-ACGT base was seen while packing
+  unsigned int out_overflow;
+};
+
+}  // namespace oic
+#endif

@@ -1,0 +1,519 @@
+/*
+ * oic_extend.cuh -- K3/K4: one warp per read pair: Process_Matches -> Extend_Alignment -> forward / reverse
+ * prefix edit distance -> Add_Overlap -> Output_Overlap.
+ *
+ * Replaces (reference, OIC/ = src/overlapInCore/, LIBO/ = src/overlapInCore/liboverlap/):
+ *   Process_String_Olaps / Process_Matches      OIC/overlapInCore-Process_String_Overlaps.C:400-800
+ *   prefixEditDistance::Extend_Alignment        LIBO/prefixEditDistance-extend.C:87-229
+ *   prefixEditDistance::forward / reverse       LIBO/prefixEditDistance-forward.C:110-285, -reverse.C:130-300
+ *   Set_Right_Delta / Set_Left_Delta            LIBO/prefixEditDistance-forward.C:48-87, -reverse.C:52-109
+ *   Output_Overlap / Output_Partial_Overlap     OIC/overlapInCore-Output.C:75-313
+ *
+ * The DP is the "furthest reaching row per diagonal" recurrence: row e holds, for every diagonal d of the
+ * pruned band, the longest prefix of A matched with e errors.  The lanes of the warp own consecutive
+ * diagonals of the current row; the slide along a diagonal compares 32 bases per step on the 2-bit packed
+ * strings; end-of-string detection, band trimming and the best-cell search are warp ballots / reductions.
+ * All rows are kept (band-compressed: only the computed extent of each row) in the warp's private slice of a
+ * global scratch arena because the traceback needs them for the delta list.  Integer only, except the
+ * branch-point score, which is IEEE double without FMA contraction (OIC_DMUL/OIC_DSUB).
+ */
+#ifndef OIC_EXTEND_CUH
+#define OIC_EXTEND_CUH
+#include "oic_search.cuh"
+
+namespace oic {
+
+struct ExtArgs {
+  const uint64_t *fwd, *rc;
+  const int64_t *rd_pos;
+  const uint32_t *rd_len;
+  const uint32_t *qs_read;
+  uint32_t first_id, hash_ri_bgn, hash_bgn_id;
+  const uint8_t *str_flags;   // bit0 lscreen, bit1 rscreen per hash string
+  const uint8_t *qs_screen;   // same per query strand
+  Seed *seeds;
+  const Pair *pairs;
+  const PairInfo *info;
+  uint32_t n_pairs;
+  const uint32_t *task_list;  // optional indirection (retry pass)
+  uint32_t n_tasks;
+  // parameters
+  int K, partial, unique_olap, use_hopeless, min_olap_len;
+  unsigned long long filter_by_kmer_count;
+  double erate, minkmer_factor, branch_match_value, min_branch_tail_slope;
+  const int32_t *match_limit;   // Edit_Match_Limit[0 .. max_rows)
+  int max_rows;
+  // per-warp scratch
+  int32_t *vals; unsigned long long rowcap;   // row values, rowcap ints per warp
+  int4 *rowmeta;                              // max_rows per warp: {lo, tlo, thi, off}
+  int32_t *deltas;                            // per warp: stack[max_rows+2] rdelta[max_rows+2] ldelta[2*max_rows+4]
+  // output
+  uint32_t *out; uint32_t out_cap;            // 6 words per record
+  uint32_t *retry_list;
+  DevCounters *ctr;
+};
+
+struct WarpScratch {
+  int32_t *vals;
+  int4 *meta;
+  int32_t *stack, *rdelta, *ldelta;
+  unsigned long long rowcap;
+  int max_rows;
+  const int32_t *match_limit;
+  unsigned long long cells, words;   // per-lane partial counters
+};
+
+__device__ __forceinline__ int row_get(const WarpScratch &ws, int k, int d) {
+  int4 m = ws.meta[k];
+  if (d < m.y || d > m.z) return -2;
+  return ws.vals[m.w + d - m.x];
+}
+
+// lane 0 only.  Walk rows e..1 backwards choosing the predecessor by the rule that built the row.
+__device__ int traceback(const WarpScratch &ws, int e, int d, int32_t *stack, int &ns) {
+  int4 me = ws.meta[e];
+  int last = ws.vals[me.w + d - me.x];
+  ns = 0;
+  for (int k = e; k > 0; k--) {
+    int4 m = ws.meta[k - 1];
+    int g0 = (d < m.y || d > m.z) ? -2 : ws.vals[m.w + d - m.x];
+    int gm = (d - 1 < m.y || d - 1 > m.z) ? -2 : ws.vals[m.w + d - 1 - m.x];
+    int gp = (d + 1 < m.y || d + 1 > m.z) ? -2 : ws.vals[m.w + d + 1 - m.x];
+    int from = 0, mx = 1 + g0;
+    if (gm > mx) { from = -1; mx = gm; }
+    if (1 + gp > mx) { from = 1; mx = 1 + gp; }
+    if (from == -1) { stack[ns++] = mx - last - 1; d--; last = gm; }
+    else if (from == 1) { stack[ns++] = last - (mx - 1); d++; last = gp; }
+  }
+  return last;
+}
+
+/* One direction of the prefix edit distance.  DIR = +1: A[i], T[i]; DIR = -1: A[-i], T[-i] (a0 / t0 are the
+ * stream positions of A[0] / T[0]).  Warp-uniform arguments and results.  Returns errors, or -1 if the
+ * rows did not fit the scratch (overflow). */
+template <int DIR>
+__device__ int dp_run(const ExtArgs &a, WarpScratch &ws, const uint64_t *__restrict__ A, int64_t a0, int m,
+                      const uint64_t *__restrict__ T, int64_t t0, int n, int error_limit, int &a_end, int &t_end,
+                      int &leftover, int &to_end, int &delta_len) {
+  const int l = lane_id();
+  int row = (DIR > 0) ? match_fwd(A, a0, T, t0, m) : match_rev(A, a0, T, t0, m);
+  if (l == 0) {
+    ws.cells += 1;
+    ws.words += (unsigned)(row + 1 + 15) / 16;
+    ws.meta[0] = make_int4(0, 0, 0, 0);
+    ws.vals[0] = row;
+  }
+  delta_len = 0;
+  leftover = 0;
+  if (row == m) {
+    a_end = t_end = DIR * m;
+    leftover = m;
+    to_end = 1;
+    return 0;
+  }
+  int left = 0, right = 0;
+  double max_score = 0.0;
+  int max_score_len = 0, max_score_best_d = 0, max_score_best_e = 0;
+  int best_d = 0, best_e = 0, longest = 0;
+  int plo = 0, ptlo = 0, pthi = 0, poff = 0;   // previous row: computed lo, trimmed lo/hi, offset
+  int next_off = 1;
+  int fin_e = -1, fin_d = 0;                   // cell the traceback starts from
+  int errors = 0;
+  to_end = 0;
+  __syncwarp();
+
+  for (int e = 1; e <= error_limit; e++) {
+    left = imax(left - 1, -e);
+    right = imin(right + 1, e);
+    const int width = right - left + 1;
+    if (e >= ws.max_rows || (unsigned long long)next_off + width > ws.rowcap) return -1;
+    const int off = next_off;
+    next_off += width;
+
+    bool ended = false;
+    int d_end = 0, r_end = 0;
+    for (int cb = left; cb <= right; cb += 32) {
+      const int d = cb + l;
+      const bool act = d <= right;
+      int r = -1, wc = 0;
+      if (act) {
+        int g0 = (d < ptlo || d > pthi) ? -2 : ws.vals[poff + d - plo];
+        int gm = (d - 1 < ptlo || d - 1 > pthi) ? -2 : ws.vals[poff + d - 1 - plo];
+        int gp = (d + 1 < ptlo || d + 1 > pthi) ? -2 : ws.vals[poff + d + 1 - plo];
+        r = 1 + g0;
+        if (gm > r) r = gm;
+        if (1 + gp > r) r = 1 + gp;
+        const int r0 = r;
+        const int lim = imin(m, n - d);
+        if (r < lim)
+          r += (DIR > 0) ? match_fwd(A, a0 + r, T, t0 + r + d, lim - r) : match_rev(A, a0 - r, T, t0 - (r + d), lim - r);
+        ws.vals[off + d - left] = r;
+        wc = (r - r0 + 1 + 15) / 16;
+      }
+      const unsigned em = __ballot_sync(FULL, act && (r == m || r + d == n));
+      if (em) {
+        const int first = __ffs(em) - 1;
+        if (l <= first) { ws.cells += 1; ws.words += wc; }
+        d_end = cb + first;
+        r_end = __shfl_sync(FULL, r, first);
+        ended = true;
+        break;
+      }
+      if (act) { ws.cells += 1; ws.words += wc; }
+    }
+    __syncwarp();
+
+    if (ended) {
+      const double score = OIC_DSUB(OIC_DMUL((double)r_end, a.branch_match_value), (double)e);
+      const int tail_len = r_end - max_score_len;
+      bool abort = false;
+      if (a.partial && score < max_score) abort = true;
+      if (e > MIN_BRANCH_END_DIST / 2 && tail_len >= MIN_BRANCH_END_DIST) {
+        const double slope = OIC_DDIV(OIC_DSUB(max_score, score), (double)tail_len);
+        if (slope >= a.min_branch_tail_slope) abort = true;
+      }
+      if (l == 0) ws.meta[e] = make_int4(left, left, right, off);
+      if (abort) break;   // fall through to the "best so far" exit
+      if (DIR > 0) {
+        // force the last error to be a mismatch rather than an insertion (forward.C:213-219)
+        int gp = (d_end + 1 < ptlo || d_end + 1 > pthi) ? -2 : ws.vals[poff + d_end + 1 - plo];
+        if (r_end == m && 1 + gp == r_end && d_end < right) {
+          d_end++;
+          if (l == 0) ws.vals[off + d_end - left] = r_end;
+        }
+      }
+      a_end = DIR * r_end;
+      t_end = DIR * (r_end + d_end);
+      fin_e = e; fin_d = d_end;
+      errors = e;
+      to_end = 1;
+      break;
+    }
+
+    // band trimming (forward.C:235-254): cells whose progress is below Edit_Match_Limit[e] leave the band
+    const int lim = ws.match_limit[e];
+    int nl = right + 1;
+    for (int cb = left; cb <= right; cb += 32) {
+      const int d = cb + l;
+      const bool ok = d <= right && (ws.vals[off + d - left] + imax(d, 0) >= lim);
+      const unsigned mk = __ballot_sync(FULL, ok);
+      if (mk) { nl = cb + __ffs(mk) - 1; break; }
+    }
+    if (nl > right) {
+      if (l == 0) ws.meta[e] = make_int4(left, nl, right, off);
+      break;
+    }
+    int nr = nl;
+    for (int ce = right; ce >= nl; ce -= 32) {
+      const int d = ce - l;
+      const bool ok = d >= nl && (ws.vals[off + d - left] + imax(d, 0) >= lim);
+      const unsigned mk = __ballot_sync(FULL, ok);
+      if (mk) { nr = ce - (__ffs(mk) - 1); break; }
+    }
+    if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
+
+    // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
+    long long bk = -(1LL << 62);
+    for (int cb = nl; cb <= nr; cb += 32) {
+      const int d = cb + l;
+      if (d <= nr) {
+        long long k = (long long)ws.vals[off + d - left] * 4294967296LL + (long long)(0x7fffffff - (d - nl));
+        if (k > bk) bk = k;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      long long ok = __shfl_xor_sync(FULL, bk, o);
+      if (ok > bk) bk = ok;
+    }
+    const int rowmax = (int)(bk >> 32);   // arithmetic shift: floor(bk / 2^32)
+    if (rowmax > longest) {
+      longest = rowmax;
+      best_d = nl + (0x7fffffff - (int)(bk & 0xffffffffLL));
+      best_e = e;
+    }
+    const double score = OIC_DSUB(OIC_DMUL((double)longest, a.branch_match_value), (double)e);
+    if (score > max_score) {
+      max_score = score;
+      max_score_len = longest;
+      max_score_best_d = best_d;
+      max_score_best_e = best_e;
+    }
+    plo = left; ptlo = nl; pthi = nr; poff = off;
+    left = nl; right = nr;
+    __syncwarp();
+  }
+
+  if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
+    a_end = DIR * max_score_len;
+    t_end = DIR * (max_score_len + max_score_best_d);
+    fin_e = max_score_best_e; fin_d = max_score_best_d;
+    errors = max_score_best_e;
+    to_end = 0;
+  }
+  __syncwarp();
+
+  // traceback on lane 0
+  int dl = 0, lo_out = 0, te = t_end;
+  if (l == 0) {
+    int ns;
+    int last = traceback(ws, fin_e, fin_d, ws.stack, ns);
+    if (DIR > 0) {   // Set_Right_Delta
+      ws.stack[ns++] = last + 1;
+      for (int i = ns - 1; i > 0; i--) {
+        int sgn = (ws.stack[i - 1] > 0) - (ws.stack[i - 1] < 0);
+        ws.rdelta[dl++] = iabs(ws.stack[i]) * sgn;
+      }
+    } else {         // Set_Left_Delta
+      lo_out = last;
+      for (int i = 0; i < ns; i++) ws.ldelta[i] = ws.stack[i];
+      dl = ns;
+      // a leading +1 indel becomes a substitution by pulling t_end in by one (reverse.C:92-108)
+      if (dl > 1 && ws.ldelta[0] == 1 && te + n > 0) {
+        int x = ws.ldelta[1];
+        ws.ldelta[0] = (x > 0) ? x + 1 : x - 1;
+        for (int i = 1; i < dl - 1; i++) ws.ldelta[i] = ws.ldelta[i + 1];
+        dl--;
+        te--;
+      }
+    }
+  }
+  delta_len = __shfl_sync(FULL, dl, 0);
+  if (DIR < 0) {
+    leftover = __shfl_sync(FULL, lo_out, 0);
+    t_end = __shfl_sync(FULL, te, 0);
+  }
+  __syncwarp();
+  return errors;
+}
+
+/* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
+ * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
+__device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const uint64_t *S, int64_t sp, int s_len,
+                                const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
+                                int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
+  const int l = lane_id();
+  int right_errors = 0, left_errors = 0, leftover = 0, dummy = 0;
+  int r_to_end = 1, l_to_end = 1;
+  const int s_left_begin = m_start - 1, s_right_begin = m_start + m_len, s_right_len = s_len - s_right_begin;
+  const int t_left_begin = m_offset - 1, t_right_begin = m_offset + m_len, t_right_len = t_len - t_right_begin;
+  const int total_olap = imin(m_start, m_offset) + m_len + imin(s_right_len, t_right_len);
+  const int err_limit = (int)ceil(OIC_DMUL((double)total_olap, a.erate));
+  int rlen = 0, llen = 0;
+  bool neg_right = false, neg_left = false;
+
+  if (s_right_len == 0 || t_right_len == 0) {
+    s_hi = t_hi = 0;
+  } else if (s_right_len <= t_right_len) {
+    right_errors = dp_run<+1>(a, ws, S, sp + s_right_begin, s_right_len, T, tp + t_right_begin, t_right_len, err_limit,
+                              s_hi, t_hi, dummy, r_to_end, rlen);
+    neg_right = true;
+  } else {
+    right_errors = dp_run<+1>(a, ws, T, tp + t_right_begin, t_right_len, S, sp + s_right_begin, s_right_len, err_limit,
+                              t_hi, s_hi, dummy, r_to_end, rlen);
+  }
+  if (right_errors < 0) return -1;
+  s_hi += s_right_begin - 1;
+  t_hi += t_right_begin - 1;
+
+  if (s_left_begin < 0 || t_left_begin < 0) {
+    s_lo = t_lo = 0;
+  } else if (s_right_begin <= t_right_begin) {
+    left_errors = dp_run<-1>(a, ws, S, sp + s_left_begin, s_left_begin + 1, T, tp + t_left_begin, t_left_begin + 1,
+                             err_limit - right_errors, s_lo, t_lo, leftover, l_to_end, llen);
+  } else {
+    left_errors = dp_run<-1>(a, ws, T, tp + t_left_begin, t_left_begin + 1, S, sp + s_left_begin, s_left_begin + 1,
+                             err_limit - right_errors, t_lo, s_lo, leftover, l_to_end, llen);
+    neg_left = true;
+  }
+  if (left_errors < 0) return -1;
+  s_lo += s_left_begin + 1;
+  t_lo += t_left_begin + 1;
+  errors = left_errors + right_errors;
+  const int kind = !r_to_end ? (!l_to_end ? 0 : 2) : (!l_to_end ? 1 : 3);
+
+  if (l == 0) {
+    if (neg_left) for (int i = 0; i < llen; i++) ws.ldelta[i] = -ws.ldelta[i];
+    const int rs = neg_right ? -1 : 1;   // sign applied to right_delta before the splice
+    if (rlen > 0) {
+      int r0 = rs * ws.rdelta[0];
+      ws.ldelta[llen] = (r0 > 0) ? -(r0 + leftover + m_len) : -(r0 - leftover - m_len);
+      for (int i = 1; i < rlen; i++) ws.ldelta[llen + i] = -(rs * ws.rdelta[i]);
+    }
+  }
+  delta_len = llen + rlen;
+  __syncwarp();
+  return kind;
+}
+
+constexpr int EXT_WARPS = 4;
+
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
+  const int l = lane_id();
+  const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  WarpScratch ws;
+  ws.vals = a.vals + (unsigned long long)gw * a.rowcap;
+  ws.meta = a.rowmeta + (unsigned long long)gw * a.max_rows;
+  int32_t *dbase = a.deltas + (unsigned long long)gw * (4ull * a.max_rows + 8);
+  ws.stack = dbase;
+  ws.rdelta = dbase + (a.max_rows + 2);
+  ws.ldelta = dbase + 2 * (a.max_rows + 2);
+  ws.rowcap = a.rowcap;
+  ws.max_rows = a.max_rows;
+  ws.match_limit = a.match_limit;
+  ws.cells = ws.words = 0;
+  unsigned long long ext_calls = 0;
+
+  while (true) {
+    uint32_t ti = 0;
+    if (l == 0) ti = atomicAdd(&a.ctr->pair_cursor, 1u);
+    ti = __shfl_sync(FULL, ti, 0);
+    if (ti >= a.n_tasks) break;
+    const uint32_t pi = a.task_list ? a.task_list[ti] : ti;
+    const Pair pr = a.pairs[pi];
+    const PairInfo inf = a.info[pi];
+    const uint32_t ri = a.qs_read[pr.qs >> 1];
+    const int dir = pr.qs & 1;
+    const uint64_t *S = dir ? a.rc : a.fwd;
+    const int64_t sp = a.rd_pos[ri];
+    const int s_len = (int)a.rd_len[ri];
+    const uint32_t s_id = a.first_id + ri;
+    const uint32_t hri = a.hash_ri_bgn + pr.str;
+    const uint64_t *T = a.fwd;
+    const int64_t tp = a.rd_pos[hri];
+    const int t_len = (int)a.rd_len[hri];
+    const uint32_t t_id = a.hash_bgn_id + pr.str;
+    Seed *seeds = a.seeds + pr.first;
+    int n = (int)pr.n;
+
+    // --minkmers filter: computeMinimumKmers (Process_String_Overlaps.C:75-86,725)
+    if (a.filter_by_kmer_count != 0) {
+      double ovl = (double)(inf.diag_end - inf.diag_bgn);
+      if (ovl < 0) ovl = -ovl;
+      unsigned long long expected = 0;
+      if (!(ovl < (double)a.K)) expected = (unsigned long long)(int)floor(OIC_DMUL(a.minkmer_factor, ovl - a.K + 1));
+      unsigned long long need = a.filter_by_kmer_count > expected ? a.filter_by_kmer_count : expected;
+      if (need > (unsigned long long)inf.diag_ct) {
+        if (l == 0) atomicAdd(&a.ctr->kmer_hits_skipped, 1ull);
+        continue;
+      }
+    }
+    // hopeless check for a singleton seed far from both ends (Process_String_Overlaps.C:433-464)
+    if (a.use_hopeless && n == 1 && !a.partial) {
+      const Seed m = seeds[0];
+      const unsigned qsc = a.qs_screen[pr.qs], hsc = a.str_flags[pr.str];
+      bool hopeless = false;
+      const int s_head = m.start, t_head = m.offset;
+      if (s_head <= t_head) { if (s_head > HOPELESS_MATCH && !(qsc & 1)) hopeless = true; }
+      else { if (t_head > HOPELESS_MATCH && !(hsc & 1)) hopeless = true; }
+      const int s_tail = s_len - s_head - m.len + 1, t_tail = t_len - t_head - m.len + 1;
+      if (s_tail <= t_tail) { if (s_tail > HOPELESS_MATCH && !(qsc & 2)) hopeless = true; }
+      else { if (t_tail > HOPELESS_MATCH && !(hsc & 2)) hopeless = true; }
+      if (hopeless) {
+        if (l == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
+        continue;
+      }
+    }
+
+    OlapInfo distinct[MAX_DISTINCT_OLAPS];
+    int distinct_ct = 0;
+    bool overflow = false;
+
+    while (n > 0) {
+      // first of the longest seeds, in list order (Process_String_Overlaps.C:473-480)
+      long long bk = -1;
+      for (int i = l; i < n; i += 32) {
+        long long k = (long long)seeds[i].len * 4294967296LL + (long long)(0x7fffffff - i);
+        if (k > bk) bk = k;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        long long ok = __shfl_xor_sync(FULL, bk, o);
+        if (ok > bk) bk = ok;
+      }
+      const int li = 0x7fffffff - (int)(bk & 0xffffffffLL);
+      const Seed lg = seeds[li];
+      int s_lo, s_hi, t_lo, t_hi, errors, dlen;
+      ext_calls++;
+      const int kind = extend_alignment(a, ws, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+                                        errors, dlen);
+      if (kind < 0) { overflow = true; break; }
+
+      if (kind == 3 || a.partial) {
+        if (1 + s_hi - s_lo >= a.min_olap_len && 1 + t_hi - t_lo >= a.min_olap_len) {
+          const int olap_len = 1 + imin(s_hi - s_lo, t_hi - t_lo);
+          const double quality = OIC_DDIV((double)errors, (double)olap_len);
+          if (errors <= (int)ceil(OIC_DMUL((double)olap_len, a.erate)))
+            add_overlap(a.partial, s_lo, s_hi, t_lo, t_hi, quality, dlen, distinct, distinct_ct);
+        }
+      }
+      if (inf.consistent) break;
+
+      // drop the extended seed and every seed that lies on this alignment (Process_String_Overlaps.C:514-531)
+      int newn = 0;
+      for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + l;
+        bool keep = false;
+        Seed nd;
+        if (i < n) {
+          nd = seeds[i];
+          bool remove = (i == li) ||
+                        ((kind == 3 || a.partial) && s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= s_hi + SHIFT_SLACK &&
+                         lies_on_alignment(nd.start, nd.offset, s_lo, t_lo, ws.ldelta, dlen));
+          keep = !remove;
+        }
+        const unsigned km = __ballot_sync(FULL, keep);
+        __syncwarp();
+        if (keep) seeds[newn + __popc(km & ((1u << l) - 1))] = nd;
+        newn += __popc(km);
+        __syncwarp();
+      }
+      n = newn;
+    }
+
+    if (overflow) {
+      if (l == 0) a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
+      continue;
+    }
+
+    if (l == 0) {
+      int overlaps_output = 0;
+      if (distinct_ct > 0) {
+        int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
+        if (a.partial) { if (a.unique_olap) choose_best_partial(distinct, distinct_ct, deleted); }
+        else { if (a.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
+        int nout = 0;
+        for (int i = 0; i < distinct_ct; i++) nout += !deleted[i];
+        uint32_t ob = atomicAdd(&a.ctr->n_out, (unsigned)nout);
+        for (int i = 0; i < distinct_ct; i++) {
+          if (deleted[i]) continue;
+          if (ob >= a.out_cap) { atomicOr(&a.ctr->out_overflow, 1u); break; }
+          uint32_t *w = a.out + 6ull * ob;
+          if (a.partial) output_partial(w, s_id, t_id, dir, distinct[i], s_len, t_len);
+          else {
+            int contained = output_overlap(w, s_id, s_len, dir, t_id, t_len, distinct[i]);
+            if (contained) atomicAdd(&a.ctr->contained, 1ull); else atomicAdd(&a.ctr->dovetail, 1ull);
+          }
+          ob++;
+          overlaps_output++;
+        }
+        atomicAdd(&a.ctr->total_overlaps, (unsigned long long)overlaps_output);
+      }
+      if (overlaps_output == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
+      else {
+        atomicAdd(&a.ctr->kmer_hits_with_olap, 1ull);
+        if (overlaps_output > 1) atomicAdd(&a.ctr->multi_overlap, 1ull);
+      }
+    }
+  }
+
+  unsigned long long c = warp_sum64(ws.cells), w = warp_sum64(ws.words);
+  if (l == 0) {
+    if (c) atomicAdd(&a.ctr->ext_cells, c);
+    if (w) atomicAdd(&a.ctr->ext_words, w);
+    if (ext_calls) atomicAdd(&a.ctr->ext_calls, ext_calls);
+  }
+}
+
+}  // namespace oic
+#endif

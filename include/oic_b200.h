@@ -1,0 +1,158 @@
+/*
+ * include/oic_b200.h -- C ABI of the B200-native overlapInCore hot path (liboic_b200.so).
+ *
+ * The reference (sgblanch/canu, "Canu 1.6") has no plugin/FFI interface for this path: the
+ * boundary it offers is the process `overlapInCore [options] gkpStore` (OIC/overlapInCore.C:306).
+ * This ABI is what a reference-side maintainer (or our own drop-in executable
+ * canu_b200/host/overlapInCore.cpp) binds instead of the in-process C++ calls; every entry point
+ * names the reference function it replaces.  Paths: OIC/ = src/overlapInCore/,
+ * LIBO/ = src/overlapInCore/liboverlap/, ST/ = src/stores/.
+ *
+ * Conventions: plain pointers and sizes only; every call returns 0 on success or a negative
+ * OIC_ERR_* code (text via oic_last_error); the caller owns all host buffers; the library owns all
+ * device memory; no exceptions cross the boundary; a context is bound to one CUDA device and is
+ * not thread-safe (one context per host thread / per GPU).  There is NO CPU fallback: without a
+ * CUDA device oic_create fails with OIC_ERR_CUDA.
+ */
+#ifndef OIC_B200_H
+#define OIC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OIC_OK                0
+#define OIC_ERR_CUDA        (-1)   /* CUDA runtime error / no device                          */
+#define OIC_ERR_ARG         (-2)   /* bad argument                                            */
+#define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31, -l, -w ...)  */
+#define OIC_ERR_BASES       (-4)   /* non-ACGT base in a loaded read (not supported yet)      */
+#define OIC_ERR_CAPACITY    (-5)   /* an internal device buffer could not be sized            */
+#define OIC_ERR_STATE       (-6)   /* call order violated (e.g. search before build)          */
+
+/* Mirror of the reference's global `oicParameters G` (OIC/overlapInCore.H:418-530), restricted to
+ * what the hot path reads.  Field meaning and defaults are the reference's. */
+typedef struct {
+  int32_t  kmer_len;             /* -k <n>            G.Kmer_Len                                     */
+  double   max_erate;            /* --maxerate        G.maxErate; pass the strtof()-rounded value     */
+  int32_t  min_olap_len;         /* --minlength       G.Min_Olap_Len                                  */
+  int32_t  partial;              /* -G                G.Doing_Partial_Overlaps                        */
+  int32_t  unique_olap;          /* -u(1)/-m(0)       G.Unique_Olap_Per_Pair                          */
+  int32_t  use_hopeless_check;   /* !-z               G.Use_Hopeless_Check (forced 0 if erate > 0.06) */
+  uint32_t hash_bits;            /* --hashbits        G.Hash_Mask_Bits (only feeds the load limit)    */
+  double   hash_load;            /* --hashload        G.Max_Hash_Load                                 */
+  uint32_t max_hash_strings;     /* --hashstrings     G.Max_Hash_Strings                              */
+  uint64_t max_hash_data_len;    /* --hashdatalen     G.Max_Hash_Data_Len                             */
+  uint64_t frag_olap_limit;      /* -l                must be UINT64_MAX (unlimited) in this build    */
+  uint64_t filter_by_kmer_count; /* --minkmers        G.Filter_By_Kmer_Count (0 = off)                */
+  uint32_t num_threads;          /* -t                only feeds the scheduler quirk (see driver)     */
+  uint32_t bgn_hash_id, end_hash_id;  /* -h a-b                                                       */
+  uint32_t bgn_ref_id,  end_ref_id;   /* -r a-b                                                       */
+} oic_params_t;
+
+/* The 8 counters of the -s stats file (OIC/overlapInCore.C:569-588) plus the work counters the
+ * rooflines are computed from. */
+typedef struct {
+  uint64_t kmer_hits_without_olap, kmer_hits_with_olap, kmer_hits_skipped, multi_overlap;
+  uint64_t total_overlaps, contained, dovetail;
+  uint64_t n_hash_bases, n_inserts, n_distinct;               /* hash build                      */
+  uint64_t n_query_bases, n_windows, n_found, n_refs, n_add_ref; /* seed scan                    */
+  uint64_t n_runs, n_pairs;                                   /* exact-match runs / read pairs    */
+  uint64_t ext_calls, ext_cells, ext_words;                   /* C and W of I_ext = 6C + 4W       */
+  uint32_t n_hash_blocks, last_end_hash_id;
+} oic_stats_t;
+
+/* Accumulated device time per stage, CUDA events on the library's stream (milliseconds) and launch counts. */
+typedef struct {
+  float    ms_pack, ms_build, ms_scan, ms_group, ms_extend, ms_total_search;
+  uint64_t launches;             /* kernels launched by this context since the last reset */
+  uint64_t h2d_bytes, d2h_bytes; /* bytes moved across PCIe by this context since reset   */
+} oic_timings_t;
+
+/* One overlap as written to the .ovb file: 6 x uint32 = a_iid, b_iid, dat0.hi, dat0.lo, dat1.hi, dat1.lo
+ * (ST/ovOverlap.H:93-124 with AS_MAX_READLEN_BITS = 21, ST/ovStoreFile.C:196-221). */
+typedef struct { uint32_t w[6]; } oic_ovb_record_t;
+
+typedef struct oic_ctx oic_ctx_t;
+
+/* main() set-up (OIC/overlapInCore.C:306-560): validates options, builds Edit_Match_Limit /
+ * Error_Bound (LIBO/prefixEditDistance.C:35-97, LIBO/Binomial_Bound.C:119-194) and binds `device`. */
+int  oic_create(const oic_params_t *params, int device, oic_ctx_t **out);
+void oic_destroy(oic_ctx_t *ctx);
+const char *oic_last_error(const oic_ctx_t *ctx);   /* ctx may be NULL: error of the last failed oic_create */
+
+/* Replaces gkStore_loadReadData + the tolower copy loops (OIC/overlapInCore-Build_Hash_Index.C:563-586,
+ * OIC/overlapInCore-Process_Overlaps.C:117-134): reads first_id .. first_id+n-1 (1-based IDs), ASCII bases
+ * (any case) at bases[offsets[i] .. +lengths[i]); hash_ok / ref_ok are the -H / -R library filters per read
+ * (NULL = all pass).  Bases are 2-bit packed on the device (both strands) and stay resident in HBM.
+ * Replaces any previously loaded reads. */
+int oic_load_reads(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const uint64_t *offsets,
+                   const uint32_t *lengths, const char *bases, const uint8_t *hash_ok, const uint8_t *ref_ok);
+
+/* Mark_Skip_Kmers input (OIC/overlapInCore-Build_Hash_Index.C:233-286): n k-mers of exactly kmer_len
+ * characters, concatenated.  Applied at the end of every subsequent hash build. */
+int oic_set_skip_kmers(oic_ctx_t *ctx, uint64_t n, const char *kmers);
+
+/* Build_Hash_Index(gkp, bgnID, endID) (OIC/overlapInCore-Build_Hash_Index.C:443-675): builds the k-mer
+ * index of reads bgn_id.. until --hashstrings / --hashdatalen / --hashload trips; *last_id = last read
+ * actually loaded (the reference's return value). */
+int oic_build_hash_index(oic_ctx_t *ctx, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id);
+
+/* Process_Overlaps over the query reads bgn_ref_id..end_ref_id (inclusive) against the current hash block
+ * (OIC/overlapInCore-Process_Overlaps.C:78-181 -> Find_Overlaps -> Process_String_Olaps -> Extend_Alignment
+ * -> Output_Overlap).  Every read in the range is processed: the scheduler quirk of the reference's
+ * block hand-out (a final block that starts at endRefID is dropped) is applied by oic_overlap_driver,
+ * or by the caller when it shards the range.  Overlaps are appended to the context's result buffer. */
+int oic_process_overlaps(oic_ctx_t *ctx, uint32_t bgn_ref_id, uint32_t end_ref_id);
+
+/* OverlapDriver() (OIC/overlapInCore.C:190-300): the whole hash-sub-block loop over params' -h / -r
+ * ranges including the scheduler quirk for params.num_threads. */
+int oic_overlap_driver(oic_ctx_t *ctx);
+
+/* Last query read the reference would process for a -r range and -t (OIC/overlapInCore.C:249,
+ * OIC/overlapInCore-Process_Overlaps.C:86); 0 if the range is empty.  Pure host arithmetic. */
+uint32_t oic_last_processed_ref(uint32_t bgn_ref_id, uint32_t end_ref_id, uint32_t num_threads);
+
+/* Results (what Output_Overlap pushes to ovFile::writeOverlap, OIC/overlapInCore-Output.C:75-313). */
+uint64_t oic_num_overlaps(const oic_ctx_t *ctx);
+int  oic_copy_overlaps(oic_ctx_t *ctx, oic_ovb_record_t *dst, uint64_t capacity, uint64_t *n_copied);
+void oic_clear_overlaps(oic_ctx_t *ctx);
+int  oic_get_stats(const oic_ctx_t *ctx, oic_stats_t *out);
+int  oic_get_timings(oic_ctx_t *ctx, oic_timings_t *out);
+void oic_reset_timings(oic_ctx_t *ctx);
+
+/* ---- multi-GPU: the immutable product of a hash build, for replication by NCCL broadcast ------------
+ * After oic_build_hash_index on the root rank, oic_hash_block_meta/oic_hash_block_buffers expose the
+ * device buffers (table, occurrence array, string flags); non-root ranks call oic_hash_block_reserve with
+ * the root's meta to allocate identically sized buffers, the caller broadcasts each buffer in place
+ * (ncclBroadcast / torch.distributed.broadcast over NVLink), then oic_hash_block_commit makes the block
+ * current.  Reads must already be loaded identically on every rank. */
+typedef struct {
+  uint64_t table_slots;      /* power of two                                */
+  uint64_t n_occ;            /* occurrence entries                          */
+  uint32_t n_strings;        /* string slots in the block                   */
+  uint32_t bgn_id, last_id;  /* read IDs covered                            */
+  uint32_t has_empty;        /* any screened (Empty) k-mer present          */
+  uint64_t n_distinct;
+} oic_hash_meta_t;
+typedef struct { void *ptr; uint64_t bytes; } oic_dev_buffer_t;
+#define OIC_HASH_BLOCK_NBUF 3
+int oic_hash_block_meta(const oic_ctx_t *ctx, oic_hash_meta_t *meta);
+int oic_hash_block_reserve(oic_ctx_t *ctx, const oic_hash_meta_t *meta);
+int oic_hash_block_buffers(const oic_ctx_t *ctx, oic_dev_buffer_t bufs[OIC_HASH_BLOCK_NBUF]);
+int oic_hash_block_commit(oic_ctx_t *ctx, const oic_hash_meta_t *meta);
+
+/* ---- stage dumps for parity tests (not used by the product path) -----------------------------------
+ * k-mer index of the current hash block as sorted CSR: keys ascending, occ (string<<32 | offset) DESCENDING
+ * per key, flags bit0 = Empty.  Call with NULL pointers to get the sizes. */
+int oic_dump_index(oic_ctx_t *ctx, uint64_t *n_keys, uint64_t *n_occ, uint64_t *keys, uint64_t *occ_start,
+                   uint64_t *occ, uint8_t *flags);
+/* per (query, strand, hash read) accumulators and their seed lists of the LAST oic_process_overlaps call,
+ * when enabled with oic_set_debug(ctx, 1).  pair record: q_id, h_id, strand, consistent, diag_ct, diag_bgn,
+ * diag_end, n_matches, first_match (9 x int64); match record: offset, len, start (3 x int32). */
+void oic_set_debug(oic_ctx_t *ctx, uint32_t mask);
+int oic_dump_pairs(oic_ctx_t *ctx, uint64_t *n_pairs, uint64_t *n_matches, int64_t *pairs, int32_t *matches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
