@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- overlapInCore hot path on N B200s of one node (contract: see the task statement / DESIGN.md section 6).
+
+Workload (BASELINE.json's metric config: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2 % error, k=22):
+one STEP = one overlapInCore job of that sweep = build the k-mer index of one 100 Mbp hash block (1x of the genome)
+and overlap one 100 Mbp query block per GPU against it (every query ID is below the hash IDs, as in the
+triangular sweep).  N > 1: weak scaling -- rank 0 builds the hash block, the table / occurrence array / flags are
+replicated with an NCCL broadcast over NVLink, every rank scans and extends its own query block; no other
+data-path collective.  `value` = query Mbp/s of the whole job (all ranks) with the packed reads resident in HBM;
+`e2e` = the same job through the C ABI from HOST buffers (ASCII reads in pinned memory -> H2D + pack -> build ->
+scan -> extend -> overlap records back on the host), every step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--scale S]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+GENOME = 100_000_000
+BLOCK_BASES = 100_000_000      # canu's utg/obt hash block (-bl 100000000)
+K = 22
+ERATE = "0.06"
+READ_ERR = 0.02
+LEN_MIN, LEN_MAX = 5000, 15000
+SEED = 1003
+
+
+def params_for(n_hash_reads, n_total, threads=1):
+    import helpers as H
+    return H.default_params(kmer_len=K, max_erate=H.strtof(ERATE), min_olap_len=500, hash_bits=23, hash_load=0.75,
+                            max_hash_strings=n_hash_reads, max_hash_data_len=2 * BLOCK_BASES, num_threads=threads,
+                            bgn_hash_id=n_total - n_hash_reads + 1, end_hash_id=n_total, bgn_ref_id=1,
+                            end_ref_id=n_total - n_hash_reads)
+
+
+def gen_blocks(genome_len, n_blocks, block_bases, seed):
+    """reads for n_blocks blocks of ~block_bases each, sampled from one genome (each block = block_bases/genome coverage)"""
+    import helpers as H
+    cov = n_blocks * block_bases / genome_len
+    return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed)
+
+
+def split_blocks(reads, n_blocks):
+    """contiguous read-ID ranges of equal read count: blocks 0..n-2 are query blocks, the last one is the hash block"""
+    per = reads.n // n_blocks
+    return [(i * per + 1, (i + 1) * per if i < n_blocks - 1 else reads.n) for i in range(n_blocks)]
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.stop_flag = False
+        self.rows = []
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                              stderr=subprocess.DEVNULL, timeout=5).decode().strip()
+                self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def reference_leg(steps, warmup, scale_mbp=20, cores=None):
+    """The reference's own CPU overlapInCore (oracle/_ref, built from /root/reference/src by oracle/build_ref.sh) on a
+    bounded sample of the same workload: same read/error model and the same 1x-hash-block vs 1x-query-block density,
+    on a genome of `scale_mbp` Mbp instead of 100 (so one step ends in tens of seconds)."""
+    import helpers as H
+    cores = cores or os.cpu_count()
+    g = scale_mbp * 1_000_000
+    reads = gen_blocks(g, 2, g, SEED + 7)
+    (qb, qe), (hb, he) = split_blocks(reads, 2)
+    qbases = int(reads.lengths[qb - 1:qe].sum())
+    P = params_for(he - hb + 1, reads.n, threads=cores)
+    sample = ("reference overlapInCore -t %d, genome %d Mbp: hash block %d reads (%.1f Mbp, 1x) x query block %d reads (%.1f Mbp, 1x), "
+              "same read model/flags as the 100 Mbp job; wall time of the process (store open + hash build + search + .ovb)"
+              % (cores, scale_mbp, he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, qe - qb + 1, qbases / 1e6))
+    kind = "reference" if H.have_ref() else "port"
+    times, n_ovl = [], 0
+    with tempfile.TemporaryDirectory() as wd:
+        if kind == "reference":
+            store = H.make_store(reads, wd)
+            args = H.oic_args(P, ERATE)
+            for i in range(warmup + steps):
+                t0 = time.time()
+                ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref%d" % i), args, cores)
+                dt = time.time() - t0
+                if i >= warmup:
+                    times.append(dt)
+                n_ovl = H.parse_stats(st).get("Total overlaps produced", 0)
+        else:
+            cores = 1
+            for i in range(warmup + steps):
+                t0 = time.time()
+                res = H.run_oracle(reads, P)
+                dt = time.time() - t0
+                if i >= warmup:
+                    times.append(dt)
+                n_ovl = len(res["overlaps"])
+    t = float(np.mean(times))
+    return dict(value=qbases / 1e6 / t, unit="query Mbp/s", cores=cores, kind=kind, sample=sample,
+                seconds_per_step=t, overlaps_per_sec=n_ovl / t, overlaps=int(n_ovl))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink genome and blocks (debug only; 1.0 = the named config)")
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    metric = "overlapInCore query Mbp/sec (+overlaps/sec), 30x 100 Mbp genome, one hash block x one query block per GPU per step"
+    config = {"workload": "c3: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, "
+                          "100 Mbp hash block (1x) broadcast, one 100 Mbp query block per GPU",
+              "hash_block_mbp": BLOCK_BASES * a.scale / 1e6, "query_block_mbp_per_gpu": BLOCK_BASES * a.scale / 1e6,
+              "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (world, " by NCCL broadcast" if world > 1 else ""),
+              "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed"}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        r = reference_leg(max(1, min(a.steps, 2)), min(a.warmup, 1))
+        line = {"impl": "reference", "metric": metric, "value": r["value"], "unit": r["unit"], "n_gpus": a.gpus, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": 1000 * r["seconds_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic", "config": config,
+                "overlaps_per_sec": r["overlaps_per_sec"],
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": r["value"], "unit": r["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import helpers as H
+    from canu_b200 import api
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    genome = int(GENOME * a.scale)
+    block = int(BLOCK_BASES * a.scale)
+    # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
+    reads = gen_blocks(genome, world + 1, block, SEED)
+    blocks = split_blocks(reads, world + 1)
+    hb, he = blocks[-1]
+    qb, qe = blocks[rank]
+    q_bases_rank = int(reads.lengths[qb - 1:qe].sum())
+    q_bases_all = int(reads.lengths[:hb - 1].sum())
+    P = params_for(he - hb + 1, reads.n)
+
+    # this rank needs its query block and the hash block: gather them into one pinned host buffer (IDs stay global
+    # for the hash block; the query block keeps its own IDs because the overlapper is given first_id per load)
+    sel = list(range(qb, qe + 1)) + list(range(hb, he + 1))
+    lens = reads.lengths[np.array(sel) - 1].astype(np.uint32)
+    offs = np.zeros(len(sel), dtype=np.uint64)
+    np.cumsum(lens[:-1], out=offs[1:])
+    total = int(lens.sum())
+    pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
+    hostbuf = pinned.numpy()
+    w = 0
+    for (b, e) in ((qb, qe), (hb, he)):
+        o0, o1 = int(reads.offsets[b - 1]), int(reads.offsets[e])
+        hostbuf[w:w + (o1 - o0)] = reads.bases[o0:o1]
+        w += o1 - o0
+    n_q = qe - qb + 1
+    n_h = he - hb + 1
+    # local IDs: queries 1..n_q, hash n_q+1..n_q+n_h  (query ID < hash ID, as in the sweep)
+    LP = dict(P)
+    LP.update(bgn_hash_id=n_q + 1, end_hash_id=n_q + n_h, bgn_ref_id=1, end_ref_id=n_q, max_hash_strings=n_h)
+
+    ov = api.Overlapper(LP, device=local)
+
+    class DevView:
+        def __init__(self, ptr, nbytes):
+            self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+    def replicate_hash_block():
+        """rank 0 has built the block: broadcast meta, then the three device buffers in place (NCCL over NVLink)."""
+        meta = api.HashMeta()
+        if rank == 0:
+            meta = ov.hash_block_meta()
+        mt = torch.tensor([meta.table_slots, meta.n_occ, meta.n_strings, meta.bgn_id, meta.last_id, meta.has_empty, meta.n_distinct],
+                          dtype=torch.int64, device="cuda")
+        dist.broadcast(mt, 0)
+        if rank != 0:
+            v = [int(x) for x in mt.tolist()]
+            meta = api.HashMeta(v[0], v[1], v[2], v[3], v[4], v[5], v[6])
+            ov.hash_block_reserve(meta)
+        for ptr, nbytes in buffers_of(meta):
+            t = torch.as_tensor(DevView(ptr, nbytes), device="cuda")
+            dist.broadcast(t, 0)
+        if rank != 0:
+            ov.hash_block_commit(meta)
+
+    def buffers_of(meta):
+        # buffer sizes follow from meta on every rank (the library reports the sizes of the CURRENT block on rank 0)
+        bufs = ov.hash_block_buffers()
+        sizes = [meta.table_slots * 16, (meta.n_occ + 32) * 8, (meta.n_strings + 8) & ~3]
+        return [(bufs[i][0], sizes[i]) for i in range(3)]
+
+    def job(load):
+        """one step; returns number of overlap records of this rank"""
+        if load:
+            ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
+        ov.clear_overlaps()
+        if world == 1:
+            ov.build_hash_index(n_q + 1, n_q + n_h)
+        else:
+            if rank == 0:
+                ov.build_hash_index(n_q + 1, n_q + n_h)
+            replicate_hash_block()
+        ov.process_overlaps(1, n_q)
+        n = ov.num_overlaps()
+        if load:
+            ov.overlaps()   # records back in a host buffer
+        return n
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(nsteps, load):
+        barrier()
+        t0 = time.perf_counter()
+        n = 0
+        for _ in range(nsteps):
+            n = job(load)
+        barrier()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+            nn = torch.tensor([n], dtype=torch.int64, device="cuda")
+            dist.all_reduce(nn)
+            n = int(nn.item())
+        return dt, n
+
+    ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
+    for _ in range(a.warmup):
+        job(False)
+    sampler = ClockSampler(local)
+    sampler.start()
+    ov.reset_timings()
+    st0 = ov.stats()
+    dt, n_ovl = timed(a.steps, False)
+    tm = ov.timings()
+    st1 = ov.stats()
+    job(True)   # warm the end-to-end path once
+    ov.reset_timings()
+    dt_e2e, n_ovl_e2e = timed(a.steps, True)
+    tm_e2e = ov.timings()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    ov.close()
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    d = {k: st1[k] - st0[k] for k in st0 if isinstance(st0[k], int)}
+    steps = a.steps
+    # algorithmic bytes: B_scan = 0.25 N_qb + 4 N_win + 8 N_found + 8 N_ref ; B_build = 0.25 N_b + 16 N_ins
+    b_scan = (0.25 * d["n_query_bases"] + 4 * d["n_windows"] + 8 * d["n_found"] + 8 * d["n_refs"]) / steps
+    b_build = (0.25 * d["n_hash_bases"] + 16 * d["n_inserts"]) / steps
+    i_ext = (6 * d["ext_cells"] + 4 * d["ext_words"]) / steps
+    ms_scan, ms_build, ms_ext, ms_group = tm["ms_scan"] / steps, tm["ms_build"] / steps, tm["ms_extend"] / steps, tm["ms_group"] / steps
+    scan_gbs = b_scan / (ms_scan * 1e-3) / 1e9 if ms_scan > 0 else 0.0
+    build_gbs = b_build / (ms_build * 1e-3) / 1e9 if ms_build > 0 else 0.0
+    ext_gops = i_ext / (ms_ext * 1e-3) / 1e9 if ms_ext > 0 else 0.0
+    roof = {"kernel": "k_seed_scan", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak, "unit": "GB/s",
+            "frac": scan_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": b_scan, "ms_per_launch": ms_scan,
+            "formula": "0.25*N_query_bases + 4*N_windows + 8*N_found + 8*N_refs (SURVEY.md 8(d)), rank 0's block"}
+    stages = {"build": {"ms": ms_build, "algorithmic_GBps": build_gbs, "frac_hbm": build_gbs / hbm_peak,
+                        "formula": "0.25*N_hash_bases + 16*N_inserts; whole build (insert+scan+fill+sort kernels)"},
+              "seed_scan": {"ms": ms_scan, "algorithmic_GBps": scan_gbs, "frac_hbm": scan_gbs / hbm_peak},
+              "group_runs": {"ms": ms_group},
+              "extend": {"ms": ms_ext, "int32_Gops": ext_gops, "formula": "6*C + 4*W (cells, 16-base words)",
+                         "frac_int32_nominal": ext_gops / 18600.0}}
+    value = q_bases_all / 1e6 * steps / dt
+    e2e_v = q_bases_all / 1e6 * steps / dt_e2e
+    line = {"metric": metric, "value": value, "unit": "query Mbp/s", "n_gpus": world, "steps": steps, "warmup": a.warmup,
+            "ms_per_step": 1000 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8/int32 (2-bit packed bases, int32 edit rows, f64 branch score)", "data": "synthetic",
+            "config": config, "overlaps_per_sec": n_ovl * 1.0 / (dt / steps), "overlaps_per_step": n_ovl,
+            "clocks": sampler.summary(),
+            "e2e": {"value": e2e_v, "unit": "query Mbp/s", "ms_per_step": 1000 * dt_e2e / steps,
+                    "overlaps_per_sec": n_ovl_e2e * 1.0 / (dt_e2e / steps),
+                    "h2d_bytes_per_step": tm_e2e["h2d_bytes"] // steps, "d2h_bytes_per_step": tm_e2e["d2h_bytes"] // steps},
+            "device_ms_per_step": (tm["ms_build"] + tm["ms_total_search"]) / steps,
+            "gpu_launches": int(tm["launches"]), "roofline": roof, "stages": stages,
+            "work_per_step_rank0": {k: d[k] // steps for k in ("n_inserts", "n_distinct", "n_windows", "n_found", "n_refs", "n_add_ref",
+                                                                 "n_runs", "n_pairs", "ext_calls", "ext_cells", "ext_words")}}
+    if world == 1 and not a.no_cpu:
+        r = reference_leg(1, 0)
+        line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line["cpu_baseline"]["overlaps_per_sec"] = r["overlaps_per_sec"]
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

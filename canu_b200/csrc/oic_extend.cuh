@@ -418,6 +418,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
     OlapInfo distinct[MAX_DISTINCT_OLAPS];
     int distinct_ct = 0;
     bool overflow = false;
+    const unsigned long long snap_cells = ws.cells, snap_words = ws.words, snap_calls = ext_calls;
 
     while (n > 0) {
       // first of the longest seeds, in list order (Process_String_Overlaps.C:473-480)
@@ -471,7 +472,8 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
       n = newn;
     }
 
-    if (overflow) {
+    if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
+      ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
       if (l == 0) a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
       continue;
     }
