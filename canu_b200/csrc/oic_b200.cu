@@ -131,7 +131,7 @@ struct oic_ctx {
 
   // search buffers
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
-      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas;
+      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2;
   DevBuf d_ctr, d_flag;
   uint64_t rec_cap = 0;       // run records per batch
   uint64_t batch_bases = 0;
@@ -324,7 +324,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_str_flags, &c->d_str_use, &c->d_win_slot, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
-                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas,
+                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2,
                     &c->d_ctr, &c->d_flag};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -519,6 +519,7 @@ int ensure_pair_scratch(oic_ctx *c, unsigned n_warps, unsigned long long rowcap)
   CK(c->d_vals.ensure((size_t)n_warps * rowcap * 4));
   CK(c->d_rowmeta.ensure((size_t)n_warps * c->max_rows * sizeof(int4)));
   CK(c->d_deltas.ensure((size_t)n_warps * (4ull * c->max_rows + 8) * 4));
+  CK(c->d_dirs.ensure((size_t)n_warps * c->max_rows * DW * 4));
   return 0;
 }
 
@@ -653,8 +654,20 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       StageTimer t3(c, &c->tm.ms_extend);
       const unsigned grid = 148 * 4;
       const unsigned n_warps = grid * EXT_WARPS;
-      const unsigned long long rowcap = (unsigned long long)c->max_rows * 160 + 1024;
+      // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
+      // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
+      const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) + 1024;
+      const unsigned long long budget = (12ull << 30) / 4 / n_warps;
+      const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
       if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
+      // longest-processing-time-first order
+      CK(c->d_order.ensure((size_t)n_pairs * 4 + 4));
+      CK(c->d_hist2.ensure(ORDER_BINS * 4));
+      CK(cudaMemsetAsync(c->d_hist2.p, 0, ORDER_BINS * 4, c->stream));
+      k_pair_hist<<<nblocks(n_pairs, 256), 256, 0, c->stream>>>(c->d_pairs.as<Pair>(), n_pairs, c->d_hist2.as<uint32_t>());
+      k_pair_bins_scan<<<1, ORDER_BINS, 0, c->stream>>>(c->d_hist2.as<uint32_t>());
+      k_pair_scatter<<<nblocks(n_pairs, 256), 256, 0, c->stream>>>(c->d_pairs.as<Pair>(), n_pairs, c->d_hist2.as<uint32_t>(), c->d_order.as<uint32_t>());
+      c->tm.launches += 3;
       const uint32_t out_cap = n_pairs * (P.unique_olap ? 1u : (uint32_t)MAX_DISTINCT_OLAPS);
       CK(c->d_out.ensure((size_t)out_cap * 24 + 24));
       CK(c->d_retry.ensure((size_t)n_pairs * 4 + 4));
@@ -663,7 +676,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.first_id = c->first_id; ea.hash_ri_bgn = c->hb.bgn_id - c->first_id; ea.hash_bgn_id = c->hb.bgn_id;
       ea.str_flags = c->d_str_flags.as<uint8_t>(); ea.qs_screen = c->d_qs_screen.as<uint8_t>();
       ea.seeds = rp.dst; ea.pairs = ga.pairs; ea.info = rp.info; ea.n_pairs = n_pairs;
-      ea.task_list = nullptr; ea.n_tasks = n_pairs;
+      ea.task_list = c->d_order.as<uint32_t>(); ea.n_tasks = n_pairs;
       ea.K = P.kmer_len; ea.partial = P.partial; ea.unique_olap = P.unique_olap; ea.use_hopeless = P.use_hopeless_check;
       ea.min_olap_len = P.min_olap_len; ea.filter_by_kmer_count = P.filter_by_kmer_count;
       ea.erate = P.max_erate; ea.minkmer_factor = exp(-1.0 * (double)P.kmer_len * P.max_erate);
@@ -671,6 +684,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.min_branch_tail_slope = (P.max_erate > 0.06) ? 1.0 : 0.20;          // LIBO/prefixEditDistance.C:41
       ea.match_limit = c->d_match_limit.as<int32_t>(); ea.max_rows = c->max_rows;
       ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
+      ea.dirs = c->d_dirs.as<uint32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
@@ -683,12 +697,13 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         const uint32_t nr = hc.n_retry;
         k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
         const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) + 1024;
-        const unsigned grid2 = 37;
+        const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, (24ull << 30) / 4 / big / EXT_WARPS));
         DevBuf keep_retry;
         CK(keep_retry.ensure((size_t)nr * 4));
         CK(cudaMemcpyAsync(keep_retry.p, c->d_retry.p, (size_t)nr * 4, cudaMemcpyDeviceToDevice, c->stream));
         if (ensure_pair_scratch(c, grid2 * EXT_WARPS, big)) { keep_retry.release(); return OIC_ERR_CUDA; }
         ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = big; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
+        ea.dirs = c->d_dirs.as<uint32_t>();
         ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->pair_cursor, 0, 4, c->stream));
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));

@@ -46,6 +46,7 @@ struct ExtArgs {
   // per-warp scratch
   int32_t *vals; unsigned long long rowcap;   // row values, rowcap ints per warp
   int4 *rowmeta;                              // max_rows per warp: {lo, tlo, thi, off}
+  uint32_t *dirs;                             // per warp: DW direction words per row (shared-memory path)
   int32_t *deltas;                            // per warp: stack[max_rows+2] rdelta[max_rows+2] ldelta[2*max_rows+4]
   // output
   uint32_t *out; uint32_t out_cap;            // 6 words per record
@@ -287,9 +288,27 @@ __device__ int dp_run(const ExtArgs &a, WarpScratch &ws, const uint64_t *__restr
   return errors;
 }
 
+}  // namespace oic
+#include "oic_extend_fast.cuh"
+namespace oic {
+
+// shared-memory path first; the generic global-memory path only for runs with a row wider than SW
+template <int DIR>
+__device__ int dp_any(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *A, int64_t a0, int m, const uint64_t *T,
+                      int64_t t0, int n, int error_limit, int &a_end, int &t_end, int &leftover, int &to_end, int &delta_len) {
+  const unsigned long long sc = ws.cells, sw = ws.words;
+  int r = dp_run_fast<DIR>(a, ws, fs, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
+  if (r == -2) {
+    ws.cells = sc; ws.words = sw;
+    __syncwarp();
+    r = dp_run<DIR>(a, ws, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
+  }
+  return r;
+}
+
 /* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
  * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
-__device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const uint64_t *S, int64_t sp, int s_len,
+__device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
                                 const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
                                 int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
   const int l = lane_id();
@@ -305,11 +324,11 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const uint64_
   if (s_right_len == 0 || t_right_len == 0) {
     s_hi = t_hi = 0;
   } else if (s_right_len <= t_right_len) {
-    right_errors = dp_run<+1>(a, ws, S, sp + s_right_begin, s_right_len, T, tp + t_right_begin, t_right_len, err_limit,
+    right_errors = dp_any<+1>(a, ws, fs, S, sp + s_right_begin, s_right_len, T, tp + t_right_begin, t_right_len, err_limit,
                               s_hi, t_hi, dummy, r_to_end, rlen);
     neg_right = true;
   } else {
-    right_errors = dp_run<+1>(a, ws, T, tp + t_right_begin, t_right_len, S, sp + s_right_begin, s_right_len, err_limit,
+    right_errors = dp_any<+1>(a, ws, fs, T, tp + t_right_begin, t_right_len, S, sp + s_right_begin, s_right_len, err_limit,
                               t_hi, s_hi, dummy, r_to_end, rlen);
   }
   if (right_errors < 0) return -1;
@@ -319,10 +338,10 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const uint64_
   if (s_left_begin < 0 || t_left_begin < 0) {
     s_lo = t_lo = 0;
   } else if (s_right_begin <= t_right_begin) {
-    left_errors = dp_run<-1>(a, ws, S, sp + s_left_begin, s_left_begin + 1, T, tp + t_left_begin, t_left_begin + 1,
+    left_errors = dp_any<-1>(a, ws, fs, S, sp + s_left_begin, s_left_begin + 1, T, tp + t_left_begin, t_left_begin + 1,
                              err_limit - right_errors, s_lo, t_lo, leftover, l_to_end, llen);
   } else {
-    left_errors = dp_run<-1>(a, ws, T, tp + t_left_begin, t_left_begin + 1, S, sp + s_left_begin, s_left_begin + 1,
+    left_errors = dp_any<-1>(a, ws, fs, T, tp + t_left_begin, t_left_begin + 1, S, sp + s_left_begin, s_left_begin + 1,
                              err_limit - right_errors, t_lo, s_lo, leftover, l_to_end, llen);
     neg_left = true;
   }
@@ -332,13 +351,12 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const uint64_
   errors = left_errors + right_errors;
   const int kind = !r_to_end ? (!l_to_end ? 0 : 2) : (!l_to_end ? 1 : 3);
 
-  if (l == 0) {
-    if (neg_left) for (int i = 0; i < llen; i++) ws.ldelta[i] = -ws.ldelta[i];
+  {
+    if (neg_left) for (int i = l; i < llen; i += 32) ws.ldelta[i] = -ws.ldelta[i];
     const int rs = neg_right ? -1 : 1;   // sign applied to right_delta before the splice
-    if (rlen > 0) {
-      int r0 = rs * ws.rdelta[0];
-      ws.ldelta[llen] = (r0 > 0) ? -(r0 + leftover + m_len) : -(r0 - leftover - m_len);
-      for (int i = 1; i < rlen; i++) ws.ldelta[llen + i] = -(rs * ws.rdelta[i]);
+    for (int i = l; i < rlen; i += 32) {
+      const int r = rs * ws.rdelta[i];
+      ws.ldelta[llen + i] = (i == 0) ? ((r > 0) ? -(r + leftover + m_len) : -(r - leftover - m_len)) : -r;
     }
   }
   delta_len = llen + rlen;
@@ -363,6 +381,11 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
   ws.match_limit = a.match_limit;
   ws.cells = ws.words = 0;
   unsigned long long ext_calls = 0;
+  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 2];
+  FastScratch fs;
+  fs.row0 = s_rows[threadIdx.x >> 5][0];
+  fs.row1 = s_rows[threadIdx.x >> 5][1];
+  fs.dirs = a.dirs + (unsigned long long)gw * a.max_rows * DW;
 
   while (true) {
     uint32_t ti = 0;
@@ -436,7 +459,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
       const Seed lg = seeds[li];
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
-      const int kind = extend_alignment(a, ws, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const int kind = extend_alignment(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
       if (kind < 0) { overflow = true; break; }
 

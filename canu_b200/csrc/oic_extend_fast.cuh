@@ -1,0 +1,295 @@
+/*
+ * oic_extend_fast.cuh -- shared-memory variant of one prefix-edit-distance run (the common case).
+ *
+ * Same recurrence and the same exits as dp_run() in oic_extend.cuh (LIBO/prefixEditDistance-forward.C:110-285,
+ * -reverse.C:130-300), for runs whose rows never get wider than SW diagonals:
+ *   - rows e-1 and e live in the warp's slice of shared memory (the "edit array staged in shared memory");
+ *     every row is also streamed to the global history (coalesced, fire-and-forget) for the delta values;
+ *   - each cell records which neighbour it came from (2 bits; two ballots per 32 diagonals), so the traceback
+ *     (Set_Right_Delta / Set_Left_Delta, forward.C:48-87, reverse.C:52-109) no longer chases values through
+ *     memory row by row: 32 rows at a time are loaded by the 32 lanes, the diagonal is walked with shuffles,
+ *     and the few predecessor values the deltas need are fetched in one parallel round trip;
+ *   - band trimming and the best-cell search are ballots and redux.max on the row in shared memory.
+ * Returns -2 when a row is wider than SW (the caller reruns the direction with the generic dp_run()).
+ */
+#ifndef OIC_EXTEND_FAST_CUH
+#define OIC_EXTEND_FAST_CUH
+
+namespace oic {
+
+constexpr int SW = 512;             // widest row the shared-memory path takes
+constexpr int DW = 2 * (SW / 32);   // direction words per row
+constexpr int FROM_NONE = -9;
+
+struct FastScratch {
+  int32_t *row0, *row1;   // shared memory, SW + 2 ints each
+  uint32_t *dirs;         // global, DW words per row
+};
+
+// predecessor rule of the recurrence at diagonal d of the row after `prev` (values in shared memory)
+__device__ __forceinline__ int rule_from(const int32_t *prev, int plo, int ptlo, int pthi, int d, int &r0) {
+  const int ip = d - plo;
+  const int g0 = (d < ptlo || d > pthi) ? -2 : prev[ip];
+  const int gm = (d - 1 < ptlo || d - 1 > pthi) ? -2 : prev[ip - 1];
+  const int gp = (d + 1 < ptlo || d + 1 > pthi) ? -2 : prev[ip + 1];
+  int r = 1 + g0, from = 0;
+  if (gm > r) { r = gm; from = -1; }
+  if (1 + gp > r) { r = 1 + gp; from = 1; }
+  r0 = r;
+  return from;
+}
+
+// event i of the traceback (an indel step): encoded (pred + 4) * 4 + (from + 1) in ws.stack[i]
+__device__ __forceinline__ int tb_entry(const int32_t *ev, int i, int start_val) {
+  const int e = ev[i];
+  const int pred = (e >> 2) - 4, from = (e & 3) - 1;
+  const int lastp = i ? ((ev[i - 1] >> 2) - 4) : start_val;
+  const int mx = pred + (from == -1 ? 0 : 1);
+  return (from == -1) ? mx - lastp - 1 : lastp - (mx - 1);
+}
+
+/* Cooperative traceback from cell (fin_e, fin_d).  from0 != FROM_NONE overrides the stored direction of the
+ * first row (the exit row's cell may have been rewritten by the "last error is a mismatch" tweak).
+ * Leaves the events in ws.stack[0 .. nev) and returns nev. */
+__device__ int traceback_fast(const WarpScratch &ws, const FastScratch &fs, int fin_e, int fin_d, int from0) {
+  const int l = lane_id();
+  int nev = 0;
+  int dcur = fin_d;
+  for (int kb = fin_e; kb >= 1; kb -= 32) {
+    const int k = kb - l;
+    const bool valid = k >= 1;
+    int lo = 0, cs = 0;
+    uint2 w0 = make_uint2(0, 0), w1 = w0, w2 = w0;
+    int4 mp = make_int4(0, 0, 0, 0);
+    if (valid) {
+      lo = ws.meta[k].x;
+      mp = ws.meta[k - 1];
+      int imin = dcur - 31 - lo;
+      cs = (imin > 0 ? imin : 0) >> 5;
+      const uint2 *dp = reinterpret_cast<const uint2 *>(fs.dirs + (size_t)k * DW);
+      w0 = dp[cs];
+      if (cs + 1 < SW / 32) w1 = dp[cs + 1];
+      if (cs + 2 < SW / 32) w2 = dp[cs + 2];
+    }
+    int my_from = 0, my_d = 0;
+    const int steps = kb < 32 ? kb : 32;
+    for (int j = 0; j < steps; j++) {
+      int f = 0;
+      if (l == j) {
+        const int i = dcur - lo;
+        const int c = (i >> 5) - cs, bit = i & 31;
+        const uint2 w = (c == 0) ? w0 : ((c == 1) ? w1 : w2);
+        f = ((w.x >> bit) & 1) ? -1 : (((w.y >> bit) & 1) ? 1 : 0);
+        if (from0 != FROM_NONE && k == fin_e) f = from0;
+        my_from = f;
+        my_d = dcur;
+      }
+      f = __shfl_sync(FULL, f, j);
+      dcur += f;
+    }
+    const bool ev = valid && my_from != 0;
+    const unsigned em = __ballot_sync(FULL, ev);
+    if (ev) {
+      const int pv = ws.vals[mp.w + (my_d + my_from) - mp.x];
+      ws.stack[nev + __popc(em & ((1u << l) - 1))] = (pv + 4) * 4 + (my_from + 1);
+    }
+    nev += __popc(em);
+  }
+  __syncwarp();
+  return nev;
+}
+
+template <int DIR>
+__device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *__restrict__ A, int64_t a0,
+                           int m, const uint64_t *__restrict__ T, int64_t t0, int n, int error_limit, int &a_end, int &t_end,
+                           int &leftover, int &to_end, int &delta_len) {
+  const int l = lane_id();
+  const int row0 = (DIR > 0) ? match_fwd(A, a0, T, t0, m) : match_rev(A, a0, T, t0, m);
+  int32_t *prev = fs.row0, *cur = fs.row1;
+  if (l == 0) {
+    ws.cells += 1;
+    ws.words += (unsigned)(row0 + 1 + 15) / 16;
+    ws.meta[0] = make_int4(0, 0, 0, 0);
+    ws.vals[0] = row0;
+    prev[0] = row0;
+  }
+  delta_len = 0;
+  leftover = 0;
+  if (row0 == m) {
+    a_end = t_end = DIR * m;
+    leftover = m;
+    to_end = 1;
+    return 0;
+  }
+  int left = 0, right = 0;
+  double max_score = 0.0;
+  int max_score_len = 0, max_score_best_d = 0, max_score_best_e = 0;
+  int best_d = 0, best_e = 0, longest = 0;
+  int plo = 0, ptlo = 0, pthi = 0;
+  int next_off = 1;
+  int fin_e = -1, fin_d = 0, fin_val = 0, from0 = FROM_NONE;
+  int errors = 0;
+  to_end = 0;
+  __syncwarp();
+
+  for (int e = 1; e <= error_limit; e++) {
+    left = imax(left - 1, -e);
+    right = imin(right + 1, e);
+    const int width = right - left + 1;
+    if (width > SW) return -2;
+    if (e >= ws.max_rows || (unsigned long long)next_off + width > ws.rowcap) return -1;
+    const int off = next_off;
+    next_off += width;
+    const int nch = (width + 31) >> 5;
+
+    bool ended = false;
+    int d_end = 0, r_end = 0;
+    for (int c = 0; c < nch; c++) {
+      const int i = 32 * c + l;
+      const int d = left + i;
+      const bool act = i < width;
+      int r = -1, wc = 0, from = 0;
+      if (act) {
+        int r0;
+        from = rule_from(prev, plo, ptlo, pthi, d, r0);
+        r = r0;
+        const int lim = imin(m, n - d);
+        if (r < lim)
+          r += (DIR > 0) ? match_fwd(A, a0 + r, T, t0 + r + d, lim - r) : match_rev(A, a0 - r, T, t0 - (r + d), lim - r);
+        cur[i] = r;
+        ws.vals[off + i] = r;
+        wc = (r - r0 + 1 + 15) / 16;
+      }
+      const unsigned bm = __ballot_sync(FULL, from == -1), bp = __ballot_sync(FULL, from == 1);
+      if (l == 0) *reinterpret_cast<uint2 *>(fs.dirs + (size_t)e * DW + 2 * c) = make_uint2(bm, bp);
+      const unsigned em = __ballot_sync(FULL, act && (r == m || r + d == n));
+      if (em) {
+        const int first = __ffs(em) - 1;
+        if (l <= first) { ws.cells += 1; ws.words += wc; }
+        d_end = left + 32 * c + first;
+        r_end = __shfl_sync(FULL, r, first);
+        ended = true;
+        break;
+      }
+      if (act) { ws.cells += 1; ws.words += wc; }
+    }
+    __syncwarp();
+
+    if (ended) {
+      const double score = OIC_DSUB(OIC_DMUL((double)r_end, a.branch_match_value), (double)e);
+      const int tail_len = r_end - max_score_len;
+      bool abort = false;
+      if (a.partial && score < max_score) abort = true;
+      if (e > MIN_BRANCH_END_DIST / 2 && tail_len >= MIN_BRANCH_END_DIST) {
+        const double slope = OIC_DDIV(OIC_DSUB(max_score, score), (double)tail_len);
+        if (slope >= a.min_branch_tail_slope) abort = true;
+      }
+      if (l == 0) ws.meta[e] = make_int4(left, left, right, off);
+      if (abort) break;
+      if (DIR > 0) {   // force the last error to be a mismatch rather than an insertion (forward.C:213-219)
+        const int gp = (d_end + 1 < ptlo || d_end + 1 > pthi) ? -2 : prev[d_end + 1 - plo];
+        if (r_end == m && 1 + gp == r_end && d_end < right) {
+          d_end++;
+          if (l == 0) ws.vals[off + d_end - left] = r_end;
+        }
+      }
+      a_end = DIR * r_end;
+      t_end = DIR * (r_end + d_end);
+      fin_e = e; fin_d = d_end; fin_val = r_end;
+      int r0;
+      from0 = rule_from(prev, plo, ptlo, pthi, d_end, r0);
+      errors = e;
+      to_end = 1;
+      break;
+    }
+
+    // band trimming (forward.C:235-254)
+    const int lim = ws.match_limit[e];
+    int nl = right + 1;
+    for (int c = 0; c < nch; c++) {
+      const int i = 32 * c + l, d = left + i;
+      const bool ok = i < width && (cur[i] + imax(d, 0) >= lim);
+      const unsigned mk = __ballot_sync(FULL, ok);
+      if (mk) { nl = left + 32 * c + __ffs(mk) - 1; break; }
+    }
+    if (nl > right) {
+      if (l == 0) ws.meta[e] = make_int4(left, nl, right, off);
+      break;
+    }
+    int nr = nl;
+    for (int c = nch - 1; c >= 0; c--) {
+      const int i = 32 * c + l, d = left + i;
+      const bool ok = i < width && d >= nl && (cur[i] + imax(d, 0) >= lim);
+      const unsigned mk = __ballot_sync(FULL, ok);
+      if (mk) { nr = left + 32 * c + (31 - __clz(mk)); break; }
+    }
+    if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
+
+    // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
+    int rowbest = -0x7fffffff, rowbest_d = 0;
+    for (int c = (nl - left) >> 5; c <= ((nr - left) >> 5); c++) {
+      const int i = 32 * c + l, d = left + i;
+      const int v = (d >= nl && d <= nr) ? cur[i] : -0x7fffffff;
+      const int mx = __reduce_max_sync(FULL, v);
+      if (mx > rowbest) {
+        rowbest = mx;
+        rowbest_d = left + 32 * c + __ffs(__ballot_sync(FULL, v == mx)) - 1;
+      }
+    }
+    if (rowbest > longest) { longest = rowbest; best_d = rowbest_d; best_e = e; }
+    const double score = OIC_DSUB(OIC_DMUL((double)longest, a.branch_match_value), (double)e);
+    if (score > max_score) {
+      max_score = score;
+      max_score_len = longest;
+      max_score_best_d = best_d;
+      max_score_best_e = best_e;
+    }
+    plo = left; ptlo = nl; pthi = nr;
+    left = nl; right = nr;
+    int32_t *t = prev; prev = cur; cur = t;
+    __syncwarp();
+  }
+
+  if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
+    a_end = DIR * max_score_len;
+    t_end = DIR * (max_score_len + max_score_best_d);
+    fin_e = max_score_best_e; fin_d = max_score_best_d;
+    fin_val = fin_e ? max_score_len : row0;
+    from0 = FROM_NONE;
+    errors = max_score_best_e;
+    to_end = 0;
+  }
+  __syncwarp();
+
+  const int ns = traceback_fast(ws, fs, fin_e, fin_d, from0);
+  const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
+  if (DIR > 0) {
+    // Set_Right_Delta: st = entries, then last + 1; delta[x] = |st[ns - x]| * sign(st[ns - x - 1])
+    for (int x = l; x < ns; x += 32) {
+      const int i = ns - x;
+      const int sti = (i == ns) ? last + 1 : tb_entry(ws.stack, i, fin_val);
+      const int stm = tb_entry(ws.stack, i - 1, fin_val);
+      ws.rdelta[x] = iabs(sti) * ((stm > 0) - (stm < 0));
+    }
+    delta_len = ns;
+  } else {
+    // Set_Left_Delta; a leading +1 indel becomes a substitution by pulling t_end in by one (reverse.C:92-108)
+    leftover = last;
+    bool fix = false;
+    int e1 = 0;
+    if (ns > 1 && tb_entry(ws.stack, 0, fin_val) == 1 && t_end + n > 0) { fix = true; e1 = tb_entry(ws.stack, 1, fin_val); }
+    if (!fix) {
+      for (int x = l; x < ns; x += 32) ws.ldelta[x] = tb_entry(ws.stack, x, fin_val);
+      delta_len = ns;
+    } else {
+      for (int x = l; x < ns - 1; x += 32) ws.ldelta[x] = (x == 0) ? ((e1 > 0) ? e1 + 1 : e1 - 1) : tb_entry(ws.stack, x + 1, fin_val);
+      delta_len = ns - 1;
+      t_end--;
+    }
+  }
+  __syncwarp();
+  return errors;
+}
+
+}  // namespace oic
+#endif

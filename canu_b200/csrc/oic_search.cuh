@@ -369,5 +369,33 @@ __global__ void __launch_bounds__(128) k_replay(ReplayArgs a) {
   a.info[pi] = inf;
 }
 
+// ---- longest-processing-time-first order of the pairs: pairs with many seeds need many sequential extensions,
+// so they enter the work queue first (counting sort by seed count, descending)
+constexpr int ORDER_BINS = 1024;
+__global__ void k_pair_hist(const Pair *__restrict__ pairs, uint32_t n, uint32_t *hist) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t k = pairs[i].n;
+  atomicAdd(&hist[ORDER_BINS - 1 - (k < ORDER_BINS - 1 ? k : ORDER_BINS - 1)], 1u);
+}
+__global__ void __launch_bounds__(ORDER_BINS) k_pair_bins_scan(uint32_t *hist) {
+  __shared__ uint32_t s[ORDER_BINS];
+  s[threadIdx.x] = hist[threadIdx.x];
+  __syncthreads();
+  for (int o = 1; o < ORDER_BINS; o <<= 1) {
+    uint32_t v = threadIdx.x >= (unsigned)o ? s[threadIdx.x - o] : 0;
+    __syncthreads();
+    s[threadIdx.x] += v;
+    __syncthreads();
+  }
+  hist[threadIdx.x] = s[threadIdx.x] - hist[threadIdx.x];   // exclusive
+}
+__global__ void k_pair_scatter(const Pair *__restrict__ pairs, uint32_t n, uint32_t *cursor, uint32_t *order) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t k = pairs[i].n;
+  order[atomicAdd(&cursor[ORDER_BINS - 1 - (k < ORDER_BINS - 1 ? k : ORDER_BINS - 1)], 1u)] = i;
+}
+
 }  // namespace oic
 #endif
