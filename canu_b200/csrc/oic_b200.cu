@@ -312,7 +312,7 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   cudaMemset(c->d_ctr.p, 0, sizeof(DevCounters));
   const char *rc = getenv("OIC_REC_CAP"), *bb = getenv("OIC_BATCH_BASES");
   c->rec_cap = rc ? strtoull(rc, nullptr, 10) : (48ull << 20);
-  c->batch_bases = bb ? strtoull(bb, nullptr, 10) : (24ull << 20);
+  c->batch_bases = bb ? strtoull(bb, nullptr, 10) : (512ull << 20);
   *out = c;
   return OIC_OK;
 }
@@ -687,7 +687,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.dirs = c->d_dirs.as<uint32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
-      k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+      k_process_pairs<true><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       c->tm.launches += 1;
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
       CK(cudaGetLastError());
@@ -707,7 +707,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->pair_cursor, 0, 4, c->stream));
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));
-        k_process_pairs<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_process_pairs<false><<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
         c->tm.launches += 2;
         int r2 = read_counters(c, hc);
         keep_retry.release();
@@ -715,6 +715,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         CK(cudaGetLastError());
         if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch (internal)");
       }
+      if (getenv("OIC_PHASE_CLOCKS"))
+        fprintf(stderr, "[oic] pair kernel: pairs %u warps %u | Mcycles: dp %.1f traceback %.1f prune %.1f | warp busy sum %.1f max %.1f | longest pair %.1f\n",
+                n_pairs, n_warps, hc.t_dp / 1e6, hc.t_tb / 1e6, hc.t_prune / 1e6, hc.t_warp_sum / 1e6, hc.t_warp_max / 1e6, hc.t_pair_max / 1e6);
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         size_t old = c->overlaps.size();

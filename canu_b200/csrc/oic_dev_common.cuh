@@ -35,6 +35,13 @@ constexpr int READ_LEAD_BASES = 64;  // zero bases before the first read
 
 constexpr unsigned FULL = 0xffffffffu;
 
+// phase clocks of the pair kernel: compile with -DOIC_PHASE_CLOCKS to enable (perturbs scheduling)
+#ifdef OIC_PHASE_CLOCKS
+#define OIC_CLOCK() clock64()
+#else
+#define OIC_CLOCK() 0LL
+#endif
+
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
 /* 32 bases starting at stream position p (p >= 0) */
@@ -114,6 +121,8 @@ struct DevCounters {
   unsigned int n_out;          // overlap records written
   unsigned int bad_base;       // a non-ACGT base was seen while packing
   unsigned int out_overflow;
+  // phase clocks of the pair kernel (SM cycles summed over warps; t_warp_max = busiest warp)
+  unsigned long long t_dp, t_tb, t_prune, t_warp_sum, t_warp_max, t_pair_max;
 };
 
 }  // namespace oic

@@ -62,6 +62,7 @@ struct WarpScratch {
   int max_rows;
   const int32_t *match_limit;
   unsigned long long cells, words;   // per-lane partial counters
+  long long t_tb;
 };
 
 __device__ __forceinline__ int row_get(const WarpScratch &ws, int k, int d) {
@@ -293,26 +294,28 @@ __device__ int dp_run(const ExtArgs &a, WarpScratch &ws, const uint64_t *__restr
 namespace oic {
 
 // shared-memory path first; the generic global-memory path only for runs with a row wider than SW
-template <int DIR>
-__device__ int dp_any(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *A, int64_t a0, int m, const uint64_t *T,
-                      int64_t t0, int n, int error_limit, int &a_end, int &t_end, int &leftover, int &to_end, int &delta_len) {
-  const unsigned long long sc = ws.cells, sw = ws.words;
-  int r = dp_run_fast<DIR>(a, ws, fs, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
-  if (r == -2) {
-    ws.cells = sc; ws.words = sw;
-    __syncwarp();
-    r = dp_run<DIR>(a, ws, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
+// FAST: shared-memory path (a row wider than SW sends the whole pair to the generic kernel, like a scratch overflow);
+// !FAST: the generic global-memory path, used by the retry kernel only -- keeps the hot kernel's code small enough
+// for the instruction cache.
+template <int DIR, bool FAST>
+__device__ __forceinline__ int dp_any(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *A, int64_t a0, int m,
+                                      const uint64_t *T, int64_t t0, int n, int error_limit, int &a_end, int &t_end, int &leftover,
+                                      int &to_end, int &delta_len) {
+  if (FAST) {
+    int r = dp_run_fast(DIR, a, ws, fs, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
+    return r == -2 ? -1 : r;
   }
-  return r;
+  return dp_run<DIR>(a, ws, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
 }
 
 /* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
  * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
+template <bool FAST>
 __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
                                 const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
                                 int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
   const int l = lane_id();
-  int right_errors = 0, left_errors = 0, leftover = 0, dummy = 0;
+  int right_errors = 0, left_errors = 0, leftover = 0;
   int r_to_end = 1, l_to_end = 1;
   const int s_left_begin = m_start - 1, s_right_begin = m_start + m_len, s_right_len = s_len - s_right_begin;
   const int t_left_begin = m_offset - 1, t_right_begin = m_offset + m_len, t_right_len = t_len - t_right_begin;
@@ -321,31 +324,40 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
   int rlen = 0, llen = 0;
   bool neg_right = false, neg_left = false;
 
-  if (s_right_len == 0 || t_right_len == 0) {
-    s_hi = t_hi = 0;
-  } else if (s_right_len <= t_right_len) {
-    right_errors = dp_any<+1>(a, ws, fs, S, sp + s_right_begin, s_right_len, T, tp + t_right_begin, t_right_len, err_limit,
-                              s_hi, t_hi, dummy, r_to_end, rlen);
-    neg_right = true;
-  } else {
-    right_errors = dp_any<+1>(a, ws, fs, T, tp + t_right_begin, t_right_len, S, sp + s_right_begin, s_right_len, err_limit,
-                              t_hi, s_hi, dummy, r_to_end, rlen);
+  // Two runs, right of the seed (forward) then left of it (reverse); in each the string with the shorter tail plays
+  // "A" (extend.C:136-187).  One call site (direction is a run-time argument of the shared-memory path) keeps a single
+  // copy of the DP in the kernel.
+  s_hi = t_hi = s_lo = t_lo = 0;
+#pragma unroll 1
+  for (int side = 0; side < 2; side++) {
+    const bool skip = side == 0 ? (s_right_len == 0 || t_right_len == 0) : (s_left_begin < 0 || t_left_begin < 0);
+    if (skip) continue;
+    const bool s_is_a = side == 0 ? (s_right_len <= t_right_len) : (s_right_begin <= t_right_begin);
+    const int s_from = side == 0 ? s_right_begin : s_left_begin, t_from = side == 0 ? t_right_begin : t_left_begin;
+    const int s_n = side == 0 ? s_right_len : s_left_begin + 1, t_n = side == 0 ? t_right_len : t_left_begin + 1;
+    const uint64_t *A = s_is_a ? S : T, *B = s_is_a ? T : S;
+    const int64_t a0 = s_is_a ? sp + s_from : tp + t_from, b0 = s_is_a ? tp + t_from : sp + s_from;
+    const int m = s_is_a ? s_n : t_n, n = s_is_a ? t_n : s_n;
+    const int limit = side == 0 ? err_limit : err_limit - right_errors;
+    int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
+    if (FAST) {
+      errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
+      if (errs == -2) errs = -1;
+    } else {
+      errs = side == 0 ? dp_run<+1>(a, ws, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl)
+                       : dp_run<-1>(a, ws, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
+    }
+    if (errs < 0) return -1;
+    if (side == 0) {
+      right_errors = errs; r_to_end = to_end; rlen = dl; neg_right = s_is_a;
+      s_hi = s_is_a ? a_end : b_end; t_hi = s_is_a ? b_end : a_end;
+    } else {
+      left_errors = errs; l_to_end = to_end; llen = dl; neg_left = !s_is_a; leftover = lo;
+      s_lo = s_is_a ? a_end : b_end; t_lo = s_is_a ? b_end : a_end;
+    }
   }
-  if (right_errors < 0) return -1;
   s_hi += s_right_begin - 1;
   t_hi += t_right_begin - 1;
-
-  if (s_left_begin < 0 || t_left_begin < 0) {
-    s_lo = t_lo = 0;
-  } else if (s_right_begin <= t_right_begin) {
-    left_errors = dp_any<-1>(a, ws, fs, S, sp + s_left_begin, s_left_begin + 1, T, tp + t_left_begin, t_left_begin + 1,
-                             err_limit - right_errors, s_lo, t_lo, leftover, l_to_end, llen);
-  } else {
-    left_errors = dp_any<-1>(a, ws, fs, T, tp + t_left_begin, t_left_begin + 1, S, sp + s_left_begin, s_left_begin + 1,
-                             err_limit - right_errors, t_lo, s_lo, leftover, l_to_end, llen);
-    neg_left = true;
-  }
-  if (left_errors < 0) return -1;
   s_lo += s_left_begin + 1;
   t_lo += t_left_begin + 1;
   errors = left_errors + right_errors;
@@ -366,7 +378,8 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
 
 constexpr int EXT_WARPS = 4;
 
-__global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
+template <bool FAST>
+__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) {
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   WarpScratch ws;
@@ -380,6 +393,9 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
   ws.max_rows = a.max_rows;
   ws.match_limit = a.match_limit;
   ws.cells = ws.words = 0;
+  ws.t_tb = 0;
+  long long t_ext = 0, t_prune = 0, t_pair_max = 0;
+  const long long t_begin = OIC_CLOCK();
   unsigned long long ext_calls = 0;
   __shared__ int32_t s_rows[EXT_WARPS][2][SW + 2];
   FastScratch fs;
@@ -408,6 +424,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
     const uint32_t t_id = a.hash_bgn_id + pr.str;
     Seed *seeds = a.seeds + pr.first;
     int n = (int)pr.n;
+    const long long t_pair0 = OIC_CLOCK();
 
     // --minkmers filter: computeMinimumKmers (Process_String_Overlaps.C:75-86,725)
     if (a.filter_by_kmer_count != 0) {
@@ -459,8 +476,10 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
       const Seed lg = seeds[li];
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
-      const int kind = extend_alignment(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const long long te0 = OIC_CLOCK();
+      const int kind = extend_alignment<FAST>(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
+      t_ext += OIC_CLOCK() - te0;
       if (kind < 0) { overflow = true; break; }
 
       if (kind == 3 || a.partial) {
@@ -474,6 +493,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
       if (inf.consistent) break;
 
       // drop the extended seed and every seed that lies on this alignment (Process_String_Overlaps.C:514-531)
+      const long long tp0 = OIC_CLOCK();
       int newn = 0;
       for (int i0 = 0; i0 < n; i0 += 32) {
         const int i = i0 + l;
@@ -493,7 +513,9 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
         __syncwarp();
       }
       n = newn;
+      t_prune += OIC_CLOCK() - tp0;
     }
+    { long long tp = OIC_CLOCK() - t_pair0; if (tp > t_pair_max) t_pair_max = tp; }
 
     if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
       ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
@@ -534,6 +556,13 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_process_pairs(ExtArgs a) {
 
   unsigned long long c = warp_sum64(ws.cells), w = warp_sum64(ws.words);
   if (l == 0) {
+    const long long tw = OIC_CLOCK() - t_begin;
+    atomicAdd(&a.ctr->t_dp, (unsigned long long)(t_ext - ws.t_tb));
+    atomicAdd(&a.ctr->t_tb, (unsigned long long)ws.t_tb);
+    atomicAdd(&a.ctr->t_prune, (unsigned long long)t_prune);
+    atomicAdd(&a.ctr->t_warp_sum, (unsigned long long)tw);
+    atomicMax(&a.ctr->t_warp_max, (unsigned long long)tw);
+    atomicMax(&a.ctr->t_pair_max, (unsigned long long)t_pair_max);
     if (c) atomicAdd(&a.ctr->ext_cells, c);
     if (w) atomicAdd(&a.ctr->ext_words, w);
     if (ext_calls) atomicAdd(&a.ctr->ext_calls, ext_calls);

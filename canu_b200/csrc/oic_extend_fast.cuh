@@ -20,6 +20,7 @@ namespace oic {
 constexpr int SW = 512;             // widest row the shared-memory path takes
 constexpr int DW = 2 * (SW / 32);   // direction words per row
 constexpr int FROM_NONE = -9;
+constexpr int UNR = 2;              // chunks of a row in flight together
 
 struct FastScratch {
   int32_t *row0, *row1;   // shared memory, SW + 2 ints each
@@ -73,6 +74,7 @@ __device__ int traceback_fast(const WarpScratch &ws, const FastScratch &fs, int 
     }
     int my_from = 0, my_d = 0;
     const int steps = kb < 32 ? kb : 32;
+#pragma unroll 1
     for (int j = 0; j < steps; j++) {
       int f = 0;
       if (l == j) {
@@ -99,12 +101,30 @@ __device__ int traceback_fast(const WarpScratch &ws, const FastScratch &fs, int 
   return nev;
 }
 
-template <int DIR>
-__device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *__restrict__ A, int64_t a0,
+/* 32-base compare step in either direction: number of equal bases starting at A[pa], T[pt] and walking by DIR
+ * (32 if all equal).  The reverse direction bit-reverses the XOR so one find-first-set serves both: the two bits of
+ * a base swap places, which does not matter for "first base that differs". */
+__device__ __forceinline__ int step32(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T, int64_t pt, int DIR) {
+  const int back = DIR > 0 ? 0 : 31;
+  uint64_t x = ext32(A, pa - back) ^ ext32(T, pt - back);
+  if (DIR < 0) x = __brevll(x);
+  return x ? ((__ffsll((long long)x) - 1) >> 1) : 32;
+}
+__device__ __forceinline__ int match_dir(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T, int64_t pt, int limit, int DIR) {
+  int r = 0;
+  while (r < limit) {
+    const int adv = step32(A, pa + DIR * r, T, pt + DIR * r, DIR);
+    r += adv;
+    if (adv < 32) break;
+  }
+  return r < limit ? r : limit;
+}
+
+__device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *__restrict__ A, int64_t a0,
                            int m, const uint64_t *__restrict__ T, int64_t t0, int n, int error_limit, int &a_end, int &t_end,
                            int &leftover, int &to_end, int &delta_len) {
   const int l = lane_id();
-  const int row0 = (DIR > 0) ? match_fwd(A, a0, T, t0, m) : match_rev(A, a0, T, t0, m);
+  const int row0 = match_dir(A, a0, T, t0, m, DIR);
   int32_t *prev = fs.row0, *cur = fs.row1;
   if (l == 0) {
     ws.cells += 1;
@@ -142,36 +162,70 @@ __device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch 
     next_off += width;
     const int nch = (width + 31) >> 5;
 
+    // Cells of the row, UNR chunks (32 diagonals each) per pass: the predecessor rule and the first 32-base compare of
+    // every chunk are issued back to back (independent loads in flight), longer slides finish in the rare-path loop.
+    // The trimming predicate (progress >= Edit_Match_Limit[e]) is evaluated on the fly.
+    const int lim = ws.match_limit[e];
     bool ended = false;
     int d_end = 0, r_end = 0;
-    for (int c = 0; c < nch; c++) {
-      const int i = 32 * c + l;
-      const int d = left + i;
-      const bool act = i < width;
-      int r = -1, wc = 0, from = 0;
-      if (act) {
-        int r0;
-        from = rule_from(prev, plo, ptlo, pthi, d, r0);
-        r = r0;
-        const int lim = imin(m, n - d);
-        if (r < lim)
-          r += (DIR > 0) ? match_fwd(A, a0 + r, T, t0 + r + d, lim - r) : match_rev(A, a0 - r, T, t0 - (r + d), lim - r);
-        cur[i] = r;
-        ws.vals[off + i] = r;
-        wc = (r - r0 + 1 + 15) / 16;
+    int nl = right + 1, nr = left - 1;
+    for (int c0 = 0; c0 < nch && !ended; c0 += UNR) {
+      int r[UNR], r0[UNR], fr[UNR], cap[UNR];
+      bool more[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const int i = 32 * (c0 + u) + l, d = left + i;
+        r0[u] = -1; fr[u] = 0; cap[u] = -1;
+        if (i < width) {
+          fr[u] = rule_from(prev, plo, ptlo, pthi, d, r0[u]);
+          cap[u] = imin(m, n - d);
+        }
       }
-      const unsigned bm = __ballot_sync(FULL, from == -1), bp = __ballot_sync(FULL, from == 1);
-      if (l == 0) *reinterpret_cast<uint2 *>(fs.dirs + (size_t)e * DW + 2 * c) = make_uint2(bm, bp);
-      const unsigned em = __ballot_sync(FULL, act && (r == m || r + d == n));
-      if (em) {
-        const int first = __ffs(em) - 1;
-        if (l <= first) { ws.cells += 1; ws.words += wc; }
-        d_end = left + 32 * c + first;
-        r_end = __shfl_sync(FULL, r, first);
-        ended = true;
-        break;
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const int d = left + 32 * (c0 + u) + l;
+        r[u] = r0[u];
+        more[u] = false;
+        if (r0[u] < cap[u]) {   // (inactive lanes have r0 = cap = -1)
+          const int adv = step32(A, a0 + DIR * r0[u], T, t0 + DIR * (r0[u] + d), DIR);
+          r[u] = r0[u] + adv;
+          more[u] = (adv == 32) && r[u] < cap[u];
+          if (r[u] > cap[u]) r[u] = cap[u];
+        }
       }
-      if (act) { ws.cells += 1; ws.words += wc; }
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const int c = c0 + u;
+        if (c < nch && !ended) {   // warp-uniform
+          const int i = 32 * c + l, d = left + i;
+          const bool act = i < width;
+          if (more[u])
+            r[u] += match_dir(A, a0 + DIR * r[u], T, t0 + DIR * (r[u] + d), cap[u] - r[u], DIR);
+          int wc = 0;
+          if (act) {
+            cur[i] = r[u];
+            ws.vals[off + i] = r[u];
+            wc = (r[u] - r0[u] + 1 + 15) / 16;
+          }
+          const unsigned bm = __ballot_sync(FULL, fr[u] == -1), bp = __ballot_sync(FULL, fr[u] == 1);
+          if (l == 0) *reinterpret_cast<uint2 *>(fs.dirs + (size_t)e * DW + 2 * c) = make_uint2(bm, bp);
+          const unsigned em = __ballot_sync(FULL, act && (r[u] == m || r[u] + d == n));
+          if (em) {
+            const int first = __ffs(em) - 1;
+            if (l <= first) { ws.cells += 1; ws.words += wc; }
+            d_end = left + 32 * c + first;
+            r_end = __shfl_sync(FULL, r[u], first);
+            ended = true;
+          } else {
+            if (act) { ws.cells += 1; ws.words += wc; }
+            const unsigned okm = __ballot_sync(FULL, act && (r[u] + imax(d, 0) >= lim));
+            if (okm) {
+              if (nl > right) nl = left + 32 * c + __ffs(okm) - 1;
+              nr = left + 32 * c + (31 - __clz(okm));
+            }
+          }
+        }
+      }
     }
     __syncwarp();
 
@@ -196,32 +250,17 @@ __device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch 
       a_end = DIR * r_end;
       t_end = DIR * (r_end + d_end);
       fin_e = e; fin_d = d_end; fin_val = r_end;
-      int r0;
-      from0 = rule_from(prev, plo, ptlo, pthi, d_end, r0);
+      int r0x;
+      from0 = rule_from(prev, plo, ptlo, pthi, d_end, r0x);
       errors = e;
       to_end = 1;
       break;
     }
 
-    // band trimming (forward.C:235-254)
-    const int lim = ws.match_limit[e];
-    int nl = right + 1;
-    for (int c = 0; c < nch; c++) {
-      const int i = 32 * c + l, d = left + i;
-      const bool ok = i < width && (cur[i] + imax(d, 0) >= lim);
-      const unsigned mk = __ballot_sync(FULL, ok);
-      if (mk) { nl = left + 32 * c + __ffs(mk) - 1; break; }
-    }
+    // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches the limit
     if (nl > right) {
       if (l == 0) ws.meta[e] = make_int4(left, nl, right, off);
       break;
-    }
-    int nr = nl;
-    for (int c = nch - 1; c >= 0; c--) {
-      const int i = 32 * c + l, d = left + i;
-      const bool ok = i < width && d >= nl && (cur[i] + imax(d, 0) >= lim);
-      const unsigned mk = __ballot_sync(FULL, ok);
-      if (mk) { nr = left + 32 * c + (31 - __clz(mk)); break; }
     }
     if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
 
@@ -261,6 +300,7 @@ __device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch 
   }
   __syncwarp();
 
+  const long long tb0 = OIC_CLOCK();
   const int ns = traceback_fast(ws, fs, fin_e, fin_d, from0);
   const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
   if (DIR > 0) {
@@ -288,6 +328,7 @@ __device__ int dp_run_fast(const ExtArgs &a, WarpScratch &ws, const FastScratch 
     }
   }
   __syncwarp();
+  ws.t_tb += OIC_CLOCK() - tb0;
   return errors;
 }
 
