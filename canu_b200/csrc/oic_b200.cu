@@ -519,7 +519,6 @@ int ensure_pair_scratch(oic_ctx *c, unsigned n_warps, unsigned long long rowcap)
   CK(c->d_vals.ensure((size_t)n_warps * rowcap * 4));
   CK(c->d_rowmeta.ensure((size_t)n_warps * c->max_rows * sizeof(int4)));
   CK(c->d_deltas.ensure((size_t)n_warps * (4ull * c->max_rows + 8) * 4));
-  CK(c->d_dirs.ensure((size_t)n_warps * c->max_rows * DW * 4));
   return 0;
 }
 
@@ -656,7 +655,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       const unsigned n_warps = grid * EXT_WARPS;
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
-      const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) + 1024;
+      const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 4ull * c->max_rows + 1024;
       const unsigned long long budget = (12ull << 30) / 4 / n_warps;
       const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
       if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
@@ -684,10 +683,12 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.min_branch_tail_slope = (P.max_erate > 0.06) ? 1.0 : 0.20;          // LIBO/prefixEditDistance.C:41
       ea.match_limit = c->d_match_limit.as<int32_t>(); ea.max_rows = c->max_rows;
       ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
-      ea.dirs = c->d_dirs.as<uint32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
-      k_process_pairs<true><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+      ea.dbg_pair = nullptr;
+      DevBuf d_dbg;
+      if (getenv("OIC_PHASE_CLOCKS")) { CK(d_dbg.ensure((size_t)n_pairs * 12)); CK(cudaMemsetAsync(d_dbg.p, 0, (size_t)n_pairs * 12, c->stream)); ea.dbg_pair = d_dbg.as<uint32_t>(); }
+      k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       c->tm.launches += 1;
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
       CK(cudaGetLastError());
@@ -696,18 +697,17 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         // in place; finished pairs are not read again) and rerun just those pairs with worst-case scratch
         const uint32_t nr = hc.n_retry;
         k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
-        const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) + 1024;
+        const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 4ull * c->max_rows + 1024;
         const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, (24ull << 30) / 4 / big / EXT_WARPS));
         DevBuf keep_retry;
         CK(keep_retry.ensure((size_t)nr * 4));
         CK(cudaMemcpyAsync(keep_retry.p, c->d_retry.p, (size_t)nr * 4, cudaMemcpyDeviceToDevice, c->stream));
         if (ensure_pair_scratch(c, grid2 * EXT_WARPS, big)) { keep_retry.release(); return OIC_ERR_CUDA; }
         ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = big; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
-        ea.dirs = c->d_dirs.as<uint32_t>();
-        ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
+          ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->pair_cursor, 0, 4, c->stream));
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));
-        k_process_pairs<false><<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_process_pairs<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
         c->tm.launches += 2;
         int r2 = read_counters(c, hc);
         keep_retry.release();
@@ -718,6 +718,16 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       if (getenv("OIC_PHASE_CLOCKS"))
         fprintf(stderr, "[oic] pair kernel: pairs %u warps %u | Mcycles: dp %.1f traceback %.1f prune %.1f | warp busy sum %.1f max %.1f | longest pair %.1f\n",
                 n_pairs, n_warps, hc.t_dp / 1e6, hc.t_tb / 1e6, hc.t_prune / 1e6, hc.t_warp_sum / 1e6, hc.t_warp_max / 1e6, hc.t_pair_max / 1e6);
+      if (ea.dbg_pair) {
+        std::vector<uint32_t> dp(3ull * n_pairs); std::vector<Pair> hp(n_pairs);
+        cudaMemcpy(dp.data(), d_dbg.p, (size_t)n_pairs * 12, cudaMemcpyDeviceToHost);
+        cudaMemcpy(hp.data(), c->d_pairs.p, (size_t)n_pairs * sizeof(Pair), cudaMemcpyDeviceToHost);
+        std::vector<uint32_t> idx(n_pairs); for (uint32_t i = 0; i < n_pairs; i++) idx[i] = i;
+        std::sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return dp[3ull * x] > dp[3ull * y]; });
+        for (uint32_t k = 0; k < 8 && k < n_pairs; k++) { uint32_t i = idx[k]; uint32_t ri = qs_read[hp[i].qs >> 1];
+          fprintf(stderr, "[oic]   heavy pair %u: %.1f Mcycles, seeds %u, ext calls %u, lane0 cells %u, qlen %u hlen %u\n", i, dp[3ull * i] * 1024 / 1e6, hp[i].n, dp[3ull * i + 1], dp[3ull * i + 2], c->h_len[ri], c->h_len[c->hb.bgn_id - c->first_id + hp[i].str]); }
+        d_dbg.release();
+      }
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         size_t old = c->overlaps.size();

@@ -13,8 +13,9 @@
  * pruned band, the longest prefix of A matched with e errors.  The lanes of the warp own consecutive
  * diagonals of the current row; the slide along a diagonal compares 32 bases per step on the 2-bit packed
  * strings; end-of-string detection, band trimming and the best-cell search are warp ballots / reductions.
- * All rows are kept (band-compressed: only the computed extent of each row) in the warp's private slice of a
- * global scratch arena because the traceback needs them for the delta list.  Integer only, except the
+ * All rows are kept (band-compressed: only the computed extent of each row, plus 2 direction bits per cell) in the
+ * warp's private slice of a global scratch arena because the traceback needs them for the delta list; the two
+ * live rows are staged in shared memory (oic_extend_fast.cuh).  Integer only, except the
  * branch-point score, which is IEEE double without FMA contraction (OIC_DMUL/OIC_DSUB).
  */
 #ifndef OIC_EXTEND_CUH
@@ -46,11 +47,11 @@ struct ExtArgs {
   // per-warp scratch
   int32_t *vals; unsigned long long rowcap;   // row values, rowcap ints per warp
   int4 *rowmeta;                              // max_rows per warp: {lo, tlo, thi, off}
-  uint32_t *dirs;                             // per warp: DW direction words per row (shared-memory path)
   int32_t *deltas;                            // per warp: stack[max_rows+2] rdelta[max_rows+2] ldelta[2*max_rows+4]
   // output
   uint32_t *out; uint32_t out_cap;            // 6 words per record
   uint32_t *retry_list;
+  uint32_t *dbg_pair;   // optional: per pair {kcycles, extension calls, lane-0 cells}
   DevCounters *ctr;
 };
 
@@ -65,252 +66,13 @@ struct WarpScratch {
   long long t_tb;
 };
 
-__device__ __forceinline__ int row_get(const WarpScratch &ws, int k, int d) {
-  int4 m = ws.meta[k];
-  if (d < m.y || d > m.z) return -2;
-  return ws.vals[m.w + d - m.x];
-}
-
-// lane 0 only.  Walk rows e..1 backwards choosing the predecessor by the rule that built the row.
-__device__ int traceback(const WarpScratch &ws, int e, int d, int32_t *stack, int &ns) {
-  int4 me = ws.meta[e];
-  int last = ws.vals[me.w + d - me.x];
-  ns = 0;
-  for (int k = e; k > 0; k--) {
-    int4 m = ws.meta[k - 1];
-    int g0 = (d < m.y || d > m.z) ? -2 : ws.vals[m.w + d - m.x];
-    int gm = (d - 1 < m.y || d - 1 > m.z) ? -2 : ws.vals[m.w + d - 1 - m.x];
-    int gp = (d + 1 < m.y || d + 1 > m.z) ? -2 : ws.vals[m.w + d + 1 - m.x];
-    int from = 0, mx = 1 + g0;
-    if (gm > mx) { from = -1; mx = gm; }
-    if (1 + gp > mx) { from = 1; mx = 1 + gp; }
-    if (from == -1) { stack[ns++] = mx - last - 1; d--; last = gm; }
-    else if (from == 1) { stack[ns++] = last - (mx - 1); d++; last = gp; }
-  }
-  return last;
-}
-
-/* One direction of the prefix edit distance.  DIR = +1: A[i], T[i]; DIR = -1: A[-i], T[-i] (a0 / t0 are the
- * stream positions of A[0] / T[0]).  Warp-uniform arguments and results.  Returns errors, or -1 if the
- * rows did not fit the scratch (overflow). */
-template <int DIR>
-__device__ int dp_run(const ExtArgs &a, WarpScratch &ws, const uint64_t *__restrict__ A, int64_t a0, int m,
-                      const uint64_t *__restrict__ T, int64_t t0, int n, int error_limit, int &a_end, int &t_end,
-                      int &leftover, int &to_end, int &delta_len) {
-  const int l = lane_id();
-  int row = (DIR > 0) ? match_fwd(A, a0, T, t0, m) : match_rev(A, a0, T, t0, m);
-  if (l == 0) {
-    ws.cells += 1;
-    ws.words += (unsigned)(row + 1 + 15) / 16;
-    ws.meta[0] = make_int4(0, 0, 0, 0);
-    ws.vals[0] = row;
-  }
-  delta_len = 0;
-  leftover = 0;
-  if (row == m) {
-    a_end = t_end = DIR * m;
-    leftover = m;
-    to_end = 1;
-    return 0;
-  }
-  int left = 0, right = 0;
-  double max_score = 0.0;
-  int max_score_len = 0, max_score_best_d = 0, max_score_best_e = 0;
-  int best_d = 0, best_e = 0, longest = 0;
-  int plo = 0, ptlo = 0, pthi = 0, poff = 0;   // previous row: computed lo, trimmed lo/hi, offset
-  int next_off = 1;
-  int fin_e = -1, fin_d = 0;                   // cell the traceback starts from
-  int errors = 0;
-  to_end = 0;
-  __syncwarp();
-
-  for (int e = 1; e <= error_limit; e++) {
-    left = imax(left - 1, -e);
-    right = imin(right + 1, e);
-    const int width = right - left + 1;
-    if (e >= ws.max_rows || (unsigned long long)next_off + width > ws.rowcap) return -1;
-    const int off = next_off;
-    next_off += width;
-
-    bool ended = false;
-    int d_end = 0, r_end = 0;
-    for (int cb = left; cb <= right; cb += 32) {
-      const int d = cb + l;
-      const bool act = d <= right;
-      int r = -1, wc = 0;
-      if (act) {
-        int g0 = (d < ptlo || d > pthi) ? -2 : ws.vals[poff + d - plo];
-        int gm = (d - 1 < ptlo || d - 1 > pthi) ? -2 : ws.vals[poff + d - 1 - plo];
-        int gp = (d + 1 < ptlo || d + 1 > pthi) ? -2 : ws.vals[poff + d + 1 - plo];
-        r = 1 + g0;
-        if (gm > r) r = gm;
-        if (1 + gp > r) r = 1 + gp;
-        const int r0 = r;
-        const int lim = imin(m, n - d);
-        if (r < lim)
-          r += (DIR > 0) ? match_fwd(A, a0 + r, T, t0 + r + d, lim - r) : match_rev(A, a0 - r, T, t0 - (r + d), lim - r);
-        ws.vals[off + d - left] = r;
-        wc = (r - r0 + 1 + 15) / 16;
-      }
-      const unsigned em = __ballot_sync(FULL, act && (r == m || r + d == n));
-      if (em) {
-        const int first = __ffs(em) - 1;
-        if (l <= first) { ws.cells += 1; ws.words += wc; }
-        d_end = cb + first;
-        r_end = __shfl_sync(FULL, r, first);
-        ended = true;
-        break;
-      }
-      if (act) { ws.cells += 1; ws.words += wc; }
-    }
-    __syncwarp();
-
-    if (ended) {
-      const double score = OIC_DSUB(OIC_DMUL((double)r_end, a.branch_match_value), (double)e);
-      const int tail_len = r_end - max_score_len;
-      bool abort = false;
-      if (a.partial && score < max_score) abort = true;
-      if (e > MIN_BRANCH_END_DIST / 2 && tail_len >= MIN_BRANCH_END_DIST) {
-        const double slope = OIC_DDIV(OIC_DSUB(max_score, score), (double)tail_len);
-        if (slope >= a.min_branch_tail_slope) abort = true;
-      }
-      if (l == 0) ws.meta[e] = make_int4(left, left, right, off);
-      if (abort) break;   // fall through to the "best so far" exit
-      if (DIR > 0) {
-        // force the last error to be a mismatch rather than an insertion (forward.C:213-219)
-        int gp = (d_end + 1 < ptlo || d_end + 1 > pthi) ? -2 : ws.vals[poff + d_end + 1 - plo];
-        if (r_end == m && 1 + gp == r_end && d_end < right) {
-          d_end++;
-          if (l == 0) ws.vals[off + d_end - left] = r_end;
-        }
-      }
-      a_end = DIR * r_end;
-      t_end = DIR * (r_end + d_end);
-      fin_e = e; fin_d = d_end;
-      errors = e;
-      to_end = 1;
-      break;
-    }
-
-    // band trimming (forward.C:235-254): cells whose progress is below Edit_Match_Limit[e] leave the band
-    const int lim = ws.match_limit[e];
-    int nl = right + 1;
-    for (int cb = left; cb <= right; cb += 32) {
-      const int d = cb + l;
-      const bool ok = d <= right && (ws.vals[off + d - left] + imax(d, 0) >= lim);
-      const unsigned mk = __ballot_sync(FULL, ok);
-      if (mk) { nl = cb + __ffs(mk) - 1; break; }
-    }
-    if (nl > right) {
-      if (l == 0) ws.meta[e] = make_int4(left, nl, right, off);
-      break;
-    }
-    int nr = nl;
-    for (int ce = right; ce >= nl; ce -= 32) {
-      const int d = ce - l;
-      const bool ok = d >= nl && (ws.vals[off + d - left] + imax(d, 0) >= lim);
-      const unsigned mk = __ballot_sync(FULL, ok);
-      if (mk) { nr = ce - (__ffs(mk) - 1); break; }
-    }
-    if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
-
-    // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
-    long long bk = -(1LL << 62);
-    for (int cb = nl; cb <= nr; cb += 32) {
-      const int d = cb + l;
-      if (d <= nr) {
-        long long k = (long long)ws.vals[off + d - left] * 4294967296LL + (long long)(0x7fffffff - (d - nl));
-        if (k > bk) bk = k;
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      long long ok = __shfl_xor_sync(FULL, bk, o);
-      if (ok > bk) bk = ok;
-    }
-    const int rowmax = (int)(bk >> 32);   // arithmetic shift: floor(bk / 2^32)
-    if (rowmax > longest) {
-      longest = rowmax;
-      best_d = nl + (0x7fffffff - (int)(bk & 0xffffffffLL));
-      best_e = e;
-    }
-    const double score = OIC_DSUB(OIC_DMUL((double)longest, a.branch_match_value), (double)e);
-    if (score > max_score) {
-      max_score = score;
-      max_score_len = longest;
-      max_score_best_d = best_d;
-      max_score_best_e = best_e;
-    }
-    plo = left; ptlo = nl; pthi = nr; poff = off;
-    left = nl; right = nr;
-    __syncwarp();
-  }
-
-  if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
-    a_end = DIR * max_score_len;
-    t_end = DIR * (max_score_len + max_score_best_d);
-    fin_e = max_score_best_e; fin_d = max_score_best_d;
-    errors = max_score_best_e;
-    to_end = 0;
-  }
-  __syncwarp();
-
-  // traceback on lane 0
-  int dl = 0, lo_out = 0, te = t_end;
-  if (l == 0) {
-    int ns;
-    int last = traceback(ws, fin_e, fin_d, ws.stack, ns);
-    if (DIR > 0) {   // Set_Right_Delta
-      ws.stack[ns++] = last + 1;
-      for (int i = ns - 1; i > 0; i--) {
-        int sgn = (ws.stack[i - 1] > 0) - (ws.stack[i - 1] < 0);
-        ws.rdelta[dl++] = iabs(ws.stack[i]) * sgn;
-      }
-    } else {         // Set_Left_Delta
-      lo_out = last;
-      for (int i = 0; i < ns; i++) ws.ldelta[i] = ws.stack[i];
-      dl = ns;
-      // a leading +1 indel becomes a substitution by pulling t_end in by one (reverse.C:92-108)
-      if (dl > 1 && ws.ldelta[0] == 1 && te + n > 0) {
-        int x = ws.ldelta[1];
-        ws.ldelta[0] = (x > 0) ? x + 1 : x - 1;
-        for (int i = 1; i < dl - 1; i++) ws.ldelta[i] = ws.ldelta[i + 1];
-        dl--;
-        te--;
-      }
-    }
-  }
-  delta_len = __shfl_sync(FULL, dl, 0);
-  if (DIR < 0) {
-    leftover = __shfl_sync(FULL, lo_out, 0);
-    t_end = __shfl_sync(FULL, te, 0);
-  }
-  __syncwarp();
-  return errors;
-}
-
 }  // namespace oic
 #include "oic_extend_fast.cuh"
 namespace oic {
 
 // shared-memory path first; the generic global-memory path only for runs with a row wider than SW
-// FAST: shared-memory path (a row wider than SW sends the whole pair to the generic kernel, like a scratch overflow);
-// !FAST: the generic global-memory path, used by the retry kernel only -- keeps the hot kernel's code small enough
-// for the instruction cache.
-template <int DIR, bool FAST>
-__device__ __forceinline__ int dp_any(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *A, int64_t a0, int m,
-                                      const uint64_t *T, int64_t t0, int n, int error_limit, int &a_end, int &t_end, int &leftover,
-                                      int &to_end, int &delta_len) {
-  if (FAST) {
-    int r = dp_run_fast(DIR, a, ws, fs, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
-    return r == -2 ? -1 : r;
-  }
-  return dp_run<DIR>(a, ws, A, a0, m, T, t0, n, error_limit, a_end, t_end, leftover, to_end, delta_len);
-}
-
 /* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
  * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
-template <bool FAST>
 __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
                                 const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
                                 int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
@@ -340,13 +102,7 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
     const int m = s_is_a ? s_n : t_n, n = s_is_a ? t_n : s_n;
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
-    if (FAST) {
-      errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
-      if (errs == -2) errs = -1;
-    } else {
-      errs = side == 0 ? dp_run<+1>(a, ws, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl)
-                       : dp_run<-1>(a, ws, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
-    }
+    errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
     if (errs < 0) return -1;
     if (side == 0) {
       right_errors = errs; r_to_end = to_end; rlen = dl; neg_right = s_is_a;
@@ -378,7 +134,6 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
 
 constexpr int EXT_WARPS = 4;
 
-template <bool FAST>
 __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) {
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -401,7 +156,6 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
   FastScratch fs;
   fs.row0 = s_rows[threadIdx.x >> 5][0];
   fs.row1 = s_rows[threadIdx.x >> 5][1];
-  fs.dirs = a.dirs + (unsigned long long)gw * a.max_rows * DW;
 
   while (true) {
     uint32_t ti = 0;
@@ -477,7 +231,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
       const long long te0 = OIC_CLOCK();
-      const int kind = extend_alignment<FAST>(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const int kind = extend_alignment(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
       t_ext += OIC_CLOCK() - te0;
       if (kind < 0) { overflow = true; break; }
@@ -515,7 +269,8 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       n = newn;
       t_prune += OIC_CLOCK() - tp0;
     }
-    { long long tp = OIC_CLOCK() - t_pair0; if (tp > t_pair_max) t_pair_max = tp; }
+    { long long tp = OIC_CLOCK() - t_pair0; if (tp > t_pair_max) t_pair_max = tp;
+      if (l == 0 && a.dbg_pair) { a.dbg_pair[3ull * pi] = (uint32_t)(tp >> 10); a.dbg_pair[3ull * pi + 1] = (uint32_t)(ext_calls - snap_calls); a.dbg_pair[3ull * pi + 2] = (uint32_t)((ws.cells - snap_cells) ); } }
 
     if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
       ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;

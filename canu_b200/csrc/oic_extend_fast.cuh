@@ -1,30 +1,33 @@
 /*
- * oic_extend_fast.cuh -- shared-memory variant of one prefix-edit-distance run (the common case).
+ * oic_extend_fast.cuh -- one direction of the banded prefix edit distance, warp-synchronous.
  *
- * Same recurrence and the same exits as dp_run() in oic_extend.cuh (LIBO/prefixEditDistance-forward.C:110-285,
- * -reverse.C:130-300), for runs whose rows never get wider than SW diagonals:
- *   - rows e-1 and e live in the warp's slice of shared memory (the "edit array staged in shared memory");
- *     every row is also streamed to the global history (coalesced, fire-and-forget) for the delta values;
- *   - each cell records which neighbour it came from (2 bits; two ballots per 32 diagonals), so the traceback
- *     (Set_Right_Delta / Set_Left_Delta, forward.C:48-87, reverse.C:52-109) no longer chases values through
- *     memory row by row: 32 rows at a time are loaded by the 32 lanes, the diagonal is walked with shuffles,
- *     and the few predecessor values the deltas need are fetched in one parallel round trip;
- *   - band trimming and the best-cell search are ballots and redux.max on the row in shared memory.
- * Returns -2 when a row is wider than SW (the caller reruns the direction with the generic dp_run()).
+ * Recurrence, exits and tie-breaks of prefixEditDistance::forward / ::reverse
+ * (LIBO/prefixEditDistance-forward.C:110-285, -reverse.C:130-300) and of Set_Right_Delta / Set_Left_Delta
+ * (forward.C:48-87, reverse.C:52-109):
+ *   - row e holds, per diagonal d of the pruned band, the longest prefix of A matched with e errors; the lanes own
+ *     consecutive diagonals, UNR chunks of 32 diagonals are in flight together (predecessor rule + first 32-base
+ *     compare of every chunk issued back to back), longer slides finish in a rare-path loop;
+ *   - rows e-1 and e are staged in the warp's slice of shared memory while they are at most SW wide (the common
+ *     case); wider rows (spurious seeds whose band is never trimmed) are read back from the global history;
+ *   - every row is appended to the warp's global history (values, then 2 direction bits per cell as two ballot
+ *     words per 32 diagonals): the traceback loads 32 rows at a time (one row per lane), walks the diagonal with
+ *     shuffles, and fetches the few predecessor values the deltas need in one parallel round trip;
+ *   - the band-trimming predicate (progress >= Edit_Match_Limit[e]) is a ballot taken while the cells are computed;
+ *     the best cell of the trimmed band is a redux.max + ballot per chunk.
+ * Integer only, except the branch-point score: IEEE double without FMA contraction.
+ * Returns -1 when the rows do not fit the warp's history (the pair is rerun with worst-case scratch).
  */
 #ifndef OIC_EXTEND_FAST_CUH
 #define OIC_EXTEND_FAST_CUH
 
 namespace oic {
 
-constexpr int SW = 512;             // widest row the shared-memory path takes
-constexpr int DW = 2 * (SW / 32);   // direction words per row
+constexpr int SW = 512;             // widest row staged in shared memory
 constexpr int FROM_NONE = -9;
 constexpr int UNR = 2;              // chunks of a row in flight together
 
 struct FastScratch {
   int32_t *row0, *row1;   // shared memory, SW + 2 ints each
-  uint32_t *dirs;         // global, DW words per row
 };
 
 // predecessor rule of the recurrence at diagonal d of the row after `prev` (values in shared memory)
@@ -52,7 +55,9 @@ __device__ __forceinline__ int tb_entry(const int32_t *ev, int i, int start_val)
 /* Cooperative traceback from cell (fin_e, fin_d).  from0 != FROM_NONE overrides the stored direction of the
  * first row (the exit row's cell may have been rewritten by the "last error is a mismatch" tweak).
  * Leaves the events in ws.stack[0 .. nev) and returns nev. */
-__device__ int traceback_fast(const WarpScratch &ws, const FastScratch &fs, int fin_e, int fin_d, int from0) {
+__device__ __forceinline__ int traceback_fast(const WarpScratch &ws, int fin_e, int fin_d, int from0) {
+  // Row k of the history: meta[k] = {lo, trimmed lo, trimmed hi, offset}; values at vals[offset ..], the direction
+  // words right behind them (the row's computed width follows from row k-1: hi = min(trimmed hi of k-1 + 1, k)).
   const int l = lane_id();
   int nev = 0;
   int dcur = fin_d;
@@ -63,14 +68,16 @@ __device__ int traceback_fast(const WarpScratch &ws, const FastScratch &fs, int 
     uint2 w0 = make_uint2(0, 0), w1 = w0, w2 = w0;
     int4 mp = make_int4(0, 0, 0, 0);
     if (valid) {
-      lo = ws.meta[k].x;
+      const int4 mk = ws.meta[k];
       mp = ws.meta[k - 1];
-      int imin = dcur - 31 - lo;
-      cs = (imin > 0 ? imin : 0) >> 5;
-      const uint2 *dp = reinterpret_cast<const uint2 *>(fs.dirs + (size_t)k * DW);
-      w0 = dp[cs];
-      if (cs + 1 < SW / 32) w1 = dp[cs + 1];
-      if (cs + 2 < SW / 32) w2 = dp[cs + 2];
+      lo = mk.x;
+      const int width = imin(mp.z + 1, k) - lo + 1, nch = (width + 31) >> 5;
+      const int imin_ = dcur - 31 - lo;
+      cs = (imin_ > 0 ? imin_ : 0) >> 5;
+      const uint32_t *dp = reinterpret_cast<const uint32_t *>(ws.vals + mk.w + width);
+      if (cs < nch) w0 = make_uint2(dp[2 * cs], dp[2 * cs + 1]);
+      if (cs + 1 < nch) w1 = make_uint2(dp[2 * cs + 2], dp[2 * cs + 3]);
+      if (cs + 2 < nch) w2 = make_uint2(dp[2 * cs + 4], dp[2 * cs + 5]);
     }
     int my_from = 0, my_d = 0;
     const int steps = kb < 32 ? kb : 32;
@@ -125,13 +132,14 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
                            int &leftover, int &to_end, int &delta_len) {
   const int l = lane_id();
   const int row0 = match_dir(A, a0, T, t0, m, DIR);
-  int32_t *prev = fs.row0, *cur = fs.row1;
+  int32_t *sm_prev = fs.row0, *sm_cur = fs.row1;   // shared-memory staging (rows up to SW wide)
+  const int32_t *prev = sm_prev;                   // where row e-1 is read from: shared memory or the global history
   if (l == 0) {
     ws.cells += 1;
     ws.words += (unsigned)(row0 + 1 + 15) / 16;
     ws.meta[0] = make_int4(0, 0, 0, 0);
     ws.vals[0] = row0;
-    prev[0] = row0;
+    sm_prev[0] = row0;
   }
   delta_len = 0;
   leftover = 0;
@@ -156,11 +164,13 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
     left = imax(left - 1, -e);
     right = imin(right + 1, e);
     const int width = right - left + 1;
-    if (width > SW) return -2;
-    if (e >= ws.max_rows || (unsigned long long)next_off + width > ws.rowcap) return -1;
-    const int off = next_off;
-    next_off += width;
     const int nch = (width + 31) >> 5;
+    if (e >= ws.max_rows || (unsigned long long)next_off + width + 2 * nch > ws.rowcap) return -1;
+    const int off = next_off;
+    next_off += width + 2 * nch;
+    const bool wide = width > SW;                              // too wide for the staging buffer: use the history itself
+    int32_t *cur = wide ? ws.vals + off : sm_cur;
+    uint32_t *dirs = reinterpret_cast<uint32_t *>(ws.vals + off + width);
 
     // Cells of the row, UNR chunks (32 diagonals each) per pass: the predecessor rule and the first 32-base compare of
     // every chunk are issued back to back (independent loads in flight), longer slides finish in the rare-path loop.
@@ -204,11 +214,11 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
           int wc = 0;
           if (act) {
             cur[i] = r[u];
-            ws.vals[off + i] = r[u];
+            if (!wide) ws.vals[off + i] = r[u];
             wc = (r[u] - r0[u] + 1 + 15) / 16;
           }
           const unsigned bm = __ballot_sync(FULL, fr[u] == -1), bp = __ballot_sync(FULL, fr[u] == 1);
-          if (l == 0) *reinterpret_cast<uint2 *>(fs.dirs + (size_t)e * DW + 2 * c) = make_uint2(bm, bp);
+          if (l == 0) { dirs[2 * c] = bm; dirs[2 * c + 1] = bp; }
           const unsigned em = __ballot_sync(FULL, act && (r[u] == m || r[u] + d == n));
           if (em) {
             const int first = __ffs(em) - 1;
@@ -285,7 +295,8 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
     }
     plo = left; ptlo = nl; pthi = nr;
     left = nl; right = nr;
-    int32_t *t = prev; prev = cur; cur = t;
+    prev = cur;
+    if (!wide) { int32_t *t = sm_prev; sm_prev = sm_cur; sm_cur = t; }
     __syncwarp();
   }
 
@@ -301,7 +312,7 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
   __syncwarp();
 
   const long long tb0 = OIC_CLOCK();
-  const int ns = traceback_fast(ws, fs, fin_e, fin_d, from0);
+  const int ns = traceback_fast(ws, fin_e, fin_d, from0);
   const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
   if (DIR > 0) {
     // Set_Right_Delta: st = entries, then last + 1; delta[x] = |st[ns - x]| * sign(st[ns - x - 1])

@@ -372,11 +372,16 @@ __global__ void __launch_bounds__(128) k_replay(ReplayArgs a) {
 // ---- longest-processing-time-first order of the pairs: pairs with many seeds need many sequential extensions,
 // so they enter the work queue first (counting sort by seed count, descending)
 constexpr int ORDER_BINS = 1024;
+// cost proxy of a pair: many seeds = many sequential extensions; one or two seeds may be a spurious k-mer hit whose
+// band is never trimmed (up to error_limit^2 cells), so those go first as well
+__device__ __forceinline__ uint32_t pair_bin(uint32_t n_seeds) {
+  uint32_t k = n_seeds <= 2 ? ORDER_BINS - 1 : (n_seeds < ORDER_BINS - 2 ? n_seeds : ORDER_BINS - 2);
+  return ORDER_BINS - 1 - k;
+}
 __global__ void k_pair_hist(const Pair *__restrict__ pairs, uint32_t n, uint32_t *hist) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t k = pairs[i].n;
-  atomicAdd(&hist[ORDER_BINS - 1 - (k < ORDER_BINS - 1 ? k : ORDER_BINS - 1)], 1u);
+  atomicAdd(&hist[pair_bin(pairs[i].n)], 1u);
 }
 __global__ void __launch_bounds__(ORDER_BINS) k_pair_bins_scan(uint32_t *hist) {
   __shared__ uint32_t s[ORDER_BINS];
@@ -393,8 +398,7 @@ __global__ void __launch_bounds__(ORDER_BINS) k_pair_bins_scan(uint32_t *hist) {
 __global__ void k_pair_scatter(const Pair *__restrict__ pairs, uint32_t n, uint32_t *cursor, uint32_t *order) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t k = pairs[i].n;
-  order[atomicAdd(&cursor[ORDER_BINS - 1 - (k < ORDER_BINS - 1 ? k : ORDER_BINS - 1)], 1u)] = i;
+  order[atomicAdd(&cursor[pair_bin(pairs[i].n)], 1u)] = i;
 }
 
 }  // namespace oic
