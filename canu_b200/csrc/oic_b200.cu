@@ -655,7 +655,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       const unsigned n_warps = grid * EXT_WARPS;
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
-      const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 4ull * c->max_rows + 1024;
+      const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
       const unsigned long long budget = (12ull << 30) / 4 / n_warps;
       const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
       if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
@@ -697,7 +697,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         // in place; finished pairs are not read again) and rerun just those pairs with worst-case scratch
         const uint32_t nr = hc.n_retry;
         k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
-        const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 4ull * c->max_rows + 1024;
+        const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
         const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, (24ull << 30) / 4 / big / EXT_WARPS));
         DevBuf keep_retry;
         CK(keep_retry.ensure((size_t)nr * 4));

@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
   long long t_ext = 0, t_prune = 0, t_pair_max = 0;
   const long long t_begin = OIC_CLOCK();
   unsigned long long ext_calls = 0;
-  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 2];
+  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 4];
   FastScratch fs;
   fs.row0 = s_rows[threadIdx.x >> 5][0];
   fs.row1 = s_rows[threadIdx.x >> 5][1];

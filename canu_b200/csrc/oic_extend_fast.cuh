@@ -27,20 +27,30 @@ constexpr int FROM_NONE = -9;
 constexpr int UNR = 2;              // chunks of a row in flight together
 
 struct FastScratch {
-  int32_t *row0, *row1;   // shared memory, SW + 2 ints each
+  int32_t *row0, *row1;   // shared memory, SW + 4 ints each (2-int margins for the -2 sentinels)
 };
 
-// predecessor rule of the recurrence at diagonal d of the row after `prev` (values in shared memory)
-__device__ __forceinline__ int rule_from(const int32_t *prev, int plo, int ptlo, int pthi, int d, int &r0) {
-  const int ip = d - plo;
-  const int g0 = (d < ptlo || d > pthi) ? -2 : prev[ip];
-  const int gm = (d - 1 < ptlo || d - 1 > pthi) ? -2 : prev[ip - 1];
-  const int gp = (d + 1 < ptlo || d + 1 > pthi) ? -2 : prev[ip + 1];
-  int r = 1 + g0, from = 0;
-  if (gm > r) { r = gm; from = -1; }
-  if (1 + gp > r) { r = 1 + gp; from = 1; }
-  r0 = r;
-  return from;
+/* Packed strings as 32-bit words (16 bases each); p is a signed base offset from the word pointer. */
+__device__ __forceinline__ uint32_t ext16(const uint32_t *__restrict__ Wp, int p) {
+  const int w = p >> 4;
+  return __funnelshift_r(Wp[w], Wp[w + 1], (p & 15) * 2);
+}
+/* 16-base compare step in either direction: number of equal bases starting at offsets pa / pt and walking by DIR
+ * (16 if all equal) */
+__device__ __forceinline__ int step16(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int DIR) {
+  const int back = DIR > 0 ? 0 : 15;
+  const uint32_t x = ext16(Ap, pa - back) ^ ext16(Tp, pt - back);
+  if (x == 0) return 16;
+  return DIR > 0 ? ((__ffs((int)x) - 1) >> 1) : (__clz((int)x) >> 1);
+}
+__device__ __forceinline__ int match_dir(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int limit, int DIR) {
+  int r = 0;
+  while (r < limit) {
+    const int adv = step16(Ap, pa + DIR * r, Tp, pt + DIR * r, DIR);
+    r += adv;
+    if (adv < 16) break;
+  }
+  return r < limit ? r : limit;
 }
 
 // event i of the traceback (an indel step): encoded (pred + 4) * 4 + (from + 1) in ws.stack[i]
@@ -74,7 +84,7 @@ __device__ __forceinline__ int traceback_fast(const WarpScratch &ws, int fin_e, 
       const int width = imin(mp.z + 1, k) - lo + 1, nch = (width + 31) >> 5;
       const int imin_ = dcur - 31 - lo;
       cs = (imin_ > 0 ? imin_ : 0) >> 5;
-      const uint32_t *dp = reinterpret_cast<const uint32_t *>(ws.vals + mk.w + width);
+      const uint32_t *dp = reinterpret_cast<const uint32_t *>(ws.vals + mk.w + width + 2);
       if (cs < nch) w0 = make_uint2(dp[2 * cs], dp[2 * cs + 1]);
       if (cs + 1 < nch) w1 = make_uint2(dp[2 * cs + 2], dp[2 * cs + 3]);
       if (cs + 2 < nch) w2 = make_uint2(dp[2 * cs + 4], dp[2 * cs + 5]);
@@ -127,19 +137,26 @@ __device__ __forceinline__ int match_dir(const uint64_t *__restrict__ A, int64_t
   return r < limit ? r : limit;
 }
 
+/* History layout of row e (ints, in the warp's slice `vals`): [2 margin][width values][2 margin][2 * nch direction words];
+ * meta[e] = {lo, trimmed lo, trimmed hi, offset of the first value}.  The live rows have the same 2-int margins: after
+ * trimming, the four cells just outside the band are overwritten with the reference's -2 sentinel (forward.C:155-161),
+ * so the predecessor rule needs no bounds checks. */
 __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *__restrict__ A, int64_t a0,
                            int m, const uint64_t *__restrict__ T, int64_t t0, int n, int error_limit, int &a_end, int &t_end,
                            int &leftover, int &to_end, int &delta_len) {
   const int l = lane_id();
-  const int row0 = match_dir(A, a0, T, t0, m, DIR);
-  int32_t *sm_prev = fs.row0, *sm_cur = fs.row1;   // shared-memory staging (rows up to SW wide)
-  const int32_t *prev = sm_prev;                   // where row e-1 is read from: shared memory or the global history
+  const uint32_t *Ap = reinterpret_cast<const uint32_t *>(A) + (a0 >> 4);
+  const uint32_t *Tp = reinterpret_cast<const uint32_t *>(T) + (t0 >> 4);
+  const int aph = (int)(a0 & 15), tph = (int)(t0 & 15);
+  const int row0 = match_dir(Ap, aph, Tp, tph, m, DIR);
+  int32_t *sm_prev = fs.row0 + 2, *sm_cur = fs.row1 + 2;   // shared-memory staging (rows up to SW wide)
+  const int32_t *prev = sm_prev;                           // row e-1: shared memory, or the global history when wide
+  if (l < 5) sm_prev[l - 2] = (l == 2) ? row0 : -2;
   if (l == 0) {
     ws.cells += 1;
     ws.words += (unsigned)(row0 + 1 + 15) / 16;
-    ws.meta[0] = make_int4(0, 0, 0, 0);
-    ws.vals[0] = row0;
-    sm_prev[0] = row0;
+    ws.meta[0] = make_int4(0, 0, 0, 2);
+    ws.vals[2] = row0;
   }
   delta_len = 0;
   leftover = 0;
@@ -153,10 +170,12 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
   double max_score = 0.0;
   int max_score_len = 0, max_score_best_d = 0, max_score_best_e = 0;
   int best_d = 0, best_e = 0, longest = 0;
-  int plo = 0, ptlo = 0, pthi = 0;
-  int next_off = 1;
+  int plo = 0;
+  int next_off = 5;
   int fin_e = -1, fin_d = 0, fin_val = 0, from0 = FROM_NONE;
   int errors = 0;
+  unsigned wsum = 0;    // per-lane count of 16-base compare words (W of the roofline formula)
+  unsigned ncell = 0;   // warp-uniform count of cells (C)
   to_end = 0;
   __syncwarp();
 
@@ -165,73 +184,78 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
     right = imin(right + 1, e);
     const int width = right - left + 1;
     const int nch = (width + 31) >> 5;
-    if (e >= ws.max_rows || (unsigned long long)next_off + width + 2 * nch > ws.rowcap) return -1;
-    const int off = next_off;
-    next_off += width + 2 * nch;
-    const bool wide = width > SW;                              // too wide for the staging buffer: use the history itself
+    if (e >= ws.max_rows || (unsigned long long)next_off + width + 4 + 2 * nch > ws.rowcap) { errors = -1; break; }
+    const int off = next_off + 2;
+    next_off += width + 4 + 2 * nch;
+    const bool wide = width > SW;                        // too wide for the staging buffer: use the history itself
     int32_t *cur = wide ? ws.vals + off : sm_cur;
-    uint32_t *dirs = reinterpret_cast<uint32_t *>(ws.vals + off + width);
-
-    // Cells of the row, UNR chunks (32 diagonals each) per pass: the predecessor rule and the first 32-base compare of
-    // every chunk are issued back to back (independent loads in flight), longer slides finish in the rare-path loop.
-    // The trimming predicate (progress >= Edit_Match_Limit[e]) is evaluated on the fly.
+    uint32_t *dirs = reinterpret_cast<uint32_t *>(ws.vals + off + width + 2);
     const int lim = ws.match_limit[e];
+    const int pshift = left - plo;                       // index of diagonal `left` in the previous row
+
     bool ended = false;
     int d_end = 0, r_end = 0;
     int nl = right + 1, nr = left - 1;
+    int gmax = -1, gpos = 0;                             // highest cell of the row, lowest diagonal on ties
     for (int c0 = 0; c0 < nch && !ended; c0 += UNR) {
       int r[UNR], r0[UNR], fr[UNR], cap[UNR];
-      bool more[UNR];
 #pragma unroll
-      for (int u = 0; u < UNR; u++) {
+      for (int u = 0; u < UNR; u++) {                    // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
         const int i = 32 * (c0 + u) + l, d = left + i;
         r0[u] = -1; fr[u] = 0; cap[u] = -1;
         if (i < width) {
-          fr[u] = rule_from(prev, plo, ptlo, pthi, d, r0[u]);
+          const int ip = i + pshift;
+          const int g0 = prev[ip], gm = prev[ip - 1], gp = prev[ip + 1];
+          int x = 1 + g0, f = 0;
+          if (gm > x) { x = gm; f = -1; }
+          if (1 + gp > x) { x = 1 + gp; f = 1; }
+          r0[u] = x; fr[u] = f;
           cap[u] = imin(m, n - d);
         }
       }
 #pragma unroll
-      for (int u = 0; u < UNR; u++) {
+      for (int u = 0; u < UNR; u++) {                    // first 16 bases of every slide, loads back to back
         const int d = left + 32 * (c0 + u) + l;
         r[u] = r0[u];
-        more[u] = false;
-        if (r0[u] < cap[u]) {   // (inactive lanes have r0 = cap = -1)
-          const int adv = step32(A, a0 + DIR * r0[u], T, t0 + DIR * (r0[u] + d), DIR);
-          r[u] = r0[u] + adv;
-          more[u] = (adv == 32) && r[u] < cap[u];
-          if (r[u] > cap[u]) r[u] = cap[u];
+        if (r0[u] < cap[u]) {                            // (inactive lanes have r0 = cap = -1)
+          r[u] = r0[u] + step16(Ap, aph + DIR * r0[u], Tp, tph + DIR * (r0[u] + d), DIR);
         }
       }
 #pragma unroll
       for (int u = 0; u < UNR; u++) {
         const int c = c0 + u;
-        if (c < nch && !ended) {   // warp-uniform
+        if (c < nch && !ended) {                         // warp-uniform
           const int i = 32 * c + l, d = left + i;
           const bool act = i < width;
-          if (more[u])
-            r[u] += match_dir(A, a0 + DIR * r[u], T, t0 + DIR * (r[u] + d), cap[u] - r[u], DIR);
-          int wc = 0;
+          if (r[u] - r0[u] == 16 && r[u] < cap[u])       // rare: the slide goes on past 16 bases
+            r[u] += match_dir(Ap, aph + DIR * r[u], Tp, tph + DIR * (r[u] + d), cap[u] - r[u], DIR);
+          if (r[u] > cap[u]) r[u] = cap[u];
           if (act) {
             cur[i] = r[u];
             if (!wide) ws.vals[off + i] = r[u];
-            wc = (r[u] - r0[u] + 1 + 15) / 16;
           }
           const unsigned bm = __ballot_sync(FULL, fr[u] == -1), bp = __ballot_sync(FULL, fr[u] == 1);
           if (l == 0) { dirs[2 * c] = bm; dirs[2 * c + 1] = bp; }
           const unsigned em = __ballot_sync(FULL, act && (r[u] == m || r[u] + d == n));
+          const unsigned wc = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
           if (em) {
             const int first = __ffs(em) - 1;
-            if (l <= first) { ws.cells += 1; ws.words += wc; }
+            if (l <= first) wsum += wc;
+            ncell += 32 * c + first + 1;
             d_end = left + 32 * c + first;
             r_end = __shfl_sync(FULL, r[u], first);
             ended = true;
           } else {
-            if (act) { ws.cells += 1; ws.words += wc; }
+            wsum += wc;
             const unsigned okm = __ballot_sync(FULL, act && (r[u] + imax(d, 0) >= lim));
             if (okm) {
               if (nl > right) nl = left + 32 * c + __ffs(okm) - 1;
               nr = left + 32 * c + (31 - __clz(okm));
+            }
+            const int mx = __reduce_max_sync(FULL, act ? r[u] : -1);
+            if (mx > gmax) {
+              gmax = mx;
+              gpos = left + 32 * c + __ffs(__ballot_sync(FULL, act && r[u] == mx)) - 1;
             }
           }
         }
@@ -251,7 +275,7 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
       if (l == 0) ws.meta[e] = make_int4(left, left, right, off);
       if (abort) break;
       if (DIR > 0) {   // force the last error to be a mismatch rather than an insertion (forward.C:213-219)
-        const int gp = (d_end + 1 < ptlo || d_end + 1 > pthi) ? -2 : prev[d_end + 1 - plo];
+        const int gp = prev[d_end + 1 - plo];
         if (r_end == m && 1 + gp == r_end && d_end < right) {
           d_end++;
           if (l == 0) ws.vals[off + d_end - left] = r_end;
@@ -260,14 +284,21 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
       a_end = DIR * r_end;
       t_end = DIR * (r_end + d_end);
       fin_e = e; fin_d = d_end; fin_val = r_end;
-      int r0x;
-      from0 = rule_from(prev, plo, ptlo, pthi, d_end, r0x);
+      {   // direction of the exit cell, by the rule (the cell may be one the row never computed)
+        const int ip = d_end - plo;
+        const int g0 = prev[ip], gm = prev[ip - 1], gp = prev[ip + 1];
+        int x = 1 + g0;
+        from0 = 0;
+        if (gm > x) { x = gm; from0 = -1; }
+        if (1 + gp > x) from0 = 1;
+      }
       errors = e;
       to_end = 1;
       break;
     }
+    ncell += width;
 
-    // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches the limit
+    // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches Edit_Match_Limit[e]
     if (nl > right) {
       if (l == 0) ws.meta[e] = make_int4(left, nl, right, off);
       break;
@@ -275,17 +306,21 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
     if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
 
     // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
-    int rowbest = -0x7fffffff, rowbest_d = 0;
-    for (int c = (nl - left) >> 5; c <= ((nr - left) >> 5); c++) {
-      const int i = 32 * c + l, d = left + i;
-      const int v = (d >= nl && d <= nr) ? cur[i] : -0x7fffffff;
-      const int mx = __reduce_max_sync(FULL, v);
-      if (mx > rowbest) {
-        rowbest = mx;
-        rowbest_d = left + 32 * c + __ffs(__ballot_sync(FULL, v == mx)) - 1;
+    if (gmax > longest) {
+      if (gpos < nl || gpos > nr) {   // rare: the row's top cell was trimmed away -> exact search inside the band
+        gmax = -1;
+        for (int c = (nl - left) >> 5; c <= ((nr - left) >> 5); c++) {
+          const int i = 32 * c + l, d = left + i;
+          const int v = (d >= nl && d <= nr) ? cur[i] : -1;
+          const int mx = __reduce_max_sync(FULL, v);
+          if (mx > gmax) {
+            gmax = mx;
+            gpos = left + 32 * c + __ffs(__ballot_sync(FULL, v == mx)) - 1;
+          }
+        }
       }
+      if (gmax > longest) { longest = gmax; best_d = gpos; best_e = e; }
     }
-    if (rowbest > longest) { longest = rowbest; best_d = rowbest_d; best_e = e; }
     const double score = OIC_DSUB(OIC_DMUL((double)longest, a.branch_match_value), (double)e);
     if (score > max_score) {
       max_score = score;
@@ -293,12 +328,18 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
       max_score_best_d = best_d;
       max_score_best_e = best_e;
     }
-    plo = left; ptlo = nl; pthi = nr;
+    // -2 sentinels on the four cells just outside the trimmed band
+    __syncwarp();
+    if (l < 4) cur[(l < 2 ? nl - 1 - l : nr - 1 + l) - left] = -2;
+    plo = left;
     left = nl; right = nr;
     prev = cur;
     if (!wide) { int32_t *t = sm_prev; sm_prev = sm_cur; sm_cur = t; }
     __syncwarp();
   }
+  ws.cells += (l == 0) ? ncell : 0;
+  ws.words += wsum;
+  if (errors < 0) return -1;
 
   if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
     a_end = DIR * max_score_len;
@@ -310,7 +351,6 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
     to_end = 0;
   }
   __syncwarp();
-
   const long long tb0 = OIC_CLOCK();
   const int ns = traceback_fast(ws, fin_e, fin_d, from0);
   const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;

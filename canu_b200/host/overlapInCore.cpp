@@ -1,0 +1,302 @@
+/*
+ * overlapInCore.cpp -- drop-in replacement of the reference's overlapInCore executable (OIC/overlapInCore.C:306-595):
+ * same command line, gkpStore input, <-o>.ovb / <base>.counts / <-s> stats outputs.  All overlap computation is done
+ * by liboic_b200.so (CUDA, include/oic_b200.h); this file is argv, file formats and the OverlapDriver loop.
+ *
+ * Additive options (ignored by nothing in the pipeline because the reference does not have them):
+ *   --gpus N      shard the query range of every hash sub-block over N GPUs (one host thread + one context per GPU;
+ *                 every GPU builds the same hash block from the same reads -- deterministic, no collective needed here;
+ *                 the NCCL-broadcast variant lives in bench.py where torch.distributed provides the communicator)
+ *   --device D    first CUDA device to use (default 0)
+ */
+#include <ctype.h>
+#include <errno.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/oic_b200.h"
+#include "stores.h"
+
+using namespace oichost;
+
+namespace {
+
+// AS_UTL_decodeRange (UTL/AS_UTL_decodeRange.C:103-152): "a-b" or "a"
+void decode_range(const char *s, uint32_t &lo, uint32_t &hi) {
+  char *end = nullptr;
+  unsigned long long a = strtoull(s, &end, 10);
+  if (end == s) { fprintf(stderr, "ERROR: invalid range '%s'\n", s); exit(1); }
+  unsigned long long b = a;
+  if (*end == '-') b = strtoull(end + 1, nullptr, 10);
+  lo = (uint32_t)a;
+  hi = (uint32_t)b;
+}
+
+void usage(const char *argv0) {
+  fprintf(stderr, "USAGE:  %s [options] <gkpStorePath>\n\n", argv0);
+  fprintf(stderr, "-G          do partial overlaps\n");
+  fprintf(stderr, "-h <range>  to specify fragments to put in hash table\n");
+  fprintf(stderr, "-H <range>  libraries to put in the hash table\n");
+  fprintf(stderr, "-k          if one or two digits, the length of a kmer, otherwise\n");
+  fprintf(stderr, "            the filename containing a list of kmers to ignore in the hash table\n");
+  fprintf(stderr, "-m          allow multiple overlaps per oriented fragment pair\n");
+  fprintf(stderr, "-o          specify output file name\n");
+  fprintf(stderr, "-r <range>  specify old fragments to overlap\n");
+  fprintf(stderr, "-R <range>  libraries to overlap\n");
+  fprintf(stderr, "-s          specify statistics file name\n");
+  fprintf(stderr, "-t <n>      use <n> parallel threads (only decides which reads the reference's scheduler would process)\n");
+  fprintf(stderr, "-u          allow only 1 overlap per oriented fragment pair\n");
+  fprintf(stderr, "-z          skip the hopeless check\n\n");
+  fprintf(stderr, "--maxerate <n>     only output overlaps with fraction <n> or less error (e.g., 0.06 == 6%%)\n");
+  fprintf(stderr, "--minlength <n>    only output overlaps of <n> or more bases\n");
+  fprintf(stderr, "--minkmers         filter pairs by expected k-mer count\n\n");
+  fprintf(stderr, "--hashbits n       n bits for the hash mask (here: only sets the load limit).\n");
+  fprintf(stderr, "--hashstrings n    Load at most n strings into the hash table at one time.\n");
+  fprintf(stderr, "--hashdatalen n    Load at most n bytes into the hash table at one time.\n");
+  fprintf(stderr, "--hashload f       Load to at most 0.0 < f < 1.0 capacity (default 0.7).\n");
+  fprintf(stderr, "--maxreadlen n     accepted, no effect on results\n\n");
+  fprintf(stderr, "--gpus n           B200s to shard the query reads over (default 1)\n");
+  fprintf(stderr, "--device d         first CUDA device (default 0)\n");
+}
+
+struct Shard {
+  oic_ctx_t *ctx = nullptr;
+  int rc = 0;
+  std::string err;
+};
+
+}  // namespace
+
+int main(int argc, char **argv) {
+  oic_params_t P;
+  memset(&P, 0, sizeof(P));
+  // oicParameters::initialize() (OIC/overlapInCore.H:425-464)
+  P.max_erate = 0.06;
+  P.bgn_hash_id = 1; P.end_hash_id = UINT32_MAX;
+  P.bgn_ref_id = 1; P.end_ref_id = UINT32_MAX;
+  P.frag_olap_limit = UINT64_MAX;
+  P.unique_olap = 1;
+  P.hash_bits = 22; P.hash_load = 0.6; P.max_hash_strings = 10000; P.max_hash_data_len = 100000000;
+  P.num_threads = 1;
+  P.use_hopeless_check = 1;
+  uint32_t min_lib_hash = 0, max_lib_hash = UINT32_MAX, min_lib_ref = 0, max_lib_ref = UINT32_MAX;
+  const char *skip_file = nullptr, *out_name = nullptr, *stat_name = nullptr, *store_path = nullptr;
+  bool window_filter = false;
+  int n_gpus = 1, device0 = 0;
+  uint64_t max_string_num = (1ull << 31) - 1;
+
+  if (argc == 2 && strcmp(argv[1], "--version") == 0) { fprintf(stdout, "overlapInCore (B200-native, Canu 1.6 compatible)\n"); return 0; }
+
+  int err = 0;
+  for (int arg = 1; arg < argc; arg++) {
+    const char *a = argv[arg];
+    auto need = [&](void) -> const char * {
+      if (arg + 1 >= argc) { fprintf(stderr, "ERROR: option '%s' needs a value\n", a); exit(1); }
+      return argv[++arg];
+    };
+    if (strcmp(a, "-G") == 0) P.partial = 1;
+    else if (strcmp(a, "-h") == 0) decode_range(need(), P.bgn_hash_id, P.end_hash_id);
+    else if (strcmp(a, "-H") == 0) decode_range(need(), min_lib_hash, max_lib_hash);
+    else if (strcmp(a, "-r") == 0) decode_range(need(), P.bgn_ref_id, P.end_ref_id);
+    else if (strcmp(a, "-R") == 0) decode_range(need(), min_lib_ref, max_lib_ref);
+    else if (strcmp(a, "-k") == 0) {
+      const char *v = need();   // one or two digits = k-mer length, anything else = skip file (OIC/overlapInCore.C:332-342)
+      if ((isdigit(v[0]) && v[1] == 0) || (isdigit(v[0]) && isdigit(v[1]) && v[2] == 0)) P.kmer_len = (int32_t)strtoull(v, nullptr, 10);
+      else {
+        FILE *t = fopen(v, "r");
+        if (!t) { fprintf(stderr, "ERROR: Failed to open -k '%s': %s\n", v, strerror(errno)); exit(1); }
+        fclose(t);
+        skip_file = v;
+      }
+    } else if (strcmp(a, "-l") == 0) {
+      long v = strtol(need(), nullptr, 10);
+      P.frag_olap_limit = v < 1 ? UINT64_MAX : (uint64_t)v;
+    } else if (strcmp(a, "-m") == 0) P.unique_olap = 0;
+    else if (strcmp(a, "-u") == 0) P.unique_olap = 1;
+    else if (strcmp(a, "--hashbits") == 0) P.hash_bits = (uint32_t)strtoull(need(), nullptr, 10);
+    else if (strcmp(a, "--hashstrings") == 0) P.max_hash_strings = (uint32_t)strtoull(need(), nullptr, 10);
+    else if (strcmp(a, "--hashdatalen") == 0) P.max_hash_data_len = strtoull(need(), nullptr, 10);
+    else if (strcmp(a, "--hashload") == 0) P.hash_load = atof(need());
+    else if (strcmp(a, "--maxreadlen") == 0) {
+      // re-splits the reference's 30-bit string reference (OIC/overlapInCore.C:366-378): only the string limit matters here
+      uint32_t desired = (uint32_t)strtoul(need(), nullptr, 10), bits = 1;
+      while ((1u << bits) < desired) bits++;
+      max_string_num = (1ull << (30 - bits)) - 1;
+    } else if (strcmp(a, "-o") == 0) out_name = need();
+    else if (strcmp(a, "-s") == 0) stat_name = need();
+    else if (strcmp(a, "-t") == 0) P.num_threads = (uint32_t)strtoull(need(), nullptr, 10);
+    else if (strcmp(a, "--minlength") == 0) P.min_olap_len = (int32_t)strtol(need(), nullptr, 10);
+    else if (strcmp(a, "--minkmers") == 0)   // evaluated with the K / erate / minlength seen SO FAR (OIC/overlapInCore.C:392-393)
+      P.filter_by_kmer_count = (uint64_t)(int)floor(exp(-1.0 * (double)P.kmer_len * P.max_erate) * (P.min_olap_len - P.kmer_len + 1));
+    else if (strcmp(a, "--maxerate") == 0) P.max_erate = strtof(need(), nullptr);   // float precision, widened (:395)
+    else if (strcmp(a, "-w") == 0) window_filter = true;
+    else if (strcmp(a, "-z") == 0) P.use_hopeless_check = 0;
+    else if (strcmp(a, "--gpus") == 0) n_gpus = atoi(need());
+    else if (strcmp(a, "--device") == 0) device0 = atoi(need());
+    else if (store_path == nullptr) store_path = a;
+    else { fprintf(stderr, "Unknown option '%s'\n", a); err++; }
+  }
+  if (P.max_erate > 0.06) {   // OIC/overlapInCore.C:416-421
+    if (window_filter) fprintf(stderr, "High error rates requested -- window-filter turned off despite -w flag!\n");
+    window_filter = false;
+    P.use_hopeless_check = 0;
+  }
+  if (P.max_hash_strings == 0) fprintf(stderr, "* No memory model supplied; -M needed!\n"), err++;
+  if (P.kmer_len == 0) fprintf(stderr, "* No kmer length supplied; -k needed!\n"), err++;
+  if (P.max_hash_strings > max_string_num) fprintf(stderr, "Too many strings (--hashstrings), must be less than %llu\n", (unsigned long long)max_string_num), err++;
+  if (out_name == nullptr) fprintf(stderr, "ERROR:  No output file name specified\n"), err++;
+  if (err || store_path == nullptr) { usage(argv[0]); return 1; }
+  if (window_filter) { fprintf(stderr, "ERROR: -w (window filter) is not supported by this build\n"); return 1; }
+  if (P.num_threads == 0) P.num_threads = 1;
+  if (n_gpus < 1) n_gpus = 1;
+
+  // ---- input
+  GkStore store(store_path);
+  const uint32_t num_reads = store.num_reads();
+  if (P.bgn_hash_id < 1) P.bgn_hash_id = 1;
+  if (P.end_hash_id > num_reads) P.end_hash_id = num_reads;
+  if (P.bgn_ref_id < 1) P.bgn_ref_id = 1;
+  if (P.end_ref_id > num_reads) P.end_ref_id = num_reads;
+  const uint32_t first_id = std::min(P.bgn_hash_id, P.bgn_ref_id);
+  const uint32_t last_id = std::max(P.end_hash_id, P.end_ref_id);
+  const uint32_t n = last_id >= first_id ? last_id - first_id + 1 : 0;
+  std::vector<uint64_t> offsets(n);
+  std::vector<uint32_t> lengths(n);
+  std::vector<uint8_t> hash_ok(n), ref_ok(n);
+  uint64_t total = 0;
+  for (uint32_t i = 0; i < n; i++) {
+    const GkRead &r = store.read(first_id + i);
+    offsets[i] = total;
+    lengths[i] = r.seq_len();
+    total += r.seq_len();
+    const uint32_t lib = r.library_id();
+    hash_ok[i] = !(lib < min_lib_hash || lib > max_lib_hash);   // Build_Hash_Index.C:555-557
+    ref_ok[i] = !(lib < min_lib_ref || lib > max_lib_ref);      // Process_Overlaps.C:108-110
+  }
+  std::vector<char> bases(total + 1);
+  {
+    const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++)
+      th.emplace_back([&, t]() {
+        for (uint64_t i = (uint64_t)n * t / nt, e = (uint64_t)n * (t + 1) / nt; i < e; i++)
+          store.load_sequence(first_id + (uint32_t)i, bases.data() + offsets[i]);
+      });
+    for (auto &t : th) t.join();
+  }
+  fprintf(stderr, "Loaded reads %u-%u (%llu bases) from '%s'\n", first_id, last_id, (unsigned long long)total, store_path);
+
+  std::vector<char> skip;   // Mark_Skip_Kmers input: '>' header line, then exactly K bases (Build_Hash_Index.C:233-286)
+  uint64_t n_skip = 0;
+  if (skip_file) {
+    FILE *f = fopen(skip_file, "r");
+    char line[1000];
+    int ct = 0;
+    while (fgets(line, sizeof(line), f)) {
+      ct++;
+      int len = (int)strlen(line) - 1;
+      if (line[0] != '>' || len < 0 || line[len] != '\n') { fprintf(stderr, "ERROR:  Bad line %d in kmer skip file\n%s", ct, line); return 1; }
+      if (!fgets(line, sizeof(line), f)) { fprintf(stderr, "ERROR:  Bad line after %d in kmer skip file\n", ct); return 1; }
+      ct++;
+      len = (int)strlen(line) - 1;
+      if (len != P.kmer_len || line[len] != '\n') { fprintf(stderr, "ERROR:  Bad line %d in kmer skip file\n%s", ct, line); return 1; }
+      skip.insert(skip.end(), line, line + len);
+      n_skip++;
+    }
+    fclose(f);
+    fprintf(stderr, "Read %llu kmers to mark to skip\n", (unsigned long long)n_skip);
+  }
+
+  // ---- contexts, one per GPU
+  std::vector<Shard> sh(n_gpus);
+  for (int g = 0; g < n_gpus; g++) {
+    int rc = oic_create(&P, device0 + g, &sh[g].ctx);
+    if (rc) { fprintf(stderr, "ERROR: %s\n", oic_last_error(nullptr)); return 1; }
+  }
+  auto on_all = [&](auto fn) -> bool {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_gpus; g++) th.emplace_back([&, g]() { sh[g].rc = fn(g); if (sh[g].rc) sh[g].err = oic_last_error(sh[g].ctx); });
+    for (auto &t : th) t.join();
+    for (int g = 0; g < n_gpus; g++)
+      if (sh[g].rc) { fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str()); return false; }
+    return true;
+  };
+  if (n == 0) { fprintf(stderr, "ERROR: empty read range\n"); return 1; }
+  if (!on_all([&](int g) {
+        int rc = oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
+        if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
+        return rc;
+      })) return 1;
+
+  // ---- OverlapDriver (OIC/overlapInCore.C:190-300)
+  OvbWriter out(out_name);
+  std::vector<uint32_t> rec;
+  uint64_t bgn = P.bgn_hash_id, end = (uint64_t)P.bgn_hash_id + P.max_hash_strings - 1;
+  while (bgn < P.end_hash_id) {
+    if (end > P.end_hash_id) end = P.end_hash_id;
+    std::vector<uint32_t> last(n_gpus, 0);
+    if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g]); })) return 1;
+    fprintf(stderr, "Hash block %llu-%u built\n", (unsigned long long)bgn, last[0]);
+    const uint32_t last_ref = oic_last_processed_ref(P.bgn_ref_id, P.end_ref_id, P.num_threads);
+    if (last_ref >= P.bgn_ref_id) {
+      // contiguous shards balanced by bases x expected partners: a query only pairs with hash reads of higher ID
+      std::vector<double> w(last_ref - P.bgn_ref_id + 2, 0.0);
+      for (uint32_t id = P.bgn_ref_id; id <= last_ref; id++) {
+        double partners = id < bgn ? (double)(last[0] - bgn + 1) : (id < last[0] ? (double)(last[0] - id) : 0.0);
+        w[id - P.bgn_ref_id + 1] = w[id - P.bgn_ref_id] + (double)lengths[id - first_id] * partners + 1.0;
+      }
+      std::vector<uint32_t> cut(n_gpus + 1, P.bgn_ref_id);
+      for (int g = 1; g <= n_gpus; g++) {
+        double target = w.back() * g / n_gpus;
+        cut[g] = P.bgn_ref_id + (uint32_t)(std::lower_bound(w.begin(), w.end(), target) - w.begin());
+        if (cut[g] > last_ref + 1 || g == n_gpus) cut[g] = last_ref + 1;
+      }
+      if (!on_all([&](int g) { return cut[g + 1] > cut[g] ? oic_process_overlaps(sh[g].ctx, cut[g], cut[g + 1] - 1) : 0; })) return 1;
+      for (int g = 0; g < n_gpus; g++) {
+        uint64_t k = oic_num_overlaps(sh[g].ctx), got = 0;
+        rec.resize(6 * k);
+        oic_copy_overlaps(sh[g].ctx, reinterpret_cast<oic_ovb_record_t *>(rec.data()), k, &got);
+        out.write(rec.data(), got);
+        oic_clear_overlaps(sh[g].ctx);
+      }
+    }
+    bgn = (uint64_t)last[0] + 1;
+    end = bgn + P.max_hash_strings - 1;
+  }
+  out.close();
+
+  // ---- -s stats (OIC/overlapInCore.C:569-588)
+  oic_stats_t tot, s;
+  memset(&tot, 0, sizeof(tot));
+  for (int g = 0; g < n_gpus; g++) {
+    oic_get_stats(sh[g].ctx, &s);
+    tot.kmer_hits_without_olap += s.kmer_hits_without_olap; tot.kmer_hits_with_olap += s.kmer_hits_with_olap;
+    tot.multi_overlap += s.multi_overlap; tot.total_overlaps += s.total_overlaps;
+    tot.contained += s.contained; tot.dovetail += s.dovetail;
+    oic_destroy(sh[g].ctx);
+  }
+  FILE *stats = stderr;
+  if (stat_name) {
+    stats = fopen(stat_name, "w");
+    if (!stats) { fprintf(stderr, "WARNING: failed to open '%s' for writing: %s\n", stat_name, strerror(errno)); stats = stderr; }
+  }
+  fprintf(stats, " Kmer hits without olaps = %lld\n", (long long)tot.kmer_hits_without_olap);
+  fprintf(stats, "    Kmer hits with olaps = %lld\n", (long long)tot.kmer_hits_with_olap);
+  fprintf(stats, "  Multiple overlaps/pair = %lld\n", (long long)tot.multi_overlap);
+  fprintf(stats, " Total overlaps produced = %lld\n", (long long)tot.total_overlaps);
+  fprintf(stats, "      Contained overlaps = %lld\n", (long long)tot.contained);
+  fprintf(stats, "       Dovetail overlaps = %lld\n", (long long)tot.dovetail);
+  fprintf(stats, "Rejected by short window = %lld\n", 0LL);
+  fprintf(stats, " Rejected by long window = %lld\n", 0LL);
+  if (stats != stderr) fclose(stats);
+  fprintf(stderr, "Bye.\n");
+  return 0;
+}

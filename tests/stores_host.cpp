@@ -1,0 +1,48 @@
+// Test harness for canu_b200/host/stores.cpp (no CUDA): exported with C linkage for ctypes.
+#include <string.h>
+
+#include "../canu_b200/host/stores.h"
+
+using namespace oichost;
+
+extern "C" {
+
+// number of reads; lengths[] / libs[] (size num_reads, may be null) are filled for IDs 1..num_reads
+uint32_t sh_store_info(const char *path, uint32_t *lengths, uint32_t *libs, uint32_t cap) {
+  GkStore s(path);
+  for (uint32_t id = 1; id <= s.num_reads() && id <= cap; id++) {
+    if (lengths) lengths[id - 1] = s.read(id).seq_len();
+    if (libs) libs[id - 1] = s.read(id).library_id();
+  }
+  return s.num_reads();
+}
+
+// concatenated ASCII sequences of reads 1..num_reads into out (caller sized it from the lengths)
+void sh_store_bases(const char *path, char *out) {
+  GkStore s(path);
+  uint64_t at = 0;
+  for (uint32_t id = 1; id <= s.num_reads(); id++) {
+    s.load_sequence(id, out + at);
+    at += s.read(id).seq_len();
+  }
+}
+
+// write n 24-byte records in `pieces` write() calls (exercises the block boundary logic)
+void sh_write_ovb(const char *name, const uint32_t *rec, uint64_t n, uint32_t pieces) {
+  OvbWriter w(name);
+  if (pieces == 0) pieces = 1;
+  uint64_t done = 0;
+  for (uint32_t p = 0; p < pieces; p++) {
+    uint64_t upto = n * (p + 1) / pieces;
+    w.write(rec + 6 * done, upto - done);
+    done = upto;
+  }
+  w.close();
+}
+
+void sh_counts_name(const char *name, char *out, uint32_t cap) {
+  std::string s = counts_name_for(name);
+  strncpy(out, s.c_str(), cap - 1);
+  out[cap - 1] = 0;
+}
+}

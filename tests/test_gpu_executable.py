@@ -1,0 +1,67 @@
+"""GPU end-to-end test of the drop-in executable canu_b200/bin/overlapInCore: gkpStore in, .ovb/.counts/.stats out,
+compared byte-for-byte (after the reference's own overlapConvert | sort) with the reference binary's outputs in
+tests/golden/.  The store is written by the reference's gatekeeperCreate (oracle/_ref, prebuilt, travels to the box).
+"""
+import gzip
+import hashlib
+import json
+import os
+import subprocess
+
+import pytest
+
+import cases
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+BIN = os.path.join(H.ROOT, "canu_b200", "bin", "overlapInCore")
+
+needs_tools = pytest.mark.skipif(not (H.have_ref() and os.access(BIN, os.X_OK)),
+                                 reason="oracle/_ref tools or canu_b200/bin/overlapInCore not built")
+
+
+def run_case(name, wd, extra=()):
+    reads, P, erate, threads, skip = cases.build_case(name)
+    store = H.make_store(reads, wd)
+    args = H.oic_args(P, erate)
+    if skip:
+        sf = os.path.join(wd, "skip.fasta")
+        cases.write_skip_file(skip, sf)
+        args += ["-k", sf]
+    ovb, st = H.run_overlapper(BIN, store, os.path.join(wd, "mine"), args + list(extra), threads)
+    return store, ovb, st
+
+
+@needs_tools
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_executable_vs_golden(name, tmp_path):
+    store, ovb, st = run_case(name, str(tmp_path))
+    got = H.dump_ovb_sorted(store, ovb)
+    want = gzip.open(os.path.join(GOLDEN, name + ".txt.gz")).read().decode().splitlines()
+    assert got == want
+    meta = json.load(open(os.path.join(GOLDEN, name + ".json")))
+    assert H.parse_stats(st) == meta["stats"]
+    assert open(st).read().count("\n") == 8
+    assert hashlib.md5(open(os.path.join(str(tmp_path), "mine.counts"), "rb").read()).hexdigest() == meta["counts_md5"]
+
+
+@needs_tools
+def test_executable_usage_errors(tmp_path):
+    """no -k / no -o: usage on stderr and exit status 1, like the reference (OIC/overlapInCore.C:423-470)"""
+    r = subprocess.run([BIN, "-o", str(tmp_path / "x.ovb"), "nostore"], capture_output=True)
+    assert r.returncode == 1 and b"No kmer length supplied" in r.stderr
+    r = subprocess.run([BIN, "-k", "22", "nostore"], capture_output=True)
+    assert r.returncode == 1 and b"No output file name" in r.stderr
+
+
+@needs_tools
+def test_executable_two_shards_same_gpu_count(tmp_path):
+    """--gpus larger than the box has must fail loudly, not fall back"""
+    import torch
+    n = torch.cuda.device_count()
+    reads, P, erate, threads, skip = cases.build_case("c4_short")
+    store = H.make_store(reads, str(tmp_path))
+    r = subprocess.run([BIN, "--gpus", str(n + 1)] + H.oic_args(P, erate) + ["-o", str(tmp_path / "x.ovb"), store], capture_output=True)
+    assert r.returncode != 0
