@@ -42,7 +42,12 @@ def test_executable_vs_golden(name, tmp_path):
     want = gzip.open(os.path.join(GOLDEN, name + ".txt.gz")).read().decode().splitlines()
     assert got == want
     meta = json.load(open(os.path.join(GOLDEN, name + ".json")))
-    assert H.parse_stats(st) == meta["stats"]
+    mine, ref = H.parse_stats(st), dict(meta["stats"])
+    if "-G" in H.oic_args(cases.build_case(name)[1], "0.06"):
+        # -G: the reference bumps an unsynchronised global from every thread (OIC/overlapInCore-Output.C:253), so its
+        # own total is racy (<= the record count); ours is the record count
+        assert mine.pop("Total overlaps produced") == len(want) >= ref.pop("Total overlaps produced")
+    assert mine == ref
     assert open(st).read().count("\n") == 8
     assert hashlib.md5(open(os.path.join(str(tmp_path), "mine.counts"), "rb").read()).hexdigest() == meta["counts_md5"]
 
