@@ -6,7 +6,7 @@
  * ST/ = src/stores/, UTL/ = src/AS_UTL/ under /root/reference.
  *
  * Parity status: PINNED against the reference binary (oracle/_ref/overlapInCore, built by
- * oracle/build_ref.sh from the reference sources) -- tests/test_oracle_vs_ref.py compares the
+ * oracle/build_ref.sh from the reference sources) -- tests/golden/make_golden.py ran it on the seeded cases and tests/test_oracle.py compares the
  * sorted overlap records and the .stats counters on seeded synthetic stores.  The reference
  * ships no golden vectors for this path.
  */
