@@ -51,12 +51,6 @@ def gen_blocks(genome_len, n_blocks, block_bases, seed):
     return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed)
 
 
-def split_blocks(reads, n_blocks):
-    """contiguous read-ID ranges of equal read count: blocks 0..n-2 are query blocks, the last one is the hash block"""
-    per = reads.n // n_blocks
-    return [(i * per + 1, (i + 1) * per if i < n_blocks - 1 else reads.n) for i in range(n_blocks)]
-
-
 class ClockSampler(threading.Thread):
     def __init__(self, gpu_index):
         super().__init__(daemon=True)
@@ -93,7 +87,8 @@ def reference_leg(steps, warmup, scale_mbp=20, cores=None):
     cores = cores or os.cpu_count()
     g = scale_mbp * 1_000_000
     reads = gen_blocks(g, 2, g, SEED + 7)
-    (qb, qe), (hb, he) = split_blocks(reads, 2)
+    from canu_b200 import shard
+    (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
     qbases = int(reads.lengths[qb - 1:qe].sum())
     P = params_for(he - hb + 1, reads.n, threads=cores)
     sample = ("reference overlapInCore -t %d, genome %d Mbp: hash block %d reads (%.1f Mbp, 1x) x query block %d reads (%.1f Mbp, 1x), "
@@ -173,32 +168,20 @@ def main():
     block = int(BLOCK_BASES * a.scale)
     # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
     reads = gen_blocks(genome, world + 1, block, SEED)
-    blocks = split_blocks(reads, world + 1)
-    hb, he = blocks[-1]
-    qb, qe = blocks[rank]
+    from canu_b200 import shard
+    blocks = shard.split_blocks(reads.n, world + 1)
+    rj = shard.RankJob(blocks, rank)
+    hb, he, qb, qe, n_q, n_h = rj.hb, rj.he, rj.qb, rj.qe, rj.n_q, rj.n_h
     q_bases_rank = int(reads.lengths[qb - 1:qe].sum())
     q_bases_all = int(reads.lengths[:hb - 1].sum())
     P = params_for(he - hb + 1, reads.n)
 
-    # this rank needs its query block and the hash block: gather them into one pinned host buffer (IDs stay global
-    # for the hash block; the query block keeps its own IDs because the overlapper is given first_id per load)
-    sel = list(range(qb, qe + 1)) + list(range(hb, he + 1))
-    lens = reads.lengths[np.array(sel) - 1].astype(np.uint32)
-    offs = np.zeros(len(sel), dtype=np.uint64)
-    np.cumsum(lens[:-1], out=offs[1:])
-    total = int(lens.sum())
+    # this rank needs its query block and the hash block, gathered into one pinned host buffer in a local ID space
+    # (queries 1..n_q, hash n_q+1..n_q+n_h: query ID < hash ID, as in the sweep); canu_b200/shard.py maps records back
+    total = int(reads.lengths[rj.ids - 1].sum())
     pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
-    hostbuf = pinned.numpy()
-    w = 0
-    for (b, e) in ((qb, qe), (hb, he)):
-        o0, o1 = int(reads.offsets[b - 1]), int(reads.offsets[e])
-        hostbuf[w:w + (o1 - o0)] = reads.bases[o0:o1]
-        w += o1 - o0
-    n_q = qe - qb + 1
-    n_h = he - hb + 1
-    # local IDs: queries 1..n_q, hash n_q+1..n_q+n_h  (query ID < hash ID, as in the sweep)
-    LP = dict(P)
-    LP.update(bgn_hash_id=n_q + 1, end_hash_id=n_q + n_h, bgn_ref_id=1, end_ref_id=n_q, max_hash_strings=n_h)
+    _, offs, lens = rj.select(reads.bases, reads.offsets[:-1], reads.lengths, out=pinned.numpy())
+    LP = rj.local_params(P)
 
     ov = api.Overlapper(LP, device=local)
 
@@ -244,7 +227,9 @@ def main():
         ov.process_overlaps(1, n_q)
         n = ov.num_overlaps()
         if load:
-            ov.overlaps()   # records back in a host buffer
+            rec = ov.overlaps()   # records back in a host buffer
+            if world > 1:         # per-GPU records gathered on the host side, in store IDs
+                shard.gather_records(rj.to_global(rec), dist, device="cuda")
         return n
 
     def barrier():

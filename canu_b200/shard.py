@@ -1,0 +1,78 @@
+"""Host-side logic of the multi-GPU split: which reads a rank loads, the local ID space it runs in,
+the mapping of its overlap records back to store IDs, and the host gather of per-rank records.
+
+The split is the one the reference pipeline already makes between processes (overlapInCorePartition: independent
+(hash range, query range) jobs, OIC/overlapInCorePartition.C:388-) applied between the GPUs of one box: the hash block is the
+same on every rank, query blocks are disjoint.  No collective touches the search itself.
+"""
+import numpy as np
+
+
+def split_blocks(n_reads, n_blocks):
+    """contiguous 1-based read-ID ranges of equal read count; blocks 0..n-2 are query blocks, the last is the hash block"""
+    per = n_reads // n_blocks
+    return [(i * per + 1, (i + 1) * per if i < n_blocks - 1 else n_reads) for i in range(n_blocks)]
+
+
+class RankJob:
+    """Rank `rank` of `world`: query block `rank` against the hash block (the last block).
+
+    Local IDs: queries 1..n_q, hash reads n_q+1..n_q+n_h (every query ID below every hash ID, as in the triangular sweep,
+    so the `query < hash` rule of OIC/overlapInCore-Find_Overlaps.C:316-318 keeps every pair)."""
+
+    def __init__(self, blocks, rank):
+        self.qb, self.qe = blocks[rank]
+        self.hb, self.he = blocks[-1]
+        self.n_q = self.qe - self.qb + 1
+        self.n_h = self.he - self.hb + 1
+        self.ids = np.concatenate([np.arange(self.qb, self.qe + 1), np.arange(self.hb, self.he + 1)])
+
+    def local_params(self, P):
+        LP = dict(P)
+        LP.update(bgn_hash_id=self.n_q + 1, end_hash_id=self.n_q + self.n_h, bgn_ref_id=1, end_ref_id=self.n_q,
+                  max_hash_strings=self.n_h)
+        return LP
+
+    def select(self, bases, offsets, lengths, out=None):
+        """this rank's reads, concatenated: (bases uint8, offsets uint64[n], lengths uint32[n]); `out` may be a pinned buffer"""
+        lens = np.asarray(lengths)[self.ids - 1].astype(np.uint32)
+        offs = np.zeros(len(lens), dtype=np.uint64)
+        np.cumsum(lens[:-1], out=offs[1:])
+        total = int(lens.sum())
+        if out is None:
+            out = np.empty(total, dtype=np.uint8)
+        w = 0
+        for (b, e) in ((self.qb, self.qe), (self.hb, self.he)):
+            o0, o1 = int(offsets[b - 1]), int(offsets[e - 1]) + int(lengths[e - 1])
+            out[w:w + (o1 - o0)] = bases[o0:o1]
+            w += o1 - o0
+        assert w == total
+        return out[:total], offs, lens
+
+    def to_global(self, rec):
+        """(n, 6) uint32 .ovb words with local IDs -> store IDs (words 0 and 1 are a_iid, b_iid: ST/ovStoreFile.C:196-221)"""
+        rec = np.array(rec, dtype=np.uint32).reshape(-1, 6)
+        for col in (0, 1):
+            v = rec[:, col].astype(np.int64)
+            rec[:, col] = np.where(v <= self.n_q, v + self.qb - 1, v - self.n_q - 1 + self.hb).astype(np.uint32)
+        return rec
+
+
+def gather_records(rec, dist, device="cpu"):
+    """All ranks call; every rank gets the concatenation (rank order) of the (n, 6) uint32 record arrays.  Works on gloo
+    (CPU tensors) and NCCL (device='cuda'): two all_gathers, sizes then padded payloads."""
+    import torch
+    world = dist.get_world_size()
+    rec = np.ascontiguousarray(rec, dtype=np.uint32).reshape(-1, 6)
+    n = torch.tensor([rec.shape[0]], dtype=torch.int64, device=device)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n)
+    sizes = [int(s.item()) for s in sizes]
+    cap = max(max(sizes), 1)
+    pad = np.zeros((cap, 6), dtype=np.int32)
+    pad[:rec.shape[0]] = rec.view(np.int32)
+    mine = torch.from_numpy(pad).to(device)
+    parts = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    out = [p.cpu().numpy().view(np.uint32)[:sizes[r]] for r, p in enumerate(parts)]
+    return np.concatenate(out, axis=0)
