@@ -131,7 +131,7 @@ struct oic_ctx {
 
   // search buffers
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
-      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2;
+      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool;
   DevBuf d_ctr, d_flag;
   uint64_t rec_cap = 0;       // run records per batch
   uint64_t batch_bases = 0;
@@ -324,7 +324,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_str_flags, &c->d_str_use, &c->d_win_slot, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
-                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2,
+                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool,
                     &c->d_ctr, &c->d_flag};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -685,13 +685,28 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
-      ea.dbg_pair = nullptr;
-      DevBuf d_dbg;
-      if (getenv("OIC_PHASE_CLOCKS")) { CK(d_dbg.ensure((size_t)n_pairs * 12)); CK(cudaMemsetAsync(d_dbg.p, 0, (size_t)n_pairs * 12, c->stream)); ea.dbg_pair = d_dbg.as<uint32_t>(); }
+      // speculative second round (oic_extend.cuh): state per pair, one result slot per seed, a pool for the delta lists
+      const unsigned long long dpool_cap = std::min<unsigned long long>(1ull << 28, (unsigned long long)n_runs * 64 + (16ull << 20));
+      CK(c->d_pstate.ensure((size_t)n_pairs * sizeof(PairState)));
+      CK(c->d_pend.ensure((size_t)n_pairs * 4 + 4));
+      CK(c->d_tasks.ensure((size_t)n_runs * sizeof(uint2) + 8));
+      CK(c->d_results.ensure((size_t)n_runs * sizeof(TaskResult)));
+      CK(c->d_alive.ensure((size_t)n_runs + 4));
+      CK(c->d_dpool.ensure((size_t)dpool_cap * 4));
+      ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
+      ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
+      ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>();
+      ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       c->tm.launches += 1;
+      if (ea.handoff) {
+        k_extend_tasks<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
+        c->tm.launches += 2;
+      }
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
       CK(cudaGetLastError());
+      const DevCounters hc_first = hc;
       if (hc.n_retry) {
         // pairs whose rows did not fit the per-warp scratch: regenerate the seed lists (the pruning above edits them
         // in place; finished pairs are not read again) and rerun just those pairs with worst-case scratch
@@ -704,7 +719,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         CK(cudaMemcpyAsync(keep_retry.p, c->d_retry.p, (size_t)nr * 4, cudaMemcpyDeviceToDevice, c->stream));
         if (ensure_pair_scratch(c, grid2 * EXT_WARPS, big)) { keep_retry.release(); return OIC_ERR_CUDA; }
         ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = big; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
-          ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr;
+        ea.task_list = keep_retry.as<uint32_t>(); ea.n_tasks = nr; ea.handoff = 0;
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->pair_cursor, 0, 4, c->stream));
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));
         k_process_pairs<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
@@ -716,18 +731,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch (internal)");
       }
       if (getenv("OIC_PHASE_CLOCKS"))
-        fprintf(stderr, "[oic] pair kernel: pairs %u warps %u | Mcycles: dp %.1f traceback %.1f prune %.1f | warp busy sum %.1f max %.1f | longest pair %.1f\n",
-                n_pairs, n_warps, hc.t_dp / 1e6, hc.t_tb / 1e6, hc.t_prune / 1e6, hc.t_warp_sum / 1e6, hc.t_warp_max / 1e6, hc.t_pair_max / 1e6);
-      if (ea.dbg_pair) {
-        std::vector<uint32_t> dp(3ull * n_pairs); std::vector<Pair> hp(n_pairs);
-        cudaMemcpy(dp.data(), d_dbg.p, (size_t)n_pairs * 12, cudaMemcpyDeviceToHost);
-        cudaMemcpy(hp.data(), c->d_pairs.p, (size_t)n_pairs * sizeof(Pair), cudaMemcpyDeviceToHost);
-        std::vector<uint32_t> idx(n_pairs); for (uint32_t i = 0; i < n_pairs; i++) idx[i] = i;
-        std::sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return dp[3ull * x] > dp[3ull * y]; });
-        for (uint32_t k = 0; k < 8 && k < n_pairs; k++) { uint32_t i = idx[k]; uint32_t ri = qs_read[hp[i].qs >> 1];
-          fprintf(stderr, "[oic]   heavy pair %u: %.1f Mcycles, seeds %u, ext calls %u, lane0 cells %u, qlen %u hlen %u\n", i, dp[3ull * i] * 1024 / 1e6, hp[i].n, dp[3ull * i + 1], dp[3ull * i + 2], c->h_len[ri], c->h_len[c->hb.bgn_id - c->first_id + hp[i].str]); }
-        d_dbg.release();
-      }
+        fprintf(stderr, "[oic] pair stage: pairs %u | handed over %u | speculative tasks %u used %u | delta pool %llu of %llu | retried %u\n",
+                n_pairs, hc_first.n_pend, hc_first.n_spec_tasks, hc_first.n_spec_used, (unsigned long long)hc_first.dpool_used, dpool_cap, hc_first.n_retry);
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         size_t old = c->overlaps.size();

@@ -121,6 +121,12 @@ struct DevCounters {
   unsigned int n_out;          // overlap records written
   unsigned int bad_base;       // a non-ACGT base was seen while packing
   unsigned int out_overflow;
+  // speculative second round of the pair stage (oic_extend.cuh)
+  unsigned int n_pend, pend_cursor;        // pairs handed over after their first extension
+  unsigned int n_spec_tasks, task_cursor;  // (pair, seed) extension tasks of those pairs
+  unsigned int n_spec_used;                // tasks whose result the commit pass consumed
+  unsigned int pad0;
+  unsigned long long dpool_used;           // ints of the delta pool handed out
   // phase clocks of the pair kernel (SM cycles summed over warps; t_warp_max = busiest warp)
   unsigned long long t_dp, t_tb, t_prune, t_warp_sum, t_warp_max, t_pair_max;
 };

@@ -51,8 +51,28 @@ struct ExtArgs {
   // output
   uint32_t *out; uint32_t out_cap;            // 6 words per record
   uint32_t *retry_list;
-  uint32_t *dbg_pair;   // optional: per pair {kcycles, extension calls, lane-0 cells}
+  // speculative round: pairs that still have seeds after their first extension (see k_extend_tasks / k_commit_pairs)
+  int handoff;                                // k_process_pairs: 1 = stop after the first extension and hand the pair over
+  struct PairState *pstate;                   // per pair
+  uint32_t *pend_list;                        // pairs handed over
+  uint2 *tasks;                               // {pair, seed index}
+  struct TaskResult *results;                 // per seed (index = pairs[pi].first + j)
+  uint8_t *alive;                             // per seed, scratch of the commit pass
+  int32_t *dpool; unsigned long long dpool_cap;   // delta lists of the speculative results
   DevCounters *ctr;
+};
+
+struct PairState {        // what k_process_pairs knows about a pair after its first extension
+  OlapInfo distinct[MAX_DISTINCT_OLAPS];
+  int32_t distinct_ct;
+  uint32_t n_rem;         // seeds left, compacted in place at pairs[pi].first
+  unsigned long long cells, words;   // work of the first extension (counted when the pair is finalised)
+};
+struct TaskResult {       // one speculative Extend_Alignment
+  int32_t s_lo, s_hi, t_lo, t_hi, errors, kind, dlen;   // kind < 0: the extension could not be run (scratch / pool overflow)
+  uint32_t pad;
+  unsigned long long delta_off;      // first int of the delta list in dpool (only stored when kind allows pruning)
+  unsigned long long cells, words;
 };
 
 struct WarpScratch {
@@ -134,9 +154,29 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
 
 constexpr int EXT_WARPS = 4;
 
-__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) {
-  const int l = lane_id();
-  const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+struct PairCtx {   // the strings and IDs of one pair
+  const uint64_t *S, *T;
+  int64_t sp, tp;
+  int s_len, t_len, dir;
+  uint32_t s_id, t_id;
+};
+__device__ __forceinline__ PairCtx pair_ctx(const ExtArgs &a, const Pair &pr) {
+  PairCtx x;
+  const uint32_t ri = a.qs_read[pr.qs >> 1];
+  x.dir = pr.qs & 1;
+  x.S = x.dir ? a.rc : a.fwd;
+  x.sp = a.rd_pos[ri];
+  x.s_len = (int)a.rd_len[ri];
+  x.s_id = a.first_id + ri;
+  const uint32_t hri = a.hash_ri_bgn + pr.str;
+  x.T = a.fwd;
+  x.tp = a.rd_pos[hri];
+  x.t_len = (int)a.rd_len[hri];
+  x.t_id = a.hash_bgn_id + pr.str;
+  return x;
+}
+
+__device__ __forceinline__ WarpScratch warp_scratch(const ExtArgs &a, uint32_t gw) {
   WarpScratch ws;
   ws.vals = a.vals + (unsigned long long)gw * a.rowcap;
   ws.meta = a.rowmeta + (unsigned long long)gw * a.max_rows;
@@ -149,8 +189,84 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
   ws.match_limit = a.match_limit;
   ws.cells = ws.words = 0;
   ws.t_tb = 0;
-  long long t_ext = 0, t_prune = 0, t_pair_max = 0;
-  const long long t_begin = OIC_CLOCK();
+  return ws;
+}
+
+/* first of the longest seeds, in list order (Process_String_Overlaps.C:473-480); alive == nullptr: all of them */
+__device__ __forceinline__ int longest_seed(const Seed *seeds, const uint8_t *alive, int n) {
+  const int l = lane_id();
+  long long bk = -1;
+  for (int i = l; i < n; i += 32) {
+    if (alive && !alive[i]) continue;
+    const long long k = (long long)seeds[i].len * 4294967296LL + (long long)(0x7fffffff - i);
+    if (k > bk) bk = k;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const long long ok = __shfl_xor_sync(FULL, bk, o);
+    if (ok > bk) bk = ok;
+  }
+  return bk < 0 ? -1 : 0x7fffffff - (int)(bk & 0xffffffffLL);
+}
+
+/* the accept test of Process_Matches (Process_String_Overlaps.C:488-512) */
+__device__ __forceinline__ void accept_overlap(const ExtArgs &a, int kind, int s_lo, int s_hi, int t_lo, int t_hi, int errors, int dlen,
+                                               OlapInfo *distinct, int &distinct_ct) {
+  if (kind == 3 || a.partial) {
+    if (1 + s_hi - s_lo >= a.min_olap_len && 1 + t_hi - t_lo >= a.min_olap_len) {
+      const int olap_len = 1 + imin(s_hi - s_lo, t_hi - t_lo);
+      const double quality = OIC_DDIV((double)errors, (double)olap_len);
+      if (errors <= (int)ceil(OIC_DMUL((double)olap_len, a.erate)))
+        add_overlap(a.partial, s_lo, s_hi, t_lo, t_hi, quality, dlen, distinct, distinct_ct);
+    }
+  }
+}
+
+/* end of Process_Matches for one pair: merge / choose the distinct overlaps, write the records, bump the -s counters
+ * (Process_String_Overlaps.C:540-600, Output.C).  Lane 0 only. */
+__device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct) {
+  int overlaps_output = 0;
+  if (distinct_ct > 0) {
+    int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
+    if (a.partial) { if (a.unique_olap) choose_best_partial(distinct, distinct_ct, deleted); }
+    else { if (a.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
+    int nout = 0;
+    for (int i = 0; i < distinct_ct; i++) nout += !deleted[i];
+    uint32_t ob = atomicAdd(&a.ctr->n_out, (unsigned)nout);
+    for (int i = 0; i < distinct_ct; i++) {
+      if (deleted[i]) continue;
+      if (ob >= a.out_cap) { atomicOr(&a.ctr->out_overflow, 1u); break; }
+      uint32_t *w = a.out + 6ull * ob;
+      if (a.partial) output_partial(w, x.s_id, x.t_id, x.dir, distinct[i], x.s_len, x.t_len);
+      else {
+        const int contained = output_overlap(w, x.s_id, x.s_len, x.dir, x.t_id, x.t_len, distinct[i]);
+        if (contained) atomicAdd(&a.ctr->contained, 1ull); else atomicAdd(&a.ctr->dovetail, 1ull);
+      }
+      ob++;
+      overlaps_output++;
+    }
+    atomicAdd(&a.ctr->total_overlaps, (unsigned long long)overlaps_output);
+  }
+  if (overlaps_output == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
+  else {
+    atomicAdd(&a.ctr->kmer_hits_with_olap, 1ull);
+    if (overlaps_output > 1) atomicAdd(&a.ctr->multi_overlap, 1ull);
+  }
+}
+
+/*
+ * Pass 1 of the pair stage: one warp per pair (atomic work queue, heavy pairs first).
+ * a.handoff == 0: the whole Process_Matches loop (used for the retry list, with worst-case scratch).
+ * a.handoff == 1: the filters and the FIRST extension only.  Extensions of one pair do not depend on each other --
+ *   only whether a seed is still in the list depends on the alignments accepted before it -- so a pair that still
+ *   has seeds after its first extension is handed over: its remaining seeds are all extended speculatively, one warp
+ *   each, by k_extend_tasks, and k_commit_pairs then replays the loop over the stored results.  This removes the serial
+ *   chain of a pair (up to ~100 extensions of the same 15 kb overlap) from the critical path of the stage.
+ */
+__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) {
+  const int l = lane_id();
+  const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  WarpScratch ws = warp_scratch(a, gw);
   unsigned long long ext_calls = 0;
   __shared__ int32_t s_rows[EXT_WARPS][2][SW + 4];
   FastScratch fs;
@@ -165,20 +281,9 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
     const uint32_t pi = a.task_list ? a.task_list[ti] : ti;
     const Pair pr = a.pairs[pi];
     const PairInfo inf = a.info[pi];
-    const uint32_t ri = a.qs_read[pr.qs >> 1];
-    const int dir = pr.qs & 1;
-    const uint64_t *S = dir ? a.rc : a.fwd;
-    const int64_t sp = a.rd_pos[ri];
-    const int s_len = (int)a.rd_len[ri];
-    const uint32_t s_id = a.first_id + ri;
-    const uint32_t hri = a.hash_ri_bgn + pr.str;
-    const uint64_t *T = a.fwd;
-    const int64_t tp = a.rd_pos[hri];
-    const int t_len = (int)a.rd_len[hri];
-    const uint32_t t_id = a.hash_bgn_id + pr.str;
+    const PairCtx x = pair_ctx(a, pr);
     Seed *seeds = a.seeds + pr.first;
     int n = (int)pr.n;
-    const long long t_pair0 = OIC_CLOCK();
 
     // --minkmers filter: computeMinimumKmers (Process_String_Overlaps.C:75-86,725)
     if (a.filter_by_kmer_count != 0) {
@@ -200,7 +305,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       const int s_head = m.start, t_head = m.offset;
       if (s_head <= t_head) { if (s_head > HOPELESS_MATCH && !(qsc & 1)) hopeless = true; }
       else { if (t_head > HOPELESS_MATCH && !(hsc & 1)) hopeless = true; }
-      const int s_tail = s_len - s_head - m.len + 1, t_tail = t_len - t_head - m.len + 1;
+      const int s_tail = x.s_len - s_head - m.len + 1, t_tail = x.t_len - t_head - m.len + 1;
       if (s_tail <= t_tail) { if (s_tail > HOPELESS_MATCH && !(qsc & 2)) hopeless = true; }
       else { if (t_tail > HOPELESS_MATCH && !(hsc & 2)) hopeless = true; }
       if (hopeless) {
@@ -211,43 +316,21 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
 
     OlapInfo distinct[MAX_DISTINCT_OLAPS];
     int distinct_ct = 0;
-    bool overflow = false;
+    bool overflow = false, handed = false;
     const unsigned long long snap_cells = ws.cells, snap_words = ws.words, snap_calls = ext_calls;
 
     while (n > 0) {
-      // first of the longest seeds, in list order (Process_String_Overlaps.C:473-480)
-      long long bk = -1;
-      for (int i = l; i < n; i += 32) {
-        long long k = (long long)seeds[i].len * 4294967296LL + (long long)(0x7fffffff - i);
-        if (k > bk) bk = k;
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        long long ok = __shfl_xor_sync(FULL, bk, o);
-        if (ok > bk) bk = ok;
-      }
-      const int li = 0x7fffffff - (int)(bk & 0xffffffffLL);
+      const int li = longest_seed(seeds, nullptr, n);
       const Seed lg = seeds[li];
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
-      const long long te0 = OIC_CLOCK();
-      const int kind = extend_alignment(a, ws, fs, S, sp, s_len, T, tp, t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const int kind = extend_alignment(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
-      t_ext += OIC_CLOCK() - te0;
       if (kind < 0) { overflow = true; break; }
-
-      if (kind == 3 || a.partial) {
-        if (1 + s_hi - s_lo >= a.min_olap_len && 1 + t_hi - t_lo >= a.min_olap_len) {
-          const int olap_len = 1 + imin(s_hi - s_lo, t_hi - t_lo);
-          const double quality = OIC_DDIV((double)errors, (double)olap_len);
-          if (errors <= (int)ceil(OIC_DMUL((double)olap_len, a.erate)))
-            add_overlap(a.partial, s_lo, s_hi, t_lo, t_hi, quality, dlen, distinct, distinct_ct);
-        }
-      }
+      accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
       if (inf.consistent) break;
 
       // drop the extended seed and every seed that lies on this alignment (Process_String_Overlaps.C:514-531)
-      const long long tp0 = OIC_CLOCK();
       int newn = 0;
       for (int i0 = 0; i0 < n; i0 += 32) {
         const int i = i0 + l;
@@ -267,60 +350,146 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
         __syncwarp();
       }
       n = newn;
-      t_prune += OIC_CLOCK() - tp0;
+      if (a.handoff && n > 0) { handed = true; break; }
     }
-    { long long tp = OIC_CLOCK() - t_pair0; if (tp > t_pair_max) t_pair_max = tp;
-      if (l == 0 && a.dbg_pair) { a.dbg_pair[3ull * pi] = (uint32_t)(tp >> 10); a.dbg_pair[3ull * pi + 1] = (uint32_t)(ext_calls - snap_calls); a.dbg_pair[3ull * pi + 2] = (uint32_t)((ws.cells - snap_cells) ); } }
 
     if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
       ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
       if (l == 0) a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
       continue;
     }
-
-    if (l == 0) {
-      int overlaps_output = 0;
-      if (distinct_ct > 0) {
-        int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
-        if (a.partial) { if (a.unique_olap) choose_best_partial(distinct, distinct_ct, deleted); }
-        else { if (a.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
-        int nout = 0;
-        for (int i = 0; i < distinct_ct; i++) nout += !deleted[i];
-        uint32_t ob = atomicAdd(&a.ctr->n_out, (unsigned)nout);
-        for (int i = 0; i < distinct_ct; i++) {
-          if (deleted[i]) continue;
-          if (ob >= a.out_cap) { atomicOr(&a.ctr->out_overflow, 1u); break; }
-          uint32_t *w = a.out + 6ull * ob;
-          if (a.partial) output_partial(w, s_id, t_id, dir, distinct[i], s_len, t_len);
-          else {
-            int contained = output_overlap(w, s_id, s_len, dir, t_id, t_len, distinct[i]);
-            if (contained) atomicAdd(&a.ctr->contained, 1ull); else atomicAdd(&a.ctr->dovetail, 1ull);
-          }
-          ob++;
-          overlaps_output++;
-        }
-        atomicAdd(&a.ctr->total_overlaps, (unsigned long long)overlaps_output);
+    if (handed) {
+      // park the pair: its first extension is counted when (and if) k_commit_pairs finalises it
+      const unsigned long long cw = warp_sum64(ws.words - snap_words);
+      PairState *ps = a.pstate + pi;
+      if (l == 0) {
+        for (int i = 0; i < distinct_ct; i++) ps->distinct[i] = distinct[i];
+        ps->distinct_ct = distinct_ct;
+        ps->n_rem = (uint32_t)n;
+        ps->cells = ws.cells - snap_cells;
+        ps->words = cw;
+        a.pend_list[atomicAdd(&a.ctr->n_pend, 1u)] = pi;
       }
-      if (overlaps_output == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
-      else {
-        atomicAdd(&a.ctr->kmer_hits_with_olap, 1ull);
-        if (overlaps_output > 1) atomicAdd(&a.ctr->multi_overlap, 1ull);
-      }
+      uint32_t tb = 0;
+      if (l == 0) tb = atomicAdd(&a.ctr->n_spec_tasks, (unsigned)n);
+      tb = __shfl_sync(FULL, tb, 0);
+      for (int i = l; i < n; i += 32) a.tasks[tb + i] = make_uint2(pi, (uint32_t)i);
+      ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
+      continue;
     }
+    if (l == 0) finalize_pair(a, x, distinct, distinct_ct);
   }
 
   unsigned long long c = warp_sum64(ws.cells), w = warp_sum64(ws.words);
   if (l == 0) {
-    const long long tw = OIC_CLOCK() - t_begin;
-    atomicAdd(&a.ctr->t_dp, (unsigned long long)(t_ext - ws.t_tb));
-    atomicAdd(&a.ctr->t_tb, (unsigned long long)ws.t_tb);
-    atomicAdd(&a.ctr->t_prune, (unsigned long long)t_prune);
-    atomicAdd(&a.ctr->t_warp_sum, (unsigned long long)tw);
-    atomicMax(&a.ctr->t_warp_max, (unsigned long long)tw);
-    atomicMax(&a.ctr->t_pair_max, (unsigned long long)t_pair_max);
     if (c) atomicAdd(&a.ctr->ext_cells, c);
     if (w) atomicAdd(&a.ctr->ext_words, w);
     if (ext_calls) atomicAdd(&a.ctr->ext_calls, ext_calls);
+  }
+}
+
+/*
+ * Pass 2: one warp per (pair, remaining seed): a single Extend_Alignment, result + delta list stored for the commit pass.
+ * Tasks are taken from the END of the list: heavy pairs start first in pass 1 but finish (and emit their tasks) last.
+ */
+__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_extend_tasks(ExtArgs a) {
+  const int l = lane_id();
+  const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  WarpScratch ws = warp_scratch(a, gw);
+  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 4];
+  FastScratch fs;
+  fs.row0 = s_rows[threadIdx.x >> 5][0];
+  fs.row1 = s_rows[threadIdx.x >> 5][1];
+  const uint32_t n_tasks = a.ctr->n_spec_tasks;
+
+  while (true) {
+    uint32_t ti = 0;
+    if (l == 0) ti = atomicAdd(&a.ctr->task_cursor, 1u);
+    ti = __shfl_sync(FULL, ti, 0);
+    if (ti >= n_tasks) break;
+    const uint2 tk = a.tasks[n_tasks - 1 - ti];
+    const Pair pr = a.pairs[tk.x];
+    const PairCtx x = pair_ctx(a, pr);
+    const Seed sd = a.seeds[pr.first + tk.y];
+    ws.cells = ws.words = 0;
+    TaskResult r;
+    r.pad = 0; r.delta_off = 0;
+    r.kind = extend_alignment(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, r.s_lo, r.s_hi, r.t_lo, r.t_hi,
+                              r.errors, r.dlen);
+    if (r.kind == 3 || (a.partial && r.kind >= 0)) {   // the delta list is only read to prune seeds on an accepted-kind alignment
+      unsigned long long off = 0;
+      if (l == 0) off = atomicAdd(&a.ctr->dpool_used, (unsigned long long)r.dlen);
+      off = __shfl_sync(FULL, off, 0);
+      if (off + (unsigned long long)r.dlen > a.dpool_cap) r.kind = -1;
+      else {
+        r.delta_off = off;
+        for (int i = l; i < r.dlen; i += 32) a.dpool[off + i] = ws.ldelta[i];
+      }
+    }
+    r.words = warp_sum64(ws.words);
+    r.cells = ws.cells;   // lane 0 holds the count
+    if (l == 0) a.results[pr.first + tk.y] = r;
+  }
+}
+
+/*
+ * Pass 3: one warp per handed-over pair: the rest of the Process_Matches loop over the stored results.  A result is
+ * consumed only if its seed is still in the list when its turn comes, exactly as the serial loop would have extended it;
+ * results of seeds pruned before their turn are discarded (speculation waste).  Any unusable result sends the pair to
+ * the retry list (full serial loop with worst-case scratch); nothing of the pair has been output or counted until here.
+ */
+__global__ void __launch_bounds__(128) k_commit_pairs(ExtArgs a) {
+  const int l = lane_id();
+  const uint32_t n_pend = a.ctr->n_pend;
+  while (true) {
+    uint32_t ti = 0;
+    if (l == 0) ti = atomicAdd(&a.ctr->pend_cursor, 1u);
+    ti = __shfl_sync(FULL, ti, 0);
+    if (ti >= n_pend) break;
+    const uint32_t pi = a.pend_list[ti];
+    const Pair pr = a.pairs[pi];
+    const PairCtx x = pair_ctx(a, pr);
+    const PairState *ps = a.pstate + pi;
+    const Seed *seeds = a.seeds + pr.first;
+    const TaskResult *res = a.results + pr.first;
+    uint8_t *alive = a.alive + pr.first;
+    const int n = (int)ps->n_rem;
+    OlapInfo distinct[MAX_DISTINCT_OLAPS];
+    int distinct_ct = ps->distinct_ct;
+    for (int i = 0; i < distinct_ct; i++) distinct[i] = ps->distinct[i];
+    for (int i = l; i < n; i += 32) alive[i] = 1;
+    __syncwarp();
+    unsigned long long calls = 1, cells = ps->cells, words = ps->words;
+    unsigned used = 0;
+    bool failed = false;
+    while (true) {
+      const int li = longest_seed(seeds, alive, n);
+      if (li < 0) break;
+      const TaskResult r = res[li];
+      if (r.kind < 0) { failed = true; break; }
+      calls++; cells += r.cells; words += r.words; used++;
+      accept_overlap(a, r.kind, r.s_lo, r.s_hi, r.t_lo, r.t_hi, r.errors, r.dlen, distinct, distinct_ct);
+      const bool prune = (r.kind == 3 || a.partial);
+      const int32_t *delta = a.dpool + r.delta_off;
+      for (int i = l; i < n; i += 32) {
+        if (!alive[i]) continue;
+        const Seed nd = seeds[i];
+        if (i == li || (prune && r.s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= r.s_hi + SHIFT_SLACK &&
+                        lies_on_alignment(nd.start, nd.offset, r.s_lo, r.t_lo, delta, r.dlen)))
+          alive[i] = 0;
+      }
+      __syncwarp();
+    }
+    if (l == 0) {
+      if (failed) a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
+      else {
+        finalize_pair(a, x, distinct, distinct_ct);
+        atomicAdd(&a.ctr->ext_calls, calls);
+        atomicAdd(&a.ctr->ext_cells, cells);
+        atomicAdd(&a.ctr->ext_words, words);
+        atomicAdd(&a.ctr->n_spec_used, used);
+      }
+    }
   }
 }
 
