@@ -131,7 +131,7 @@ struct oic_ctx {
 
   // search buffers
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
-      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool;
+      d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool, d_wide;
   DevBuf d_ctr, d_flag;
   uint64_t rec_cap = 0;       // run records per batch
   uint64_t batch_bases = 0;
@@ -324,7 +324,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_str_flags, &c->d_str_use, &c->d_win_slot, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
-                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool,
+                    &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
                     &c->d_ctr, &c->d_flag};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -692,17 +692,19 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       CK(c->d_tasks.ensure((size_t)n_runs * sizeof(uint2) + 8));
       CK(c->d_results.ensure((size_t)n_runs * sizeof(TaskResult)));
       CK(c->d_alive.ensure((size_t)n_runs + 4));
+      CK(c->d_wide.ensure((size_t)n_runs * 4 + 4));
       CK(c->d_dpool.ensure((size_t)dpool_cap * 4));
       ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
-      ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>();
+      ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       c->tm.launches += 1;
       if (ea.handoff) {
-        k_extend_tasks<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_extend_tasks<true><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_extend_tasks<false><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
         k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
-        c->tm.launches += 2;
+        c->tm.launches += 3;
       }
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
       CK(cudaGetLastError());
@@ -731,8 +733,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch (internal)");
       }
       if (getenv("OIC_PHASE_CLOCKS"))
-        fprintf(stderr, "[oic] pair stage: pairs %u | handed over %u | speculative tasks %u used %u | delta pool %llu of %llu | retried %u\n",
-                n_pairs, hc_first.n_pend, hc_first.n_spec_tasks, hc_first.n_spec_used, (unsigned long long)hc_first.dpool_used, dpool_cap, hc_first.n_retry);
+        fprintf(stderr, "[oic] pair stage: pairs %u | handed over %u | speculative tasks %u used %u | delta pool %llu of %llu | retried %u | wide tasks %u\n",
+                n_pairs, hc_first.n_pend, hc_first.n_spec_tasks, hc_first.n_spec_used, (unsigned long long)hc_first.dpool_used, dpool_cap, hc_first.n_retry, hc_first.n_wide_tasks);
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         size_t old = c->overlaps.size();

@@ -125,6 +125,8 @@ struct DevCounters {
   unsigned int n_pend, pend_cursor;        // pairs handed over after their first extension
   unsigned int n_spec_tasks, task_cursor;  // (pair, seed) extension tasks of those pairs
   unsigned int n_spec_used;                // tasks whose result the commit pass consumed
+  unsigned int n_wide_tasks, wide_cursor;  // tasks rerun with the generic row loop
+  unsigned int pad1;
   unsigned int pad0;
   unsigned long long dpool_used;           // ints of the delta pool handed out
   // phase clocks of the pair kernel (SM cycles summed over warps; t_warp_max = busiest warp)

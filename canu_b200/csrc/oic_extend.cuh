@@ -58,6 +58,7 @@ struct ExtArgs {
   uint2 *tasks;                               // {pair, seed index}
   struct TaskResult *results;                 // per seed (index = pairs[pi].first + j)
   uint8_t *alive;                             // per seed, scratch of the commit pass
+  uint32_t *wide_list;                        // tasks the lean kernel could not run (a row wider than SW)
   int32_t *dpool; unsigned long long dpool_cap;   // delta lists of the speculative results
   DevCounters *ctr;
 };
@@ -88,12 +89,14 @@ struct WarpScratch {
 
 }  // namespace oic
 #include "oic_extend_fast.cuh"
+#include "oic_extend_lean.cuh"
 namespace oic {
 
 // shared-memory path first; the generic global-memory path only for runs with a row wider than SW
 /* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
  * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
-__device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
+template <bool LEAN>
+__device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
                                 const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
                                 int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
   const int l = lane_id();
@@ -122,8 +125,9 @@ __device__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScr
     const int m = s_is_a ? s_n : t_n, n = s_is_a ? t_n : s_n;
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
-    errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
-    if (errs < 0) return -1;
+    if (LEAN) errs = dp_run_lean(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
+    else errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
+    if (errs < 0) return errs;   // -1 history overflow, -2 (lean only) row wider than the shared-memory staging
     if (side == 0) {
       right_errors = errs; r_to_end = to_end; rlen = dl; neg_right = s_is_a;
       s_hi = s_is_a ? a_end : b_end; t_hi = s_is_a ? b_end : a_end;
@@ -324,7 +328,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       const Seed lg = seeds[li];
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
-      const int kind = extend_alignment(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const int kind = extend_alignment<false>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
       if (kind < 0) { overflow = true; break; }
       accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
@@ -391,31 +395,40 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
 /*
  * Pass 2: one warp per (pair, remaining seed): a single Extend_Alignment, result + delta list stored for the commit pass.
  * Tasks are taken from the END of the list: heavy pairs start first in pass 1 but finish (and emit their tasks) last.
+ * LEAN = true: the shared-memory-only row loop; a task that meets a row wider than SW is queued for the LEAN = false
+ * instance of the kernel (generic row loop), which runs right after on just those tasks.
  */
+template <bool LEAN>
 __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_extend_tasks(ExtArgs a) {
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   WarpScratch ws = warp_scratch(a, gw);
-  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 4];
+  __shared__ int32_t s_rows[EXT_WARPS][2][LEAN ? LSTRIDE : SW + 4];
   FastScratch fs;
   fs.row0 = s_rows[threadIdx.x >> 5][0];
   fs.row1 = s_rows[threadIdx.x >> 5][1];
-  const uint32_t n_tasks = a.ctr->n_spec_tasks;
+  const uint32_t n_all = a.ctr->n_spec_tasks;
+  const uint32_t n_tasks = LEAN ? n_all : a.ctr->n_wide_tasks;
 
   while (true) {
     uint32_t ti = 0;
-    if (l == 0) ti = atomicAdd(&a.ctr->task_cursor, 1u);
+    if (l == 0) ti = atomicAdd(LEAN ? &a.ctr->task_cursor : &a.ctr->wide_cursor, 1u);
     ti = __shfl_sync(FULL, ti, 0);
     if (ti >= n_tasks) break;
-    const uint2 tk = a.tasks[n_tasks - 1 - ti];
+    const uint32_t tidx = LEAN ? n_all - 1 - ti : a.wide_list[ti];
+    const uint2 tk = a.tasks[tidx];
     const Pair pr = a.pairs[tk.x];
     const PairCtx x = pair_ctx(a, pr);
     const Seed sd = a.seeds[pr.first + tk.y];
     ws.cells = ws.words = 0;
     TaskResult r;
     r.pad = 0; r.delta_off = 0;
-    r.kind = extend_alignment(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, r.s_lo, r.s_hi, r.t_lo, r.t_hi,
-                              r.errors, r.dlen);
+    r.kind = extend_alignment<LEAN>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, r.s_lo, r.s_hi, r.t_lo, r.t_hi,
+                                    r.errors, r.dlen);
+    if (LEAN && r.kind == LEAN_WIDE) {
+      if (l == 0) a.wide_list[atomicAdd(&a.ctr->n_wide_tasks, 1u)] = tidx;
+      continue;
+    }
     if (r.kind == 3 || (a.partial && r.kind >= 0)) {   // the delta list is only read to prune seeds on an accepted-kind alignment
       unsigned long long off = 0;
       if (l == 0) off = atomicAdd(&a.ctr->dpool_used, (unsigned long long)r.dlen);

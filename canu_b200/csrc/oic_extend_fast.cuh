@@ -137,6 +137,55 @@ __device__ __forceinline__ int match_dir(const uint64_t *__restrict__ A, int64_t
   return r < limit ? r : limit;
 }
 
+/* After the row loop of one direction: pick the exit cell (or fall back to the best cell seen), trace back, build the
+ * delta list (Set_Right_Delta / Set_Left_Delta).  Shared by the generic and the lean row loops. */
+__device__ __forceinline__ int dp_finish(const int DIR, WarpScratch &ws, int n, int row0, int fin_e, int fin_d, int fin_val, int from0, int errors,
+                                         int max_score_len, int max_score_best_d, int max_score_best_e, int &a_end, int &t_end,
+                                         int &leftover, int &to_end, int &delta_len) {
+  const int l = lane_id();
+
+  if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
+    a_end = DIR * max_score_len;
+    t_end = DIR * (max_score_len + max_score_best_d);
+    fin_e = max_score_best_e; fin_d = max_score_best_d;
+    fin_val = fin_e ? max_score_len : row0;
+    from0 = FROM_NONE;
+    errors = max_score_best_e;
+    to_end = 0;
+  }
+  __syncwarp();
+  const long long tb0 = OIC_CLOCK();
+  const int ns = traceback_fast(ws, fin_e, fin_d, from0);
+  const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
+  if (DIR > 0) {
+    // Set_Right_Delta: st = entries, then last + 1; delta[x] = |st[ns - x]| * sign(st[ns - x - 1])
+    for (int x = l; x < ns; x += 32) {
+      const int i = ns - x;
+      const int sti = (i == ns) ? last + 1 : tb_entry(ws.stack, i, fin_val);
+      const int stm = tb_entry(ws.stack, i - 1, fin_val);
+      ws.rdelta[x] = iabs(sti) * ((stm > 0) - (stm < 0));
+    }
+    delta_len = ns;
+  } else {
+    // Set_Left_Delta; a leading +1 indel becomes a substitution by pulling t_end in by one (reverse.C:92-108)
+    leftover = last;
+    bool fix = false;
+    int e1 = 0;
+    if (ns > 1 && tb_entry(ws.stack, 0, fin_val) == 1 && t_end + n > 0) { fix = true; e1 = tb_entry(ws.stack, 1, fin_val); }
+    if (!fix) {
+      for (int x = l; x < ns; x += 32) ws.ldelta[x] = tb_entry(ws.stack, x, fin_val);
+      delta_len = ns;
+    } else {
+      for (int x = l; x < ns - 1; x += 32) ws.ldelta[x] = (x == 0) ? ((e1 > 0) ? e1 + 1 : e1 - 1) : tb_entry(ws.stack, x + 1, fin_val);
+      delta_len = ns - 1;
+      t_end--;
+    }
+  }
+  __syncwarp();
+  ws.t_tb += OIC_CLOCK() - tb0;
+  return errors;
+}
+
 /* History layout of row e (ints, in the warp's slice `vals`): [2 margin][width values][2 margin][2 * nch direction words];
  * meta[e] = {lo, trimmed lo, trimmed hi, offset of the first value}.  The live rows have the same 2-int margins: after
  * trimming, the four cells just outside the band are overwritten with the reference's -2 sentinel (forward.C:155-161),
@@ -340,47 +389,8 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
   ws.cells += (l == 0) ? ncell : 0;
   ws.words += wsum;
   if (errors < 0) return -1;
-
-  if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
-    a_end = DIR * max_score_len;
-    t_end = DIR * (max_score_len + max_score_best_d);
-    fin_e = max_score_best_e; fin_d = max_score_best_d;
-    fin_val = fin_e ? max_score_len : row0;
-    from0 = FROM_NONE;
-    errors = max_score_best_e;
-    to_end = 0;
-  }
-  __syncwarp();
-  const long long tb0 = OIC_CLOCK();
-  const int ns = traceback_fast(ws, fin_e, fin_d, from0);
-  const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
-  if (DIR > 0) {
-    // Set_Right_Delta: st = entries, then last + 1; delta[x] = |st[ns - x]| * sign(st[ns - x - 1])
-    for (int x = l; x < ns; x += 32) {
-      const int i = ns - x;
-      const int sti = (i == ns) ? last + 1 : tb_entry(ws.stack, i, fin_val);
-      const int stm = tb_entry(ws.stack, i - 1, fin_val);
-      ws.rdelta[x] = iabs(sti) * ((stm > 0) - (stm < 0));
-    }
-    delta_len = ns;
-  } else {
-    // Set_Left_Delta; a leading +1 indel becomes a substitution by pulling t_end in by one (reverse.C:92-108)
-    leftover = last;
-    bool fix = false;
-    int e1 = 0;
-    if (ns > 1 && tb_entry(ws.stack, 0, fin_val) == 1 && t_end + n > 0) { fix = true; e1 = tb_entry(ws.stack, 1, fin_val); }
-    if (!fix) {
-      for (int x = l; x < ns; x += 32) ws.ldelta[x] = tb_entry(ws.stack, x, fin_val);
-      delta_len = ns;
-    } else {
-      for (int x = l; x < ns - 1; x += 32) ws.ldelta[x] = (x == 0) ? ((e1 > 0) ? e1 + 1 : e1 - 1) : tb_entry(ws.stack, x + 1, fin_val);
-      delta_len = ns - 1;
-      t_end--;
-    }
-  }
-  __syncwarp();
-  ws.t_tb += OIC_CLOCK() - tb0;
-  return errors;
+  return dp_finish(DIR, ws, n, row0, fin_e, fin_d, fin_val, from0, errors, max_score_len, max_score_best_d, max_score_best_e, a_end, t_end,
+                   leftover, to_end, delta_len);
 }
 
 }  // namespace oic
