@@ -125,8 +125,19 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
     const int m = s_is_a ? s_n : t_n, n = s_is_a ? t_n : s_n;
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
-    if (LEAN) errs = dp_run_lean(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
-    else errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
+    if (LEAN) {
+      // the lean loop only walks forward: the leftward run compares the same bases on the reverse-complement streams
+      // (base i of a read is base len-1-i of its reverse complement, stored at the same stream offset)
+      const uint64_t *Ax = A, *Bx = B;
+      int64_t ax = a0, bx = b0;
+      if (side == 1) {
+        const uint64_t *So = (S == a.fwd) ? a.rc : a.fwd, *To = (T == a.fwd) ? a.rc : a.fwd;
+        const int64_t s0 = sp + (s_len - 1 - s_from), t0 = tp + (t_len - 1 - t_from);
+        Ax = s_is_a ? So : To; Bx = s_is_a ? To : So;
+        ax = s_is_a ? s0 : t0; bx = s_is_a ? t0 : s0;
+      }
+      errs = dp_run_lean(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, Ax, ax, m, Bx, bx, n, limit, a_end, b_end, lo, to_end, dl);
+    } else errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
     if (errs < 0) return errs;   // -1 history overflow, -2 (lean only) row wider than the shared-memory staging
     if (side == 0) {
       right_errors = errs; r_to_end = to_end; rlen = dl; neg_right = s_is_a;

@@ -15,6 +15,24 @@ namespace oic {
 
 constexpr int LSTRIDE = SW + 72;   // ints per live row: 2 margin + SW + idle-lane slack of the last chunk pair
 constexpr int LEAN_WIDE = -2;
+constexpr int LEAN_IDLE = (int)0x80000000;
+
+/* Equal leading bases of the 16-base windows at A[pa ..] and T[pt ..], walking FORWARD (16 if all equal).  The lean loop
+ * only walks forward: the reverse direction is run on the reverse-complement streams (same comparisons, mirrored). */
+__device__ __forceinline__ uint32_t ldg_nc(const uint32_t *p) {   // the bases are "laundered" 64-bit registers: say they are global
+  uint32_t v;
+  asm("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void stg_s32(int32_t *p, int32_t v) { asm volatile("st.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t lean_ext16(const uint32_t *Wp, int p) {
+  const uint32_t *q = Wp + (p >> 4);
+  return __funnelshift_r(ldg_nc(q), ldg_nc(q + 1), (p & 15) * 2);
+}
+__device__ __forceinline__ int lean_step(const uint32_t *Ap, int pa, const uint32_t *Tp, int pt) {
+  const uint32_t x = lean_ext16(Ap, pa) ^ lean_ext16(Tp, pt);
+  return __clz((int)__brev(x)) >> 1;   // clz(0) = 32 -> 16
+}
 
 __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, WarpScratch &ws, int32_t *srow0, int32_t *srow1,
                                            const uint64_t *__restrict__ A, int64_t a0, int m, const uint64_t *__restrict__ T, int64_t t0,
@@ -22,8 +40,10 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   const int l = lane_id();
   const uint32_t *Ap = reinterpret_cast<const uint32_t *>(A) + (a0 >> 4);
   const uint32_t *Tp = reinterpret_cast<const uint32_t *>(T) + (t0 >> 4);
+  asm volatile("" : "+l"(Ap));   // keep the two string bases as plain 64-bit registers: one IMAD.WIDE per window address
+  asm volatile("" : "+l"(Tp));
   const int aph = (int)(a0 & 15), tph = (int)(t0 & 15);
-  const int row0 = match_dir(Ap, aph, Tp, tph, m, DIR);
+  const int row0 = match_dir(Ap, aph, Tp, tph, m, 1);
   int32_t *prev = srow0 + 2, *cur = srow1 + 2;
   if (l < 5) prev[l - 2] = (l == 2) ? row0 : -2;
   if (l == 0) {
@@ -52,6 +72,8 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   unsigned ncell = 0;   // warp-uniform count of cells (C)
   to_end = 0;
   int lim_next = ws.match_limit[1];
+  const int rowcap = (int)(ws.rowcap > 0x7fffffffull ? 0x7fffffffull : ws.rowcap);
+  const int max_e = imin(error_limit, ws.max_rows - 1);
   __syncwarp();
 
   for (int e = 1; e <= error_limit; e++) {
@@ -60,72 +82,70 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     const int width = right - left + 1;
     const int nch = (width + 31) >> 5;
     if (width > SW) { errors = LEAN_WIDE; break; }
-    if (e >= ws.max_rows || (unsigned long long)next_off + width + 4 + 2 * nch > ws.rowcap) { errors = -1; break; }
+    if (e > max_e || next_off + width + 4 + 2 * nch > rowcap) { errors = -1; break; }
     const int off = next_off + 2;
     next_off += width + 4 + 2 * nch;
-    int32_t *hist = ws.vals + off;
+    int32_t *hp = ws.vals + off + l;                     // this lane's cells of the row in the history
+    asm volatile("" : "+l"(hp));
     const int lim = lim_next;
-    if (e + 1 < ws.max_rows) lim_next = ws.match_limit[e + 1];
-    const int pshift = left - plo;                       // index of diagonal `left` in the previous row
+    lim_next = ws.match_limit[imin(e + 1, max_e)];
+    const int32_t *pp = prev + (left - plo) + l;         // this lane's cell of chunk 0 in the previous row
+    int32_t *cp = cur + l;
 
     bool ended = false;
     int d_end = 0, r_end = 0;
-    int nl = 0x7fffffff, nr = (int)0x80000000;
-    int gmax = -1, gpos = 0;                             // highest cell of the row, lowest diagonal on ties
-    unsigned my_bm = 0, my_bp = 0;                       // lane c keeps the direction words of chunk c
+    // lane c keeps the ballot words of chunk c; they are folded into band / best cell once per row
+    unsigned my_bm = 0, my_bp = 0, my_ok = 0, my_pm = 0;
+    int my_mx = -1;
 
 #pragma unroll 1
     for (int c0 = 0; c0 < nch; c0 += 2) {
       int r[2], r0[2], cap[2], dd[2];
-      bool fm[2], fp[2], cont[2];
 #pragma unroll
       for (int u = 0; u < 2; u++) {                      // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
-        const int i = 32 * (c0 + u) + l, d = left + i;
-        const int ip = i + pshift;
-        const int g0 = prev[ip] + 1, gm = prev[ip - 1], gp = prev[ip + 1] + 1;
+        const int c = c0 + u, i = 32 * c + l, d = left + i;
+        const int g0 = pp[32 * c] + 1, gm = pp[32 * c - 1], gp = pp[32 * c + 1] + 1;
         const int x = imax(g0, gm);
-        fp[u] = gp > x;
-        fm[u] = gm > g0;
+        const unsigned bp = __ballot_sync(FULL, gp > x);
+        const unsigned bm = __ballot_sync(FULL, gm > g0) & ~bp;
+        if (l == c) { my_bm = bm; my_bp = bp; }
         r0[u] = imax(x, gp);
         dd[u] = d;
-        cap[u] = (i < width) ? imin(m, n - d) : (int)0x80000000;
+        cap[u] = (i < width) ? imin(m, n - d) : LEAN_IDLE;
       }
+      int more = 0;                                      // bit u: the slide of chunk u goes on
 #pragma unroll
       for (int u = 0; u < 2; u++) {                      // first 16 bases of every slide, loads back to back
         r[u] = r0[u];
-        cont[u] = false;
         if (r0[u] < cap[u]) {
-          const int adv = step16(Ap, aph + DIR * r0[u], Tp, tph + DIR * (r0[u] + dd[u]), DIR);
+          const int adv = lean_step(Ap, aph + r0[u], Tp, tph + r0[u] + dd[u]);
           r[u] = r0[u] + adv;
-          cont[u] = (adv == 16) && (r[u] < cap[u]);
+          more |= ((adv == 16) && (r[u] < cap[u])) ? (1 << u) : 0;
         }
       }
-      while (__any_sync(FULL, cont[0] || cont[1])) {     // slides longer than 16 bases
+      while (__any_sync(FULL, more != 0)) {              // slides longer than 16 bases (the cells on the alignment path)
 #pragma unroll
         for (int u = 0; u < 2; u++) {
-          if (cont[u]) {
-            const int adv = step16(Ap, aph + DIR * r[u], Tp, tph + DIR * (r[u] + dd[u]), DIR);
+          if (more & (1 << u)) {
+            const int adv = lean_step(Ap, aph + r[u], Tp, tph + r[u] + dd[u]);
             r[u] += adv;
-            cont[u] = (adv == 16) && (r[u] < cap[u]);
+            if (!((adv == 16) && (r[u] < cap[u]))) more &= ~(1 << u);
           }
         }
       }
-      unsigned em[2], okm[2], pm[2], wc[2];
-      int mx[2];
+      unsigned em[2], wc[2];
 #pragma unroll
       for (int u = 0; u < 2; u++) {
-        const int i = 32 * (c0 + u) + l;
+        const int c = c0 + u, i = 32 * c + l;
         const bool act = i < width;
         r[u] = imin(r[u], cap[u]);
-        if (act) { cur[i] = r[u]; hist[i] = r[u]; }
-        const unsigned bp = __ballot_sync(FULL, act && fp[u]);
-        const unsigned bm = __ballot_sync(FULL, act && fm[u]) & ~bp;
-        if (l == c0 + u) { my_bm = bm; my_bp = bp; }
-        em[u] = __ballot_sync(FULL, act && (r[u] == m || r[u] + dd[u] == n));
+        if (act) { cp[32 * c] = r[u]; stg_s32(hp + 32 * c, r[u]); }
+        em[u] = __ballot_sync(FULL, act && r[u] == cap[u]);            // reached the end of A (r == m) or of T (r + d == n)
         wc[u] = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
-        okm[u] = __ballot_sync(FULL, act && (r[u] + imax(dd[u], 0) >= lim));
-        mx[u] = __reduce_max_sync(FULL, act ? r[u] : -1);
-        pm[u] = __ballot_sync(FULL, act && r[u] == mx[u]);
+        const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
+        const int mx = __reduce_max_sync(FULL, r[u]);
+        const unsigned pm = __ballot_sync(FULL, r[u] == mx);
+        if (l == c) { my_ok = ok; my_mx = mx; my_pm = pm; }
       }
       if (em[0] | em[1]) {                               // a cell reached the end of A or T: the row stops at the first one
         const int u = em[0] ? 0 : 1;
@@ -138,17 +158,9 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         ended = true;
         break;
       }
-#pragma unroll
-      for (int u = 0; u < 2; u++) {
-        const int base = left + 32 * (c0 + u);
-        wsum += wc[u];
-        nl = imin(nl, okm[u] ? base + __ffs(okm[u]) - 1 : 0x7fffffff);
-        nr = imax(nr, okm[u] ? base + 31 - __clz(okm[u]) : (int)0x80000000);
-        const bool better = mx[u] > gmax;
-        gpos = better ? base + __ffs(pm[u]) - 1 : gpos;
-        gmax = better ? mx[u] : gmax;
-      }
+      wsum += wc[0] + wc[1];
     }
+    int32_t *hist = ws.vals + off;
     {   // direction words of the row: two per chunk, right behind the values (and their 2-int margin)
       uint32_t *dirs = reinterpret_cast<uint32_t *>(hist + width + 2);
       if (l < nch) { dirs[2 * l] = my_bm; dirs[2 * l + 1] = my_bp; }
@@ -191,11 +203,21 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     ncell += width;
 
     // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches Edit_Match_Limit[e]
-    if (nl > right) {
+    const unsigned has = __ballot_sync(FULL, my_ok != 0);
+    if (has == 0) {
       if (l == 0) ws.meta[e] = make_int4(left, right + 1, right, off);
       break;
     }
+    const int cf = __ffs(has) - 1, cl = 31 - __clz(has);
+    const int nl = left + 32 * cf + __ffs(__shfl_sync(FULL, my_ok, cf)) - 1;
+    const int nr = left + 32 * cl + 31 - __clz(__shfl_sync(FULL, my_ok, cl));
     if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
+    int gmax = __reduce_max_sync(FULL, my_mx);           // highest cell of the row, lowest diagonal on ties
+    int gpos = 0;
+    if (gmax > longest) {
+      const int cw = __ffs(__ballot_sync(FULL, my_mx == gmax)) - 1;
+      gpos = left + 32 * cw + __ffs(__shfl_sync(FULL, my_pm, cw)) - 1;
+    }
 
     // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
     if (gmax > longest) {
