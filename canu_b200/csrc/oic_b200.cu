@@ -651,8 +651,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
     // ---- K3 pairs
     if (n_pairs) {
       StageTimer t3(c, &c->tm.ms_extend);
-      const unsigned grid = 148 * 4;
-      const unsigned n_warps = grid * EXT_WARPS;
+      const unsigned grid = 148 * 4, grid_tasks = 148 * TASK_BLOCKS_PER_SM;
+      const unsigned n_warps = grid_tasks * EXT_WARPS;
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
       const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
@@ -701,7 +701,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       c->tm.launches += 1;
       if (ea.handoff) {
-        k_extend_tasks<true><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_extend_tasks<true><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
         k_extend_tasks<false><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
         k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
         c->tm.launches += 3;

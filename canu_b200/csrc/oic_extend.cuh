@@ -168,6 +168,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
 }
 
 constexpr int EXT_WARPS = 4;
+constexpr int TASK_BLOCKS_PER_SM = 4;   // resident blocks of the lean task kernel (5 -> 96 registers, small spills, measured slower)
 
 struct PairCtx {   // the strings and IDs of one pair
   const uint64_t *S, *T;
@@ -410,7 +411,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
  * instance of the kernel (generic row loop), which runs right after on just those tasks.
  */
 template <bool LEAN>
-__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_extend_tasks(ExtArgs a) {
+__global__ void __launch_bounds__(EXT_WARPS * 32, LEAN ? TASK_BLOCKS_PER_SM : 4) k_extend_tasks(ExtArgs a) {
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   WarpScratch ws = warp_scratch(a, gw);
