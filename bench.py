@@ -295,16 +295,41 @@ def main():
     scan_gbs = b_scan / (ms_scan * 1e-3) / 1e9 if ms_scan > 0 else 0.0
     build_gbs = b_build / (ms_build * 1e-3) / 1e9 if ms_build > 0 else 0.0
     ext_gops = i_ext / (ms_ext * 1e-3) / 1e9 if ms_ext > 0 else 0.0
-    roof = {"kernel": "k_seed_scan", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak, "unit": "GB/s",
-            "frac": scan_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
-            "algorithmic_bytes_per_launch": b_scan, "ms_per_launch": ms_scan,
-            "formula": "0.25*N_query_bases + 4*N_windows + 8*N_found + 8*N_refs (SURVEY.md 8(d)), rank 0's block"}
+    # the dominant kernel is the speculative extension (k_extend_tasks<true>, ~70 % of the step): INT32-issue bound.
+    # achieved = algorithmic integer ops (6 per DP cell + 4 per 16-base compare word) / its own launch time;
+    # peak = INT32 ALU rate measured on this GPU by oic_measure_int32_peak (LOP3+IADD3 chains), nominal 148*64*clock as fallback
+    try:
+        alu_peak, imad_peak = api.measure_int32_peak(local)
+        int_src = "measured (oic_measure_int32_peak: LOP3+IADD3 chains; IMAD chains %.0f Gop/s)" % imad_peak
+    except Exception:
+        alu_peak, int_src = 148 * 64 * 1.965, "nominal 148 SM x 64 lanes x 1.965 GHz"
+    ms_tasks = tm["ms_ext_tasks"] / steps
+    ms_first, ms_commit = tm["ms_ext_first"] / steps, tm["ms_ext_commit"] / steps
+    # cells / words of the first extensions run in k_process_pairs; the task kernel does the rest (ext_calls - n_pairs of ext_calls)
+    share = 1.0 - (d["n_pairs"] / max(1, d["ext_calls"]))
+    i_tasks = i_ext * share
+    tasks_gops = i_tasks / (ms_tasks * 1e-3) / 1e9 if ms_tasks > 0 else 0.0
+    traffic = None
+    try:   # dram read+write bytes of one launch from the committed `ncu --set full` capture of this kernel (profiles/)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_extend_tasks_summary.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    roof = {"kernel": "k_extend_tasks<true>", "bound": "int32", "achieved": tasks_gops, "peak": alu_peak, "unit": "Gop/s",
+            "frac": tasks_gops / alu_peak if alu_peak else None, "traffic": traffic, "peak_source": int_src,
+            "algorithmic_ops_per_launch": i_tasks, "ms_per_launch": ms_tasks,
+            "formula": "6*C + 4*W (C = DP cells, W = 16-base compare words) x share of extension calls run by this kernel; "
+                       "not an HBM- or tensor-bound kernel: rows live in shared memory, sequences in L1/L2",
+            "hbm_side": {"kernel": "k_seed_scan", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": scan_gbs / hbm_peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": b_scan,
+                         "ms_per_launch": ms_scan,
+                         "formula": "0.25*N_query_bases + 4*N_windows + 8*N_found + 8*N_refs (SURVEY.md 8(d)), rank 0's block"}}
     stages = {"build": {"ms": ms_build, "algorithmic_GBps": build_gbs, "frac_hbm": build_gbs / hbm_peak,
                         "formula": "0.25*N_hash_bases + 16*N_inserts; whole build (insert+scan+fill+sort kernels)"},
               "seed_scan": {"ms": ms_scan, "algorithmic_GBps": scan_gbs, "frac_hbm": scan_gbs / hbm_peak},
               "group_runs": {"ms": ms_group},
-              "extend": {"ms": ms_ext, "int32_Gops": ext_gops, "formula": "6*C + 4*W (cells, 16-base words)",
-                         "frac_int32_nominal": ext_gops / 18600.0}}
+              "extend": {"ms": ms_ext, "ms_first_extensions": ms_first, "ms_speculative_tasks": ms_tasks, "ms_commit": ms_commit,
+                         "int32_Gops": ext_gops, "formula": "6*C + 4*W (cells, 16-base words)",
+                         "frac_int32": ext_gops / alu_peak if alu_peak else None}}
     value = q_bases_all / 1e6 * steps / dt
     e2e_v = q_bases_all / 1e6 * steps / dt_e2e
     line = {"metric": metric, "value": value, "unit": "query Mbp/s", "n_gpus": world, "steps": steps, "warmup": a.warmup,

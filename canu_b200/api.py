@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "oic_process_overlaps", "oic_overlap_driver", "oic_last_processed_ref", "oic_num_overlaps", "oic_copy_overlaps",
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
-    "oic_dump_pairs",
+    "oic_dump_pairs", "oic_measure_int32_peak",
 ]
 
 
@@ -52,7 +52,8 @@ class Stats(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("ms_pack", C.c_float), ("ms_build", C.c_float), ("ms_scan", C.c_float), ("ms_group", C.c_float),
                 ("ms_extend", C.c_float), ("ms_total_search", C.c_float), ("launches", C.c_uint64),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("ms_ext_first", C.c_float), ("ms_ext_tasks", C.c_float), ("ms_ext_commit", C.c_float), ("pad", C.c_float)]
 
 
 class HashMeta(C.Structure):
@@ -275,3 +276,14 @@ class Overlapper:
         self._check(self.lib.oic_dump_pairs(self._h, C.byref(npair), C.byref(nm), pairs.ctypes.data, matches.ctypes.data),
                     "oic_dump_pairs")
         return pairs, matches
+
+
+def measure_int32_peak(device=0):
+    """(alu_gops, imad_gops): measured INT32 issue rates of the GPU (thread Gop/s); roofline denominator of the extension."""
+    lib = load_library()
+    a, m = C.c_double(0), C.c_double(0)
+    lib.oic_measure_int32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    rc = lib.oic_measure_int32_peak(device, C.byref(a), C.byref(m))
+    if rc != 0:
+        raise OicError("oic_measure_int32_peak failed (%d)" % rc)
+    return a.value, m.value

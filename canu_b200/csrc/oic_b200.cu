@@ -140,6 +140,7 @@ struct oic_ctx {
   oic_stats_t stats = {};
   oic_timings_t tm = {};
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  cudaEvent_t ev_k[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // inner kernel timers of the pair stage
 
   // debug dumps of the last oic_process_overlaps call
   std::vector<int64_t> dbg_pairs;
@@ -304,6 +305,8 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   c->device = device;
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev_k[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[1])) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev_k[2])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[3])) != cudaSuccess ||
       (e = c->d_ctr.ensure(sizeof(DevCounters))) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e);
     delete c;
@@ -329,6 +332,7 @@ void oic_destroy(oic_ctx_t *c) {
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  for (int i = 0; i < 6; i++) if (c->ev_k[i]) cudaEventDestroy(c->ev_k[i]);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -698,16 +702,28 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
       ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;
+      cudaEventRecord(c->ev_k[0], c->stream);
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+      cudaEventRecord(c->ev_k[1], c->stream);
       c->tm.launches += 1;
       if (ea.handoff) {
         k_extend_tasks<true><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        cudaEventRecord(c->ev_k[2], c->stream);
         k_extend_tasks<false><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
         k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
+        cudaEventRecord(c->ev_k[3], c->stream);
         c->tm.launches += 3;
       }
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
       CK(cudaGetLastError());
+      {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, c->ev_k[0], c->ev_k[1]) == cudaSuccess) c->tm.ms_ext_first += ms;
+        if (ea.handoff) {
+          if (cudaEventElapsedTime(&ms, c->ev_k[1], c->ev_k[2]) == cudaSuccess) c->tm.ms_ext_tasks += ms;
+          if (cudaEventElapsedTime(&ms, c->ev_k[2], c->ev_k[3]) == cudaSuccess) c->tm.ms_ext_commit += ms;
+        }
+      }
       const DevCounters hc_first = hc;
       if (hc.n_retry) {
         // pairs whose rows did not fit the per-warp scratch: regenerate the seed lists (the pruning above edits them
@@ -755,6 +771,28 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   s.kmer_hits_skipped += hc.kmer_hits_skipped; s.multi_overlap += hc.multi_overlap;
   s.total_overlaps += hc.total_overlaps; s.contained += hc.contained; s.dovetail += hc.dovetail;
   return 0;
+}
+
+
+// INT32 throughput probe (roofline denominator of the extension stage): every thread runs 8 independent chains of
+// LOP3 + IADD3 (the ALU pipe that the edit-distance rows live on) or of IMAD (the FMA pipe); one warp instruction = 32 ops.
+template <int MODE>
+__global__ void k_int_probe(uint32_t *out, int iters, uint32_t seed) {
+  uint32_t x[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) x[i] = seed + threadIdx.x * 8u + i;
+  const uint32_t y = seed * 2654435761u + blockIdx.x, z = seed ^ 0x9e3779b9u;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      if (MODE == 0) x[i] = (x[i] ^ y) + z;        // LOP3 + IADD3
+      else x[i] = x[i] * y + z;                    // IMAD
+    }
+  }
+  uint32_t r = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) r ^= x[i];
+  if (r == 0x12345678u) out[0] = r;                // keeps the chains alive
 }
 
 }  // namespace
@@ -931,6 +969,39 @@ int oic_dump_pairs(oic_ctx_t *c, uint64_t *n_pairs, uint64_t *n_matches, int64_t
   if (n_matches) *n_matches = c->dbg_matches.size() / 3;
   if (pairs && !c->dbg_pairs.empty()) memcpy(pairs, c->dbg_pairs.data(), c->dbg_pairs.size() * 8);
   if (matches && !c->dbg_matches.empty()) memcpy(matches, c->dbg_matches.data(), c->dbg_matches.size() * 4);
+  return OIC_OK;
+}
+
+
+/* Measured INT32 issue rates of this GPU in Gop/s (thread operations): alu = LOP3/IADD3 chains, imad = IMAD chains. */
+int oic_measure_int32_peak(int device, double *alu_gops, double *imad_gops) {
+  if (cudaSetDevice(device) != cudaSuccess) return OIC_ERR_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return OIC_ERR_CUDA;
+  uint32_t *d = nullptr;
+  if (cudaMalloc(&d, 64) != cudaSuccess) return OIC_ERR_CUDA;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+  double res[2] = {0, 0};
+  for (int mode = 0; mode < 2; mode++) {
+    for (int rep = 0; rep < 3; rep++) {
+      cudaEventRecord(e0);
+      if (mode == 0) k_int_probe<0><<<blocks, threads>>>(d, iters, 17u + rep);
+      else k_int_probe<1><<<blocks, threads>>>(d, iters, 17u + rep);
+      cudaEventRecord(e1);
+      cudaEventSynchronize(e1);
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, e1);
+      const double ops = (double)blocks * threads * iters * 8.0 * (mode == 0 ? 2.0 : 1.0);
+      if (rep && ms > 0) res[mode] = std::max(res[mode], ops / (ms * 1e-3) / 1e9);
+    }
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d);
+  if (cudaGetLastError() != cudaSuccess) return OIC_ERR_CUDA;
+  if (alu_gops) *alu_gops = res[0];
+  if (imad_gops) *imad_gops = res[1];
   return OIC_OK;
 }
 

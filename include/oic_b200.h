@@ -66,6 +66,8 @@ typedef struct {
   float    ms_pack, ms_build, ms_scan, ms_group, ms_extend, ms_total_search;
   uint64_t launches;             /* kernels launched by this context since the last reset */
   uint64_t h2d_bytes, d2h_bytes; /* bytes moved across PCIe by this context since reset   */
+  /* inside ms_extend: first extension of every pair / speculative extension tasks (the dominant kernel) / wide reruns + commit */
+  float    ms_ext_first, ms_ext_tasks, ms_ext_commit, pad;
 } oic_timings_t;
 
 /* One overlap as written to the .ovb file: 6 x uint32 = a_iid, b_iid, dat0.hi, dat0.lo, dat1.hi, dat1.lo
@@ -151,6 +153,11 @@ int oic_dump_index(oic_ctx_t *ctx, uint64_t *n_keys, uint64_t *n_occ, uint64_t *
  * diag_end, n_matches, first_match (9 x int64); match record: offset, len, start (3 x int32). */
 void oic_set_debug(oic_ctx_t *ctx, uint32_t mask);
 int oic_dump_pairs(oic_ctx_t *ctx, uint64_t *n_pairs, uint64_t *n_matches, int64_t *pairs, int32_t *matches);
+
+/* Roofline denominator of the extension stage: INT32 issue rates of `device`, measured (thread Gop/s).  alu = chains of
+ * LOP3 + IADD3 (the pipe the edit-distance rows live on; reference code measured against: LIBO/prefixEditDistance-forward.C
+ * inner loop), imad = chains of IMAD.  Takes a few milliseconds. */
+int oic_measure_int32_peak(int device, double *alu_gops, double *imad_gops);
 
 #ifdef __cplusplus
 }
