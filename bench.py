@@ -332,6 +332,7 @@ def main():
                          "frac_int32": ext_gops / alu_peak if alu_peak else None}}
     value = q_bases_all / 1e6 * steps / dt
     e2e_v = q_bases_all / 1e6 * steps / dt_e2e
+    e2e_stages = {k: tm_e2e[k] / steps for k in ("ms_pack", "ms_build", "ms_scan", "ms_group", "ms_extend")}
     line = {"metric": metric, "value": value, "unit": "query Mbp/s", "n_gpus": world, "steps": steps, "warmup": a.warmup,
             "ms_per_step": 1000 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8/int32 (2-bit packed bases, int32 edit rows, f64 branch score)", "data": "synthetic",
@@ -339,7 +340,8 @@ def main():
             "clocks": sampler.summary(),
             "e2e": {"value": e2e_v, "unit": "query Mbp/s", "ms_per_step": 1000 * dt_e2e / steps,
                     "overlaps_per_sec": n_ovl_e2e * 1.0 / (dt_e2e / steps),
-                    "h2d_bytes_per_step": tm_e2e["h2d_bytes"] // steps, "d2h_bytes_per_step": tm_e2e["d2h_bytes"] // steps},
+                    "h2d_bytes_per_step": tm_e2e["h2d_bytes"] // steps, "d2h_bytes_per_step": tm_e2e["d2h_bytes"] // steps,
+                    "stages_ms": e2e_stages},
             "device_ms_per_step": (tm["ms_build"] + tm["ms_total_search"]) / steps,
             "gpu_launches": int(tm["launches"]), "roofline": roof, "stages": stages,
             "work_per_step_rank0": {k: d[k] // steps for k in ("n_inserts", "n_distinct", "n_windows", "n_found", "n_refs", "n_add_ref",

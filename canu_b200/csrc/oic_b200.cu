@@ -127,12 +127,15 @@ struct oic_ctx {
   // hash block
   bool hash_ready = false;
   oic_hash_meta_t hb = {};
-  DevBuf d_table, d_occ, d_str_flags, d_str_use, d_win_slot, d_blk, d_big_list, d_occ_tmp, d_hist;
+  DevBuf d_table, d_occ, d_str_flags, d_str_use, d_filter, d_ovf_slot, d_ovf_occ, d_multi_list, d_first_occ, d_cnt, d_mid_list, d_blk, d_big_list, d_occ_tmp, d_hist;
+  bool have_occupancy = false;   // occupancy bitmap of the current hash block is valid
 
   // search buffers
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
       d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool, d_wide;
   DevBuf d_ctr, d_flag;
+  DevBuf d_ascii, d_asc_off;                  // staging of oic_load_reads (kept: a 200 MB cudaMalloc/cudaFree per call costs milliseconds)
+  double ml_erate = -1.0; int ml_rows = -1;   // what d_match_limit was built for
   uint64_t rec_cap = 0;       // run records per batch
   uint64_t batch_bases = 0;
 
@@ -191,6 +194,21 @@ int zero_counters(oic_ctx *c) {
   return 0;
 }
 
+// occupancy bitmap of the table (oic_build.cuh k_occupancy); OIC_OCCUPANCY=0 turns it off
+bool use_occupancy() {
+  static const char *env = getenv("OIC_OCCUPANCY");
+  return !(env && env[0] == '0');
+}
+int build_occupancy(oic_ctx *c, uint64_t slots) {
+  c->have_occupancy = false;
+  if (!use_occupancy()) return 0;
+  CK(c->d_filter.ensure(slots / 8 + 64));
+  k_occupancy<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_filter.as<uint32_t>());
+  c->tm.launches += 1;
+  c->have_occupancy = true;
+  return 0;
+}
+
 __global__ void k_table_init(Slot *t, uint64_t n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) reinterpret_cast<uint4 *>(t)[i] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
@@ -204,7 +222,8 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   uint64_t n_windows = 0;
   for (uint32_t s = 0; s < n_strings; s++)
     if (use[s] && c->h_len[ri_bgn + s] >= (uint32_t)K) n_windows += c->h_len[ri_bgn + s] - K + 1;
-  if (n_windows >= (1ull << 31)) return c->fail(OIC_ERR_CAPACITY, "hash block has %llu k-mers (limit 2^31)", (unsigned long long)n_windows);
+  if (n_windows >= (1ull << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %llu k-mers (limit 2^30)", (unsigned long long)n_windows);
+  if (n_strings >= (1u << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %u reads (limit 2^30)", n_strings);
   uint64_t want = 2 * (n_windows + c->skip_keys.size()) + 16;
   uint64_t slots = 1024;
   while (slots < want) slots <<= 1;
@@ -216,16 +235,21 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   const uint32_t ri_last = ri_bgn + n_strings - 1;
   const int64_t region_end = c->h_pos[ri_last] + c->h_len[ri_last];
   const uint64_t region_words = (uint64_t)((region_end - region_pos + 31) >> 5);
-  CK(c->d_win_slot.ensure(region_words * 32 * sizeof(uint32_t)));
-  const uint64_t n_scan_blocks = (slots + SCAN_ITEMS - 1) / SCAN_ITEMS;
-  CK(c->d_blk.ensure((n_scan_blocks + 2) * sizeof(uint32_t)));
+  // worst case: every window belongs to a repeated k-mer
+  CK(c->d_ovf_slot.ensure((n_windows + 32) * sizeof(uint32_t)));
+  CK(c->d_ovf_occ.ensure((n_windows + 32) * sizeof(uint64_t)));
+  CK(c->d_multi_list.ensure((n_windows / 2 + 32) * sizeof(uint32_t)));
+  CK(c->d_first_occ.ensure((n_windows / 2 + 32) * sizeof(uint64_t)));
+  CK(c->d_cnt.ensure((n_windows / 2 + 32) * sizeof(uint32_t)));
+  CK(c->d_mid_list.ensure((n_windows / (SMALL_LIST + 1) + 32) * sizeof(uint32_t)));
+  CK(c->d_big_list.ensure((n_windows / 33 + 32) * sizeof(uint32_t)));
+  CK(c->d_occ.ensure((n_windows + 32) * sizeof(uint64_t)));
 
   if (zero_counters(c)) return OIC_ERR_CUDA;
   k_table_init<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots);
   CK(cudaMemsetAsync(c->d_str_flags.p, 0, ((size_t)n_strings + 8) & ~(size_t)3, c->stream));
   CK(cudaMemcpyAsync(c->d_str_use.p, use.data(), n_strings, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += n_strings;
-  CK(cudaMemsetAsync(c->d_win_slot.p, 0xff, region_words * 32 * sizeof(uint32_t), c->stream));
 
   BuildArgs a;
   a.fwd = c->d_fwd.as<uint64_t>();
@@ -239,33 +263,33 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   a.K = K;
   a.table = c->d_table.as<Slot>();
   a.slot_mask = slots - 1;
-  a.win_slot = c->d_win_slot.as<uint32_t>();
-  a.occ = nullptr;
+  a.ovf_slot = c->d_ovf_slot.as<uint32_t>();
+  a.ovf_occ = c->d_ovf_occ.as<uint64_t>();
+  a.multi_list = c->d_multi_list.as<uint32_t>();
+  a.first_occ = c->d_first_occ.as<uint64_t>();
+  a.cnt = c->d_cnt.as<uint32_t>();
+  a.mid_list = c->d_mid_list.as<uint32_t>();
+  a.big_list = c->d_big_list.as<uint32_t>();
+  a.occ = c->d_occ.as<uint64_t>();
   a.ctr = c->d_ctr.as<DevCounters>();
 
+  // no host round trip between the kernels: the list kernels take their sizes from the device counters
   k_insert<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
-  k_scan_slots_reduce<<<(unsigned)n_scan_blocks, SCAN_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_blk.as<uint32_t>());
-  k_scan_u32_single<<<1, SCAN_THREADS, 0, c->stream>>>(c->d_blk.as<uint32_t>(), (uint32_t)n_scan_blocks);
-  k_scan_slots_apply<<<(unsigned)n_scan_blocks, SCAN_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_blk.as<uint32_t>());
-  c->tm.launches += 5;
-  uint32_t n_occ = 0;
-  CK(cudaMemcpyAsync(&n_occ, c->d_blk.as<uint32_t>() + n_scan_blocks, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  c->tm.d2h_bytes += 4;
-  if (n_occ != n_windows) return c->fail(OIC_ERR_STATE, "internal: %u occurrences counted, %llu expected", n_occ, (unsigned long long)n_windows);
-
-  CK(c->d_occ.ensure(((size_t)n_occ + 32) * sizeof(uint64_t)));
-  CK(c->d_big_list.ensure(((size_t)n_occ / 33 + 2) * sizeof(uint32_t)));
-  a.occ = c->d_occ.as<uint64_t>();
-  k_fill<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
-  k_sort_small<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_occ.as<uint64_t>(), c->d_big_list.as<uint32_t>(),
-                                                             c->d_ctr.as<DevCounters>());
-  c->tm.launches += 2;
+  k_multi_prep<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  k_multi_count<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  k_multi_alloc<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  k_multi_fill<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  k_multi_sort<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  k_sort_mid<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  c->tm.launches += 8;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
+  if (hc.n_inserts != n_windows) return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
+  const uint32_t n_occ = hc.n_ovf + hc.n_multi;
+  if (hc.occ_cursor != n_occ) return c->fail(OIC_ERR_STATE, "internal: %u list entries allocated, %u on the overflow list", hc.occ_cursor, n_occ);
   if (hc.n_big_lists) {
     CK(c->d_occ_tmp.ensure(((size_t)n_occ + 32) * sizeof(uint64_t)));
     unsigned grid = std::min<unsigned>(hc.n_big_lists, 148 * 8);
-    k_sort_big<<<grid, BIG_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), c->d_big_list.as<uint32_t>(), hc.n_big_lists, c->d_occ.as<uint64_t>(),
+    k_sort_big<<<grid, BIG_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), c->d_big_list.as<uint32_t>(), c->d_ctr.as<DevCounters>(), c->d_occ.as<uint64_t>(),
                                                     c->d_occ_tmp.as<uint64_t>());
     c->tm.launches += 1;
   }
@@ -299,6 +323,14 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   }
   if (device < 0 || device >= ndev) { g_create_error = "bad device index"; return OIC_ERR_ARG; }
   if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OIC_ERR_CUDA; }
+  {
+    // the index is probed with independent random 16-byte loads: ask L2 to fetch single 32-byte sectors from HBM instead
+    // of promoting every miss to a 64/128-byte fetch (a hint; OIC_L2_FETCH=64|128 restores larger fetches)
+    const char *fg = getenv("OIC_L2_FETCH");
+    const size_t gran = fg ? strtoull(fg, nullptr, 10) : 32;
+    if (gran) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, gran);
+    cudaGetLastError();
+  }
   oic_ctx *c = new oic_ctx();
   c->P = *p;
   if (c->P.max_erate > 0.06) c->P.use_hopeless_check = 0;   // OIC/overlapInCore.C:416-421
@@ -324,7 +356,7 @@ void oic_destroy(oic_ctx_t *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DevBuf *bufs[] = {&c->d_fwd, &c->d_rc, &c->d_pos, &c->d_len, &c->d_match_limit, &c->d_skip_keys, &c->d_table, &c->d_occ,
-                    &c->d_str_flags, &c->d_str_use, &c->d_win_slot, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
+                    &c->d_ascii, &c->d_asc_off, &c->d_str_flags, &c->d_str_use, &c->d_filter, &c->d_ovf_slot, &c->d_ovf_occ, &c->d_multi_list, &c->d_first_occ, &c->d_cnt, &c->d_mid_list, &c->d_blk, &c->d_big_list, &c->d_occ_tmp, &c->d_hist,
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
@@ -372,7 +404,7 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
   CK(c->d_rc.ensure(c->stream_words * 8));
   CK(c->d_pos.ensure((size_t)(n + 1) * 8));
   CK(c->d_len.ensure((size_t)(n + 1) * 4));
-  DevBuf d_ascii, d_off;
+  DevBuf &d_ascii = c->d_ascii, &d_off = c->d_asc_off;
   const uint64_t asc_bytes = asc_hi - asc_lo;
   CK(d_ascii.ensure(asc_bytes + 64));
   CK(d_off.ensure((size_t)n * 8));
@@ -390,8 +422,6 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
   c->tm.launches += 1;
   DevCounters hc;
   int rcode = read_counters(c, hc);
-  d_ascii.release();
-  d_off.release();
   if (rcode) return rcode;
   CK(cudaGetLastError());
   t.stop();
@@ -399,12 +429,15 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
 
   // Edit_Match_Limit for every row an extension can reach: error limit <= ceil(erate * longest read)
   c->max_rows = (int)ceil(c->P.max_erate * (double)c->max_read_len) + 3;
-  std::vector<int32_t> ml;
-  build_match_limit(c->P.max_erate, c->max_rows + 1, ml);
-  CK(c->d_match_limit.ensure(ml.size() * 4));
-  CK(cudaMemcpyAsync(c->d_match_limit.p, ml.data(), ml.size() * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  c->tm.h2d_bytes += ml.size() * 4;
+  if (c->ml_erate != c->P.max_erate || c->ml_rows != c->max_rows) {
+    std::vector<int32_t> ml;
+    build_match_limit(c->P.max_erate, c->max_rows + 1, ml);
+    CK(c->d_match_limit.ensure(ml.size() * 4));
+    CK(cudaMemcpyAsync(c->d_match_limit.p, ml.data(), ml.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->tm.h2d_bytes += ml.size() * 4;
+    c->ml_erate = c->P.max_erate; c->ml_rows = c->max_rows;
+  }
   return OIC_OK;
 }
 
@@ -498,6 +531,7 @@ int oic_build_hash_index(oic_ctx_t *c, uint32_t bgn_id, uint32_t end_id, uint32_
     CK(cudaMemcpyAsync(&has_empty, c->d_flag.p, 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
   }
+  if (build_occupancy(c, c->hb.table_slots)) return OIC_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaGetLastError());
   t.stop();
@@ -568,6 +602,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.n_queries = nq;
   sa.first_id = c->first_id; sa.hash_bgn_id = c->hb.bgn_id; sa.K = P.kmer_len;
   sa.table = c->d_table.as<Slot>(); sa.slot_mask = c->hb.table_slots - 1; sa.occ = c->d_occ.as<uint64_t>();
+  sa.occupancy = c->have_occupancy ? c->d_filter.as<uint32_t>() : nullptr;
   sa.has_empty = (int)c->hb.has_empty;
   sa.recs = c->d_recs.as<Seed>(); sa.max_chunks = max_chunks;
   sa.chunk_next = c->d_chunk_next.as<uint32_t>(); sa.chunk_cnt = c->d_chunk_cnt.as<uint32_t>(); sa.chunk_qs = c->d_chunk_qs.as<uint32_t>();
@@ -925,7 +960,11 @@ int oic_hash_block_buffers(const oic_ctx_t *c, oic_dev_buffer_t b[OIC_HASH_BLOCK
 }
 int oic_hash_block_commit(oic_ctx_t *c, const oic_hash_meta_t *m) {
   if (!c || !m) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
   c->hb = *m;
+  // the occupancy bitmap is not shipped: rebuilt here from the table that arrived
+  if (build_occupancy(c, m->table_slots)) return OIC_ERR_CUDA;
+  CK(cudaStreamSynchronize(c->stream));
   c->hash_ready = true;
   c->stats.n_hash_blocks++;
   c->stats.last_end_hash_id = m->last_id;
@@ -945,17 +984,19 @@ int oic_dump_index(oic_ctx_t *c, uint64_t *n_keys, uint64_t *n_occ, uint64_t *ke
     if (t[i].key != EMPTY_KEY) idx.push_back((uint32_t)i);
   std::sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return t[a].key < t[b].key; });
   if (n_keys) *n_keys = idx.size();
-  if (n_occ) *n_occ = c->hb.n_occ;
+  uint64_t total = 0;
+  for (size_t k = 0; k < idx.size(); k++) total += pay_len(t[idx[k]].pay);
+  if (n_occ) *n_occ = total;
   if (!keys) return OIC_OK;
   uint64_t w = 0;
   for (size_t k = 0; k < idx.size(); k++) {
     const Slot &s = t[idx[k]];
     keys[k] = s.key;
     occ_start[k] = w;
-    flags[k] = (s.lenflags & EMPTY_FLAG) ? 1 : 0;
-    uint32_t n = s.lenflags & LEN_MASK;
+    flags[k] = pay_empty(s.pay) ? 1 : 0;
+    const uint32_t n = pay_len(s.pay);
     for (uint32_t j = 0; j < n; j++) {
-      uint64_t e = o[s.start + j];
+      const uint64_t e = pay_is_list(s.pay) ? o[pay_start(s.pay) + j] : s.pay;
       occ[w++] = ((uint64_t)occ_str(e) << 32) | occ_off(e);
     }
   }

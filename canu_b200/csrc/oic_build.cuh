@@ -8,12 +8,13 @@
  * the screened-end flags, (d) the hash-load cut-off (which read is the last one loaded).
  *
  *   k_pack_reads   ASCII -> 2-bit words, forward and reverse-complement streams
- *   k_insert       one warp per 32-base word of the block: 32 windows, one per lane; claim/find the slot
- *                  (atomicCAS on the key), count the occurrence, remember the slot of every window
- *   k_scan_*       exclusive scan of the per-slot counts -> CSR starts (3-phase, in place in the table)
- *   k_fill         scatter every window's (string, offset, previous base) into its list
- *   k_sort_small   lists of 2..32 entries: one warp per list, bitonic network in registers (descending)
- *   k_sort_big     longer lists: one block per list, LSD radix sort (descending) through a ping-pong buffer
+ *   k_insert       one warp per 32-base word of the block: 32 windows, one per lane; one CAS on the key per probe, the
+ *                  occurrence ORed into the slot (k-mers seen once stay inline in the slot); repeats go to an overflow list; 
+ *   k_multi_prep / _count / _alloc / _fill   per repeated k-mer: count its overflow entries, reserve its run of the
+ *                  occurrence array (bump allocator), scatter the entries into it
+ *   k_multi_sort   runs of 2..6 entries: one thread each (sorting network in registers, descending);
+ *   k_sort_mid     7..32 entries: one warp per run (bitonic);  k_sort_big: longer runs, one block each (LSD radix)
+ *   k_occupancy    bitmap of occupied slots (L2-resident), tested by the seed scan before it touches the table
  *   k_first_occ    histogram of "read in which a k-mer first appears" -> hash-load cut-off on the host
  *   k_mark_skip    Empty bit + screened ends for the -k skip list (and absent k-mers when the hopeless check is on)
  */
@@ -91,7 +92,12 @@ struct BuildArgs {
   int K;
   Slot *table;
   uint64_t slot_mask;
-  uint32_t *win_slot;        // per stream position of the region: slot of the window starting there
+  uint32_t *ovf_slot;        // overflow list: every occurrence of a k-mer that occurs more than once ...
+  uint64_t *ovf_occ;         // ... {slot, occurrence word}
+  uint32_t *multi_list;      // slots of those k-mers
+  uint64_t *first_occ;       // per list: the occurrence that claimed the slot
+  uint32_t *cnt;             // per list: occurrences on the overflow list, then the fill cursor
+  uint32_t *mid_list, *big_list;
   uint64_t *occ;
   DevCounters *ctr;
 };
@@ -105,61 +111,104 @@ __device__ __forceinline__ uint32_t find_string(const BuildArgs &a, int64_t p0) 
   return lo;
 }
 
-__device__ __forceinline__ uint32_t table_insert(Slot *table, uint64_t mask, unsigned long long key, bool &claimed) {
-  uint64_t h = hash_key(key) & mask;
-  claimed = false;
-  while (true) {
-    unsigned long long cur = table[h].key;
-    if (cur == key) return (uint32_t)h;
-    if (cur == EMPTY_KEY) {
-      unsigned long long old = atomicCAS(&table[h].key, EMPTY_KEY, key);
-      if (old == EMPTY_KEY) { claimed = true; return (uint32_t)h; }
-      if (old == key) return (uint32_t)h;
-    }
-    h = (h + 1) & mask;
-  }
+/* 16-byte compare-and-swap on a slot: returns the slot's previous content */
+__device__ __forceinline__ void slot_cas(Slot *sl, unsigned long long ck, unsigned long long cp, unsigned long long nk, unsigned long long np,
+                                         unsigned long long &ok, unsigned long long &op) {
+  asm volatile("{\n .reg .b128 c, n, o;\n mov.b128 c, {%3, %4};\n mov.b128 n, {%5, %6};\n"
+               " atom.global.relaxed.gpu.cas.b128 o, [%2], c, n;\n mov.b128 {%0, %1}, o;\n}"
+               : "=l"(ok), "=l"(op) : "l"(sl), "l"(ck), "l"(cp), "l"(nk), "l"(np) : "memory");
 }
 
-__device__ __forceinline__ bool table_find(const Slot *__restrict__ table, uint64_t mask, unsigned long long key, uint32_t &slot,
-                                           uint32_t &start, uint32_t &lenflags) {
-  uint64_t h = hash_key(key) & mask;
+/* load that bypasses L1 (the table is modified by atomics of other SMs while it is read) */
+__device__ __forceinline__ unsigned long long ld_key(const Slot *sl) {
+  unsigned long long v;
+  asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(&sl->key) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool table_find(const Slot *__restrict__ table, uint64_t mask, uint64_t h, unsigned long long key, uint32_t &slot,
+                                           unsigned long long &pay) {
+  h &= mask;
   while (true) {
     uint4 v = __ldg(reinterpret_cast<const uint4 *>(table + h));
     unsigned long long cur = ((unsigned long long)v.y << 32) | v.x;
-    if (cur == key) { slot = (uint32_t)h; start = v.z; lenflags = v.w; return true; }
+    if (cur == key) { slot = (uint32_t)h; pay = ((unsigned long long)v.w << 32) | v.z; return true; }
     if (cur == EMPTY_KEY) return false;
     h = (h + 1) & mask;
   }
 }
 
-// one warp per 32-base word of the hash block's stream region
+/*
+ * One warp per 32-base word of the hash block's stream region, one window per lane.  Per probe one 8-byte CAS on the key:
+ *   - the slot was free: the window owns the k-mer and ORs its occurrence word into the payload (first occurrence of a
+ *     k-mer: ~90 % of the windows of a 1x block never need anything else);
+ *   - the key is already there: the window ORs the list mark into the payload and appends {slot, occurrence} to the
+ *     overflow list; the arrival that finds the mark clear also queues the slot for the list kernels.
+ * Both payload updates are ORs into disjoint bits, so they commute: no arrival ever waits for another one.
+ * Hash_Insert's chained bucket (Build_Hash_Index.C:296-350) appears as: slot = k-mer, list = chain.
+ */
 __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
   uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (gw >= a.region_words) return;
-  int l = lane_id();
-  int64_t p0 = a.region_pos + (int64_t)gw * 32;
-  uint32_t s = find_string(a, p0);
-  int64_t spos = a.rd_pos[a.ri_bgn + s];
-  uint32_t len = a.rd_len[a.ri_bgn + s];
-  int64_t o = p0 - spos + l;
-  bool valid = a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
-  uint64_t W0 = a.fwd[p0 >> 5], W1 = a.fwd[(p0 >> 5) + 1];
+  const int l = lane_id();
+  const int64_t p0 = a.region_pos + (int64_t)gw * 32;
+  const uint32_t s = find_string(a, p0);
+  const int64_t spos = a.rd_pos[a.ri_bgn + s];
+  const uint32_t len = a.rd_len[a.ri_bgn + s];
+  const int64_t o = p0 - spos + l;
+  const bool valid = a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
+  const uint64_t W0 = a.fwd[p0 >> 5], W1 = a.fwd[(p0 >> 5) + 1];
   uint64_t key = l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0;
   key &= (a.K == 32) ? ~0ULL : ((1ULL << (2 * a.K)) - 1);
-  bool claimed = false;
+  bool claimed = false, conv = false, later = false;
+  unsigned long long my_occ = 0;
+  uint32_t my_slot = 0;
   if (valid) {
-    uint32_t slot = table_insert(a.table, a.slot_mask, key, claimed);
-    atomicAdd(&a.table[slot].lenflags, 1u);
-    a.win_slot[(p0 - a.region_pos) + l] = slot;
+    const uint32_t pv = o > 0;
+    const uint32_t pb = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : (pv ? (uint32_t)(a.fwd[(p0 >> 5) - 1] >> 62) & 3u : 0u);
+    my_occ = occ_pack(s, (uint32_t)o, pv, pb);
+    uint64_t h = hash_key(key) & a.slot_mask;
+    // a plain load first: it brings the line into L2 with the memory-level parallelism of loads; an atomic that misses
+    // L2 is several times slower (measured on B200: CAS-first insert 25 ms, load-first 6 ms for 99 M windows)
+    unsigned long long cur = ld_key(a.table + h);
+    while (true) {
+      if (cur == EMPTY_KEY) cur = atomicCAS(&a.table[h].key, EMPTY_KEY, key);
+      if (cur == EMPTY_KEY) {
+        if (my_occ) atomicOr(&a.table[h].pay, my_occ);
+        claimed = true;
+        break;
+      }
+      if (cur == key) {
+        my_slot = (uint32_t)h;
+        conv = !pay_is_list(atomicOr(&a.table[h].pay, PAY_MULTI));
+        later = true;
+        break;
+      }
+      h = (h + 1) & a.slot_mask;
+      cur = ld_key(a.table + h);
+    }
   }
-  uint32_t nv = __popc(__ballot_sync(FULL, valid)), nc = __popc(__ballot_sync(FULL, claimed));
+  // overflow list entries of the warp: one allocation
+  const unsigned lm = __ballot_sync(FULL, later), cm = __ballot_sync(FULL, conv);
+  if (lm) {
+    uint32_t base = 0, mbase = 0;
+    if (l == 0) {
+      base = atomicAdd(&a.ctr->n_ovf, (unsigned)__popc(lm));
+      if (cm) mbase = atomicAdd(&a.ctr->n_multi, (unsigned)__popc(cm));
+    }
+    base = __shfl_sync(FULL, base, 0);
+    mbase = __shfl_sync(FULL, mbase, 0);
+    const unsigned below = (1u << l) - 1;
+    if (later) { const uint32_t w = base + __popc(lm & below); a.ovf_slot[w] = my_slot; a.ovf_occ[w] = my_occ; }
+    if (conv) a.multi_list[mbase + __popc(cm & below)] = my_slot;
+  }
+  const uint32_t nv = __popc(__ballot_sync(FULL, valid)), nc = __popc(__ballot_sync(FULL, claimed));
   if (l == 0) {
     if (nv) atomicAdd(&a.ctr->n_inserts, (unsigned long long)nv);
     if (nc) atomicAdd(&a.ctr->n_distinct, (unsigned long long)nc);
   }
 }
 
-// 3-phase exclusive scan over table[i].lenflags -> table[i].start   (SCAN_ITEMS slots per block)
+// block-wide exclusive scan helper + exclusive scan of a uint32 array (per-query-strand run counts), 3 phases
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_PER_THREAD = 16;
 constexpr int SCAN_ITEMS = SCAN_THREADS * SCAN_PER_THREAD;
@@ -184,16 +233,6 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *total)
   return r;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_slots_reduce(const Slot *__restrict__ table, uint64_t n, uint32_t *blk) {
-  uint64_t base = (uint64_t)blockIdx.x * SCAN_ITEMS + (uint64_t)threadIdx.x * SCAN_PER_THREAD;
-  uint32_t s = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_PER_THREAD; i++)
-    if (base + i < n) s += table[base + i].lenflags & LEN_MASK;
-  uint32_t tot;
-  block_excl_scan(s, &tot);
-  if (threadIdx.x == 0) blk[blockIdx.x] = tot;
-}
 // single block: exclusive scan of blk[0..nb) in place; total written to blk[nb]
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_single(uint32_t *blk, uint32_t nb) {
   __shared__ uint32_t carry;
@@ -212,23 +251,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_single(uint32_t *blk,
   }
   if (threadIdx.x == 0) blk[nb] = carry;
 }
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_slots_apply(Slot *table, uint64_t n, const uint32_t *__restrict__ blk) {
-  uint64_t base = (uint64_t)blockIdx.x * SCAN_ITEMS + (uint64_t)threadIdx.x * SCAN_PER_THREAD;
-  uint32_t c[SCAN_PER_THREAD];
-  uint32_t s = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_PER_THREAD; i++) {
-    c[i] = (base + i < n) ? (table[base + i].lenflags & LEN_MASK) : 0;
-    s += c[i];
-  }
-  uint32_t ex = block_excl_scan(s, nullptr) + blk[blockIdx.x];
-#pragma unroll
-  for (int i = 0; i < SCAN_PER_THREAD; i++) {
-    if (base + i < n && c[i]) table[base + i].start = ex;
-    ex += c[i];
-  }
-}
-
 // generic exclusive scan of a uint32 array (used for per-query-strand run counts), same 3 phases
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_reduce(const uint32_t *__restrict__ in, uint64_t n, uint32_t *blk) {
   uint64_t base = (uint64_t)blockIdx.x * SCAN_ITEMS + (uint64_t)threadIdx.x * SCAN_PER_THREAD;
@@ -258,21 +280,54 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_apply(const uint32_t 
   }
 }
 
-// same mapping as k_insert
-__global__ void __launch_bounds__(256) k_fill(BuildArgs a) {
-  uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (gw >= a.region_words) return;
-  int l = lane_id();
-  int64_t p0 = a.region_pos + (int64_t)gw * 32;
-  uint32_t slot = a.win_slot[(p0 - a.region_pos) + l];
-  if (slot == NO_SLOT) return;
-  uint32_t s = find_string(a, p0);   // (uniform over the lanes that reach here: a word never spans two strings)
-  int64_t spos = a.rd_pos[a.ri_bgn + s];
-  uint32_t o = (uint32_t)(p0 - spos + l);
-  uint32_t pv = o > 0, pb = 0;
-  if (pv) pb = base_at(a.fwd, p0 + l - 1);
-  uint32_t idx = atomicAdd(&a.table[slot].start, 1u);   // start doubles as the fill cursor; k_sort_small rewinds it
-  a.occ[idx] = occ_pack(s, o, pv, pb);
+constexpr int MULTI_GRID = 148 * 16;   // grid-stride kernels over device-side counts (no host round trip inside the build)
+constexpr int SMALL_LIST = 6;           // lists up to this length are sorted by one thread
+
+// The list kernels.  After k_insert a repeated k-mer's slot holds {first occurrence | list mark}; its other occurrences are
+// on the overflow list.  i = position of the slot in multi_list indexes the per-list arrays first_occ[] / cnt[].
+// (1) one thread per list: take the first occurrence out of the slot, leave the list index there
+__global__ void __launch_bounds__(256) k_multi_prep(BuildArgs a) {
+  const uint32_t n = a.ctr->n_multi;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t h = a.multi_list[i];
+    a.first_occ[i] = a.table[h].pay & ~PAY_MULTI;
+    a.table[h].pay = PAY_MULTI | i;
+    a.cnt[i] = 0;
+  }
+}
+// (2) one thread per overflow entry: count it; from here on the entry names its list, not its slot
+__global__ void __launch_bounds__(256) k_multi_count(BuildArgs a) {
+  const uint32_t n = a.ctr->n_ovf;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const uint32_t i = (uint32_t)a.table[a.ovf_slot[j]].pay;
+    atomicAdd(&a.cnt[i], 1u);
+    a.ovf_slot[j] = i;
+  }
+}
+// (3) one thread per list: reserve its run in `occ`, place the first occurrence, publish {length, start} in the slot
+__global__ void __launch_bounds__(256) k_multi_alloc(BuildArgs a) {
+  const uint32_t n = a.ctr->n_multi;
+  const int l = lane_id();
+  for (uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; i0 < n; i0 += gridDim.x * blockDim.x) {
+    const uint32_t i = i0 + l;
+    const uint32_t len = (i < n) ? a.cnt[i] + 1 : 0;
+    const uint32_t incl = warp_incl_scan(len);
+    uint32_t base = 0;
+    if (l == 31) base = atomicAdd(&a.ctr->occ_cursor, incl);
+    base = __shfl_sync(FULL, base, 31);
+    if (i < n) {
+      const uint32_t start = base + incl - len;
+      a.occ[start] = a.first_occ[i];
+      a.cnt[i] = start + 1;   // fill cursor
+      a.table[a.multi_list[i]].pay = PAY_MULTI | ((unsigned long long)len << 32) | start;
+    }
+  }
+}
+// (4) one thread per overflow entry
+__global__ void __launch_bounds__(256) k_multi_fill(BuildArgs a) {
+  const uint32_t n = a.ctr->n_ovf;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+    a.occ[atomicAdd(&a.cnt[a.ovf_slot[j]], 1u)] = a.ovf_occ[j];
 }
 
 // descending bitonic sort of up to 32 values held one per lane (0 pads sort to the end)
@@ -293,50 +348,58 @@ __device__ __forceinline__ uint64_t warp_sort_desc(uint64_t v) {
   return v;
 }
 
-// one warp per 32 consecutive slots; lists of 2..32 are sorted here, longer ones are queued
-__global__ void __launch_bounds__(256) k_sort_small(Slot *table, uint64_t n_slots, uint64_t *occ, uint32_t *big_list, DevCounters *ctr) {
-  uint64_t gwarp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  uint64_t s0 = gwarp * 32;
-  if (s0 >= n_slots) return;
-  int l = lane_id();
-  uint32_t len = 0, start = 0;
-  if (s0 + l < n_slots) {
-    Slot sl = table[s0 + l];
-    if (sl.key != EMPTY_KEY) {
-      len = sl.lenflags & LEN_MASK;
-      start = sl.start - len;              // rewind the fill cursor
-      if (len) table[s0 + l].start = start;
+// (5) one thread per list: short lists are sorted here (descending (string, offset): the order of
+// the reference's head-pushed chain, Build_Hash_Index.C:317-323), longer ones are queued for a warp / a block
+__global__ void __launch_bounds__(256) k_multi_sort(BuildArgs a) {
+  const uint32_t n = a.ctr->n_multi;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t h = a.multi_list[i];
+    const unsigned long long p = a.table[h].pay;
+    const uint32_t len = (uint32_t)(p >> 32) & PAY_LEN_MASK, start = (uint32_t)p;
+    if (len > 32) { a.big_list[atomicAdd(&a.ctr->n_big_lists, 1u)] = h; continue; }
+    if (len > SMALL_LIST) { a.mid_list[atomicAdd(&a.ctr->n_mid_lists, 1u)] = h; continue; }
+    uint64_t v[SMALL_LIST];
+#pragma unroll
+    for (int k = 0; k < SMALL_LIST; k++) v[k] = (k < (int)len) ? a.occ[start + k] : 0ULL;
+#pragma unroll
+    for (int r = 0; r < SMALL_LIST; r++) {
+#pragma unroll
+      for (int k = (r & 1); k + 1 < SMALL_LIST; k += 2) {
+        const uint64_t x = v[k], y = v[k + 1];
+        v[k] = x > y ? x : y;
+        v[k + 1] = x > y ? y : x;
+      }
     }
+#pragma unroll
+    for (int k = 0; k < SMALL_LIST; k++) if (k < (int)len) a.occ[start + k] = v[k];
   }
-  unsigned big = __ballot_sync(FULL, len > 32);
-  if (big) {
-    uint32_t base = 0;
-    if (l == 0) base = atomicAdd(&ctr->n_big_lists, (unsigned)__popc(big));
-    base = __shfl_sync(FULL, base, 0);
-    if (len > 32) big_list[base + __popc(big & ((1u << l) - 1))] = (uint32_t)(s0 + l);
-  }
-  unsigned todo = __ballot_sync(FULL, len >= 2 && len <= 32);
-  while (todo) {
-    int src = __ffs(todo) - 1;
-    todo &= todo - 1;
-    uint32_t n = __shfl_sync(FULL, len, src), st = __shfl_sync(FULL, start, src);
-    uint64_t v = (l < (int)n) ? occ[st + l] : 0;
+}
+
+// one warp per list of SMALL_LIST+1 .. 32 entries
+__global__ void __launch_bounds__(256) k_sort_mid(BuildArgs a) {
+  const uint32_t n = a.ctr->n_mid_lists;
+  const int l = lane_id();
+  for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += (gridDim.x * blockDim.x) >> 5) {
+    const unsigned long long p = a.table[a.mid_list[i]].pay;
+    const uint32_t len = (uint32_t)(p >> 32) & PAY_LEN_MASK, st = (uint32_t)p;
+    uint64_t v = (l < (int)len) ? a.occ[st + l] : 0;
     v = warp_sort_desc(v);
-    if (l < (int)n) occ[st + l] = v;
+    if (l < (int)len) a.occ[st + l] = v;
   }
 }
 
 // one block per long list: LSD radix sort, 8-bit digits over bits [12, 64), descending, stable
 constexpr int BIG_THREADS = 256;
 __global__ void __launch_bounds__(BIG_THREADS) k_sort_big(const Slot *__restrict__ table, const uint32_t *__restrict__ big_list,
-                                                          uint32_t n_big, uint64_t *occ, uint64_t *tmp) {
+                                                          const DevCounters *ctr, uint64_t *occ, uint64_t *tmp) {
   __shared__ uint32_t bins[256];
   __shared__ uint32_t wcnt[BIG_THREADS / 32][256];
   __shared__ int skip;
+  const uint32_t n_big = ctr->n_big_lists;
   for (uint32_t li = blockIdx.x; li < n_big; li += gridDim.x) {
     Slot sl = table[big_list[li]];
-    uint32_t n = sl.lenflags & LEN_MASK;
-    uint64_t *src = occ + sl.start, *dst = tmp + sl.start;
+    const uint32_t n = pay_len(sl.pay), st0 = pay_start(sl.pay);
+    uint64_t *src = occ + st0, *dst = tmp + st0;
     for (int shift = 12; shift < 64; shift += 8) {
       bins[threadIdx.x] = 0;
       __syncthreads();
@@ -382,8 +445,8 @@ __global__ void __launch_bounds__(BIG_THREADS) k_sort_big(const Slot *__restrict
       uint64_t *t = src; src = dst; dst = t;
     }
     // result must end up in occ
-    if (src != occ + sl.start)
-      for (uint32_t i = threadIdx.x; i < n; i += BIG_THREADS) occ[sl.start + i] = src[i];
+    if (src != occ + st0)
+      for (uint32_t i = threadIdx.x; i < n; i += BIG_THREADS) occ[st0 + i] = src[i];
     __syncthreads();
   }
 }
@@ -393,9 +456,21 @@ __global__ void k_first_occ(const Slot *__restrict__ table, uint64_t n_slots, co
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_slots) return;
   Slot sl = table[i];
-  uint32_t n = sl.lenflags & LEN_MASK;
-  if (sl.key == EMPTY_KEY || n == 0) return;
-  atomicAdd(&hist[occ_str(occ[sl.start + n - 1])], 1u);
+  if (sl.key == EMPTY_KEY) return;
+  if (!pay_is_list(sl.pay)) { atomicAdd(&hist[occ_str(sl.pay)], 1u); return; }
+  const uint32_t n = pay_len(sl.pay);
+  if (n) atomicAdd(&hist[occ_str(occ[pay_start(sl.pay) + n - 1])], 1u);
+}
+
+// Occupancy bitmap of the finished table: bit i = slot i holds a k-mer.  32 MB for a 100 Mbp block (the table is 4.3 GB), so
+// it stays in L2 while the seed scan streams table lines through it: a window whose home slot is free -- two thirds of the
+// windows that are absent from the block -- is answered by an L2 hit instead of a 128-byte HBM fetch.  One warp per 32
+// slots, coalesced, no atomics.
+__global__ void __launch_bounds__(256) k_occupancy(const Slot *__restrict__ table, uint64_t n_slots, uint32_t *bitmap) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool occ = i < n_slots && table[i].key != EMPTY_KEY;
+  const unsigned m = __ballot_sync(FULL, occ);
+  if (lane_id() == 0 && i < n_slots) bitmap[i >> 5] = m;
 }
 
 // Mark_Skip_Kmers: one thread per (k-mer, orientation) key.
@@ -405,25 +480,32 @@ __global__ void k_mark_skip(Slot *table, uint64_t mask, const uint64_t *__restri
                             uint32_t n_strings, uint8_t *str_flags8, int K, int add_absent, unsigned int *has_empty) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_keys) return;
-  unsigned long long key = keys[i];
-  uint64_t h = hash_key(key) & mask;
+  const unsigned long long key = keys[i];
+  const uint64_t hk = hash_key(key);
+  uint64_t h = hk & mask;
+  unsigned long long pay = 0;
   while (true) {
-    unsigned long long cur = table[h].key;
-    if (cur == key) break;
-    if (cur == EMPTY_KEY) {
+    Slot cur = table[h];
+    if (cur.key == EMPTY_KEY) {
       if (!add_absent) return;
-      unsigned long long old = atomicCAS(&table[h].key, EMPTY_KEY, key);
-      if (old == EMPTY_KEY || old == key) break;
+      // absent k-mer, hopeless check on: present as an Empty entry without occurrences (Build_Hash_Index.C:207-219)
+      unsigned long long ok, op;
+      slot_cas(table + h, EMPTY_KEY, 0ULL, key, PAY_MULTI | PAY_MULTI_EMPTY, ok, op);
+      if (ok == EMPTY_KEY) {
+        *has_empty = 1;
+        return;
+      }
+      cur.key = ok; cur.pay = op;
     }
+    if (cur.key == key) { pay = cur.pay; break; }
     h = (h + 1) & mask;
   }
-  uint32_t old = atomicOr(&table[h].lenflags, EMPTY_FLAG);
+  atomicOr(&table[h].pay, pay_is_list(pay) ? PAY_MULTI_EMPTY : PAY_SINGLE_EMPTY);
   *has_empty = 1;
-  uint32_t n = old & LEN_MASK;
-  uint32_t st = table[h].start;
+  const uint32_t n = pay_len(pay), st = pay_start(pay);
   unsigned int *flags32 = reinterpret_cast<unsigned int *>(str_flags8);
   for (uint32_t j = 0; j < n; j++) {
-    uint64_t oc = occ[st + j];
+    const uint64_t oc = pay_is_list(pay) ? occ[st + j] : pay;
     uint32_t s = occ_str(oc), off = occ_off(oc);
     if (s >= n_strings) continue;
     uint32_t f = 0;

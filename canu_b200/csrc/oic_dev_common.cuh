@@ -22,13 +22,26 @@ namespace oic {
 
 struct __align__(16) Slot {
   unsigned long long key;
-  uint32_t start;
-  uint32_t lenflags;  // bits 0..30 occurrence count, bit 31 = Empty (screened k-mer)
+  unsigned long long pay;   // one occurrence inline, or {Empty, length, start} of a list in `occ` (see below)
 };
 constexpr unsigned long long EMPTY_KEY = ~0ULL;
-constexpr uint32_t EMPTY_FLAG = 0x80000000u;
-constexpr uint32_t LEN_MASK = 0x7fffffffu;
 constexpr uint32_t NO_SLOT = 0xffffffffu;
+
+/* Slot payload.  A k-mer that occurs once in the block (most of them) keeps its occurrence word in the slot, so a probe
+ * that hits needs no second memory access:
+ *   single : bit 63 = 0, the occurrence word itself (oic_core.cuh occ_pack: [62:33] string, [32:12] offset, [2:0] previous
+ *            base), bit 4 = Empty (screened k-mer)
+ *   list   : bit 63 = 1, bit 62 = Empty, [61:32] length, [31:0] first entry in `occ` (length 0: a screened k-mer that is
+ *            absent from the block, Build_Hash_Index.C:207-219)
+ * While the block is being built the low word of a list payload is first the arrival count, then the fill cursor. */
+constexpr unsigned long long PAY_MULTI = 1ULL << 63;
+constexpr unsigned long long PAY_MULTI_EMPTY = 1ULL << 62;
+constexpr unsigned long long PAY_SINGLE_EMPTY = 1ULL << 4;
+constexpr uint32_t PAY_LEN_MASK = 0x3fffffffu;
+OIC_HD bool pay_is_list(unsigned long long p) { return (p >> 63) != 0; }
+OIC_HD uint32_t pay_len(unsigned long long p) { return pay_is_list(p) ? (uint32_t)(p >> 32) & PAY_LEN_MASK : 1u; }
+OIC_HD uint32_t pay_start(unsigned long long p) { return (uint32_t)p; }
+OIC_HD bool pay_empty(unsigned long long p) { return pay_is_list(p) ? ((p >> 62) & 1) != 0 : ((p >> 4) & 1) != 0; }
 
 constexpr int READ_PAD_BASES = 64;   // zero bases after every read
 constexpr int READ_LEAD_BASES = 64;  // zero bases before the first read
@@ -126,8 +139,10 @@ struct DevCounters {
   unsigned int n_spec_tasks, task_cursor;  // (pair, seed) extension tasks of those pairs
   unsigned int n_spec_used;                // tasks whose result the commit pass consumed
   unsigned int n_wide_tasks, wide_cursor;  // tasks rerun with the generic row loop
-  unsigned int pad1;
-  unsigned int pad0;
+  unsigned int n_ovf;          // hash build: occurrences of k-mers that occur more than once (entries of the overflow list)
+  unsigned int n_multi;        // hash build: k-mers that occur more than once
+  unsigned int occ_cursor;     // hash build: bump allocator of `occ`
+  unsigned int n_mid_lists;    // hash build: lists of 7..32 occurrences (sorted by a warp each)
   unsigned long long dpool_used;           // ints of the delta pool handed out
   // phase clocks of the pair kernel (SM cycles summed over warps; t_warp_max = busiest warp)
   unsigned long long t_dp, t_tb, t_prune, t_warp_sum, t_warp_max, t_pair_max;

@@ -46,6 +46,7 @@ struct ScanArgs {
   const Slot *table;
   uint64_t slot_mask;
   const uint64_t *occ;
+  const uint32_t *occupancy;      // bit i = slot i of the table is occupied (nullptr = none)
   int has_empty;
   // outputs
   Seed *recs;                     // [max_chunks * CHUNK]
@@ -62,7 +63,7 @@ constexpr int SCAN_WARPS = 4;
 
 __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
   __shared__ uint32_t s_pref[SCAN_WARPS][33];
-  __shared__ uint32_t s_start[SCAN_WARPS][32];
+  __shared__ unsigned long long s_pay[SCAN_WARPS][32];
   const int wib = threadIdx.x >> 5, l = lane_id();
   const uint32_t qs = blockIdx.x * SCAN_WARPS + wib;
   if (qs >= 2 * a.n_queries) return;
@@ -91,9 +92,17 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
     uint32_t off = t0 + l;
     bool valid = off < n_win;
     uint64_t key = (l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0) & kmask;
-    uint32_t slot, start = 0, lf = 0;
-    bool found = valid && table_find(a.table, a.slot_mask, key, slot, start, lf);
-    bool empty = found && (lf & EMPTY_FLAG);
+    // occupancy bitmap first (an L2 hit): a window whose home slot is free is absent from the block
+    const uint64_t hk = hash_key(key);
+    bool maybe = valid;
+    if (a.occupancy) {
+      const uint64_t h0 = hk & a.slot_mask;
+      maybe = valid && ((__ldg(a.occupancy + (h0 >> 5)) >> (h0 & 31)) & 1u);
+    }
+    uint32_t slot;
+    unsigned long long pay = 0;
+    bool found = maybe && table_find(a.table, a.slot_mask, hk, key, slot, pay);
+    bool empty = found && pay_empty(pay);
     if (found) c_found++;
     if (empty) {   // hi_hits: OIC/overlapInCore-Find_Overlaps.C:323-325, 359-366
       if (off == 0) screen |= 1;
@@ -104,7 +113,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
     }
     unsigned empty_mask = __ballot_sync(FULL, empty);
     if (a.has_empty && l == 0) a.tile_empty[a.qs_tile_base[qs] + (t0 >> 5)] = empty_mask;
-    uint32_t cnt = (found && !empty) ? (lf & LEN_MASK) : 0;
+    uint32_t cnt = (found && !empty) ? pay_len(pay) : 0;
     uint32_t incl = warp_incl_scan(cnt);
     uint32_t total = __shfl_sync(FULL, incl, 31);
     // previous query base / previous window Empty for every lane's window
@@ -115,7 +124,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
     if (total == 0) continue;
     __syncwarp();
     s_pref[wib][l] = incl - cnt;
-    s_start[wib][l] = start;
+    s_pay[wib][l] = pay;
     if (l == 31) s_pref[wib][32] = total;
     __syncwarp();
 
@@ -132,7 +141,8 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
           if (s_pref[wib][mid] <= r) lo = mid; else hi = mid;
         }
         owner = lo;
-        oc = __ldg(a.occ + s_start[wib][owner] + (r - s_pref[wib][owner]));
+        const unsigned long long op = s_pay[wib][owner];   // a k-mer seen once carries its occurrence in the slot
+        oc = pay_is_list(op) ? __ldg(a.occ + pay_start(op) + (r - s_pref[wib][owner])) : op;
       }
       uint32_t pbase = __shfl_sync(FULL, my_prev_base, owner);
       uint32_t pempty = __shfl_sync(FULL, my_prev_empty, owner);
