@@ -75,7 +75,7 @@ def load_library():
         return _lib
     if not os.path.exists(LIB_PATH):
         raise OicError("%s is missing: build it with `make -C canu_b200/csrc` (there is no CPU fallback)" % LIB_PATH)
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(os.environ.get("OIC_LIB", LIB_PATH))   # OIC_LIB: A/B builds of the same library during kernel work
     vp = C.c_void_p
     lib.oic_create.argtypes = [C.POINTER(Params), C.c_int, C.POINTER(vp)]
     lib.oic_destroy.argtypes = [vp]

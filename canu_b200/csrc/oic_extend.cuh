@@ -168,7 +168,10 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
 }
 
 constexpr int EXT_WARPS = 4;
-constexpr int TASK_BLOCKS_PER_SM = 4;   // resident blocks of the lean task kernel (5 -> 96 registers, small spills, measured slower)
+#ifndef OIC_TASK_BLOCKS
+#define OIC_TASK_BLOCKS 4
+#endif
+constexpr int TASK_BLOCKS_PER_SM = OIC_TASK_BLOCKS;   // resident blocks of the lean task kernel (5 -> 96 registers, small spills, measured slower)
 
 struct PairCtx {   // the strings and IDs of one pair
   const uint64_t *S, *T;
@@ -463,8 +466,15 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, LEAN ? TASK_BLOCKS_PER_SM : 4)
  * results of seeds pruned before their turn are discarded (speculation waste).  Any unusable result sends the pair to
  * the retry list (full serial loop with worst-case scratch); nothing of the pair has been output or counted until here.
  */
+constexpr int COMMIT_DCAP = 1024;   // longest delta list indexed in shared memory (longer ones are walked serially)
+
 __global__ void __launch_bounds__(128) k_commit_pairs(ExtArgs a) {
-  const int l = lane_id();
+  // Lies_On_Alignment (Process_String_Overlaps.C:307-326) walks the delta list until the alignment passes the seed's start
+  // and compares diagonals there.  The walk is the same for every seed, so it is done once per alignment as a warp scan:
+  // s_pos[i] = query position at which delta i is tested (strictly increasing), s_diag[i] = diagonal at that test;
+  // each seed then finds its delta by binary search.
+  __shared__ int32_t s_pos[4][COMMIT_DCAP], s_diag[4][COMMIT_DCAP + 1];
+  const int l = lane_id(), wib = threadIdx.x >> 5;
   const uint32_t n_pend = a.ctr->n_pend;
   while (true) {
     uint32_t ti = 0;
@@ -496,12 +506,42 @@ __global__ void __launch_bounds__(128) k_commit_pairs(ExtArgs a) {
       accept_overlap(a, r.kind, r.s_lo, r.s_hi, r.t_lo, r.t_hi, r.errors, r.dlen, distinct, distinct_ct);
       const bool prune = (r.kind == 3 || a.partial);
       const int32_t *delta = a.dpool + r.delta_off;
+      const bool indexed = prune && r.dlen <= COMMIT_DCAP;
+      if (indexed) {
+        int pos0 = r.s_lo, diag0 = r.t_lo - r.s_lo;   // running values in front of the current chunk of 32 deltas
+        for (int i0 = 0; i0 < r.dlen; i0 += 32) {
+          const int i = i0 + l;
+          const int dl = (i < r.dlen) ? delta[i] : 0;
+          const uint32_t ax = (uint32_t)iabs(dl) + (dl > 0 ? 1u : 0u);            // what delta i adds to the position in total
+          const uint32_t pq = (dl > 0 ? 0x10000u : 0u) | (dl < 0 ? 1u : 0u);      // counts of positive / negative deltas
+          const uint32_t ix = warp_incl_scan(ax), ipq = warp_incl_scan(pq);
+          const uint32_t epq = ipq - pq;                                          // exclusive
+          if (i < r.dlen) {
+            s_pos[wib][i] = pos0 + (int)(ix - (dl > 0 ? 1u : 0u));                // tested before the +1 of a positive delta
+            s_diag[wib][i] = diag0 + (int)(epq & 0xffffu) - (int)(epq >> 16);
+          }
+          const uint32_t tx = __shfl_sync(FULL, ix, 31), tpq = __shfl_sync(FULL, ipq, 31);
+          pos0 += (int)tx;
+          diag0 += (int)(tpq & 0xffffu) - (int)(tpq >> 16);
+        }
+        if (l == 0) s_diag[wib][r.dlen] = diag0;
+        __syncwarp();
+      }
       for (int i = l; i < n; i += 32) {
         if (!alive[i]) continue;
         const Seed nd = seeds[i];
-        if (i == li || (prune && r.s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= r.s_hi + SHIFT_SLACK &&
-                        lies_on_alignment(nd.start, nd.offset, r.s_lo, r.t_lo, delta, r.dlen)))
-          alive[i] = 0;
+        bool remove = (i == li);
+        if (!remove && prune && r.s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= r.s_hi + SHIFT_SLACK) {
+          if (indexed) {
+            int lo = 0, hi = r.dlen;                   // first delta whose test position is beyond the seed's start
+            while (lo < hi) {
+              const int mid = (lo + hi) >> 1;
+              if (nd.start < s_pos[wib][mid]) hi = mid; else lo = mid + 1;
+            }
+            remove = iabs((nd.offset - nd.start) - s_diag[wib][lo]) <= SHIFT_SLACK;
+          } else remove = lies_on_alignment(nd.start, nd.offset, r.s_lo, r.t_lo, delta, r.dlen);
+        }
+        if (remove) alive[i] = 0;
       }
       __syncwarp();
     }

@@ -11,9 +11,13 @@
 #ifndef OIC_EXTEND_LEAN_CUH
 #define OIC_EXTEND_LEAN_CUH
 
+#ifndef LEAN_U
+#define LEAN_U 2   /* chunks of 32 diagonals in flight together */
+#endif
 namespace oic {
 
-constexpr int LSTRIDE = SW + 72;   // ints per live row: 2 margin + SW + idle-lane slack of the last chunk pair
+constexpr int LU = LEAN_U;
+constexpr int LSTRIDE = SW + 8 + 32 * LU;   // ints per live row: 2 margin + SW + idle-lane slack of the last chunk group
 constexpr int LEAN_WIDE = -2;
 constexpr int LEAN_IDLE = (int)0x80000000;
 
@@ -99,10 +103,10 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     int my_mx = -1;
 
 #pragma unroll 1
-    for (int c0 = 0; c0 < nch; c0 += 2) {
-      int r[2], r0[2], cap[2], dd[2];
+    for (int c0 = 0; c0 < nch; c0 += LU) {
+      int r[LU], r0[LU], cap[LU], dd[LU];
 #pragma unroll
-      for (int u = 0; u < 2; u++) {                      // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
+      for (int u = 0; u < LU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
         const int c = c0 + u, i = 32 * c + l, d = left + i;
         const int g0 = pp[32 * c] + 1, gm = pp[32 * c - 1], gp = pp[32 * c + 1] + 1;
         const int x = imax(g0, gm);
@@ -115,7 +119,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       }
       int more = 0;                                      // bit u: the slide of chunk u goes on
 #pragma unroll
-      for (int u = 0; u < 2; u++) {                      // first 16 bases of every slide, loads back to back
+      for (int u = 0; u < LU; u++) {                     // first 16 bases of every slide, loads back to back
         r[u] = r0[u];
         if (r0[u] < cap[u]) {
           const int adv = lean_step(Ap, aph + r0[u], Tp, tph + r0[u] + dd[u]);
@@ -125,7 +129,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       }
       while (__any_sync(FULL, more != 0)) {              // slides longer than 16 bases (the cells on the alignment path)
 #pragma unroll
-        for (int u = 0; u < 2; u++) {
+        for (int u = 0; u < LU; u++) {
           if (more & (1 << u)) {
             const int adv = lean_step(Ap, aph + r[u], Tp, tph + r[u] + dd[u]);
             r[u] += adv;
@@ -133,32 +137,42 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
           }
         }
       }
-      unsigned em[2], wc[2];
+      unsigned em[LU], wc[LU], any_em = 0;
 #pragma unroll
-      for (int u = 0; u < 2; u++) {
+      for (int u = 0; u < LU; u++) {
         const int c = c0 + u, i = 32 * c + l;
         const bool act = i < width;
         r[u] = imin(r[u], cap[u]);
         if (act) { cp[32 * c] = r[u]; stg_s32(hp + 32 * c, r[u]); }
         em[u] = __ballot_sync(FULL, act && r[u] == cap[u]);            // reached the end of A (r == m) or of T (r + d == n)
+        any_em |= em[u];
         wc[u] = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
         const int mx = __reduce_max_sync(FULL, r[u]);
         const unsigned pm = __ballot_sync(FULL, r[u] == mx);
         if (l == c) { my_ok = ok; my_mx = mx; my_pm = pm; }
       }
-      if (em[0] | em[1]) {                               // a cell reached the end of A or T: the row stops at the first one
-        const int u = em[0] ? 0 : 1;
-        const int first = __ffs(em[u]) - 1;
-        if (u == 1) wsum += wc[0];
-        if (l <= first) wsum += wc[u];
-        ncell += 32 * (c0 + u) + first + 1;
-        d_end = left + 32 * (c0 + u) + first;
-        r_end = __shfl_sync(FULL, u ? r[1] : r[0], first);
+      if (any_em) {                                      // a cell reached the end of A or T: the row stops at the first one
+        int uu = 0;
+#pragma unroll
+        for (int u = LU - 1; u >= 0; u--) if (em[u]) uu = u;
+        unsigned emu = 0, wcu = 0;
+        int ru = 0;
+#pragma unroll
+        for (int u = 0; u < LU; u++) {
+          if (u < uu) wsum += wc[u];
+          if (u == uu) { emu = em[u]; wcu = wc[u]; ru = r[u]; }
+        }
+        const int first = __ffs(emu) - 1;
+        if (l <= first) wsum += wcu;
+        ncell += 32 * (c0 + uu) + first + 1;
+        d_end = left + 32 * (c0 + uu) + first;
+        r_end = __shfl_sync(FULL, ru, first);
         ended = true;
         break;
       }
-      wsum += wc[0] + wc[1];
+#pragma unroll
+      for (int u = 0; u < LU; u++) wsum += wc[u];
     }
     int32_t *hist = ws.vals + off;
     {   // direction words of the row: two per chunk, right behind the values (and their 2-int margin)
