@@ -204,6 +204,8 @@ def main():
         for ptr, nbytes in buffers_of(meta):
             t = torch.as_tensor(DevView(ptr, nbytes), device="cuda")
             dist.broadcast(t, 0)
+        # the library works on its own stream: the broadcast (NCCL's stream) must have landed before it reads the block
+        torch.cuda.synchronize()
         if rank != 0:
             ov.hash_block_commit(meta)
 
@@ -213,23 +215,33 @@ def main():
         sizes = [meta.table_slots * 16, (meta.n_occ + 32) * 8, (meta.n_strings + 8) & ~3]
         return [(bufs[i][0], sizes[i]) for i in range(3)]
 
+    trace = os.environ.get("OIC_BENCH_TRACE")
+
     def job(load):
         """one step; returns number of overlap records of this rank"""
+        t = [time.perf_counter()]
         if load:
             ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
         ov.clear_overlaps()
+        t.append(time.perf_counter())
         if world == 1:
             ov.build_hash_index(n_q + 1, n_q + n_h)
         else:
             if rank == 0:
                 ov.build_hash_index(n_q + 1, n_q + n_h)
+            t.append(time.perf_counter())
             replicate_hash_block()
+        t.append(time.perf_counter())
         ov.process_overlaps(1, n_q)
         n = ov.num_overlaps()
+        t.append(time.perf_counter())
         if load:
             rec = ov.overlaps()   # records back in a host buffer
             if world > 1:         # per-GPU records gathered on the host side, in store IDs
                 shard.gather_records(rj.to_global(rec), dist, device="cuda")
+        t.append(time.perf_counter())
+        if trace:
+            sys.stderr.write("[rank %d] step phases ms: %s\n" % (rank, " ".join("%.1f" % (1000 * (b - a_)) for a_, b in zip(t, t[1:]))))
         return n
 
     def barrier():
