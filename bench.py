@@ -321,22 +321,38 @@ def main():
     share = 1.0 - (d["n_pairs"] / max(1, d["ext_calls"]))
     i_tasks = i_ext * share
     tasks_gops = i_tasks / (ms_tasks * 1e-3) / 1e9 if ms_tasks > 0 else 0.0
-    traffic = None
-    try:   # dram read+write bytes of one launch from the committed `ncu --set full` capture of this kernel (profiles/)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_extend_tasks_summary.json")))["dram_bytes_per_launch"]
+    # dram read+write bytes per launch and pipe utilisation: from the committed summary of the newest `ncu --set full`
+    # capture of this command (profiles/*_kernels.json, written by tools/ncu_summary.py)
+    traffic, ncu_k, ncu_src = None, {}, None
+    try:
+        import glob
+        ncu_src = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")))[-1]
+        for k in json.load(open(ncu_src))["kernels"]:
+            ncu_k.setdefault(k["kernel"], k)
+        traffic = ncu_k["k_extend_tasks<1>"]["dram_bytes_per_launch"]
     except Exception:
         pass
+
+    def ncu_of(name):
+        k = ncu_k.get(name)
+        if not k:
+            return None
+        return {x: k.get(x) for x in ("ms", "dram_bytes_per_launch", "dram_GBps", "issue_active_pct", "alu_pipe_pct", "lsu_pipe_pct",
+                                      "warps_active_pct", "l1_hit_pct", "l2_hit_pct", "sectors_per_ld_request")}
     roof = {"kernel": "k_extend_tasks<true>", "bound": "int32", "achieved": tasks_gops, "peak": alu_peak, "unit": "Gop/s",
             "frac": tasks_gops / alu_peak if alu_peak else None, "traffic": traffic, "peak_source": int_src,
             "algorithmic_ops_per_launch": i_tasks, "ms_per_launch": ms_tasks,
             "formula": "6*C + 4*W (C = DP cells, W = 16-base compare words) x share of extension calls run by this kernel; "
                        "not an HBM- or tensor-bound kernel: rows live in shared memory, sequences in L1/L2",
+            "ncu": ncu_of("k_extend_tasks<1>"), "ncu_source": os.path.relpath(ncu_src, ROOT) if ncu_src else None,
             "hbm_side": {"kernel": "k_seed_scan", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak, "unit": "GB/s",
                          "frac": scan_gbs / hbm_peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": b_scan,
-                         "ms_per_launch": ms_scan,
+                         "ms_per_launch": ms_scan, "traffic": (ncu_k.get("k_seed_scan") or {}).get("dram_bytes_per_launch"),
+                         "ncu": ncu_of("k_seed_scan"),
                          "formula": "0.25*N_query_bases + 4*N_windows + 8*N_found + 8*N_refs (SURVEY.md 8(d)), rank 0's block"}}
     stages = {"build": {"ms": ms_build, "algorithmic_GBps": build_gbs, "frac_hbm": build_gbs / hbm_peak,
-                        "formula": "0.25*N_hash_bases + 16*N_inserts; whole build (insert+scan+fill+sort kernels)"},
+                        "formula": "0.25*N_hash_bases + 16*N_inserts; whole build (table init + insert + list kernels + occupancy bitmap)",
+                        "ncu_k_insert": ncu_of("k_insert")},
               "seed_scan": {"ms": ms_scan, "algorithmic_GBps": scan_gbs, "frac_hbm": scan_gbs / hbm_peak},
               "group_runs": {"ms": ms_group},
               "extend": {"ms": ms_ext, "ms_first_extensions": ms_first, "ms_speculative_tasks": ms_tasks, "ms_commit": ms_commit,

@@ -19,6 +19,6 @@ print("extend", d["stages"]["extend"]); print("roofline", d["roofline"]); print(
 PY
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_$TAG.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu > $OUT/ncu_launches_$TAG.log 2>&1 || { tail -5 $OUT/ncu_launches_$TAG.log; exit 3; }
-ncu --set full --clock-control none --import-source on -k regex:'k_insert|k_fill|k_sort_small|k_seed_scan|k_process_pairs|k_extend_tasks|k_commit_pairs|k_group_runs|k_run_length' \
-    --launch-skip 9 --launch-count 9 -f -o $OUT/full_$TAG python bench.py --steps 1 --warmup 1 --no-cpu > $OUT/ncu_full_$TAG.log 2>&1 || { tail -5 $OUT/ncu_full_$TAG.log; exit 4; }
+ncu --set full --clock-control none --import-source on -k regex:'k_table_init|k_insert|k_multi|k_occupancy|k_seed_scan|k_replay|k_process_pairs|k_extend_tasks|k_commit_pairs' \
+    --launch-skip 14 --launch-count 14 -f -o $OUT/full_$TAG python bench.py --steps 1 --warmup 1 --no-cpu > $OUT/ncu_full_$TAG.log 2>&1 || { tail -5 $OUT/ncu_full_$TAG.log; exit 4; }
 ls -la $OUT/full_$TAG.ncu-rep
