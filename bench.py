@@ -34,21 +34,41 @@ ERATE = "0.06"
 READ_ERR = 0.02
 LEN_MIN, LEN_MAX = 5000, 15000
 SEED = 1003
+MODE = "blocks"                # "blocks": disjoint query block(s) vs one hash block; "self": -h 1-N -r 1-N on one read set
+PARTIAL, MIN_OLAP, SUB_ONLY, HASH_BITS, REF_SCALE_MBP = 0, 500, False, 23, 20
+
+# BASELINE.json's named shapes.  The driver's bench line is c3 (the config the metric is quoted on); the others are run by
+# hand (`--workload`) for the per-shape table of DESIGN.md section 7 and are parity-test cases at reduced size in tests/.
+WORKLOADS = {
+    "c1": dict(desc="c1: synthetic 4.6 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, one hash block vs one "
+                    "query block (the same 13.8 k reads: -h 1-N -r 1-N)",
+               GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.06", READ_ERR=0.02, SEED=1001, MODE="self", REF_SCALE_MBP=0.3),
+    "c2": dict(desc="c2: synthetic 4.6 Mbp genome, 30x raw-noise reads 5-15 kb, 6% per read = 12% pairwise, k=22, --maxerate 0.15 "
+                    "(wide-band extension), -h 1-N -r 1-N",
+               GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.15", READ_ERR=0.06, SEED=1002, MODE="self", REF_SCALE_MBP=0.1),
+    "c3": dict(desc="c3: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, "
+                    "100 Mbp hash block (1x) broadcast, one 100 Mbp query block per GPU"),
+    "c4": dict(desc="c4: synthetic 100 Mbp genome, 150 bp reads (substitutions only, 0.5%), -G --minlength 40, k=22, --maxerate 0.06, "
+                    "100 Mbp hash block (667 k reads, 1x) vs one 100 Mbp query block per GPU",
+               LEN_MIN=150, LEN_MAX=150, READ_ERR=0.005, SUB_ONLY=True, PARTIAL=1, MIN_OLAP=40, HASH_BITS=24, SEED=1004, REF_SCALE_MBP=5),
+}
 
 
 def params_for(n_hash_reads, n_total, threads=1):
     import helpers as H
-    return H.default_params(kmer_len=K, max_erate=H.strtof(ERATE), min_olap_len=500, hash_bits=23, hash_load=0.75,
-                            max_hash_strings=n_hash_reads, max_hash_data_len=2 * BLOCK_BASES, num_threads=threads,
-                            bgn_hash_id=n_total - n_hash_reads + 1, end_hash_id=n_total, bgn_ref_id=1,
-                            end_ref_id=n_total - n_hash_reads)
+    common = dict(kmer_len=K, max_erate=H.strtof(ERATE), min_olap_len=MIN_OLAP, partial=PARTIAL, hash_bits=HASH_BITS, hash_load=0.75,
+                  max_hash_strings=n_hash_reads, max_hash_data_len=2 * BLOCK_BASES, num_threads=threads)
+    if MODE == "self":
+        return H.default_params(bgn_hash_id=1, end_hash_id=n_total, bgn_ref_id=1, end_ref_id=n_total, **common)
+    return H.default_params(bgn_hash_id=n_total - n_hash_reads + 1, end_hash_id=n_total, bgn_ref_id=1,
+                            end_ref_id=n_total - n_hash_reads, **common)
 
 
 def gen_blocks(genome_len, n_blocks, block_bases, seed):
     """reads for n_blocks blocks of ~block_bases each, sampled from one genome (each block = block_bases/genome coverage)"""
     import helpers as H
     cov = n_blocks * block_bases / genome_len
-    return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed)
+    return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed, sub_only=SUB_ONLY)
 
 
 class ClockSampler(threading.Thread):
@@ -79,21 +99,29 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def reference_leg(steps, warmup, scale_mbp=20, cores=None):
+def reference_leg(steps, warmup, scale_mbp=None, cores=None):
     """The reference's own CPU overlapInCore (oracle/_ref, built from /root/reference/src by oracle/build_ref.sh) on a
     bounded sample of the same workload: same read/error model and the same 1x-hash-block vs 1x-query-block density,
-    on a genome of `scale_mbp` Mbp instead of 100 (so one step ends in tens of seconds)."""
+    on a genome of `scale_mbp` Mbp (default: the workload's REF_SCALE_MBP) instead of the full one (so one step ends in tens of seconds)."""
     import helpers as H
     cores = cores or os.cpu_count()
-    g = scale_mbp * 1_000_000
-    reads = gen_blocks(g, 2, g, SEED + 7)
+    scale_mbp = REF_SCALE_MBP if scale_mbp is None else scale_mbp
+    g = int(scale_mbp * 1_000_000)
     from canu_b200 import shard
-    (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
-    qbases = int(reads.lengths[qb - 1:qe].sum())
-    P = params_for(he - hb + 1, reads.n, threads=cores)
-    sample = ("reference overlapInCore -t %d, genome %d Mbp: hash block %d reads (%.1f Mbp, 1x) x query block %d reads (%.1f Mbp, 1x), "
-              "same read model/flags as the 100 Mbp job; wall time of the process (store open + hash build + search + .ovb)"
-              % (cores, scale_mbp, he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, qe - qb + 1, qbases / 1e6))
+    if MODE == "self":
+        reads = gen_blocks(g, 1, int(g * BLOCK_BASES / GENOME), SEED + 7)
+        qbases = int(reads.lengths.sum())
+        P = params_for(reads.n, reads.n, threads=cores)
+        sample = ("reference overlapInCore -t %d, genome %.1f Mbp at the same coverage: %d reads (%.1f Mbp) against themselves (-h 1-N -r 1-N), "
+                  "same read model/flags; wall time of the process" % (cores, scale_mbp, reads.n, qbases / 1e6))
+    else:
+        reads = gen_blocks(g, 2, g, SEED + 7)
+        (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
+        qbases = int(reads.lengths[qb - 1:qe].sum())
+        P = params_for(he - hb + 1, reads.n, threads=cores)
+        sample = ("reference overlapInCore -t %d, genome %.1f Mbp: hash block %d reads (%.1f Mbp, 1x) x query block %d reads (%.1f Mbp, 1x), "
+                  "same read model/flags as the 100 Mbp job; wall time of the process (store open + hash build + search + .ovb)"
+                  % (cores, scale_mbp, he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, qe - qb + 1, qbases / 1e6))
     kind = "reference" if H.have_ref() else "port"
     times, n_ovl = [], 0
     with tempfile.TemporaryDirectory() as wd:
@@ -129,14 +157,20 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink genome and blocks (debug only; 1.0 = the named config)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json shape; c3 is the bench line")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
+    wl = WORKLOADS[a.workload]
+    globals().update({k: v for k, v in wl.items() if k != "desc"})
+    if MODE == "self" and world > 1:
+        raise SystemExit("workload %s is a single-GPU shape (one hash block vs one query block)" % a.workload)
     metric = "overlapInCore query Mbp/sec (+overlaps/sec), 30x 100 Mbp genome, one hash block x one query block per GPU per step"
-    config = {"workload": "c3: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, "
-                          "100 Mbp hash block (1x) broadcast, one 100 Mbp query block per GPU",
+    if a.workload != "c3":
+        metric = "overlapInCore query Mbp/sec (+overlaps/sec), workload %s" % a.workload
+    config = {"workload": wl["desc"],
               "hash_block_mbp": BLOCK_BASES * a.scale / 1e6, "query_block_mbp_per_gpu": BLOCK_BASES * a.scale / 1e6,
               "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (world, " by NCCL broadcast" if world > 1 else ""),
               "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed"}
@@ -166,22 +200,35 @@ def main():
 
     genome = int(GENOME * a.scale)
     block = int(BLOCK_BASES * a.scale)
-    # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
-    reads = gen_blocks(genome, world + 1, block, SEED)
     from canu_b200 import shard
-    blocks = shard.split_blocks(reads.n, world + 1)
-    rj = shard.RankJob(blocks, rank)
-    hb, he, qb, qe, n_q, n_h = rj.hb, rj.he, rj.qb, rj.qe, rj.n_q, rj.n_h
-    q_bases_rank = int(reads.lengths[qb - 1:qe].sum())
-    q_bases_all = int(reads.lengths[:hb - 1].sum())
-    P = params_for(he - hb + 1, reads.n)
-
-    # this rank needs its query block and the hash block, gathered into one pinned host buffer in a local ID space
-    # (queries 1..n_q, hash n_q+1..n_q+n_h: query ID < hash ID, as in the sweep); canu_b200/shard.py maps records back
-    total = int(reads.lengths[rj.ids - 1].sum())
-    pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
-    _, offs, lens = rj.select(reads.bases, reads.offsets[:-1], reads.lengths, out=pinned.numpy())
-    LP = rj.local_params(P)
+    if MODE == "self":
+        # one read set against itself (-h 1-N -r 1-N): pairs with query ID < hash ID
+        reads = gen_blocks(genome, 1, block, SEED)
+        n_q, n_h = reads.n, reads.n
+        q_bases_rank = q_bases_all = int(reads.lengths.sum())
+        LP = params_for(reads.n, reads.n)
+        total = q_bases_all
+        pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
+        pinned.numpy()[:] = reads.bases[:total]
+        offs, lens = reads.offsets[:-1].astype(np.uint64), reads.lengths.astype(np.uint32)
+        rj = None
+        hash_range, query_range = (1, reads.n), (1, reads.n)
+    else:
+        # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
+        reads = gen_blocks(genome, world + 1, block, SEED)
+        blocks = shard.split_blocks(reads.n, world + 1)
+        rj = shard.RankJob(blocks, rank)
+        hb, he, qb, qe, n_q, n_h = rj.hb, rj.he, rj.qb, rj.qe, rj.n_q, rj.n_h
+        q_bases_rank = int(reads.lengths[qb - 1:qe].sum())
+        q_bases_all = int(reads.lengths[:hb - 1].sum())
+        P = params_for(he - hb + 1, reads.n)
+        # this rank needs its query block and the hash block, gathered into one pinned host buffer in a local ID space
+        # (queries 1..n_q, hash n_q+1..n_q+n_h: query ID < hash ID, as in the sweep); canu_b200/shard.py maps records back
+        total = int(reads.lengths[rj.ids - 1].sum())
+        pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
+        _, offs, lens = rj.select(reads.bases, reads.offsets[:-1], reads.lengths, out=pinned.numpy())
+        LP = rj.local_params(P)
+        hash_range, query_range = (n_q + 1, n_q + n_h), (1, n_q)
 
     ov = api.Overlapper(LP, device=local)
 
@@ -225,14 +272,14 @@ def main():
         ov.clear_overlaps()
         t.append(time.perf_counter())
         if world == 1:
-            ov.build_hash_index(n_q + 1, n_q + n_h)
+            ov.build_hash_index(*hash_range)
         else:
             if rank == 0:
-                ov.build_hash_index(n_q + 1, n_q + n_h)
+                ov.build_hash_index(*hash_range)
             t.append(time.perf_counter())
             replicate_hash_block()
         t.append(time.perf_counter())
-        ov.process_overlaps(1, n_q)
+        ov.process_overlaps(*query_range)
         n = ov.num_overlaps()
         t.append(time.perf_counter())
         if load:
@@ -355,7 +402,7 @@ def main():
                         "ncu_k_insert": ncu_of("k_insert")},
               "seed_scan": {"ms": ms_scan, "algorithmic_GBps": scan_gbs, "frac_hbm": scan_gbs / hbm_peak},
               "group_runs": {"ms": ms_group},
-              "extend": {"ms": ms_ext, "ms_first_extensions": ms_first, "ms_speculative_tasks": ms_tasks, "ms_commit": ms_commit,
+              "extend": {"ms": ms_ext, "ms_first_extensions": ms_first, "ms_speculative_tasks": ms_tasks, "ms_commit": ms_commit, "ms_retry": tm["ms_ext_retry"] / steps,
                          "int32_Gops": ext_gops, "formula": "6*C + 4*W (cells, 16-base words)",
                          "frac_int32": ext_gops / alu_peak if alu_peak else None}}
     value = q_bases_all / 1e6 * steps / dt

@@ -53,7 +53,7 @@ class Timings(C.Structure):
     _fields_ = [("ms_pack", C.c_float), ("ms_build", C.c_float), ("ms_scan", C.c_float), ("ms_group", C.c_float),
                 ("ms_extend", C.c_float), ("ms_total_search", C.c_float), ("launches", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("ms_ext_first", C.c_float), ("ms_ext_tasks", C.c_float), ("ms_ext_commit", C.c_float), ("pad", C.c_float)]
+                ("ms_ext_first", C.c_float), ("ms_ext_tasks", C.c_float), ("ms_ext_commit", C.c_float), ("ms_ext_retry", C.c_float)]
 
 
 class HashMeta(C.Structure):

@@ -128,6 +128,7 @@ struct oic_ctx {
   bool hash_ready = false;
   oic_hash_meta_t hb = {};
   DevBuf d_table, d_occ, d_str_flags, d_str_use, d_filter, d_ovf_slot, d_ovf_occ, d_multi_list, d_first_occ, d_cnt, d_mid_list, d_blk, d_big_list, d_occ_tmp, d_hist;
+  unsigned long long mem_avail = 0;   // device memory the pair stage may plan with (free + what it already holds)
   bool have_occupancy = false;   // occupancy bitmap of the current hash block is valid
 
   // search buffers
@@ -339,6 +340,7 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
       (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev_k[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[1])) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev_k[2])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[3])) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev_k[4])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[5])) != cudaSuccess ||
       (e = c->d_ctr.ensure(sizeof(DevCounters))) != cudaSuccess) {
     g_create_error = cudaGetErrorString(e);
     delete c;
@@ -695,7 +697,15 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
       const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
-      const unsigned long long budget = (12ull << 30) / 4 / n_warps;
+      // memory budgets follow the device: a B200 has 180 GB, the c3 job needs 8 GB of history, the wide-band c2 job 51 GB
+      if (c->mem_avail == 0) {   // asked once per context: cudaMemGetInfo costs about a millisecond
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        c->mem_avail = (unsigned long long)free_b + c->d_vals.cap + c->d_dpool.cap;
+      }
+      const unsigned long long avail = c->mem_avail;
+      const unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::max<unsigned long long>(12ull << 30, avail * 45 / 100));
+      const unsigned long long budget = vals_bytes / 4 / n_warps;
       const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
       if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
       // longest-processing-time-first order
@@ -725,7 +735,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
       // speculative second round (oic_extend.cuh): state per pair, one result slot per seed, a pool for the delta lists
-      const unsigned long long dpool_cap = std::min<unsigned long long>(1ull << 28, (unsigned long long)n_runs * 64 + (16ull << 20));
+      const unsigned long long dpool_cap = std::min<unsigned long long>(std::max<unsigned long long>(1ull << 28, avail * 15 / 100 / 4),
+                                                                        (unsigned long long)n_runs * 512 + (16ull << 20));
       CK(c->d_pstate.ensure((size_t)n_pairs * sizeof(PairState)));
       CK(c->d_pend.ensure((size_t)n_pairs * 4 + 4));
       CK(c->d_tasks.ensure((size_t)n_runs * sizeof(uint2) + 8));
@@ -766,7 +777,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         const uint32_t nr = hc.n_retry;
         k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
         const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
-        const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, (24ull << 30) / 4 / big / EXT_WARPS));
+        const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, std::max<unsigned long long>(24ull << 30, vals_bytes) / 4 / big / EXT_WARPS));
+        cudaEventRecord(c->ev_k[4], c->stream);
         DevBuf keep_retry;
         CK(keep_retry.ensure((size_t)nr * 4));
         CK(cudaMemcpyAsync(keep_retry.p, c->d_retry.p, (size_t)nr * 4, cudaMemcpyDeviceToDevice, c->stream));
@@ -777,8 +789,10 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         CK(cudaMemsetAsync(&c->d_ctr.as<DevCounters>()->n_retry, 0, 4, c->stream));
         k_process_pairs<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea);
         c->tm.launches += 2;
+        cudaEventRecord(c->ev_k[5], c->stream);
         int r2 = read_counters(c, hc);
         keep_retry.release();
+        { float ms = 0; if (cudaEventElapsedTime(&ms, c->ev_k[4], c->ev_k[5]) == cudaSuccess) c->tm.ms_ext_retry += ms; }
         if (r2) return OIC_ERR_CUDA;
         CK(cudaGetLastError());
         if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch (internal)");

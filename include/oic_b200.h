@@ -67,7 +67,7 @@ typedef struct {
   uint64_t launches;             /* kernels launched by this context since the last reset */
   uint64_t h2d_bytes, d2h_bytes; /* bytes moved across PCIe by this context since reset   */
   /* inside ms_extend: first extension of every pair / speculative extension tasks (the dominant kernel) / wide reruns + commit */
-  float    ms_ext_first, ms_ext_tasks, ms_ext_commit, pad;
+  float    ms_ext_first, ms_ext_tasks, ms_ext_commit, ms_ext_retry;   /* retry = pairs rerun serially with worst-case scratch */
 } oic_timings_t;
 
 /* One overlap as written to the .ovb file: 6 x uint32 = a_iid, b_iid, dat0.hi, dat0.lo, dat1.hi, dat1.lo
