@@ -157,6 +157,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink genome and blocks (debug only; 1.0 = the named config)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-input", default="2bit", choices=["2bit", "ascii"],
+                    help="host buffers of the end-to-end leg: the gkpStore's 2-bit read encoding (oic_load_reads_2bit) or ASCII (oic_load_reads)")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json shape; c3 is the bench line")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -230,6 +232,13 @@ def main():
         LP = rj.local_params(P)
         hash_range, query_range = (n_q + 1, n_q + n_h), (1, n_q)
 
+    # host buffers of the end-to-end leg: the reads as the gkpStore holds them (2SEQ chunks: 4 bases per byte), pinned
+    lens64 = np.asarray(lens, dtype=np.int64)
+    pinned2 = torch.empty(int(((lens64 + 3) // 4).sum()) + 8, dtype=torch.uint8).pin_memory()
+    _, boffs = H.encode_2bit(pinned.numpy(), offs, lens, out=pinned2.numpy())
+    config["e2e_input"] = ("gkpStore 2-bit encoded reads (2SEQ chunks, ST/gkStoreEncode.C) in pinned host memory -> oic_load_reads_2bit"
+                           if a.e2e_input == "2bit" else "ASCII reads in pinned host memory -> oic_load_reads")
+
     ov = api.Overlapper(LP, device=local)
 
     class DevView:
@@ -268,7 +277,10 @@ def main():
         """one step; returns number of overlap records of this rank"""
         t = [time.perf_counter()]
         if load:
-            ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
+            if a.e2e_input == "2bit":
+                ov.load_reads_2bit(pinned2.data_ptr(), boffs, lens, first_id=1)
+            else:
+                ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
         ov.clear_overlaps()
         t.append(time.perf_counter())
         if world == 1:

@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "liboic_b200.so")
 
 ABI_SYMBOLS = [
-    "oic_create", "oic_destroy", "oic_last_error", "oic_load_reads", "oic_set_skip_kmers", "oic_build_hash_index",
+    "oic_create", "oic_destroy", "oic_last_error", "oic_load_reads", "oic_load_reads_2bit", "oic_set_skip_kmers", "oic_build_hash_index",
     "oic_process_overlaps", "oic_overlap_driver", "oic_last_processed_ref", "oic_num_overlaps", "oic_copy_overlaps",
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
@@ -82,6 +82,7 @@ def load_library():
     lib.oic_last_error.restype = C.c_char_p
     lib.oic_last_error.argtypes = [vp]
     lib.oic_load_reads.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
+    lib.oic_load_reads_2bit.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.oic_set_skip_kmers.argtypes = [vp, C.c_uint64, C.c_char_p]
     lib.oic_build_hash_index.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     lib.oic_process_overlaps.argtypes = [vp, C.c_uint32, C.c_uint32]
@@ -121,6 +122,35 @@ def default_params(**kw):
     if d["max_erate"] > 0.06:
         d["use_hopeless_check"] = 0
     return d
+
+
+def encode_2bit(bases, offsets, lengths):
+    """ASCII reads -> the gkpStore 2-bit encoding (ST/gkStoreEncode.C:45-78): 4 bases per byte, first base in bits 7-6,
+    every read starting on a byte boundary.  Returns (packed uint8, byte_offsets uint64[n]).  Raises on a non-ACGT base
+    (the store keeps such reads unencoded)."""
+    bases = np.asarray(bases, dtype=np.uint8)
+    lengths = np.asarray(lengths, dtype=np.int64)
+    offsets = np.asarray(offsets, dtype=np.int64)[:len(lengths)]
+    lut = np.full(256, 255, dtype=np.uint8)
+    for ch, v in (("a", 0), ("c", 1), ("g", 2), ("t", 3)):
+        lut[ord(ch)] = lut[ord(ch.upper())] = v
+    nbytes = (lengths + 3) // 4
+    boff = np.zeros(len(lengths), dtype=np.uint64)
+    if len(lengths) > 1:
+        np.cumsum(nbytes[:-1], out=boff[1:])
+    total = int(nbytes.sum())
+    # position of every base in a 4-bases-per-byte padded layout
+    padded = np.zeros(total * 4, dtype=np.uint8)
+    read_of_base = np.repeat(np.arange(len(lengths)), lengths)
+    within = np.arange(int(lengths.sum()), dtype=np.int64) - np.repeat(np.cumsum(lengths) - lengths, lengths)
+    src = np.repeat(offsets, lengths) + within
+    codes = lut[bases[src]]
+    if (codes == 255).any():
+        raise OicError("encode_2bit: non-ACGT base")
+    padded[boff.astype(np.int64)[read_of_base] * 4 + within] = codes
+    q = padded.reshape(-1, 4)
+    packed = (q[:, 0] << 6) | (q[:, 1] << 4) | (q[:, 2] << 2) | q[:, 3]
+    return packed.astype(np.uint8), boff
 
 
 RECORD_DT = np.dtype((np.uint32, 6))
@@ -189,6 +219,23 @@ class Overlapper:
         lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
         self._check(self.lib.oic_load_reads(self._h, first_id, len(lengths), offsets.ctypes.data, lengths.ctypes.data,
                                             bases_ptr, None, None), "oic_load_reads")
+        self.n_reads = len(lengths)
+        self.first_id = first_id
+
+    def load_reads_2bit(self, packed, byte_offsets, lengths, first_id=1, hash_ok=None, ref_ok=None):
+        """Reads in the gkpStore's 2-bit encoding (see encode_2bit / include/oic_b200.h); `packed` may be a numpy array or a
+        raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
+        if not isinstance(packed, int):
+            packed = np.ascontiguousarray(packed, dtype=np.uint8)
+            self._keep = packed
+            packed = packed.ctypes.data
+        offsets = np.ascontiguousarray(byte_offsets, dtype=np.uint64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
+        ho = np.ascontiguousarray(hash_ok, dtype=np.uint8) if hash_ok is not None else None
+        ro = np.ascontiguousarray(ref_ok, dtype=np.uint8) if ref_ok is not None else None
+        self._check(self.lib.oic_load_reads_2bit(self._h, first_id, len(lengths), offsets.ctypes.data, lengths.ctypes.data, packed,
+                                                 ho.ctypes.data if ho is not None else None,
+                                                 ro.ctypes.data if ro is not None else None), "oic_load_reads_2bit")
         self.n_reads = len(lengths)
         self.first_id = first_id
 

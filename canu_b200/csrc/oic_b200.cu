@@ -373,8 +373,10 @@ void oic_destroy(oic_ctx_t *c) {
 
 void oic_set_debug(oic_ctx_t *c, uint32_t mask) { c->debug = mask; }
 
-int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *offsets, const uint32_t *lengths,
-                   const char *bases, const uint8_t *hash_ok, const uint8_t *ref_ok) {
+/* Common part of the two loaders: read table, stream positions, device copies of them.  two_bit: bases are the store's 2-bit
+ * encoding (4 per byte) instead of ASCII. */
+static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *offsets, const uint32_t *lengths,
+                           const void *bases, const uint8_t *hash_ok, const uint8_t *ref_ok, bool two_bit) {
   if (!c || (n && (!offsets || !lengths || !bases)) || first_id < 1) return c ? c->fail(OIC_ERR_ARG, "oic_load_reads: bad argument") : OIC_ERR_ARG;
   cudaSetDevice(c->device);
   c->hash_ready = false;
@@ -393,8 +395,9 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
     if (lengths[i] > (uint32_t)MAX_READLEN) return c->fail(OIC_ERR_ARG, "read %u longer than AS_MAX_READLEN", first_id + i);
     c->h_pos[i] = pos;
     pos = (pos + lengths[i] + READ_PAD_BASES + 31) & ~(int64_t)31;
+    const uint64_t nbytes = two_bit ? ((uint64_t)lengths[i] + 3) / 4 : lengths[i];
     asc_lo = std::min(asc_lo, offsets[i]);
-    asc_hi = std::max(asc_hi, offsets[i] + lengths[i]);
+    asc_hi = std::max(asc_hi, offsets[i] + nbytes);
     c->max_read_len = std::max(c->max_read_len, lengths[i]);
   }
   c->h_pos[n] = pos;
@@ -412,15 +415,20 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
   CK(d_off.ensure((size_t)n * 8));
   std::vector<uint64_t> rel(n);
   for (uint32_t i = 0; i < n; i++) rel[i] = offsets[i] - asc_lo;
-  CK(cudaMemcpyAsync(d_ascii.p, bases + asc_lo, asc_bytes, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d_ascii.p, (const char *)bases + asc_lo, asc_bytes, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemcpyAsync(d_off.p, rel.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemcpyAsync(c->d_pos.p, c->h_pos.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemcpyAsync(c->d_len.p, c->h_len.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += asc_bytes + (uint64_t)n * 20 + 8;
   if (zero_counters(c)) return OIC_ERR_CUDA;
-  k_pack_reads<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<char>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
-                                                                     c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
-                                                                     c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>());
+  if (two_bit)
+    k_pack_2bit<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<uint8_t>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
+                                                                       c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
+                                                                       c->d_rc.as<uint64_t>());
+  else
+    k_pack_reads<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<char>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
+                                                                       c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
+                                                                       c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>());
   c->tm.launches += 1;
   DevCounters hc;
   int rcode = read_counters(c, hc);
@@ -441,6 +449,16 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
     c->ml_erate = c->P.max_erate; c->ml_rows = c->max_rows;
   }
   return OIC_OK;
+}
+
+int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *offsets, const uint32_t *lengths,
+                   const char *bases, const uint8_t *hash_ok, const uint8_t *ref_ok) {
+  return load_reads_impl(c, first_id, n, offsets, lengths, bases, hash_ok, ref_ok, false);
+}
+
+int oic_load_reads_2bit(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *byte_offsets, const uint32_t *lengths,
+                        const uint8_t *packed, const uint8_t *hash_ok, const uint8_t *ref_ok) {
+  return load_reads_impl(c, first_id, n, byte_offsets, lengths, packed, hash_ok, ref_ok, true);
 }
 
 int oic_set_skip_kmers(oic_ctx_t *c, uint64_t n, const char *kmers) {

@@ -79,6 +79,49 @@ __global__ void k_pack_reads(const char *__restrict__ ascii, const uint64_t *__r
   if (bad) atomicOr(&ctr->bad_base, 1u);
 }
 
+// Same streams from the gkpStore's own 2-bit encoding (ST/gkStoreEncode.C:81-114: 4 bases per byte, FIRST base in bits 7-6,
+// a=0 c=1 g=2 t=3, the last byte left-aligned; every read starts on a byte boundary): a quarter of the PCIe bytes of the
+// ASCII path and no decode on the host.  One thread per 64-bit word of the padded stream.
+__global__ void k_pack_2bit(const uint8_t *__restrict__ packed, const uint64_t *__restrict__ byte_off,
+                            const uint32_t *__restrict__ rd_len, const int64_t *__restrict__ rd_pos, uint32_t n_reads,
+                            uint64_t n_words_total, uint64_t *__restrict__ fwd, uint64_t *__restrict__ rc) {
+  uint64_t gw = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gw >= n_words_total) return;
+  int64_t p0 = (int64_t)gw * 32;
+  uint64_t wf = 0, wr = 0;
+  if (n_reads && p0 >= rd_pos[0]) {
+    uint32_t lo = 0, hi = n_reads;   // largest r with rd_pos[r] <= p0
+    while (hi - lo > 1) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (rd_pos[mid] <= p0) lo = mid; else hi = mid;
+    }
+    const uint32_t len = rd_len[lo];
+    const int64_t i0 = p0 - rd_pos[lo];
+    if (i0 < (int64_t)len) {
+      const uint8_t *s = packed + byte_off[lo];
+      const uint32_t nb = (len - (uint32_t)i0 < 32u) ? len - (uint32_t)i0 : 32u;   // bases of this word
+      // forward: 8 bytes, the four 2-bit groups of every byte in reverse order (first base to the low bits)
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        if (4u * j < nb) {
+          const uint32_t b = s[(i0 >> 2) + j];
+          const uint32_t r = ((b & 3u) << 6) | ((b & 0xcu) << 2) | ((b & 0x30u) >> 2) | ((b & 0xc0u) >> 6);
+          wf |= (uint64_t)r << (8 * j);
+        }
+      }
+      if (nb < 32) wf &= (1ULL << (2 * nb)) - 1;
+      // reverse complement: base i of the rc strand = 3 - base (len-1-i) of the read (AS_UTL_reverseComplement.C:114-143)
+      for (uint32_t k = 0; k < nb; k++) {
+        const uint32_t j = len - 1 - ((uint32_t)i0 + k);
+        const uint32_t x = (s[j >> 2] >> (6 - 2 * (j & 3))) & 3u;
+        wr |= (uint64_t)(x ^ 3u) << (2 * k);
+      }
+    }
+  }
+  fwd[gw] = wf;
+  rc[gw] = wr;
+}
+
 // ------------------------------------------------------------------------------------------------ K1
 struct BuildArgs {
   const uint64_t *fwd;

@@ -181,9 +181,26 @@ int main(int argc, char **argv) {
     hash_ok[i] = !(lib < min_lib_hash || lib > max_lib_hash);   // Build_Hash_Index.C:555-557
     ref_ok[i] = !(lib < min_lib_ref || lib > max_lib_ref);      // Process_Overlaps.C:108-110
   }
-  std::vector<char> bases(total + 1);
-  {
-    const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  // The store keeps ACGT-only reads 2-bit encoded (`2SEQ`); those bytes go to the GPU as they are (oic_load_reads_2bit).  If any
+  // read of the range is stored unencoded (`USEQ`), the whole range takes the ASCII path (gkRead_loadData semantics).
+  bool two_bit = getenv("OIC_ASCII_LOAD") == nullptr;
+  for (uint32_t i = 0; i < n && two_bit; i++)
+    if (lengths[i] && !store.sequence_2bit(first_id + i)) two_bit = false;
+  std::vector<char> bases;
+  const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  if (two_bit) {
+    uint64_t tb = 0;
+    for (uint32_t i = 0; i < n; i++) { offsets[i] = tb; tb += ((uint64_t)lengths[i] + 3) / 4; }
+    bases.resize(tb + 8);
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++)
+      th.emplace_back([&, t]() {
+        for (uint64_t i = (uint64_t)n * t / nt, e = (uint64_t)n * (t + 1) / nt; i < e; i++)
+          if (lengths[i]) memcpy(bases.data() + offsets[i], store.sequence_2bit(first_id + (uint32_t)i), ((uint64_t)lengths[i] + 3) / 4);
+      });
+    for (auto &t : th) t.join();
+  } else {
+    bases.resize(total + 1);
     std::vector<std::thread> th;
     for (unsigned t = 0; t < nt; t++)
       th.emplace_back([&, t]() {
@@ -231,7 +248,8 @@ int main(int argc, char **argv) {
   };
   if (n == 0) { fprintf(stderr, "ERROR: empty read range\n"); return 1; }
   if (!on_all([&](int g) {
-        int rc = oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
+        int rc = two_bit ? oic_load_reads_2bit(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), (const uint8_t *)bases.data(), hash_ok.data(), ref_ok.data())
+                         : oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
         if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
         return rc;
       })) return 1;

@@ -97,6 +97,24 @@ void GkStore::load_sequence(uint32_t id, char *out) const {
   if (!have && len) { fprintf(stderr, "gkStore: read %u has no sequence chunk\n", id); exit(1); }
 }
 
+const uint8_t *GkStore::sequence_2bit(uint32_t id) const {
+  const GkRead &r = reads_[id];
+  const uint64_t at = r.m_ptr();
+  if (at + 8 > blobs_bytes_ || memcmp(blobs_ + at, "BLOB", 4) != 0) {
+    fprintf(stderr, "gkStore: read %u: no BLOB at offset %llu of '%s/blobs'\n", id, (unsigned long long)at, path_.c_str());
+    exit(1);
+  }
+  const uint8_t *b = blobs_ + at + 8;
+  while (memcmp(b, "STOP", 4) != 0) {
+    uint32_t clen;
+    memcpy(&clen, b + 4, 4);
+    if (memcmp(b, "2SEQ", 4) == 0) return ((uint64_t)clen * 4 >= r.seq_len()) ? b + 8 : nullptr;
+    b += 8 + clen;
+    if ((size_t)(b - blobs_) + 4 > blobs_bytes_) { fprintf(stderr, "gkStore: read %u: blob runs past the end of the file\n", id); exit(1); }
+  }
+  return nullptr;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 std::string counts_name_for(const std::string &name) {
   // AS_UTL_findBaseFileName: cut at the first '.' after the last '/', then add ".counts"

@@ -33,6 +33,9 @@ class GkStore {
   const GkRead &read(uint32_t id) const { return reads_[id]; }
   // sequence of read `id` as upper-case ASCII into out[0 .. seq_len) (gkRead_loadData: 2SEQ / USEQ chunks)
   void load_sequence(uint32_t id, char *out) const;
+  // the read's `2SEQ` chunk as stored (4 bases per byte, first base in bits 7-6; ceil(seq_len/4) bytes), or nullptr when the
+  // read is kept unencoded (`USEQ`: it contains non-ACGT bases) -- fed to oic_load_reads_2bit without decoding
+  const uint8_t *sequence_2bit(uint32_t id) const;
 
  private:
   std::string path_;

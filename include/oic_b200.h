@@ -90,6 +90,14 @@ const char *oic_last_error(const oic_ctx_t *ctx);   /* ctx may be NULL: error of
 int oic_load_reads(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const uint64_t *offsets,
                    const uint32_t *lengths, const char *bases, const uint8_t *hash_ok, const uint8_t *ref_ok);
 
+/* Same, taking the reads in the gkpStore's own 2-bit encoding instead of ASCII -- the `2SEQ` blob chunk as stored
+ * (ST/gkStoreEncode.C:81-114, read by gkRead_loadData ST/gkStore.C:124-126): 4 bases per byte, first base in bits 7-6,
+ * a=0 c=1 g=2 t=3, ceil(length/4) bytes per read at packed[byte_offsets[i] ..].  Replaces gkRead_decode2bit + the copy
+ * loops: no decode on the host and a quarter of the PCIe bytes.  (Reads that the store keeps in a `USEQ` chunk contain
+ * non-ACGT bases and go through oic_load_reads.) */
+int oic_load_reads_2bit(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const uint64_t *byte_offsets,
+                        const uint32_t *lengths, const uint8_t *packed, const uint8_t *hash_ok, const uint8_t *ref_ok);
+
 /* Mark_Skip_Kmers input (OIC/overlapInCore-Build_Hash_Index.C:233-286): n k-mers of exactly kmer_len
  * characters, concatenated.  Applied at the end of every subsequent hash build. */
 int oic_set_skip_kmers(oic_ctx_t *ctx, uint64_t n, const char *kmers);

@@ -96,6 +96,27 @@ def gen_reads(genome_len, coverage, len_min, len_max, err, seed, sub_only=False,
     return Reads(bases[:total], offsets, lengths)
 
 
+def encode_2bit(reads_bases, offsets, lengths, out=None):
+    """ASCII reads -> gkpStore 2-bit encoding (tools/gen_reads.c oic_encode_2bit); returns (packed uint8, byte_offsets uint64[n]).
+    `out`: optional preallocated uint8 buffer (e.g. the numpy view of a pinned tensor) of at least sum(ceil(len/4)) bytes."""
+    gen_so, _ = build_harness_libs()
+    lib = C.CDLL(gen_so)
+    lib.oic_encode_2bit.restype = C.c_uint64
+    lib.oic_encode_2bit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    bases = np.ascontiguousarray(reads_bases, dtype=np.uint8)
+    lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
+    offsets = np.ascontiguousarray(np.asarray(offsets)[:len(lengths)], dtype=np.uint64)
+    total = int(((lengths.astype(np.int64) + 3) // 4).sum())
+    if out is None:
+        out = np.zeros(total + 8, dtype=np.uint8)
+    assert out.dtype == np.uint8 and out.size >= total
+    boff = np.zeros(len(lengths), dtype=np.uint64)
+    w = lib.oic_encode_2bit(bases.ctypes.data, offsets.ctypes.data, lengths.ctypes.data, len(lengths), out.ctypes.data, boff.ctypes.data)
+    if w == 2 ** 64 - 1:
+        raise ValueError("encode_2bit: non-ACGT base")
+    return out[:total], boff
+
+
 # ----------------------------------------------------------------------------- reference tools
 
 def make_store(reads, workdir, minlength=0):

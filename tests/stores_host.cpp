@@ -27,6 +27,20 @@ void sh_store_bases(const char *path, char *out) {
   }
 }
 
+// the stored 2-bit chunks of reads 1..num_reads, concatenated (ceil(len/4) bytes each); returns 0 if a read has none
+int sh_store_2bit(const char *path, uint8_t *out) {
+  GkStore s(path);
+  uint64_t at = 0;
+  for (uint32_t id = 1; id <= s.num_reads(); id++) {
+    const uint64_t nb = ((uint64_t)s.read(id).seq_len() + 3) / 4;
+    const uint8_t *p = s.sequence_2bit(id);
+    if (!p && nb) return 0;
+    memcpy(out + at, p, nb);
+    at += nb;
+  }
+  return 1;
+}
+
 // write n 24-byte records in `pieces` write() calls (exercises the block boundary logic)
 void sh_write_ovb(const char *name, const uint32_t *rec, uint64_t n, uint32_t pieces) {
   OvbWriter w(name);

@@ -139,3 +139,25 @@ def test_no_device_fallback_symbols():
     lib = api.load_library()
     for s in api.ABI_SYMBOLS:
         assert hasattr(lib, s)
+
+
+@pytest.mark.parametrize("name", ["c1_small", "c4_short", "multiblock"])
+def test_two_bit_load_equals_ascii_load(name):
+    """oic_load_reads_2bit (the gkpStore's 2SEQ bytes, no host decode) gives the same overlaps and counters as oic_load_reads"""
+    from canu_b200 import api
+    reads, P, erate, threads, skip = cases.build_case(name)
+    ov = make_overlapper(reads, P, skip)
+    ov.overlap_driver()
+    want, st_want = formatted(ov.overlaps()), ov.stats()
+    ov.close()
+    packed, boff = H.encode_2bit(reads.bases, reads.offsets, reads.lengths)
+    ov = api.Overlapper(P)
+    ov.load_reads_2bit(packed, boff, reads.lengths)
+    if skip:
+        ov.set_skip_kmers(skip)
+    ov.overlap_driver()
+    got, st_got = formatted(ov.overlaps()), ov.stats()
+    ov.close()
+    assert got == want
+    for k in STAT_KEYS + WORK_KEYS:
+        assert st_got[k] == st_want[k], k

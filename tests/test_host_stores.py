@@ -72,6 +72,18 @@ def test_gkstore_reader(tmp_path):
     out = np.zeros(int(lens.sum()) + 1, dtype=np.uint8)
     lib.sh_store_bases(store.encode(), out.ctypes.data)
     assert (out[:-1] == reads.bases).all()
+    # the store's own 2SEQ chunks (what oic_load_reads_2bit takes) == the harness encoder used by the tests and bench.py
+    # (tools/gen_reads.c oic_encode_2bit) == the numpy encoder of canu_b200.api: pins the 2-bit input format to the reference's
+    # gatekeeperCreate (ST/gkStoreEncode.C:45-78)
+    from canu_b200 import api
+    packed, boff = H.encode_2bit(reads.bases, reads.offsets, reads.lengths)
+    packed2, boff2 = api.encode_2bit(reads.bases, reads.offsets, reads.lengths)
+    assert np.array_equal(packed, packed2) and np.array_equal(boff, boff2)
+    raw = np.zeros(len(packed) + 8, dtype=np.uint8)
+    lib.sh_store_2bit.restype = C.c_int
+    lib.sh_store_2bit.argtypes = [C.c_char_p, C.c_void_p]
+    assert lib.sh_store_2bit(store.encode(), raw.ctypes.data) == 1
+    assert np.array_equal(raw[:len(packed)], packed)
 
 
 @pytest.mark.skipif(not H.have_ref(), reason="reference tools not built (oracle/build_ref.sh)")

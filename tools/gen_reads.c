@@ -147,6 +147,40 @@ void oic_gen_fill(const gen_params_t *p, const uint8_t *g, uint64_t nreads, cons
 
 void oic_gen_free(void *p) { free(p); }
 
+/* ASCII reads -> the gkpStore 2-bit encoding (4 bases per byte, first base in bits 7-6, a=0 c=1 g=2 t=3, every read on a
+ * byte boundary, ceil(len/4) bytes per read) -- what gatekeeperCreate writes into the `2SEQ` chunk of a read blob
+ * (reference: src/stores/gkStoreEncode.C:45-78).  Returns the number of bytes written, or (uint64_t)-1 on a non-ACGT base. */
+uint64_t oic_encode_2bit(const char *bases, const uint64_t *offsets, const uint32_t *lengths, uint64_t nreads, uint8_t *out,
+                         uint64_t *byte_offsets) {
+  uint64_t w = 0;
+  int bad = 0;
+  for (uint64_t i = 0; i < nreads; i++) { byte_offsets[i] = w; w += ((uint64_t)lengths[i] + 3) / 4; }
+#pragma omp parallel for schedule(dynamic, 64) reduction(|:bad)
+  for (uint64_t i = 0; i < nreads; i++) {
+    const char *s = bases + offsets[i];
+    uint8_t *o = out + byte_offsets[i];
+    const uint32_t len = lengths[i];
+    for (uint32_t j = 0; j < len; j += 4) {
+      uint8_t b = 0;
+      for (uint32_t k = 0; k < 4; k++) {
+        uint8_t c = 0;
+        if (j + k < len) {
+          switch (s[j + k]) {
+            case 'a': case 'A': c = 0; break;
+            case 'c': case 'C': c = 1; break;
+            case 'g': case 'G': c = 2; break;
+            case 't': case 'T': c = 3; break;
+            default: bad = 1; break;
+          }
+        }
+        b = (uint8_t)((b << 2) | c);
+      }
+      o[j / 4] = b;
+    }
+  }
+  return bad ? (uint64_t)-1 : w;
+}
+
 #ifdef GEN_MAIN
 int main(int argc, char **argv) {
   gen_params_t p;
