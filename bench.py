@@ -159,6 +159,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-input", default="2bit", choices=["2bit", "ascii"],
                     help="host buffers of the end-to-end leg: the gkpStore's 2-bit read encoding (oic_load_reads_2bit) or ASCII (oic_load_reads)")
+    ap.add_argument("--replicate", default="broadcast", choices=["broadcast", "rebuild"],
+                    help="N > 1: rank 0 builds the hash block and NCCL-broadcasts it (north star), or every rank builds its own copy")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json shape; c3 is the bench line")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -174,7 +176,8 @@ def main():
         metric = "overlapInCore query Mbp/sec (+overlaps/sec), workload %s" % a.workload
     config = {"workload": wl["desc"],
               "hash_block_mbp": BLOCK_BASES * a.scale / 1e6, "query_block_mbp_per_gpu": BLOCK_BASES * a.scale / 1e6,
-              "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (world, " by NCCL broadcast" if world > 1 else ""),
+              "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (
+                  world, "" if world == 1 else (" by NCCL broadcast" if a.replicate == "broadcast" else " by rebuilding it on every rank (no collective)")),
               "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed"}
 
     if a.impl == "reference":
@@ -283,7 +286,7 @@ def main():
                 ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
         ov.clear_overlaps()
         t.append(time.perf_counter())
-        if world == 1:
+        if world == 1 or a.replicate == "rebuild":
             ov.build_hash_index(*hash_range)
         else:
             if rank == 0:

@@ -225,7 +225,9 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
     if (use[s] && c->h_len[ri_bgn + s] >= (uint32_t)K) n_windows += c->h_len[ri_bgn + s] - K + 1;
   if (n_windows >= (1ull << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %llu k-mers (limit 2^30)", (unsigned long long)n_windows);
   if (n_strings >= (1u << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %u reads (limit 2^30)", n_strings);
-  uint64_t want = 2 * (n_windows + c->skip_keys.size()) + 16;
+  static const char *tf = getenv("OIC_TABLE_FACTOR");   // slots per k-mer window before rounding up to a power of two (default 2)
+  const double factor = tf ? std::max(1.1, atof(tf)) : 2.0;
+  uint64_t want = (uint64_t)(factor * (double)(n_windows + c->skip_keys.size())) + 16;
   uint64_t slots = 1024;
   while (slots < want) slots <<= 1;
 
