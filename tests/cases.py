@@ -34,6 +34,20 @@ CASES = {
     # -z: hopeless check off at low error rate
     "nohopeless": dict(gen=dict(genome_len=20000, coverage=12, len_min=900, len_max=2000, err=0.025, seed=77),
                        erate="0.06", params=dict(hash_bits=16, hash_load=0.75, use_hopeless_check=0), threads=2),
+    # wide band at scale: 8-12 kb reads at 12 % pairwise error -> rows wider than the 1024 diagonals staged in shared memory
+    # (generic-row rerun of the task kernel) and histories that overflow the first-pass scratch (retry path)
+    "long_wide": dict(gen=dict(genome_len=26000, coverage=4, len_min=8000, len_max=12000, err=0.06, seed=4041),
+                      erate="0.15", params=dict(hash_bits=16, hash_load=0.75, kmer_len=16), threads=2),
+    # error-free reads of very mixed length: exact-match extensions (row 0 reaches the end), containments, duplicates of
+    # whole reads inside longer ones
+    "exact_contained": dict(gen=dict(genome_len=12000, coverage=14, len_min=300, len_max=4000, err=0.0, seed=616),
+                            erate="0.03", params=dict(hash_bits=15, hash_load=0.75, min_olap_len=100), threads=3),
+    # ragged input: many reads shorter than K or than --minlength (never loaded / never queried), a few long ones
+    "ragged_tiny": dict(gen=dict(genome_len=6000, coverage=12, len_min=10, len_max=700, err=0.01, seed=8),
+                        erate="0.06", params=dict(hash_bits=14, hash_load=0.75, min_olap_len=60), threads=2),
+    # empty output: sparse reads of a large genome share no k-mer runs worth an overlap
+    "no_overlaps": dict(gen=dict(genome_len=2000000, coverage=0.02, len_min=900, len_max=1500, err=0.02, seed=12),
+                        erate="0.06", params=dict(hash_bits=14, hash_load=0.75), threads=2),
 }
 
 

@@ -1,7 +1,7 @@
 """Generate the committed golden fixtures by RUNNING THE REFERENCE BINARY (oracle/_ref/overlapInCore,
 built by oracle/build_ref.sh from /root/reference/src) on the seeded cases of tests/cases.py.
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py [case ...]
 
 For each case: <name>.txt.gz = `overlapConvert -G store -raw x.ovb | LC_ALL=C sort` (every stored field
 of every overlap record), <name>.json = the 8 counters of the -s stats file + the .counts file md5.
@@ -23,7 +23,7 @@ import cases  # noqa: E402
 
 def main():
     assert H.have_ref(), "run oracle/build_ref.sh first"
-    for name in cases.CASES:
+    for name in (sys.argv[1:] or cases.CASES):
         reads, P, erate, threads, skip = cases.build_case(name)
         with tempfile.TemporaryDirectory() as wd:
             store = H.make_store(reads, wd)
@@ -37,7 +37,7 @@ def main():
             stats = H.parse_stats(st)
             counts = open(os.path.join(wd, "ref.counts"), "rb").read()
         with gzip.GzipFile(os.path.join(HERE, name + ".txt.gz"), "wb", mtime=0) as f:
-            f.write(("\n".join(lines) + "\n").encode())
+            f.write(("".join(x + "\n" for x in lines)).encode())
         meta = dict(stats=stats, n_overlaps=len(lines), n_reads=reads.n, total_bases=int(reads.lengths.sum()),
                     counts_md5=hashlib.md5(counts).hexdigest(), threads=threads, erate=erate)
         json.dump(meta, open(os.path.join(HERE, name + ".json"), "w"), indent=1, sort_keys=True)
