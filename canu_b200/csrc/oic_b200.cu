@@ -724,7 +724,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         c->mem_avail = (unsigned long long)free_b + c->d_vals.cap + c->d_dpool.cap;
       }
       const unsigned long long avail = c->mem_avail;
-      const unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::max<unsigned long long>(12ull << 30, avail * 45 / 100));
+      unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::max<unsigned long long>(12ull << 30, avail * 45 / 100));
+      // test knobs: shrink the first-pass history / the delta pool so that the overflow -> serial retry path runs on small inputs
+      if (const char *e = getenv("OIC_VALS_BUDGET_MB")) vals_bytes = strtoull(e, nullptr, 10) << 20;
       const unsigned long long budget = vals_bytes / 4 / n_warps;
       const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
       if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
@@ -755,8 +757,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
       // speculative second round (oic_extend.cuh): state per pair, one result slot per seed, a pool for the delta lists
-      const unsigned long long dpool_cap = std::min<unsigned long long>(std::max<unsigned long long>(1ull << 28, avail * 15 / 100 / 4),
-                                                                        (unsigned long long)n_runs * 512 + (16ull << 20));
+      unsigned long long dpool_cap = std::min<unsigned long long>(std::max<unsigned long long>(1ull << 28, avail * 15 / 100 / 4),
+                                                                  (unsigned long long)n_runs * 512 + (16ull << 20));
+      if (const char *e = getenv("OIC_DPOOL_MB")) dpool_cap = (strtoull(e, nullptr, 10) << 20) / 4;
       CK(c->d_pstate.ensure((size_t)n_pairs * sizeof(PairState)));
       CK(c->d_pend.ensure((size_t)n_pairs * 4 + 4));
       CK(c->d_tasks.ensure((size_t)n_runs * sizeof(uint2) + 8));

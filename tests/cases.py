@@ -38,6 +38,10 @@ CASES = {
     # (generic-row rerun of the task kernel) and histories that overflow the first-pass scratch (retry path)
     "long_wide": dict(gen=dict(genome_len=26000, coverage=4, len_min=8000, len_max=12000, err=0.06, seed=4041),
                       erate="0.15", params=dict(hash_bits=16, hash_load=0.75, kmer_len=16), threads=2),
+    # rows wider than the 1024 diagonals staged in shared memory: 17-20 kb reads at 12 % pairwise error keep a band of
+    # ~0.56 e diagonals alive for e > 1800 errors -> the generic-row instance of the task kernel
+    "very_wide": dict(gen=dict(genome_len=22000, coverage=3.2, len_min=17000, len_max=20000, err=0.06, seed=9100),
+                      erate="0.15", params=dict(hash_bits=16, hash_load=0.75, kmer_len=16), threads=1),
     # error-free reads of very mixed length: exact-match extensions (row 0 reaches the end), containments, duplicates of
     # whole reads inside longer ones
     "exact_contained": dict(gen=dict(genome_len=12000, coverage=14, len_min=300, len_max=4000, err=0.0, seed=616),

@@ -161,3 +161,23 @@ def test_two_bit_load_equals_ascii_load(name):
     assert got == want
     for k in STAT_KEYS + WORK_KEYS:
         assert st_got[k] == st_want[k], k
+
+
+@pytest.mark.parametrize("name,env", [("c2_noisy", {"OIC_VALS_BUDGET_MB": "48"}), ("c1_small", {"OIC_DPOOL_MB": "0"}),
+                                      ("long_wide", {"OIC_VALS_BUDGET_MB": "256", "OIC_DPOOL_MB": "0"})])
+def test_overflow_retry_path(name, env, monkeypatch):
+    """Edit-row history or delta pool too small for the speculative pass: the affected pairs are rerun serially with worst-case
+    scratch (oic_b200.cu run_batch) and the records / counters must not change."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    reads, P, erate, threads, skip = cases.build_case(name)
+    ov = make_overlapper(reads, P, skip)
+    ov.overlap_driver()
+    mine, st, tm = formatted(ov.overlaps()), ov.stats(), ov.timings()
+    ov.close()
+    gold = gzip.open(os.path.join(GOLDEN, name + ".txt.gz")).read().decode().splitlines()
+    assert mine == gold
+    assert tm["ms_ext_retry"] > 0, "the knob did not trigger the retry path"
+    res = H.run_oracle(reads, P, skip_kmers=skip)
+    for k in ["ext_calls", "ext_cells", "ext_words"] + STAT_KEYS:
+        assert st[k] == res["stats"][k], k
