@@ -42,6 +42,10 @@ CASES = {
     # ~0.56 e diagonals alive for e > 1800 errors -> the generic-row instance of the task kernel
     "very_wide": dict(gen=dict(genome_len=22000, coverage=3.2, len_min=17000, len_max=20000, err=0.06, seed=9100),
                       erate="0.15", params=dict(hash_bits=16, hash_load=0.75, kmer_len=16), threads=1),
+    # --minkmers: pairs with fewer k-mer hits than exp(-K erate) x (diagonal span - K + 1) are skipped (computeMinimumKmers,
+    # Process_String_Overlaps.C:75-86; the flag is evaluated with the K / erate / --minlength seen so far, overlapInCore.C:392-393)
+    "minkmers": dict(gen=dict(genome_len=40000, coverage=14, len_min=1200, len_max=3200, err=0.03, seed=314),
+                     erate="0.09", params=dict(hash_bits=17, hash_load=0.75, kmer_len=14, min_olap_len=400, minkmers=True), threads=2),
     # error-free reads of very mixed length: exact-match extensions (row 0 reaches the end), containments, duplicates of
     # whole reads inside longer ones
     "exact_contained": dict(gen=dict(genome_len=12000, coverage=14, len_min=300, len_max=4000, err=0.0, seed=616),
@@ -60,6 +64,10 @@ def build_case(name):
     c = CASES[name]
     reads = H.gen_reads(**c["gen"])
     over = dict(c["params"])
+    if over.pop("minkmers", False):
+        import math
+        over["filter_by_kmer_count"] = int(math.floor(math.exp(-1.0 * over.get("kmer_len", 22) * H.strtof(c["erate"])) *
+                                                      (over.get("min_olap_len", 500) - over.get("kmer_len", 22) + 1)))
     over.setdefault("max_hash_strings", reads.n)
     over.setdefault("max_hash_data_len", 100000000)
     over.setdefault("end_hash_id", reads.n)

@@ -307,7 +307,7 @@ def oic_args(params, erate_str):
         a.append("-z")
     a += ["-k", str(params["kmer_len"]), "--hashbits", str(params["hash_bits"]),
           "--hashload", repr(params["hash_load"]), "--maxerate", erate_str,
-          "--minlength", str(params["min_olap_len"]),
+          "--minlength", str(params["min_olap_len"])] + (["--minkmers"] if params.get("filter_by_kmer_count") else []) + [
           "--hashstrings", str(params["max_hash_strings"]), "--hashdatalen", str(params["max_hash_data_len"])]
     if params["end_hash_id"] != 2 ** 32 - 1 or params["bgn_hash_id"] != 1:
         a += ["-h", "%d-%d" % (params["bgn_hash_id"], params["end_hash_id"])]
