@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "oic_process_overlaps", "oic_overlap_driver", "oic_last_processed_ref", "oic_num_overlaps", "oic_copy_overlaps",
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
-    "oic_dump_pairs", "oic_measure_int32_peak",
+    "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats",
 ]
 
 
@@ -84,6 +84,8 @@ def load_library():
     lib.oic_load_reads.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.oic_load_reads_2bit.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.oic_set_skip_kmers.argtypes = [vp, C.c_uint64, C.c_char_p]
+    lib.oic_set_job.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
+    lib.oic_reset_stats.argtypes = [vp]
     lib.oic_build_hash_index.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     lib.oic_process_overlaps.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.oic_overlap_driver.argtypes = [vp]
@@ -238,6 +240,14 @@ class Overlapper:
                                                  ro.ctypes.data if ro is not None else None), "oic_load_reads_2bit")
         self.n_reads = len(lengths)
         self.first_id = first_id
+
+    def set_job(self, bgn_hash_id, end_hash_id, bgn_ref_id, end_ref_id, max_hash_strings, max_hash_data_len):
+        """New -h / -r / --hashstrings / --hashdatalen for the resident reads (one job of overlapInCorePartition)."""
+        self._check(self.lib.oic_set_job(self._h, bgn_hash_id, end_hash_id, bgn_ref_id, end_ref_id, max_hash_strings,
+                                         max_hash_data_len), "oic_set_job")
+
+    def reset_stats(self):
+        self.lib.oic_reset_stats(self._h)
 
     def set_skip_kmers(self, kmers):
         self._check(self.lib.oic_set_skip_kmers(self._h, len(kmers), "".join(kmers).encode()), "oic_set_skip_kmers")

@@ -128,6 +128,9 @@ struct oic_ctx {
   bool hash_ready = false;
   oic_hash_meta_t hb = {};
   DevBuf d_table, d_occ, d_str_flags, d_str_use, d_filter, d_ovf_slot, d_ovf_occ, d_multi_list, d_first_occ, d_cnt, d_mid_list, d_blk, d_big_list, d_occ_tmp, d_hist;
+  // identity of the block in the table (oic_set_job sweeps reuse it): requested range + the two load limits
+  uint32_t hbk_bgn = 0, hbk_end = 0, hbk_strings = 0; uint64_t hbk_datalen = 0;
+  bool job_mode = false;   // set by oic_set_job: only a job sweep reuses a block; a plain oic_build_hash_index always builds
   unsigned long long mem_avail = 0;   // device memory the pair stage may plan with (free + what it already holds)
   bool have_occupancy = false;   // occupancy bitmap of the current hash block is valid
 
@@ -466,6 +469,7 @@ int oic_load_reads_2bit(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint6
 int oic_set_skip_kmers(oic_ctx_t *c, uint64_t n, const char *kmers) {
   if (!c || (n && !kmers)) return OIC_ERR_ARG;
   const int K = c->P.kmer_len;
+  c->hash_ready = false;
   c->skip_keys.clear();
   c->skip_keys.reserve(2 * n);
   auto code = [](char ch) -> int {
@@ -491,6 +495,10 @@ int oic_build_hash_index(oic_ctx_t *c, uint32_t bgn_id, uint32_t end_id, uint32_
   if (!c) return OIC_ERR_ARG;
   cudaSetDevice(c->device);
   const oic_params_t &P = c->P;
+  if (c->job_mode && c->hash_ready && c->hbk_bgn == bgn_id && c->hbk_end == end_id && c->hbk_strings == P.max_hash_strings && c->hbk_datalen == P.max_hash_data_len) {
+    if (last_id) *last_id = c->hb.last_id;   // the same request as the block in the table: nothing to do
+    return OIC_OK;
+  }
   c->hash_ready = false;
   if (bgn_id < c->first_id || end_id >= c->first_id + c->n_reads || c->n_reads == 0)
     return c->fail(OIC_ERR_ARG, "hash range %u-%u outside the loaded reads %u-%u", bgn_id, end_id, c->first_id, c->first_id + c->n_reads - 1);
@@ -561,6 +569,7 @@ int oic_build_hash_index(oic_ctx_t *c, uint32_t bgn_id, uint32_t end_id, uint32_
   c->hb.last_id = bgn_id + n_strings - 1;
   c->hb.has_empty = has_empty;
   c->hash_ready = true;
+  c->hbk_bgn = bgn_id; c->hbk_end = end_id; c->hbk_strings = P.max_hash_strings; c->hbk_datalen = P.max_hash_data_len;
   for (uint32_t s = 0; s < n_strings; s++)
     if (use[s]) c->stats.n_hash_bases += c->h_len[ri_bgn + s];
   c->stats.n_inserts += hc.n_inserts;
@@ -950,6 +959,18 @@ int oic_overlap_driver(oic_ctx_t *c) {
   return OIC_OK;
 }
 
+int oic_set_job(oic_ctx_t *c, uint32_t bgn_hash_id, uint32_t end_hash_id, uint32_t bgn_ref_id, uint32_t end_ref_id,
+                uint32_t max_hash_strings, uint64_t max_hash_data_len) {
+  if (!c) return OIC_ERR_ARG;
+  if (max_hash_strings == 0) return c->fail(OIC_ERR_ARG, "bad --hashstrings");
+  c->P.bgn_hash_id = bgn_hash_id; c->P.end_hash_id = end_hash_id;
+  c->P.bgn_ref_id = bgn_ref_id; c->P.end_ref_id = end_ref_id;
+  c->P.max_hash_strings = max_hash_strings; c->P.max_hash_data_len = max_hash_data_len;
+  c->job_mode = true;
+  return OIC_OK;
+}
+void oic_reset_stats(oic_ctx_t *c) { if (c) memset(&c->stats, 0, sizeof(c->stats)); }
+
 uint64_t oic_num_overlaps(const oic_ctx_t *c) { return c ? c->overlaps.size() : 0; }
 
 int oic_copy_overlaps(oic_ctx_t *c, oic_ovb_record_t *dst, uint64_t capacity, uint64_t *n_copied) {
@@ -1003,6 +1024,7 @@ int oic_hash_block_commit(oic_ctx_t *c, const oic_hash_meta_t *m) {
   if (build_occupancy(c, m->table_slots)) return OIC_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->hash_ready = true;
+  c->hbk_bgn = c->hbk_end = 0;   // a block that arrived by broadcast is never mistaken for a local build
   c->stats.n_hash_blocks++;
   c->stats.last_end_hash_id = m->last_id;
   return OIC_OK;

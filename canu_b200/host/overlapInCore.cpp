@@ -8,6 +8,11 @@
  *                 every GPU builds the same hash block from the same reads -- deterministic, no collective needed here;
  *                 the NCCL-broadcast variant lives in bench.py where torch.distributed provides the communicator)
  *   --device D    first CUDA device to use (default 0)
+ *   --sweep PFX   run EVERY job of an overlapInCorePartition job list (PFX.ovlbat / .ovljob / .ovlopt) in this one process:
+ *                 the store is opened and its reads sent to the GPU once, consecutive query blocks of a hash block reuse
+ *                 the built index, and every job writes the files the pipeline expects from its own process
+ *                 (OverlapInCore.pm:184-233): DIR/<batch>/<job>.ovb, .counts, .stats with DIR from --sweep-out (default ".").
+ *                 -h / -r / --hashstrings / --hashdatalen come from the job list, every other option applies to all jobs.
  */
 #include <ctype.h>
 #include <errno.h>
@@ -16,6 +21,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
 
 #include <algorithm>
 #include <string>
@@ -23,6 +29,7 @@
 #include <vector>
 
 #include "../../include/oic_b200.h"
+#include "partition.h"
 #include "stores.h"
 
 using namespace oichost;
@@ -65,6 +72,8 @@ void usage(const char *argv0) {
   fprintf(stderr, "--maxreadlen n     accepted, no effect on results\n\n");
   fprintf(stderr, "--gpus n           B200s to shard the query reads over (default 1)\n");
   fprintf(stderr, "--device d         first CUDA device (default 0)\n");
+  fprintf(stderr, "--sweep prefix     run all jobs of prefix.ovlbat/.ovljob/.ovlopt (overlapInCorePartition) in this process\n");
+  fprintf(stderr, "--sweep-out dir    directory of the per-job outputs <dir>/<batch>/<job>.ovb/.counts/.stats (default .)\n");
 }
 
 struct Shard {
@@ -91,6 +100,7 @@ int main(int argc, char **argv) {
   const char *skip_file = nullptr, *out_name = nullptr, *stat_name = nullptr, *store_path = nullptr;
   bool window_filter = false;
   int n_gpus = 1, device0 = 0;
+  const char *sweep_prefix = nullptr, *sweep_out = ".";
   uint64_t max_string_num = (1ull << 31) - 1;
 
   if (argc == 2 && strcmp(argv[1], "--version") == 0) { fprintf(stdout, "overlapInCore (B200-native, Canu 1.6 compatible)\n"); return 0; }
@@ -141,6 +151,8 @@ int main(int argc, char **argv) {
     else if (strcmp(a, "-z") == 0) P.use_hopeless_check = 0;
     else if (strcmp(a, "--gpus") == 0) n_gpus = atoi(need());
     else if (strcmp(a, "--device") == 0) device0 = atoi(need());
+    else if (strcmp(a, "--sweep") == 0) sweep_prefix = need();
+    else if (strcmp(a, "--sweep-out") == 0) sweep_out = need();
     else if (store_path == nullptr) store_path = a;
     else { fprintf(stderr, "Unknown option '%s'\n", a); err++; }
   }
@@ -152,7 +164,7 @@ int main(int argc, char **argv) {
   if (P.max_hash_strings == 0) fprintf(stderr, "* No memory model supplied; -M needed!\n"), err++;
   if (P.kmer_len == 0) fprintf(stderr, "* No kmer length supplied; -k needed!\n"), err++;
   if (P.max_hash_strings > max_string_num) fprintf(stderr, "Too many strings (--hashstrings), must be less than %llu\n", (unsigned long long)max_string_num), err++;
-  if (out_name == nullptr) fprintf(stderr, "ERROR:  No output file name specified\n"), err++;
+  if (out_name == nullptr && sweep_prefix == nullptr) fprintf(stderr, "ERROR:  No output file name specified\n"), err++;
   if (err || store_path == nullptr) { usage(argv[0]); return 1; }
   if (window_filter) { fprintf(stderr, "ERROR: -w (window filter) is not supported by this build\n"); return 1; }
   if (P.num_threads == 0) P.num_threads = 1;
@@ -161,6 +173,16 @@ int main(int argc, char **argv) {
   // ---- input
   GkStore store(store_path);
   const uint32_t num_reads = store.num_reads();
+  std::vector<OvlJob> jobs;   // --sweep: the job list; the reads loaded are the union of all ranges
+  if (sweep_prefix) {
+    if (!read_job_files(sweep_prefix, jobs) || jobs.empty()) { fprintf(stderr, "ERROR: cannot read job list '%s.ovlbat/.ovljob/.ovlopt'\n", sweep_prefix); return 1; }
+    P.bgn_hash_id = P.bgn_ref_id = UINT32_MAX;
+    P.end_hash_id = P.end_ref_id = 0;
+    for (const OvlJob &j : jobs) {
+      P.bgn_hash_id = std::min(P.bgn_hash_id, j.hash_bgn); P.end_hash_id = std::max(P.end_hash_id, j.hash_end);
+      P.bgn_ref_id = std::min(P.bgn_ref_id, j.ref_bgn); P.end_ref_id = std::max(P.end_ref_id, j.ref_end);
+    }
+  }
   if (P.bgn_hash_id < 1) P.bgn_hash_id = 1;
   if (P.end_hash_id > num_reads) P.end_hash_id = num_reads;
   if (P.bgn_ref_id < 1) P.bgn_ref_id = 1;
@@ -254,67 +276,97 @@ int main(int argc, char **argv) {
         return rc;
       })) return 1;
 
-  // ---- OverlapDriver (OIC/overlapInCore.C:190-300)
-  OvbWriter out(out_name);
-  std::vector<uint32_t> rec;
-  uint64_t bgn = P.bgn_hash_id, end = (uint64_t)P.bgn_hash_id + P.max_hash_strings - 1;
-  while (bgn < P.end_hash_id) {
-    if (end > P.end_hash_id) end = P.end_hash_id;
-    std::vector<uint32_t> last(n_gpus, 0);
-    if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g]); })) return 1;
-    fprintf(stderr, "Hash block %llu-%u built\n", (unsigned long long)bgn, last[0]);
-    const uint32_t last_ref = oic_last_processed_ref(P.bgn_ref_id, P.end_ref_id, P.num_threads);
-    if (last_ref >= P.bgn_ref_id) {
-      // contiguous shards balanced by bases x expected partners: a query only pairs with hash reads of higher ID
-      std::vector<double> w(last_ref - P.bgn_ref_id + 2, 0.0);
-      for (uint32_t id = P.bgn_ref_id; id <= last_ref; id++) {
-        double partners = id < bgn ? (double)(last[0] - bgn + 1) : (id < last[0] ? (double)(last[0] - id) : 0.0);
-        w[id - P.bgn_ref_id + 1] = w[id - P.bgn_ref_id] + (double)lengths[id - first_id] * partners + 1.0;
+  // One job = what one process of the reference does with its -h / -r / --hashstrings / --hashdatalen.
+  auto run_job = [&](const oic_params_t &J, const char *job_out, const char *job_stat) -> int {
+    if (!on_all([&](int g) {
+          oic_reset_stats(sh[g].ctx);
+          return oic_set_job(sh[g].ctx, J.bgn_hash_id, J.end_hash_id, J.bgn_ref_id, J.end_ref_id, J.max_hash_strings, J.max_hash_data_len);
+        })) return 1;
+    // ---- OverlapDriver (OIC/overlapInCore.C:190-300)
+    OvbWriter out(job_out);
+    std::vector<uint32_t> rec;
+    uint64_t bgn = J.bgn_hash_id, end = (uint64_t)J.bgn_hash_id + J.max_hash_strings - 1;
+    while (bgn < J.end_hash_id) {
+      if (end > J.end_hash_id) end = J.end_hash_id;
+      std::vector<uint32_t> last(n_gpus, 0);
+      if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g]); })) return 1;
+      fprintf(stderr, "Hash block %llu-%u built\n", (unsigned long long)bgn, last[0]);
+      const uint32_t last_ref = oic_last_processed_ref(J.bgn_ref_id, J.end_ref_id, J.num_threads);
+      if (last_ref >= J.bgn_ref_id) {
+        // contiguous shards balanced by bases x expected partners: a query only pairs with hash reads of higher ID
+        std::vector<double> w(last_ref - J.bgn_ref_id + 2, 0.0);
+        for (uint32_t id = J.bgn_ref_id; id <= last_ref; id++) {
+          double partners = id < bgn ? (double)(last[0] - bgn + 1) : (id < last[0] ? (double)(last[0] - id) : 0.0);
+          w[id - J.bgn_ref_id + 1] = w[id - J.bgn_ref_id] + (double)lengths[id - first_id] * partners + 1.0;
+        }
+        std::vector<uint32_t> cut(n_gpus + 1, J.bgn_ref_id);
+        for (int g = 1; g <= n_gpus; g++) {
+          double target = w.back() * g / n_gpus;
+          cut[g] = J.bgn_ref_id + (uint32_t)(std::lower_bound(w.begin(), w.end(), target) - w.begin());
+          if (cut[g] > last_ref + 1 || g == n_gpus) cut[g] = last_ref + 1;
+        }
+        if (!on_all([&](int g) { return cut[g + 1] > cut[g] ? oic_process_overlaps(sh[g].ctx, cut[g], cut[g + 1] - 1) : 0; })) return 1;
+        for (int g = 0; g < n_gpus; g++) {
+          uint64_t k = oic_num_overlaps(sh[g].ctx), got = 0;
+          rec.resize(6 * k);
+          oic_copy_overlaps(sh[g].ctx, reinterpret_cast<oic_ovb_record_t *>(rec.data()), k, &got);
+          out.write(rec.data(), got);
+          oic_clear_overlaps(sh[g].ctx);
+        }
       }
-      std::vector<uint32_t> cut(n_gpus + 1, P.bgn_ref_id);
-      for (int g = 1; g <= n_gpus; g++) {
-        double target = w.back() * g / n_gpus;
-        cut[g] = P.bgn_ref_id + (uint32_t)(std::lower_bound(w.begin(), w.end(), target) - w.begin());
-        if (cut[g] > last_ref + 1 || g == n_gpus) cut[g] = last_ref + 1;
-      }
-      if (!on_all([&](int g) { return cut[g + 1] > cut[g] ? oic_process_overlaps(sh[g].ctx, cut[g], cut[g + 1] - 1) : 0; })) return 1;
-      for (int g = 0; g < n_gpus; g++) {
-        uint64_t k = oic_num_overlaps(sh[g].ctx), got = 0;
-        rec.resize(6 * k);
-        oic_copy_overlaps(sh[g].ctx, reinterpret_cast<oic_ovb_record_t *>(rec.data()), k, &got);
-        out.write(rec.data(), got);
-        oic_clear_overlaps(sh[g].ctx);
-      }
+      bgn = (uint64_t)last[0] + 1;
+      end = bgn + J.max_hash_strings - 1;
     }
-    bgn = (uint64_t)last[0] + 1;
-    end = bgn + P.max_hash_strings - 1;
-  }
-  out.close();
+    out.close();
 
-  // ---- -s stats (OIC/overlapInCore.C:569-588)
-  oic_stats_t tot, s;
-  memset(&tot, 0, sizeof(tot));
-  for (int g = 0; g < n_gpus; g++) {
-    oic_get_stats(sh[g].ctx, &s);
-    tot.kmer_hits_without_olap += s.kmer_hits_without_olap; tot.kmer_hits_with_olap += s.kmer_hits_with_olap;
-    tot.multi_overlap += s.multi_overlap; tot.total_overlaps += s.total_overlaps;
-    tot.contained += s.contained; tot.dovetail += s.dovetail;
-    oic_destroy(sh[g].ctx);
+    // ---- -s stats (OIC/overlapInCore.C:569-588)
+    oic_stats_t tot, s;
+    memset(&tot, 0, sizeof(tot));
+    for (int g = 0; g < n_gpus; g++) {
+      oic_get_stats(sh[g].ctx, &s);
+      tot.kmer_hits_without_olap += s.kmer_hits_without_olap; tot.kmer_hits_with_olap += s.kmer_hits_with_olap;
+      tot.multi_overlap += s.multi_overlap; tot.total_overlaps += s.total_overlaps;
+      tot.contained += s.contained; tot.dovetail += s.dovetail;
+    }
+    FILE *stats = stderr;
+    if (job_stat) {
+      stats = fopen(job_stat, "w");
+      if (!stats) { fprintf(stderr, "WARNING: failed to open '%s' for writing: %s\n", job_stat, strerror(errno)); stats = stderr; }
+    }
+    fprintf(stats, " Kmer hits without olaps = %lld\n", (long long)tot.kmer_hits_without_olap);
+    fprintf(stats, "    Kmer hits with olaps = %lld\n", (long long)tot.kmer_hits_with_olap);
+    fprintf(stats, "  Multiple overlaps/pair = %lld\n", (long long)tot.multi_overlap);
+    fprintf(stats, " Total overlaps produced = %lld\n", (long long)tot.total_overlaps);
+    fprintf(stats, "      Contained overlaps = %lld\n", (long long)tot.contained);
+    fprintf(stats, "       Dovetail overlaps = %lld\n", (long long)tot.dovetail);
+    fprintf(stats, "Rejected by short window = %lld\n", 0LL);
+    fprintf(stats, " Rejected by long window = %lld\n", 0LL);
+    if (stats != stderr) fclose(stats);
+    return 0;
+  };
+
+  int rcode = 0;
+  if (!sweep_prefix) rcode = run_job(P, out_name, stat_name);
+  else {
+    for (const OvlJob &j : jobs) {
+      oic_params_t J = P;
+      J.bgn_hash_id = std::max<uint32_t>(1, j.hash_bgn); J.end_hash_id = std::min(num_reads, j.hash_end);
+      J.bgn_ref_id = std::max<uint32_t>(1, j.ref_bgn); J.end_ref_id = std::min(num_reads, j.ref_end);
+      if (j.max_num_reads) { J.max_hash_strings = j.max_num_reads; J.max_hash_data_len = j.max_length; }
+      char bat[16], job[16];
+      snprintf(bat, sizeof(bat), "%03u", j.batch);
+      snprintf(job, sizeof(job), "%06u", j.job);
+      const std::string dir = std::string(sweep_out) + "/" + bat, base = dir + "/" + job;
+      mkdir(sweep_out, 0777);
+      mkdir(dir.c_str(), 0777);
+      const std::string working = base + ".ovb.WORKING", final_name = base + ".ovb", st = base + ".stats";
+      fprintf(stderr, "Job %06u: %s\n", j.job, j.options().c_str());
+      if ((rcode = run_job(J, working.c_str(), st.c_str())) != 0) break;
+      rename(working.c_str(), final_name.c_str());   // the pipeline's success test is "<job>.ovb exists" (OverlapInCore.pm:220-225,405-429)
+    }
   }
-  FILE *stats = stderr;
-  if (stat_name) {
-    stats = fopen(stat_name, "w");
-    if (!stats) { fprintf(stderr, "WARNING: failed to open '%s' for writing: %s\n", stat_name, strerror(errno)); stats = stderr; }
-  }
-  fprintf(stats, " Kmer hits without olaps = %lld\n", (long long)tot.kmer_hits_without_olap);
-  fprintf(stats, "    Kmer hits with olaps = %lld\n", (long long)tot.kmer_hits_with_olap);
-  fprintf(stats, "  Multiple overlaps/pair = %lld\n", (long long)tot.multi_overlap);
-  fprintf(stats, " Total overlaps produced = %lld\n", (long long)tot.total_overlaps);
-  fprintf(stats, "      Contained overlaps = %lld\n", (long long)tot.contained);
-  fprintf(stats, "       Dovetail overlaps = %lld\n", (long long)tot.dovetail);
-  fprintf(stats, "Rejected by short window = %lld\n", 0LL);
-  fprintf(stats, " Rejected by long window = %lld\n", 0LL);
-  if (stats != stderr) fclose(stats);
+  for (int g = 0; g < n_gpus; g++) oic_destroy(sh[g].ctx);
+  if (rcode) return rcode;
   fprintf(stderr, "Bye.\n");
   return 0;
 }

@@ -98,6 +98,18 @@ int oic_load_reads(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const ui
 int oic_load_reads_2bit(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const uint64_t *byte_offsets,
                         const uint32_t *lengths, const uint8_t *packed, const uint8_t *hash_ok, const uint8_t *ref_ok);
 
+/* In-process sweep over the jobs of overlapInCorePartition (OIC/overlapInCorePartition.C, OverlapInCore.pm:184-233): the
+ * pipeline starts one overlapInCore process per (hash range, query range) job, each re-opening the store and rebuilding its
+ * hash block.  With the reads resident, a job is just a new set of ranges: oic_set_job replaces -h, -r, --hashstrings and
+ * --hashdatalen of the context (every other option stays), after which oic_overlap_driver / oic_build_hash_index /
+ * oic_process_overlaps behave exactly as a fresh process started with those options would.  A hash block that was just
+ * built for the same (-h sub-range, --hashstrings, --hashdatalen) is reused, so the consecutive query blocks of one hash
+ * block cost one build (only after oic_set_job: without it every oic_build_hash_index call builds).  oic_reset_stats
+ * zeroes the -s counters between jobs. */
+int  oic_set_job(oic_ctx_t *ctx, uint32_t bgn_hash_id, uint32_t end_hash_id, uint32_t bgn_ref_id, uint32_t end_ref_id,
+                 uint32_t max_hash_strings, uint64_t max_hash_data_len);
+void oic_reset_stats(oic_ctx_t *ctx);
+
 /* Mark_Skip_Kmers input (OIC/overlapInCore-Build_Hash_Index.C:233-286): n k-mers of exactly kmer_len
  * characters, concatenated.  Applied at the end of every subsequent hash build. */
 int oic_set_skip_kmers(oic_ctx_t *ctx, uint64_t n, const char *kmers);

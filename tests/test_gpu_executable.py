@@ -70,3 +70,39 @@ def test_executable_two_shards_same_gpu_count(tmp_path):
     store = H.make_store(reads, str(tmp_path))
     r = subprocess.run([BIN, "--gpus", str(n + 1)] + H.oic_args(P, erate) + ["-o", str(tmp_path / "x.ovb"), store], capture_output=True)
     assert r.returncode != 0
+
+
+@needs_tools
+@pytest.mark.parametrize("part_opts", [["-bl", "40000", "-rs", "60", "-ol", "500"], ["-bs", "45", "-rl", "70000", "-ol", "500"]],
+                         ids=["bl_rs", "bs_rl"])
+def test_sweep_equals_reference_jobs(part_opts, tmp_path):
+    """--sweep: every job of the reference's own overlapInCorePartition run inside ONE process (reads resident, hash blocks
+    reused across the query blocks of a hash block) writes, per job, the same overlaps / .counts / .stats as a separate
+    process of the REFERENCE overlapInCore started with that job's options (OverlapInCore.pm:184-233)."""
+    wd = str(tmp_path)
+    reads = H.gen_reads(genome_len=40000, coverage=9, len_min=600, len_max=2600, err=0.015, seed=77)
+    store = H.make_store(reads, wd)
+    prefix = os.path.join(wd, "asm.partition")
+    subprocess.check_call([os.path.join(H.REF_DIR, "overlapInCorePartition"), "-g", store] + part_opts + ["-o", prefix],
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    bats = open(prefix + ".ovlbat").read().split()
+    jobs = open(prefix + ".ovljob").read().split()
+    opts = open(prefix + ".ovlopt").read().splitlines()
+    assert len(jobs) >= 4
+    common = ["-k", "22", "--hashbits", "17", "--hashload", "0.75", "--maxerate", "0.06", "--minlength", "500"]
+    out = os.path.join(wd, "sweep")
+    with open(os.path.join(wd, "sweep.err"), "w") as ef:
+        subprocess.check_call([BIN, "-t", "3"] + common + ["--sweep", prefix, "--sweep-out", out, store], stderr=ef, stdout=ef)
+    total = 0
+    for bat, job, opt in zip(bats, jobs, opts):
+        ref_prefix = os.path.join(wd, "ref_" + job)
+        ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, ref_prefix, common + opt.split(), 3)
+        want = H.dump_ovb_sorted(store, ovb)
+        base = os.path.join(out, bat, job)
+        assert os.path.exists(base + ".ovb") and not os.path.exists(base + ".ovb.WORKING")
+        got = H.dump_ovb_sorted(store, base + ".ovb")
+        assert got == want, "job %s (%s)" % (job, opt)
+        assert H.parse_stats(base + ".stats") == H.parse_stats(st)
+        assert open(base + ".counts", "rb").read() == open(ref_prefix + ".counts", "rb").read()
+        total += len(want)
+    assert total > 1000
