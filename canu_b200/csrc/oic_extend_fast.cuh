@@ -22,7 +22,10 @@
 
 namespace oic {
 
-constexpr int SW = 1024;            // widest row staged in shared memory (lane c of the lean loop owns chunk c: at most 32 chunks)
+#ifndef OIC_SW
+#define OIC_SW 1024
+#endif
+constexpr int SW = OIC_SW;            // widest row staged in shared memory (lane c of the lean loop owns chunk c: at most 32 chunks)
 constexpr int FROM_NONE = -9;
 constexpr int UNR = 2;              // chunks of a row in flight together
 

@@ -11,6 +11,9 @@
 #ifndef OIC_EXTEND_LEAN_CUH
 #define OIC_EXTEND_LEAN_CUH
 
+#ifndef LEAN_V2
+#define LEAN_V2 1   /* branch-free first slides, merged continuation loop, lane-local best cell (0 = the round-1c loop, kept for A/B builds) */
+#endif
 #ifndef LEAN_U
 #define LEAN_U 2   /* chunks of 32 diagonals in flight together */
 #endif
@@ -118,6 +121,35 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         cap[u] = (i < width) ? imin(m, n - d) : LEAN_IDLE;
       }
       int more = 0;                                      // bit u: the slide of chunk u goes on
+#if LEAN_V2
+      // Branch-free: a cell that does not slide (idle lane, or already at the end of a string) compares the first windows
+      // of the two strings instead and discards the result, so the 4*LU loads of a chunk group issue back to back.
+#pragma unroll
+      for (int u = 0; u < LU; u++) {
+        const bool go = r0[u] < cap[u];
+        const int p = go ? r0[u] : 0, q = go ? r0[u] + dd[u] : 0;
+        int adv = lean_step(Ap, aph + p, Tp, tph + q);
+        adv = go ? adv : 0;
+        r[u] = r0[u] + adv;
+        more |= ((adv == 16) && (r[u] < cap[u])) ? (1 << u) : 0;
+      }
+      // Slides longer than 16 bases (the cells on the alignment path): few lanes, seldom both chunks of a lane, so every
+      // pass advances ONE chunk per lane (the lowest one still sliding) through a single copy of the compare.
+      while (__any_sync(FULL, more != 0)) {
+        static_assert(LU == 2, "the merged continuation loop is written for two chunks in flight");
+        const bool has = more != 0, s1 = (more == 2);
+        int rr = s1 ? r[1] : r[0];
+        const int ds = s1 ? dd[1] : dd[0], cs = s1 ? cap[1] : cap[0];
+        const int p = has ? rr : 0, q = has ? rr + ds : 0;
+        int adv = lean_step(Ap, aph + p, Tp, tph + q);
+        adv = has ? adv : 0;
+        rr += adv;
+        const bool stop = !((adv == 16) && (rr < cs));
+        r[0] = (has && !s1) ? rr : r[0];
+        r[1] = s1 ? rr : r[1];
+        more &= (has && stop) ? (s1 ? ~2 : ~1) : ~0;
+      }
+#else
 #pragma unroll
       for (int u = 0; u < LU; u++) {                     // first 16 bases of every slide, loads back to back
         r[u] = r0[u];
@@ -137,6 +169,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
           }
         }
       }
+#endif
       unsigned em[LU], wc[LU], any_em = 0;
 #pragma unroll
       for (int u = 0; u < LU; u++) {
@@ -148,9 +181,14 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         any_em |= em[u];
         wc[u] = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
+#if LEAN_V2
+        if (l == c) my_ok = ok;
+        if (r[u] > my_mx) { my_mx = r[u]; my_pm = (unsigned)i; }   // this lane's highest cell, lowest chunk on ties
+#else
         const int mx = __reduce_max_sync(FULL, r[u]);
         const unsigned pm = __ballot_sync(FULL, r[u] == mx);
         if (l == c) { my_ok = ok; my_mx = mx; my_pm = pm; }
+#endif
       }
       if (any_em) {                                      // a cell reached the end of A or T: the row stops at the first one
         int uu = 0;
@@ -229,8 +267,12 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     int gmax = __reduce_max_sync(FULL, my_mx);           // highest cell of the row, lowest diagonal on ties
     int gpos = 0;
     if (gmax > longest) {
+#if LEAN_V2
+      gpos = left + (int)__reduce_min_sync(FULL, (my_mx == gmax) ? my_pm : 0x7fffffffu);
+#else
       const int cw = __ffs(__ballot_sync(FULL, my_mx == gmax)) - 1;
       gpos = left + 32 * cw + __ffs(__shfl_sync(FULL, my_pm, cw)) - 1;
+#endif
     }
 
     // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`

@@ -24,6 +24,7 @@
 #include <sys/stat.h>
 
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <thread>
 #include <vector>
@@ -74,6 +75,11 @@ void usage(const char *argv0) {
   fprintf(stderr, "--device d         first CUDA device (default 0)\n");
   fprintf(stderr, "--sweep prefix     run all jobs of prefix.ovlbat/.ovljob/.ovlopt (overlapInCorePartition) in this process\n");
   fprintf(stderr, "--sweep-out dir    directory of the per-job outputs <dir>/<batch>/<job>.ovb/.counts/.stats (default .)\n");
+}
+
+double elapsed() {   // seconds since the first call (progress lines on stderr)
+  static const auto t0 = std::chrono::steady_clock::now();
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
 struct Shard {
@@ -171,6 +177,7 @@ int main(int argc, char **argv) {
   if (n_gpus < 1) n_gpus = 1;
 
   // ---- input
+  elapsed();
   GkStore store(store_path);
   const uint32_t num_reads = store.num_reads();
   std::vector<OvlJob> jobs;   // --sweep: the job list; the reads loaded are the union of all ranges
@@ -231,7 +238,7 @@ int main(int argc, char **argv) {
       });
     for (auto &t : th) t.join();
   }
-  fprintf(stderr, "Loaded reads %u-%u (%llu bases) from '%s'\n", first_id, last_id, (unsigned long long)total, store_path);
+  fprintf(stderr, "Loaded reads %u-%u (%llu bases) from '%s'  [%.2f s]\n", first_id, last_id, (unsigned long long)total, store_path, elapsed());
 
   std::vector<char> skip;   // Mark_Skip_Kmers input: '>' header line, then exactly K bases (Build_Hash_Index.C:233-286)
   uint64_t n_skip = 0;
@@ -269,12 +276,14 @@ int main(int argc, char **argv) {
     return true;
   };
   if (n == 0) { fprintf(stderr, "ERROR: empty read range\n"); return 1; }
+  fprintf(stderr, "%d GPU context(s) ready  [%.2f s]\n", n_gpus, elapsed());
   if (!on_all([&](int g) {
         int rc = two_bit ? oic_load_reads_2bit(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), (const uint8_t *)bases.data(), hash_ok.data(), ref_ok.data())
                          : oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
         if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
         return rc;
       })) return 1;
+  fprintf(stderr, "Reads resident on the GPU(s)  [%.2f s]\n", elapsed());
 
   // One job = what one process of the reference does with its -h / -r / --hashstrings / --hashdatalen.
   auto run_job = [&](const oic_params_t &J, const char *job_out, const char *job_stat) -> int {
@@ -360,13 +369,13 @@ int main(int argc, char **argv) {
       mkdir(sweep_out, 0777);
       mkdir(dir.c_str(), 0777);
       const std::string working = base + ".ovb.WORKING", final_name = base + ".ovb", st = base + ".stats";
-      fprintf(stderr, "Job %06u: %s\n", j.job, j.options().c_str());
+      fprintf(stderr, "Job %06u: %s  [%.2f s]\n", j.job, j.options().c_str(), elapsed());
       if ((rcode = run_job(J, working.c_str(), st.c_str())) != 0) break;
       rename(working.c_str(), final_name.c_str());   // the pipeline's success test is "<job>.ovb exists" (OverlapInCore.pm:220-225,405-429)
     }
   }
   for (int g = 0; g < n_gpus; g++) oic_destroy(sh[g].ctx);
   if (rcode) return rcode;
-  fprintf(stderr, "Bye.\n");
+  fprintf(stderr, "Bye.  [%.2f s]\n", elapsed());
   return 0;
 }

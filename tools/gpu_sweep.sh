@@ -58,4 +58,4 @@ open("$OUT/sweep_$TAG.json", "w").write(json.dumps(d) + "\n")
 print(json.dumps(d))
 PY
 grep -c "Hash block" sweep.log
-tail -3 sweep.log
+grep -v "Hash block" sweep.log | grep "\[" | awk "NR<=6 || NR%5==0" ; cp sweep.log $OUT/sweep_$TAG.log; tail -3 sweep.log
