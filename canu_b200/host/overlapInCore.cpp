@@ -24,6 +24,7 @@
 #include <sys/stat.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <string>
 #include <thread>
@@ -263,18 +264,21 @@ int main(int argc, char **argv) {
 
   // ---- contexts, one per GPU
   std::vector<Shard> sh(n_gpus);
-  for (int g = 0; g < n_gpus; g++) {
-    int rc = oic_create(&P, device0 + g, &sh[g].ctx);
-    if (rc) { fprintf(stderr, "ERROR: %s\n", oic_last_error(nullptr)); return 1; }
-  }
-  auto on_all = [&](auto fn) -> bool {
-    std::vector<std::thread> th;
-    for (int g = 0; g < n_gpus; g++) th.emplace_back([&, g]() { sh[g].rc = fn(g); if (sh[g].rc) sh[g].err = oic_last_error(sh[g].ctx); });
-    for (auto &t : th) t.join();
-    for (int g = 0; g < n_gpus; g++)
+  // run fn(g) on the contexts g0 .. g0+ng-1, one host thread each (the calling thread when there is only one)
+  auto on_range = [&](int g0, int ng, auto fn) -> bool {
+    auto body = [&](int g) { sh[g].rc = fn(g); if (sh[g].rc) sh[g].err = oic_last_error(sh[g].ctx); };
+    if (ng == 1) body(g0);
+    else {
+      std::vector<std::thread> th;
+      for (int g = g0; g < g0 + ng; g++) th.emplace_back(body, g);
+      for (auto &t : th) t.join();
+    }
+    for (int g = g0; g < g0 + ng; g++)
       if (sh[g].rc) { fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str()); return false; }
     return true;
   };
+  auto on_all = [&](auto fn) -> bool { return on_range(0, n_gpus, fn); };
+  if (!on_all([&](int g) { return oic_create(&P, device0 + g, &sh[g].ctx); })) return 1;   // CUDA context start-up in parallel
   if (n == 0) { fprintf(stderr, "ERROR: empty read range\n"); return 1; }
   fprintf(stderr, "%d GPU context(s) ready  [%.2f s]\n", n_gpus, elapsed());
   if (!on_all([&](int g) {
@@ -286,7 +290,10 @@ int main(int argc, char **argv) {
   fprintf(stderr, "Reads resident on the GPU(s)  [%.2f s]\n", elapsed());
 
   // One job = what one process of the reference does with its -h / -r / --hashstrings / --hashdatalen.
-  auto run_job = [&](const oic_params_t &J, const char *job_out, const char *job_stat) -> int {
+  // It runs on the contexts g0 .. g0+ng-1: the query range of every hash sub-block is split over them.
+  auto run_job = [&](const oic_params_t &J, const char *job_out, const char *job_stat, int g0, int ng) -> int {
+    auto on_all = [&](auto fn) -> bool { return on_range(g0, ng, fn); };
+    const int n_gpus = ng;
     if (!on_all([&](int g) {
           oic_reset_stats(sh[g].ctx);
           return oic_set_job(sh[g].ctx, J.bgn_hash_id, J.end_hash_id, J.bgn_ref_id, J.end_ref_id, J.max_hash_strings, J.max_hash_data_len);
@@ -298,7 +305,7 @@ int main(int argc, char **argv) {
     while (bgn < J.end_hash_id) {
       if (end > J.end_hash_id) end = J.end_hash_id;
       std::vector<uint32_t> last(n_gpus, 0);
-      if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g]); })) return 1;
+      if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g - g0]); })) return 1;
       fprintf(stderr, "Hash block %llu-%u built\n", (unsigned long long)bgn, last[0]);
       const uint32_t last_ref = oic_last_processed_ref(J.bgn_ref_id, J.end_ref_id, J.num_threads);
       if (last_ref >= J.bgn_ref_id) {
@@ -314,8 +321,8 @@ int main(int argc, char **argv) {
           cut[g] = J.bgn_ref_id + (uint32_t)(std::lower_bound(w.begin(), w.end(), target) - w.begin());
           if (cut[g] > last_ref + 1 || g == n_gpus) cut[g] = last_ref + 1;
         }
-        if (!on_all([&](int g) { return cut[g + 1] > cut[g] ? oic_process_overlaps(sh[g].ctx, cut[g], cut[g + 1] - 1) : 0; })) return 1;
-        for (int g = 0; g < n_gpus; g++) {
+        if (!on_all([&](int g) { const int i = g - g0; return cut[i + 1] > cut[i] ? oic_process_overlaps(sh[g].ctx, cut[i], cut[i + 1] - 1) : 0; })) return 1;
+        for (int g = g0; g < g0 + ng; g++) {
           uint64_t k = oic_num_overlaps(sh[g].ctx), got = 0;
           rec.resize(6 * k);
           oic_copy_overlaps(sh[g].ctx, reinterpret_cast<oic_ovb_record_t *>(rec.data()), k, &got);
@@ -331,7 +338,7 @@ int main(int argc, char **argv) {
     // ---- -s stats (OIC/overlapInCore.C:569-588)
     oic_stats_t tot, s;
     memset(&tot, 0, sizeof(tot));
-    for (int g = 0; g < n_gpus; g++) {
+    for (int g = g0; g < g0 + ng; g++) {
       oic_get_stats(sh[g].ctx, &s);
       tot.kmer_hits_without_olap += s.kmer_hits_without_olap; tot.kmer_hits_with_olap += s.kmer_hits_with_olap;
       tot.multi_overlap += s.multi_overlap; tot.total_overlaps += s.total_overlaps;
@@ -355,24 +362,52 @@ int main(int argc, char **argv) {
   };
 
   int rcode = 0;
-  if (!sweep_prefix) rcode = run_job(P, out_name, stat_name);
+  if (!sweep_prefix) rcode = run_job(P, out_name, stat_name, 0, n_gpus);
   else {
-    for (const OvlJob &j : jobs) {
-      oic_params_t J = P;
-      J.bgn_hash_id = std::max<uint32_t>(1, j.hash_bgn); J.end_hash_id = std::min(num_reads, j.hash_end);
-      J.bgn_ref_id = std::max<uint32_t>(1, j.ref_bgn); J.end_ref_id = std::min(num_reads, j.ref_end);
-      if (j.max_num_reads) { J.max_hash_strings = j.max_num_reads; J.max_hash_data_len = j.max_length; }
-      char bat[16], job[16];
-      snprintf(bat, sizeof(bat), "%03u", j.batch);
-      snprintf(job, sizeof(job), "%06u", j.job);
-      const std::string dir = std::string(sweep_out) + "/" + bat, base = dir + "/" + job;
-      mkdir(sweep_out, 0777);
-      mkdir(dir.c_str(), 0777);
-      const std::string working = base + ".ovb.WORKING", final_name = base + ".ovb", st = base + ".stats";
-      fprintf(stderr, "Job %06u: %s  [%.2f s]\n", j.job, j.options().c_str(), elapsed());
-      if ((rcode = run_job(J, working.c_str(), st.c_str())) != 0) break;
-      rename(working.c_str(), final_name.c_str());   // the pipeline's success test is "<job>.ovb exists" (OverlapInCore.pm:220-225,405-429)
+    // --sweep: jobs are independent (own hash range, own output files), so with several GPUs every GPU takes WHOLE jobs
+    // from a shared list, heaviest first (a job's work ~ bases of its query range): no cross-GPU barrier per job, a hash
+    // block is built only by the GPU that needs it, and every GPU thread frames / writes its own .ovb files.
+    std::vector<uint64_t> cum(n + 1, 0);
+    for (uint32_t i = 0; i < n; i++) cum[i + 1] = cum[i] + lengths[i];
+    std::vector<size_t> order(jobs.size());
+    std::vector<uint64_t> work(jobs.size(), 0);
+    for (size_t k = 0; k < jobs.size(); k++) {
+      order[k] = k;
+      const uint32_t a = std::max(first_id, std::max<uint32_t>(1, jobs[k].ref_bgn)), b = std::min(last_id, std::min(num_reads, jobs[k].ref_end));
+      if (b >= a) work[k] = cum[b - first_id + 1] - cum[a - first_id];
     }
+    if (n_gpus > 1) std::stable_sort(order.begin(), order.end(), [&](size_t x, size_t y) { return work[x] > work[y]; });
+    std::atomic<size_t> next(0);
+    std::atomic<int> failed(0);
+    mkdir(sweep_out, 0777);
+    auto worker = [&](int g) {
+      for (;;) {
+        const size_t k = next.fetch_add(1);
+        if (k >= order.size() || failed.load()) return;
+        const OvlJob &j = jobs[order[k]];
+        oic_params_t J = P;
+        J.bgn_hash_id = std::max<uint32_t>(1, j.hash_bgn); J.end_hash_id = std::min(num_reads, j.hash_end);
+        J.bgn_ref_id = std::max<uint32_t>(1, j.ref_bgn); J.end_ref_id = std::min(num_reads, j.ref_end);
+        if (j.max_num_reads) { J.max_hash_strings = j.max_num_reads; J.max_hash_data_len = j.max_length; }
+        char bat[16], job[16];
+        snprintf(bat, sizeof(bat), "%03u", j.batch);
+        snprintf(job, sizeof(job), "%06u", j.job);
+        const std::string dir = std::string(sweep_out) + "/" + bat, base = dir + "/" + job;
+        mkdir(dir.c_str(), 0777);
+        const std::string working = base + ".ovb.WORKING", final_name = base + ".ovb", st = base + ".stats";
+        fprintf(stderr, "Job %06u (GPU %d): %s  [%.2f s]\n", j.job, device0 + g, j.options().c_str(), elapsed());
+        const int rc = run_job(J, working.c_str(), st.c_str(), g, 1);
+        if (rc) { failed.store(rc); return; }
+        rename(working.c_str(), final_name.c_str());   // the pipeline's success test is "<job>.ovb exists" (OverlapInCore.pm:220-225,405-429)
+      }
+    };
+    if (n_gpus == 1) worker(0);
+    else {
+      std::vector<std::thread> th;
+      for (int g = 0; g < n_gpus; g++) th.emplace_back(worker, g);
+      for (auto &t : th) t.join();
+    }
+    rcode = failed.load();
   }
   for (int g = 0; g < n_gpus; g++) oic_destroy(sh[g].ctx);
   if (rcode) return rcode;

@@ -106,3 +106,47 @@ def test_sweep_equals_reference_jobs(part_opts, tmp_path):
         assert open(base + ".counts", "rb").read() == open(ref_prefix + ".counts", "rb").read()
         total += len(want)
     assert total > 1000
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@needs_tools
+def test_multi_gpu_executable_equals_single(tmp_path):
+    """N > 1 (needs a box with >= 2 GPUs): `--gpus 2` splits the query range of a plain job over two GPUs, and in --sweep mode
+    hands WHOLE jobs to the GPUs from a shared list; both must write the same overlaps / .counts / .stats as one GPU."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    wd = str(tmp_path)
+    reads = H.gen_reads(genome_len=40000, coverage=9, len_min=600, len_max=2600, err=0.015, seed=78)
+    store = H.make_store(reads, wd)
+    common = ["-k", "22", "--hashbits", "17", "--hashload", "0.75", "--maxerate", "0.06", "--minlength", "500"]
+    # plain job, query range sharded
+    res = {}
+    for g in (1, 2):
+        pre = os.path.join(wd, "plain%d" % g)
+        subprocess.check_call([BIN, "-t", "3", "--gpus", str(g)] + common + ["-h", "1-%d" % reads.n, "-r", "1-%d" % reads.n,
+                               "--hashstrings", "70", "--hashdatalen", "100000000", "-o", pre + ".ovb", "-s", pre + ".stats", store],
+                              stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+        res[g] = (H.dump_ovb_sorted(store, pre + ".ovb"), H.parse_stats(pre + ".stats"), open(pre + ".counts", "rb").read())
+    assert len(res[1][0]) > 500
+    assert res[1] == res[2]
+    # sweep, whole jobs per GPU
+    prefix = os.path.join(wd, "asm.partition")
+    subprocess.check_call([os.path.join(H.REF_DIR, "overlapInCorePartition"), "-g", store, "-bl", "40000", "-rs", "60", "-ol", "500", "-o", prefix],
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    bats = open(prefix + ".ovlbat").read().split()
+    jobs = open(prefix + ".ovljob").read().split()
+    for g in (1, 2):
+        subprocess.check_call([BIN, "-t", "3", "--gpus", str(g)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, "sw%d" % g), store],
+                              stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+    for bat, job in zip(bats, jobs):
+        a, b = os.path.join(wd, "sw1", bat, job), os.path.join(wd, "sw2", bat, job)
+        assert H.dump_ovb_sorted(store, a + ".ovb") == H.dump_ovb_sorted(store, b + ".ovb"), job
+        assert H.parse_stats(a + ".stats") == H.parse_stats(b + ".stats")
+        assert open(a + ".counts", "rb").read() == open(b + ".counts", "rb").read()
