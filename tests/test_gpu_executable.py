@@ -142,11 +142,19 @@ def test_multi_gpu_executable_equals_single(tmp_path):
                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     bats = open(prefix + ".ovlbat").read().split()
     jobs = open(prefix + ".ovljob").read().split()
-    for g in (1, 2):
-        subprocess.check_call([BIN, "-t", "3", "--gpus", str(g)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, "sw%d" % g), store],
-                              stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+    # one GPU; two GPUs as two forked processes (default); two GPUs as two host threads of one process
+    for name, g, env in (("sw1", 1, {}), ("sw2", 2, {}), ("sw2t", 2, {"OIC_SWEEP_THREADS": "1"})):
+        subprocess.check_call([BIN, "-t", "3", "--gpus", str(g)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, name), store],
+                              stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL, env=dict(os.environ, **env))
     for bat, job in zip(bats, jobs):
-        a, b = os.path.join(wd, "sw1", bat, job), os.path.join(wd, "sw2", bat, job)
-        assert H.dump_ovb_sorted(store, a + ".ovb") == H.dump_ovb_sorted(store, b + ".ovb"), job
-        assert H.parse_stats(a + ".stats") == H.parse_stats(b + ".stats")
-        assert open(a + ".counts", "rb").read() == open(b + ".counts", "rb").read()
+        a = os.path.join(wd, "sw1", bat, job)
+        for other in ("sw2", "sw2t"):
+            b = os.path.join(wd, other, bat, job)
+            assert os.path.exists(b + ".ovb") and not os.path.exists(b + ".ovb.WORKING")
+            assert H.dump_ovb_sorted(store, a + ".ovb") == H.dump_ovb_sorted(store, b + ".ovb"), job
+            assert H.parse_stats(a + ".stats") == H.parse_stats(b + ".stats")
+            assert open(a + ".counts", "rb").read() == open(b + ".counts", "rb").read()
+    # a sweep process that cannot get its GPU fails the whole sweep
+    r = subprocess.run([BIN, "-t", "3", "--gpus", str(_n_gpus() + 1)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, "swbad"), store],
+                       capture_output=True)
+    assert r.returncode != 0
