@@ -13,8 +13,6 @@
  *                 the built index, and every job writes the files the pipeline expects from its own process
  *                 (OverlapInCore.pm:184-233): DIR/<batch>/<job>.ovb, .counts, .stats with DIR from --sweep-out (default ".").
  *                 -h / -r / --hashstrings / --hashdatalen come from the job list, every other option applies to all jobs.
- *                 With --gpus N every GPU takes WHOLE jobs from the shared list, heaviest first, one forked process per GPU
- *                 (OIC_SWEEP_THREADS=1: one process, one host thread per GPU).
  */
 #include <ctype.h>
 #include <errno.h>
@@ -23,13 +21,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
-#include <sys/mman.h>
 #include <sys/stat.h>
-#include <sys/wait.h>
-#include <unistd.h>
 
 #include <algorithm>
-#include <new>
 #include <atomic>
 #include <chrono>
 #include <string>
@@ -268,55 +262,6 @@ int main(int argc, char **argv) {
     fprintf(stderr, "Read %llu kmers to mark to skip\n", (unsigned long long)n_skip);
   }
 
-  // ---- --sweep on several GPUs: one PROCESS per GPU, forked here -- before the first CUDA call, after the reads are in host
-  // memory (shared copy-on-write).  A process that drives 8 GPUs pays the CUDA start-up of 8 devices one after the other
-  // (measured on 8 B200: 7.6 s before the first job, 2.3 s of tear-down); a process that sees one device pays it once, and
-  // the 8 start in parallel.  The job list is shared through an anonymous shared mapping: {next job, failure flag}.
-  struct SweepShared { std::atomic<size_t> next; std::atomic<int> failed; };
-  SweepShared *shared = nullptr;
-  int gpu_label = -1;   // this process's GPU in the sweep (children only)
-  std::vector<pid_t> children;
-  if (sweep_prefix) {
-    void *m = mmap(nullptr, 4096, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
-    if (m == MAP_FAILED) { fprintf(stderr, "ERROR: mmap: %s\n", strerror(errno)); return 1; }
-    shared = new (m) SweepShared();
-    shared->next.store(0); shared->failed.store(0);
-    if (n_gpus > 1 && getenv("OIC_SWEEP_THREADS") == nullptr) {
-      std::vector<std::string> visible;   // an existing CUDA_VISIBLE_DEVICES list is honoured: --device / --gpus index into it
-      if (const char *v = getenv("CUDA_VISIBLE_DEVICES")) {
-        std::string cur;
-        for (const char *q = v;; q++) {
-          if (*q == ',' || *q == 0) { if (!cur.empty()) visible.push_back(cur); cur.clear(); if (*q == 0) break; }
-          else cur.push_back(*q);
-        }
-      }
-      fflush(stderr); fflush(stdout);
-      for (int g = 0; g < n_gpus; g++) {
-        const pid_t pid = fork();
-        if (pid < 0) { fprintf(stderr, "ERROR: fork: %s\n", strerror(errno)); return 1; }
-        if (pid == 0) {
-          const int dev = device0 + g;
-          const std::string name = visible.empty() ? std::to_string(dev) : (dev < (int)visible.size() ? visible[dev] : std::string("-1"));
-          setenv("CUDA_VISIBLE_DEVICES", name.c_str(), 1);
-          gpu_label = dev; n_gpus = 1; device0 = 0;
-          children.clear();
-          break;
-        }
-        children.push_back(pid);
-      }
-      if (gpu_label < 0) {   // the parent only waits
-        int bad = 0;
-        for (pid_t pid : children) {
-          int st = 0;
-          if (waitpid(pid, &st, 0) < 0 || !WIFEXITED(st) || WEXITSTATUS(st) != 0) bad = 1;
-        }
-        if (bad || shared->failed.load()) { fprintf(stderr, "ERROR: a sweep process failed\n"); return 1; }
-        fprintf(stderr, "Bye.  [%.2f s]\n", elapsed());
-        return 0;
-      }
-    }
-  }
-
   // ---- contexts, one per GPU
   std::vector<Shard> sh(n_gpus);
   // run fn(g) on the contexts g0 .. g0+ng-1, one host thread each (the calling thread when there is only one)
@@ -332,17 +277,26 @@ int main(int argc, char **argv) {
       if (sh[g].rc) { fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str()); return false; }
     return true;
   };
-  auto on_all = [&](auto fn) -> bool { return on_range(0, n_gpus, fn); };
-  if (!on_all([&](int g) { return oic_create(&P, device0 + g, &sh[g].ctx); })) return 1;   // CUDA context start-up in parallel
   if (n == 0) { fprintf(stderr, "ERROR: empty read range\n"); return 1; }
-  fprintf(stderr, "%d GPU context(s) ready  [%.2f s]\n", n_gpus, elapsed());
-  if (!on_all([&](int g) {
-        int rc = two_bit ? oic_load_reads_2bit(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), (const uint8_t *)bases.data(), hash_ok.data(), ref_ok.data())
-                         : oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
-        if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
-        return rc;
-      })) return 1;
-  fprintf(stderr, "Reads resident on the GPU(s)  [%.2f s]\n", elapsed());
+  // CUDA context + the reads of the whole range resident on GPU g
+  auto bring_up = [&](int g) -> int {
+    int rc = oic_create(&P, device0 + g, &sh[g].ctx);
+    if (rc) { sh[g].err = oic_last_error(nullptr); return rc; }
+    rc = two_bit ? oic_load_reads_2bit(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), (const uint8_t *)bases.data(), hash_ok.data(), ref_ok.data())
+                 : oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
+    if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
+    if (rc) sh[g].err = oic_last_error(sh[g].ctx);
+    fprintf(stderr, "GPU %d: context up, reads resident  [%.2f s]\n", device0 + g, elapsed());
+    return rc;
+  };
+  const bool lazy_bring_up = sweep_prefix != nullptr && n_gpus > 1;   // sweep workers bring their own GPU up (see below)
+  if (!lazy_bring_up) {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_gpus; g++) th.emplace_back([&, g]() { sh[g].rc = bring_up(g); });
+    for (auto &t : th) t.join();
+    for (int g = 0; g < n_gpus; g++)
+      if (sh[g].rc) { fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str()); return 1; }
+  }
 
   // One job = what one process of the reference does with its -h / -r / --hashstrings / --hashdatalen.
   // It runs on the contexts g0 .. g0+ng-1: the query range of every hash sub-block is split over them.
@@ -431,11 +385,19 @@ int main(int argc, char **argv) {
       const uint32_t a = std::max(first_id, std::max<uint32_t>(1, jobs[k].ref_bgn)), b = std::min(last_id, std::min(num_reads, jobs[k].ref_end));
       if (b >= a) work[k] = cum[b - first_id + 1] - cum[a - first_id];
     }
-    if (n_gpus > 1 || gpu_label >= 0) std::stable_sort(order.begin(), order.end(), [&](size_t x, size_t y) { return work[x] > work[y]; });
-    std::atomic<size_t> &next = shared->next;
-    std::atomic<int> &failed = shared->failed;
+    if (n_gpus > 1) std::stable_sort(order.begin(), order.end(), [&](size_t x, size_t y) { return work[x] > work[y]; });
+    std::atomic<size_t> next(0);
+    std::atomic<int> failed(0);
     mkdir(sweep_out, 0777);
+    // CUDA start-up of the devices of one box is serialised by the driver (measured on 8 B200: ~1 s per device, in threads or in
+    // separate processes alike), so every worker brings up its own GPU and starts on the job list as soon as it is ready
+    // instead of waiting for the last one.
     auto worker = [&](int g) {
+      if (lazy_bring_up && (sh[g].rc = bring_up(g)) != 0) {
+        fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str());
+        failed.store(sh[g].rc);
+        return;
+      }
       for (;;) {
         const size_t k = next.fetch_add(1);
         if (k >= order.size() || failed.load()) return;
@@ -450,7 +412,7 @@ int main(int argc, char **argv) {
         const std::string dir = std::string(sweep_out) + "/" + bat, base = dir + "/" + job;
         mkdir(dir.c_str(), 0777);
         const std::string working = base + ".ovb.WORKING", final_name = base + ".ovb", st = base + ".stats";
-        fprintf(stderr, "Job %06u (GPU %d): %s  [%.2f s]\n", j.job, gpu_label >= 0 ? gpu_label : device0 + g, j.options().c_str(), elapsed());
+        fprintf(stderr, "Job %06u (GPU %d): %s  [%.2f s]\n", j.job, device0 + g, j.options().c_str(), elapsed());
         const int rc = run_job(J, working.c_str(), st.c_str(), g, 1);
         if (rc) { failed.store(rc); return; }
         rename(working.c_str(), final_name.c_str());   // the pipeline's success test is "<job>.ovb exists" (OverlapInCore.pm:220-225,405-429)
@@ -464,7 +426,7 @@ int main(int argc, char **argv) {
     }
     rcode = failed.load();
   }
-  for (int g = 0; g < n_gpus; g++) oic_destroy(sh[g].ctx);
+  for (int g = 0; g < n_gpus; g++) if (sh[g].ctx) oic_destroy(sh[g].ctx);
   if (rcode) return rcode;
   fprintf(stderr, "Bye.  [%.2f s]\n", elapsed());
   return 0;

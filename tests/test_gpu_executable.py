@@ -142,13 +142,13 @@ def test_multi_gpu_executable_equals_single(tmp_path):
                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     bats = open(prefix + ".ovlbat").read().split()
     jobs = open(prefix + ".ovljob").read().split()
-    # one GPU; two GPUs as two forked processes (default); two GPUs as two host threads of one process
-    for name, g, env in (("sw1", 1, {}), ("sw2", 2, {}), ("sw2t", 2, {"OIC_SWEEP_THREADS": "1"})):
+    # one GPU; two GPUs (one host thread per GPU, each taking whole jobs)
+    for name, g, env in (("sw1", 1, {}), ("sw2", 2, {})):
         subprocess.check_call([BIN, "-t", "3", "--gpus", str(g)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, name), store],
                               stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL, env=dict(os.environ, **env))
     for bat, job in zip(bats, jobs):
         a = os.path.join(wd, "sw1", bat, job)
-        for other in ("sw2", "sw2t"):
+        for other in ("sw2",):
             b = os.path.join(wd, other, bat, job)
             assert os.path.exists(b + ".ovb") and not os.path.exists(b + ".ovb.WORKING")
             assert H.dump_ovb_sorted(store, a + ".ovb") == H.dump_ovb_sorted(store, b + ".ovb"), job

@@ -48,9 +48,14 @@ for line in open("ovl.ovlopt"):
     b = min(b, len(lens) - 1)
     qb += int(cum[b + 1] - cum[a])
 wall = $t3 - $t2
+import re
+stamps = [(float(m.group(2)), m.group(1)) for m in (re.search(r"^(Job|Bye|GPU \d+: context up|Loaded)[^\[]*\[([0-9.]+) s\]", l) for l in open("sweep.log")) if m]
+first_job = min([t for t, k in stamps if k == "Job"] or [0.0])
+bye = max([t for t, k in stamps if k == "Bye"] or [0.0])
 d = {"tag": "$TAG", "genome_bp": $GENOME, "coverage": $COV, "hash_block_bp": $BL, "gpus": $GPUS, "jobs": $NJOBS, "ovb_files": n_ovb,
      "reads": int(len(lens) - 1), "read_bases": int(lens.sum()), "query_bases_scanned": qb, "overlaps": n_ovl, "ovb_bytes": ovb_bytes,
      "sweep_wall_s": wall, "overlaps_per_sec": n_ovl / wall, "query_mbp_per_sec": qb / 1e6 / wall,
+     "cuda_startup_s": first_job, "jobs_phase_s": bye - first_job, "jobs_phase_query_mbp_per_sec": qb / 1e6 / max(bye - first_job, 1e-9),
      "store_build_s": $t1 - $t0, "extra_args": "$EXTRA",
      "note": "wall time of ONE overlapInCore --sweep process: store open + 2-bit reads to the GPU(s) + every job's hash build, search, "
              ".ovb (snappy) / .counts / .stats files"}
