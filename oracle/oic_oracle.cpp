@@ -610,7 +610,11 @@ void oracle_ctx::find_overlaps(const char *frag, int32_t frag_len, uint32_t frag
   left_end_screened = right_end_screened = false;
   a_olaps_for_frag = b_olaps_for_frag = 0;
 
-  int32_t eff_len = (int32_t)strlen(frag);   // the scan is NUL-driven (:341); RC turns non-ACGT into NUL
+  // The scan is NUL-driven: the first K characters are taken unconditionally (:309-311), then `while (*P != 0)` (:341) stops
+  // at the first NUL at index >= K.  Only the reverse strand can hold NULs (RC turns non-ACGT into NUL).
+  int32_t eff_len = frag_len;
+  for (int32_t i = K; i < frag_len; i++)
+    if (frag[i] == 0) { eff_len = i; break; }
   stats.n_query_bases += eff_len;
   if (eff_len >= K) {
     uint64_t key = 0, bad = 0;

@@ -53,6 +53,15 @@ CASES = {
     # ragged input: many reads shorter than K or than --minlength (never loaded / never queried), a few long ones
     "ragged_tiny": dict(gen=dict(genome_len=6000, coverage=12, len_min=10, len_max=700, err=0.01, seed=8),
                         erate="0.06", params=dict(hash_bits=14, hash_load=0.75, min_olap_len=60), threads=2),
+    # reads with N: the hash side skips windows with a non-acgt base (Build_Hash_Index.C:376-379), the forward query strand treats
+    # 'n' as a wildcard in the edit distance (prefixEditDistance-forward.C:172), the REVERSE strand is reverse-complemented with
+    # non-ACGT -> NUL (AS_UTL_reverseComplement.C:39-72): its seed scan stops at the first NUL and NUL mismatches everything
+    "n_bases": dict(gen=dict(genome_len=30000, coverage=14, len_min=900, len_max=2600, err=0.02, seed=2024),
+                    erate="0.06", params=dict(hash_bits=16, hash_load=0.75), threads=2, inject_n=dict(rate=0.0015, runs=25, seed=99)),
+    # the same in -G mode on short reads (C4 shape with N)
+    "n_bases_partial": dict(gen=dict(genome_len=12000, coverage=25, len_min=150, len_max=150, err=0.005, seed=1044, sub_only=True),
+                            erate="0.06", params=dict(hash_bits=15, hash_load=0.75, partial=1, min_olap_len=40), threads=2,
+                            inject_n=dict(rate=0.003, runs=10, seed=5)),
     # empty output: sparse reads of a large genome share no k-mer runs worth an overlap
     "no_overlaps": dict(gen=dict(genome_len=2000000, coverage=0.02, len_min=900, len_max=1500, err=0.02, seed=12),
                         erate="0.06", params=dict(hash_bits=14, hash_load=0.75), threads=2),
@@ -63,6 +72,8 @@ def build_case(name):
     """-> (reads, params dict for the oracle, erate string, threads, skip k-mer list or None)"""
     c = CASES[name]
     reads = H.gen_reads(**c["gen"])
+    if c.get("inject_n"):
+        inject_n(reads, **c["inject_n"])
     over = dict(c["params"])
     if over.pop("minkmers", False):
         import math
@@ -77,6 +88,22 @@ def build_case(name):
     if c.get("skip"):
         skip = frequent_kmers(reads, P["kmer_len"], 40)
     return reads, P, c["erate"], c["threads"], skip
+
+
+def inject_n(reads, rate, runs, seed):
+    """Overwrite single bases (fraction `rate`) and `runs` short stretches (2-12 bases) of the reads with 'N', seeded."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    total = int(reads.lengths.sum())
+    pos = rng.choice(total, size=max(1, int(total * rate)), replace=False)
+    reads.bases[pos] = ord("N")
+    for _ in range(runs):
+        rid = int(rng.integers(0, reads.n))
+        ln = int(reads.lengths[rid])
+        k = int(rng.integers(2, 13))
+        if ln > k + 2:
+            o = int(reads.offsets[rid]) + int(rng.integers(0, ln - k))
+            reads.bases[o:o + k] = ord("N")
 
 
 def frequent_kmers(reads, K, threshold):
