@@ -113,6 +113,7 @@ struct oic_ctx {
   std::vector<uint32_t> h_len;
   std::vector<uint8_t> h_hash_ok, h_ref_ok;
   uint64_t stream_words = 0;
+  uint64_t n_off = 0;          // word offset of the N-mask streams behind d_fwd / d_rc (0: no loaded read holds an N)
   uint32_t max_read_len = 0;
   DevBuf d_fwd, d_rc, d_pos, d_len;
 
@@ -259,6 +260,7 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
 
   BuildArgs a;
   a.fwd = c->d_fwd.as<uint64_t>();
+  a.n_off = c->n_off;
   a.rd_pos = c->d_pos.as<int64_t>();
   a.rd_len = c->d_len.as<uint32_t>();
   a.str_use = c->d_str_use.as<uint8_t>();
@@ -289,7 +291,7 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   k_sort_mid<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   c->tm.launches += 8;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
-  if (hc.n_inserts != n_windows) return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
+  if (c->n_off ? hc.n_inserts > n_windows : hc.n_inserts != n_windows) return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
   const uint32_t n_occ = hc.n_ovf + hc.n_multi;
   if (hc.occ_cursor != n_occ) return c->fail(OIC_ERR_STATE, "internal: %u list entries allocated, %u on the overflow list", hc.occ_cursor, n_occ);
   if (hc.n_big_lists) {
@@ -433,14 +435,30 @@ static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const ui
   else
     k_pack_reads<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<char>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
                                                                        c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
-                                                                       c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>());
+                                                                       c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>(), 0);
   c->tm.launches += 1;
+  c->n_off = 0;
   DevCounters hc;
   int rcode = read_counters(c, hc);
   if (rcode) return rcode;
   CK(cudaGetLastError());
+  if (hc.bad_base & 2) return c->fail(OIC_ERR_BASES, "a loaded read contains a letter other than ACGTN (a gkpStore never does: gatekeeper rewrites them to N)");
+  if (hc.bad_base & 1) {
+    // some read holds an N: pack again with the N-mask streams behind the base streams (same layout, 0b11 per N)
+    const uint64_t n_off = c->stream_words + 4;
+    CK(c->d_fwd.ensure((2 * n_off + 8) * 8));
+    CK(c->d_rc.ensure((2 * n_off + 8) * 8));
+    CK(cudaMemsetAsync(c->d_fwd.p, 0, (2 * n_off + 8) * 8, c->stream));
+    CK(cudaMemsetAsync(c->d_rc.p, 0, (2 * n_off + 8) * 8, c->stream));
+    k_pack_reads<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(d_ascii.as<char>(), d_off.as<uint64_t>(), c->d_len.as<uint32_t>(),
+                                                                       c->d_pos.as<int64_t>(), n, c->stream_words, c->d_fwd.as<uint64_t>(),
+                                                                       c->d_rc.as<uint64_t>(), c->d_ctr.as<DevCounters>(), n_off);
+    c->tm.launches += 1;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    c->n_off = n_off;
+  }
   t.stop();
-  if (hc.bad_base) return c->fail(OIC_ERR_BASES, "a loaded read contains a non-ACGT base; not supported in this build");
 
   // Edit_Match_Limit for every row an extension can reach: error limit <= ceil(erate * longest read)
   c->max_rows = (int)ceil(c->P.max_erate * (double)c->max_read_len) + 3;
@@ -628,7 +646,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
 
   // ---- K2a seed scan
   ScanArgs sa;
-  sa.fwd = c->d_fwd.as<uint64_t>(); sa.rc = c->d_rc.as<uint64_t>();
+  sa.fwd = c->d_fwd.as<uint64_t>(); sa.rc = c->d_rc.as<uint64_t>(); sa.n_off = c->n_off;
   sa.rd_pos = c->d_pos.as<int64_t>(); sa.rd_len = c->d_len.as<uint32_t>();
   sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.n_queries = nq;
   sa.first_id = c->first_id; sa.hash_bgn_id = c->hb.bgn_id; sa.K = P.kmer_len;
@@ -659,7 +677,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
     StageTimer t(c, &c->tm.ms_group);
     // ---- K2b run lengths
     RunLenArgs ra;
-    ra.fwd = sa.fwd; ra.rc = sa.rc; ra.rd_pos = sa.rd_pos; ra.rd_len = sa.rd_len; ra.qs_read = sa.qs_read;
+    ra.fwd = sa.fwd; ra.rc = sa.rc; ra.n_off = sa.n_off; ra.rd_pos = sa.rd_pos; ra.rd_len = sa.rd_len; ra.qs_read = sa.qs_read;
     ra.hash_ri_bgn = c->hb.bgn_id - c->first_id; ra.K = P.kmer_len; ra.recs = sa.recs; ra.n_chunks = n_chunks;
     ra.chunk_cnt = sa.chunk_cnt; ra.chunk_qs = sa.chunk_qs; ra.has_empty = sa.has_empty;
     ra.qs_tile_base = sa.qs_tile_base; ra.tile_empty = sa.tile_empty;
@@ -751,7 +769,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       CK(c->d_out.ensure((size_t)out_cap * 24 + 24));
       CK(c->d_retry.ensure((size_t)n_pairs * 4 + 4));
       ExtArgs ea;
-      ea.fwd = sa.fwd; ea.rc = sa.rc; ea.rd_pos = sa.rd_pos; ea.rd_len = sa.rd_len; ea.qs_read = sa.qs_read;
+      ea.fwd = sa.fwd; ea.rc = sa.rc; ea.n_off = sa.n_off; ea.rd_pos = sa.rd_pos; ea.rd_len = sa.rd_len; ea.qs_read = sa.qs_read;
       ea.first_id = c->first_id; ea.hash_ri_bgn = c->hb.bgn_id - c->first_id; ea.hash_bgn_id = c->hb.bgn_id;
       ea.str_flags = c->d_str_flags.as<uint8_t>(); ea.qs_screen = c->d_qs_screen.as<uint8_t>();
       ea.seeds = rp.dst; ea.pairs = ga.pairs; ea.info = rp.info; ea.n_pairs = n_pairs;
@@ -776,7 +794,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       CK(c->d_alive.ensure((size_t)n_runs + 4));
       CK(c->d_wide.ensure((size_t)n_runs * 4 + 4));
       CK(c->d_dpool.ensure((size_t)dpool_cap * 4));
-      ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
+      // reads with N take the generic row loop only (the lean loop knows no wildcards): the whole Process_Matches loop in pass 1
+      ea.handoff = (getenv("OIC_NO_SPECULATION") || c->n_off) ? 0 : 1;
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
       ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;

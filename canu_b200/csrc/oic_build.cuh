@@ -28,11 +28,14 @@ namespace oic {
 // one thread per 64-bit word of the padded stream (padding words are written as zero), both strands.
 __global__ void k_pack_reads(const char *__restrict__ ascii, const uint64_t *__restrict__ asc_off,
                              const uint32_t *__restrict__ rd_len, const int64_t *__restrict__ rd_pos, uint32_t n_reads,
-                             uint64_t n_words_total, uint64_t *__restrict__ fwd, uint64_t *__restrict__ rc, DevCounters *ctr) {
+                             uint64_t n_words_total, uint64_t *__restrict__ fwd, uint64_t *__restrict__ rc, DevCounters *ctr, uint64_t n_off) {
+  // 'N' (the only non-ACGT letter a gkpStore holds: gatekeeperCreate.C:107-136 rewrites every other one) packs as code 0 plus
+  // 0b11 in the N-mask stream that follows the base stream at word offset n_off (same layout, so every extraction helper
+  // works on it).  n_off == 0: detection pass only (ctr->bad_base bit 0 = an N was seen, bit 1 = some other letter).
   uint64_t gw = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gw >= n_words_total) return;
   int64_t p0 = (int64_t)gw * 32;
-  uint64_t wf = 0, wr = 0;
+  uint64_t wf = 0, wr = 0, mf = 0, mr = 0;
   unsigned bad = 0;
   if (n_reads && p0 >= rd_pos[0]) {
     uint32_t lo = 0, hi = n_reads;   // largest r with rd_pos[r] <= p0
@@ -56,7 +59,8 @@ __global__ void k_pack_reads(const char *__restrict__ ascii, const uint64_t *__r
             case 'c': case 'C': code = 1; break;
             case 'g': case 'G': code = 2; break;
             case 't': case 'T': code = 3; break;
-            default: code = 0; bad = 1; break;
+            case 'n': case 'N': code = 0; bad |= 1; mf |= 3ULL << (2 * k); break;
+            default: code = 0; bad |= 2; break;
           }
           wf |= (uint64_t)code << (2 * k);
           // reverse-complement base i = complement of forward base len-1-i  (AS_UTL_reverseComplement.C:114-143)
@@ -67,7 +71,8 @@ __global__ void k_pack_reads(const char *__restrict__ ascii, const uint64_t *__r
             case 'c': case 'C': rcode = 2; break;
             case 'g': case 'G': rcode = 1; break;
             case 't': case 'T': rcode = 0; break;
-            default: rcode = 0; bad = 1; break;
+            case 'n': case 'N': rcode = 0; bad |= 1; mr |= 3ULL << (2 * k); break;   // NUL in the reference's reverse strand
+            default: rcode = 0; bad |= 2; break;
           }
           wr |= (uint64_t)rcode << (2 * k);
         }
@@ -76,7 +81,8 @@ __global__ void k_pack_reads(const char *__restrict__ ascii, const uint64_t *__r
   }
   fwd[gw] = wf;
   rc[gw] = wr;
-  if (bad) atomicOr(&ctr->bad_base, 1u);
+  if (n_off) { fwd[gw + n_off] = mf; rc[gw + n_off] = mr; }
+  if (bad) atomicOr(&ctr->bad_base, bad);
 }
 
 // Same streams from the gkpStore's own 2-bit encoding (ST/gkStoreEncode.C:81-114: 4 bases per byte, FIRST base in bits 7-6,
@@ -125,6 +131,7 @@ __global__ void k_pack_2bit(const uint8_t *__restrict__ packed, const uint64_t *
 // ------------------------------------------------------------------------------------------------ K1
 struct BuildArgs {
   const uint64_t *fwd;
+  uint64_t n_off;            // word offset of the N-mask stream behind the base stream (0: no read holds an N)
   const int64_t *rd_pos;     // per read index (0-based within the loaded set)
   const uint32_t *rd_len;
   const uint8_t *str_use;    // per string slot of this block: 1 = read is loaded into the hash
@@ -198,15 +205,24 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
   const int64_t spos = a.rd_pos[a.ri_bgn + s];
   const uint32_t len = a.rd_len[a.ri_bgn + s];
   const int64_t o = p0 - spos + l;
-  const bool valid = a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
+  bool valid_n = true;
   const uint64_t W0 = a.fwd[p0 >> 5], W1 = a.fwd[(p0 >> 5) + 1];
   uint64_t key = l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0;
   key &= (a.K == 32) ? ~0ULL : ((1ULL << (2 * a.K)) - 1);
+  bool prev_n = false;
+  if (a.n_off) {   // a window with an N is not inserted (Char_Is_Bad, Build_Hash_Index.C:376-393)
+    const uint64_t M0 = a.fwd[(p0 >> 5) + a.n_off], M1 = a.fwd[(p0 >> 5) + 1 + a.n_off];
+    uint64_t mk = l ? ((M0 >> (2 * l)) | (M1 << (64 - 2 * l))) : M0;
+    mk &= (a.K == 32) ? ~0ULL : ((1ULL << (2 * a.K)) - 1);
+    if (mk) valid_n = false;
+    prev_n = l ? ((M0 >> (2 * (l - 1))) & 3u) != 0 : (o > 0 && ((a.fwd[(p0 >> 5) - 1 + a.n_off] >> 62) & 3u) != 0);
+  }
   bool claimed = false, conv = false, later = false;
   unsigned long long my_occ = 0;
   uint32_t my_slot = 0;
+  const bool valid = valid_n && a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
   if (valid) {
-    const uint32_t pv = o > 0;
+    const uint32_t pv = o > 0 && !prev_n;   // the window one base earlier holds an N: it is not in the table, a run starts here
     const uint32_t pb = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : (pv ? (uint32_t)(a.fwd[(p0 >> 5) - 1] >> 62) & 3u : 0u);
     my_occ = occ_pack(s, (uint32_t)o, pv, pb);
     uint64_t h = hash_key(key) & a.slot_mask;

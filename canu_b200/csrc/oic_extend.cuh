@@ -26,6 +26,7 @@ namespace oic {
 
 struct ExtArgs {
   const uint64_t *fwd, *rc;
+  uint64_t n_off;             // word offset of the N-mask streams behind the base streams (0: no read holds an N)
   const int64_t *rd_pos;
   const uint32_t *rd_len;
   const uint32_t *qs_read;
@@ -85,6 +86,10 @@ struct WarpScratch {
   const int32_t *match_limit;
   unsigned long long cells, words;   // per-lane partial counters
   long long t_tb;
+  // reads with N (generic row loop only): offset of the N-mask stream in 32-bit words, and which string of the current run
+  // is the query's REVERSE strand, where the reference holds NUL instead of 'n' (0 none, 1 = A, 2 = T)
+  long long n_off32;
+  int n_mode;
 };
 
 }  // namespace oic
@@ -125,6 +130,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
     const int m = s_is_a ? s_n : t_n, n = s_is_a ? t_n : s_n;
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
+    ws.n_mode = (S == a.rc) ? (s_is_a ? 1 : 2) : 0;
     if (LEAN) {
       // the lean loop only walks forward: the leftward run compares the same bases on the reverse-complement streams
       // (base i of a read is base len-1-i of its reverse complement, stored at the same stream offset)
@@ -208,6 +214,8 @@ __device__ __forceinline__ WarpScratch warp_scratch(const ExtArgs &a, uint32_t g
   ws.match_limit = a.match_limit;
   ws.cells = ws.words = 0;
   ws.t_tb = 0;
+  ws.n_off32 = 2 * (long long)a.n_off;
+  ws.n_mode = 0;
   return ws;
 }
 

@@ -40,16 +40,28 @@ __device__ __forceinline__ uint32_t ext16(const uint32_t *__restrict__ Wp, int p
 }
 /* 16-base compare step in either direction: number of equal bases starting at offsets pa / pt and walking by DIR
  * (16 if all equal) */
-__device__ __forceinline__ int step16(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int DIR) {
+/* Reads with N (noff != 0: the N-mask stream lies noff words behind the bases): 'n' in either string matches anything
+ * (prefixEditDistance-forward.C:172) -- except on the query's reverse strand, where the reference holds NUL instead of 'n'
+ * (AS_UTL_reverseComplement.C:39-72), which equals nothing but is still matched by an 'n' of the other string.
+ * nmode: 0 = both strings hold 'n', 1 = A holds NUL, 2 = T holds NUL. */
+__device__ __forceinline__ int step16(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int DIR,
+                                      long long noff = 0, int nmode = 0) {
   const int back = DIR > 0 ? 0 : 15;
-  const uint32_t x = ext16(Ap, pa - back) ^ ext16(Tp, pt - back);
+  uint32_t x = ext16(Ap, pa - back) ^ ext16(Tp, pt - back);
+  if (noff) {
+    const uint32_t ma = ext16(Ap + noff, pa - back), mt = ext16(Tp + noff, pt - back);
+    const uint32_t wild = (nmode == 1 ? 0u : ma) | (nmode == 2 ? 0u : mt);
+    const uint32_t forced = (nmode == 1 ? ma : 0u) | (nmode == 2 ? mt : 0u);
+    x = (x | forced) & ~wild;
+  }
   if (x == 0) return 16;
   return DIR > 0 ? ((__ffs((int)x) - 1) >> 1) : (__clz((int)x) >> 1);
 }
-__device__ __forceinline__ int match_dir(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int limit, int DIR) {
+__device__ __forceinline__ int match_dir(const uint32_t *__restrict__ Ap, int pa, const uint32_t *__restrict__ Tp, int pt, int limit, int DIR,
+                                         long long noff = 0, int nmode = 0) {
   int r = 0;
   while (r < limit) {
-    const int adv = step16(Ap, pa + DIR * r, Tp, pt + DIR * r, DIR);
+    const int adv = step16(Ap, pa + DIR * r, Tp, pt + DIR * r, DIR, noff, nmode);
     r += adv;
     if (adv < 16) break;
   }
@@ -200,7 +212,7 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
   const uint32_t *Ap = reinterpret_cast<const uint32_t *>(A) + (a0 >> 4);
   const uint32_t *Tp = reinterpret_cast<const uint32_t *>(T) + (t0 >> 4);
   const int aph = (int)(a0 & 15), tph = (int)(t0 & 15);
-  const int row0 = match_dir(Ap, aph, Tp, tph, m, DIR);
+  const int row0 = match_dir(Ap, aph, Tp, tph, m, DIR, ws.n_off32, ws.n_mode);
   int32_t *sm_prev = fs.row0 + 2, *sm_cur = fs.row1 + 2;   // shared-memory staging (rows up to SW wide)
   const int32_t *prev = sm_prev;                           // row e-1: shared memory, or the global history when wide
   if (l < 5) sm_prev[l - 2] = (l == 2) ? row0 : -2;
@@ -270,7 +282,7 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
         const int d = left + 32 * (c0 + u) + l;
         r[u] = r0[u];
         if (r0[u] < cap[u]) {                            // (inactive lanes have r0 = cap = -1)
-          r[u] = r0[u] + step16(Ap, aph + DIR * r0[u], Tp, tph + DIR * (r0[u] + d), DIR);
+          r[u] = r0[u] + step16(Ap, aph + DIR * r0[u], Tp, tph + DIR * (r0[u] + d), DIR, ws.n_off32, ws.n_mode);
         }
       }
 #pragma unroll
@@ -280,7 +292,7 @@ __device__ __forceinline__ int dp_run_fast(const int DIR, const ExtArgs &a, Warp
           const int i = 32 * c + l, d = left + i;
           const bool act = i < width;
           if (r[u] - r0[u] == 16 && r[u] < cap[u])       // rare: the slide goes on past 16 bases
-            r[u] += match_dir(Ap, aph + DIR * r[u], Tp, tph + DIR * (r[u] + d), cap[u] - r[u], DIR);
+            r[u] += match_dir(Ap, aph + DIR * r[u], Tp, tph + DIR * (r[u] + d), cap[u] - r[u], DIR, ws.n_off32, ws.n_mode);
           if (r[u] > cap[u]) r[u] = cap[u];
           if (act) {
             cur[i] = r[u];

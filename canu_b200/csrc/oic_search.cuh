@@ -36,6 +36,7 @@ struct PairInfo {
 
 struct ScanArgs {
   const uint64_t *fwd, *rc;
+  uint64_t n_off;                 // word offset of the N-mask streams (0: none)
   const int64_t *rd_pos;
   const uint32_t *rd_len;
   const uint32_t *qs_read;        // per query in batch: read index, or 0xffffffff if the read is skipped
@@ -78,7 +79,24 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
   const int64_t wbase = a.rd_pos[ri] >> 5;
   const uint32_t q_id = a.first_id + ri;
   const uint64_t kmask = (K == 32) ? ~0ULL : ((1ULL << (2 * K)) - 1);
-  const uint32_t n_win = len - K + 1;
+  uint32_t n_win = len - K + 1, eff_len = len;
+  if (a.n_off && strand) {
+    // The reference's reverse strand holds NUL where the read has N (AS_UTL_reverseComplement.C:39-72) and its scan is
+    // NUL-driven: the first K characters are taken as they are, then it stops at the first NUL (Find_Overlaps.C:309-341).
+    for (uint32_t b0 = 0; b0 < len && eff_len == len; b0 += 1024) {
+      const uint32_t wi = (b0 >> 5) + l;
+      uint64_t mw = (wi * 32u < len) ? W[wbase + wi + a.n_off] : 0;
+      if (wi * 32u < (uint32_t)K) mw &= ((uint32_t)K - wi * 32u >= 32u) ? 0ULL : (~0ULL << (2 * ((uint32_t)K - wi * 32u)));
+      const unsigned hit = __ballot_sync(FULL, mw != 0);
+      if (hit) {
+        const int fl = __ffs(hit) - 1;
+        const uint64_t fw = __shfl_sync(FULL, mw, fl);
+        const uint32_t pos = b0 + 32u * fl + ((__ffsll((long long)fw) - 1) >> 1);
+        if (pos < len) eff_len = pos;
+      }
+    }
+    n_win = eff_len - K + 1;   // eff_len >= K by construction
+  }
 
   // per-warp output cursor
   uint32_t cur_chunk = NO_CHUNK, cur_fill = 0, n_rec = 0;
@@ -92,6 +110,12 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
     uint32_t off = t0 + l;
     bool valid = off < n_win;
     uint64_t key = (l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0) & kmask;
+    uint64_t M0 = 0;
+    if (a.n_off) {   // a window with an N (or NUL) never verifies against the all-acgt table strings (Hash_Find's strncmp)
+      M0 = W[wbase + (t0 >> 5) + a.n_off];
+      const uint64_t M1 = W[wbase + (t0 >> 5) + 1 + a.n_off];
+      if ((l ? ((M0 >> (2 * l)) | (M1 << (64 - 2 * l))) : M0) & kmask) valid = false;
+    }
     // occupancy bitmap first (an L2 hit): a window whose home slot is free is absent from the block
     const uint64_t hk = hash_key(key);
     bool maybe = valid;
@@ -118,8 +142,9 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
     uint32_t total = __shfl_sync(FULL, incl, 31);
     // previous query base / previous window Empty for every lane's window
     uint32_t my_prev_base = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : prev_tile_last_base;
+    if (a.n_off && l && ((M0 >> (2 * (l - 1))) & 3u)) my_prev_base = 4;   // previous query base is N: that window was no hit
     uint32_t my_prev_empty = l ? ((empty_mask >> (l - 1)) & 1u) : prev_tile_last_empty;
-    prev_tile_last_base = (uint32_t)(W0 >> 62) & 3u;
+    prev_tile_last_base = ((M0 >> 62) & 3u) ? 4u : (uint32_t)(W0 >> 62) & 3u;
     prev_tile_last_empty = (empty_mask >> 31) & 1u;
     if (total == 0) continue;
     __syncwarp();
@@ -200,7 +225,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
   c_found = warp_sum64(c_found); c_refs = warp_sum64(c_refs); c_add = warp_sum64(c_add);
   if (l == 0) {
     a.qs_screen[qs] = (uint8_t)screen;
-    atomicAdd(&a.ctr->n_query_bases, (unsigned long long)len);
+    atomicAdd(&a.ctr->n_query_bases, (unsigned long long)eff_len);
     atomicAdd(&a.ctr->n_windows, (unsigned long long)n_win);
     if (c_found) atomicAdd(&a.ctr->n_found, c_found);
     if (c_refs) atomicAdd(&a.ctr->n_refs, c_refs);
@@ -212,6 +237,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
 // ------------------------------------------------------------------------------------------------
 struct RunLenArgs {
   const uint64_t *fwd, *rc;
+  uint64_t n_off;                // word offset of the N-mask streams (0: none)
   const int64_t *rd_pos;
   const uint32_t *rd_len;
   const uint32_t *qs_read;
@@ -239,7 +265,19 @@ __global__ void __launch_bounds__(256) k_run_length(RunLenArgs a) {
   int t_len = (int)a.rd_len[hri];
   int K = a.K;
   int limit = imin(s_len - (rec.start + K), t_len - (rec.offset + K));
-  int m = limit > 0 ? match_fwd(S, sp + rec.start + K, a.fwd, tp + rec.offset + K, limit) : 0;
+  int m = 0;
+  if (limit > 0) {
+    if (a.n_off == 0) m = match_fwd(S, sp + rec.start + K, a.fwd, tp + rec.offset + K, limit);
+    else {   // a window that holds an N on either side is no hit: the run of hits ends in front of it
+      const int64_t pa = sp + rec.start + K, pt = tp + rec.offset + K;
+      while (m < limit) {
+        const uint64_t x = (ext32(S, pa + m) ^ ext32(a.fwd, pt + m)) | ext32(S + a.n_off, pa + m) | ext32(a.fwd + a.n_off, pt + m);
+        if (x) { m += (__ffsll((long long)x) - 1) >> 1; break; }
+        m += 32;
+      }
+      if (m > limit) m = limit;
+    }
+  }
   int hits = 1 + m;
   if (a.has_empty && hits > 1) {
     // the run stops in front of the first screened (Empty) window: that window produces no Add_Ref

@@ -25,7 +25,7 @@ extern "C" {
 #define OIC_ERR_CUDA        (-1)   /* CUDA runtime error / no device                          */
 #define OIC_ERR_ARG         (-2)   /* bad argument                                            */
 #define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31, -l, -w ...)  */
-#define OIC_ERR_BASES       (-4)   /* non-ACGT base in a loaded read (not supported yet)      */
+#define OIC_ERR_BASES       (-4)   /* a loaded read holds a letter other than ACGTN           */
 #define OIC_ERR_CAPACITY    (-5)   /* an internal device buffer could not be sized            */
 #define OIC_ERR_STATE       (-6)   /* call order violated (e.g. search before build)          */
 

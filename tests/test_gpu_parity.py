@@ -66,7 +66,7 @@ def test_overlaps_vs_golden_and_oracle(name):
         assert meta["stats"][k] == st[v], k
 
 
-@pytest.mark.parametrize("name", ["c1_small", "repeats_skip", "loadlimit", "c4_short"])
+@pytest.mark.parametrize("name", ["c1_small", "repeats_skip", "loadlimit", "c4_short", "n_bases"])
 def test_index_vs_oracle(name):
     """k-mer index of the LAST hash block: key set, occurrence lists in chain order, Empty flags."""
     reads, P, erate, threads, skip = cases.build_case(name)
@@ -102,7 +102,7 @@ def test_index_vs_oracle(name):
     assert (idx["occ"] == ref_occ).all()
 
 
-@pytest.mark.parametrize("name", ["c1_small", "c2_noisy", "repeats_skip", "c4_short"])
+@pytest.mark.parametrize("name", ["c1_small", "c2_noisy", "repeats_skip", "c4_short", "n_bases", "n_bases_partial"])
 def test_seed_lists_vs_oracle(name):
     """Per (query, strand, hash read): seed list in list order, `consistent`, diag_ct/bgn/end."""
     reads, P, erate, threads, skip = cases.build_case(name)
