@@ -794,8 +794,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       CK(c->d_alive.ensure((size_t)n_runs + 4));
       CK(c->d_wide.ensure((size_t)n_runs * 4 + 4));
       CK(c->d_dpool.ensure((size_t)dpool_cap * 4));
-      // reads with N take the generic row loop only (the lean loop knows no wildcards): the whole Process_Matches loop in pass 1
-      ea.handoff = (getenv("OIC_NO_SPECULATION") || c->n_off) ? 0 : 1;
+      // (pairs with an N in either read are never handed over: the lean loop of pass 2 knows no wildcards)
+      ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
       ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;

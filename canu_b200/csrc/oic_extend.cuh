@@ -341,6 +341,16 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       }
     }
 
+    // a pair with an N in either read stays here for its whole loop: only this kernel's generic row loop knows the N masks
+    bool pair_n = false;
+    if (a.n_off) {
+      uint64_t acc = 0;
+      const int64_t sw = (x.sp >> 5) + (int64_t)a.n_off, tw = (x.tp >> 5) + (int64_t)a.n_off;
+      for (int w = l; w * 32 < x.s_len; w += 32) acc |= x.S[sw + w];
+      for (int w = l; w * 32 < x.t_len; w += 32) acc |= x.T[tw + w];
+      pair_n = __any_sync(FULL, acc != 0);
+    }
+
     OlapInfo distinct[MAX_DISTINCT_OLAPS];
     int distinct_ct = 0;
     bool overflow = false, handed = false;
@@ -377,7 +387,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
         __syncwarp();
       }
       n = newn;
-      if (a.handoff && n > 0) { handed = true; break; }
+      if (a.handoff && n > 0 && !pair_n) { handed = true; break; }
     }
 
     if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
