@@ -131,3 +131,51 @@ def write_skip_file(kmers, path):
     with open(path, "w") as f:
         for k in kmers:
             f.write(">1\n%s\n" % k)
+
+
+# ----------------------------------------------------------------------------- seeded random cases
+ERATES = ["0.03", "0.045", "0.06", "0.1", "0.15"]
+N_FUZZ = 64
+
+
+def fuzz_case(i):
+    """Seeded random job i -> (reads, params, erate string, threads, None): random read shape / error rate, K, --maxerate, -G,
+    -m/-u, -z, --minlength, hash sub-blocks (--hashstrings, tiny tables that trip the load cut-off), -h/-r sub-ranges,
+    thread count (scheduler quirk) and N bases.  The oracle is held to the LIVE reference binary on these (test_oracle.py,
+    where the reference is built) and the CUDA path to the oracle (test_gpu_parity.py)."""
+    import numpy as np
+    rng = np.random.default_rng(7000 + i)
+    short = rng.random() < 0.25
+    if short:
+        lmin = int(rng.integers(100, 200)); lmax = lmin + int(rng.integers(0, 120))
+        glen = int(rng.integers(4000, 12000)); cov = float(rng.uniform(10, 22))
+    else:
+        lmin = int(rng.integers(300, 1500)); lmax = lmin + int(rng.integers(0, 2500))
+        glen = int(rng.integers(8000, 30000)); cov = float(rng.uniform(6, 14))
+    err = float(rng.choice([0.0, 0.005, 0.01, 0.02, 0.04, 0.06]))
+    reads = H.gen_reads(genome_len=glen, coverage=cov, len_min=lmin, len_max=lmax, err=err, seed=int(9000 + i),
+                        sub_only=bool(rng.random() < 0.2))
+    if rng.random() < 0.35:
+        inject_n(reads, rate=float(rng.choice([0.0005, 0.002, 0.01])), runs=int(rng.integers(0, 12)), seed=int(i))
+    erate = str(rng.choice(ERATES))
+    over = dict(kmer_len=int(rng.choice([12, 14, 16, 17, 20, 22, 25, 31])),
+                hash_bits=int(rng.choice([10, 12, 14, 16])), hash_load=float(rng.choice([0.3, 0.6, 0.75, 0.9])),
+                partial=int(short or rng.random() < 0.2), unique_olap=int(rng.random() < 0.7),
+                use_hopeless_check=int(rng.random() < 0.7),
+                min_olap_len=int(rng.choice([40, 60]) if short else rng.choice([100, 250, 500])))
+    n = reads.n
+    over["max_hash_strings"] = int(rng.choice([n, max(2, n // 2), max(2, n // 5), 17]))
+    over["max_hash_data_len"] = int(rng.choice([100000000, max(2000, int(reads.lengths.sum()) // 3)]))
+    if rng.random() < 0.4:
+        a, b = sorted(int(x) for x in rng.integers(1, n + 1, size=2))
+        over["bgn_hash_id"], over["end_hash_id"] = a, max(b, a + 1)
+    else:
+        over["end_hash_id"] = n
+    if rng.random() < 0.4:
+        a, b = sorted(int(x) for x in rng.integers(1, n + 1, size=2))
+        over["bgn_ref_id"], over["end_ref_id"] = a, b
+    else:
+        over["end_ref_id"] = n
+    threads = int(rng.choice([1, 2, 3, 4, 7]))
+    P = H.default_params(max_erate=H.strtof(erate), num_threads=threads, **over)
+    return reads, P, erate, threads, None

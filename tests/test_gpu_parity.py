@@ -181,3 +181,22 @@ def test_overflow_retry_path(name, env, monkeypatch):
     res = H.run_oracle(reads, P, skip_kmers=skip)
     for k in ["ext_calls", "ext_cells", "ext_words"] + STAT_KEYS:
         assert st[k] == res["stats"][k], k
+
+
+@pytest.mark.parametrize("i", list(range(cases.N_FUZZ)))
+def test_fuzz_vs_oracle(i):
+    """Seeded random jobs (tests/cases.py fuzz_case: K, --maxerate, -G, -m/-u, -z, --minlength, hash sub-blocks, load cut-off,
+    -h/-r sub-ranges, thread counts, N bases).  The oracle is held to the live reference binary on the same jobs by
+    test_oracle.py::test_oracle_vs_live_reference_fuzz; here the CUDA path is held to the oracle: records, -s counters, work counters."""
+    reads, P, erate, threads, _ = cases.fuzz_case(i)
+    ov = make_overlapper(reads, P)
+    ov.overlap_driver()
+    mine = formatted(ov.overlaps())
+    st = ov.stats()
+    ov.close()
+    res = H.run_oracle(reads, P)
+    want = sorted(H.format_raw(o) for o in res["overlaps"])
+    assert len(mine) == len(want), (len(mine), len(want))
+    assert mine == want
+    for k in STAT_KEYS + WORK_KEYS:
+        assert st[k] == res["stats"][k], k

@@ -59,6 +59,22 @@ def test_oracle_vs_live_reference(seed, threads):
     check_stats(ref_stats, res["stats"], False)
 
 
+@pytest.mark.skipif(not H.have_ref(), reason="reference binary not built (oracle/build_ref.sh)")
+@pytest.mark.parametrize("i", list(range(cases.N_FUZZ)))
+def test_oracle_vs_live_reference_fuzz(i):
+    """Seeded random jobs (tests/cases.py fuzz_case): the oracle against the reference binary run on the spot."""
+    reads, P, erate, threads, _ = cases.fuzz_case(i)
+    with tempfile.TemporaryDirectory() as wd:
+        store = H.make_store(reads, wd)
+        ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref"),
+                                   H.oic_args(P, erate), threads)
+        ref = H.dump_ovb_sorted(store, ovb)
+        ref_stats = H.parse_stats(st)
+    res = H.run_oracle(reads, P)
+    assert sorted(H.format_raw(o) for o in res["overlaps"]) == ref
+    check_stats(ref_stats, res["stats"], P["partial"])
+
+
 def test_host_tables_monotone():
     lib = H.oracle_lib()
     import numpy as np
