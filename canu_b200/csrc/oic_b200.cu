@@ -739,7 +739,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
     // ---- K3 pairs
     if (n_pairs) {
       StageTimer t3(c, &c->tm.ms_extend);
-      const unsigned grid = 148 * 4, grid_tasks = 148 * TASK_BLOCKS_PER_SM;
+      // lean task kernel: the narrow-staging instance (more resident warps) unless the error rate makes wide bands the rule
+      const bool narrow = !(P.max_erate > 0.06) && getenv("OIC_LEAN_WIDE") == nullptr;
+      const unsigned grid = 148 * 4, grid_tasks = 148 * (narrow ? TASK_BLOCKS_NARROW : TASK_BLOCKS_WIDE);
       const unsigned n_warps = grid_tasks * EXT_WARPS;
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
@@ -804,9 +806,10 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       cudaEventRecord(c->ev_k[1], c->stream);
       c->tm.launches += 1;
       if (ea.handoff) {
-        k_extend_tasks<true><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        if (narrow) k_extend_tasks<LSW_NARROW, TASK_BLOCKS_NARROW><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        else k_extend_tasks<LSW_WIDE, TASK_BLOCKS_WIDE><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
         cudaEventRecord(c->ev_k[2], c->stream);
-        k_extend_tasks<false><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
+        k_extend_tasks<0, 4><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
         k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
         cudaEventRecord(c->ev_k[3], c->stream);
         c->tm.launches += 3;

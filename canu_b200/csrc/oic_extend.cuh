@@ -100,7 +100,8 @@ namespace oic {
 // shared-memory path first; the generic global-memory path only for runs with a row wider than SW
 /* Extend_Alignment.  kind: 0 NONE, 1 LEFT_BRANCH_PT, 2 RIGHT_BRANCH_PT, 3 DOVETAIL; -1 = scratch overflow.
  * The spliced delta list is left in ws.ldelta[0 .. delta_len). */
-template <bool LEAN>
+/* LSW = 0: generic row loop (dp_run_fast); LSW > 0: lean loop with rows of up to LSW diagonals staged in shared memory */
+template <int LSW>
 __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, const uint64_t *S, int64_t sp, int s_len,
                                 const uint64_t *T, int64_t tp, int t_len, int m_start, int m_offset, int m_len,
                                 int &s_lo, int &s_hi, int &t_lo, int &t_hi, int &errors, int &delta_len) {
@@ -131,7 +132,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
     ws.n_mode = (S == a.rc) ? (s_is_a ? 1 : 2) : 0;
-    if (LEAN) {
+    if (LSW) {
       // the lean loop only walks forward: the leftward run compares the same bases on the reverse-complement streams
       // (base i of a read is base len-1-i of its reverse complement, stored at the same stream offset)
       const uint64_t *Ax = A, *Bx = B;
@@ -142,7 +143,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
         Ax = s_is_a ? So : To; Bx = s_is_a ? To : So;
         ax = s_is_a ? s0 : t0; bx = s_is_a ? t0 : s0;
       }
-      errs = dp_run_lean(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, Ax, ax, m, Bx, bx, n, limit, a_end, b_end, lo, to_end, dl);
+      errs = dp_run_lean<LSW ? LSW : 32>(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, Ax, ax, m, Bx, bx, n, limit, a_end, b_end, lo, to_end, dl);
     } else errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
     if (errs < 0) return errs;   // -1 history overflow, -2 (lean only) row wider than the shared-memory staging
     if (side == 0) {
@@ -174,10 +175,18 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
 }
 
 constexpr int EXT_WARPS = 4;
-#ifndef OIC_TASK_BLOCKS
-#define OIC_TASK_BLOCKS 4
+// Two instances of the lean task kernel: staging width x resident blocks per SM.  Measured on B200 (c3 job): 1024 x 4 (128
+// registers) 91.6 ms; 768 x 6 (80 registers, small spills outside the row loop, more L1 left) 88.3 ms; 512 x 8 86.4 ms but 105
+// tasks meet a wider row and are rerun by the generic kernel (+3.1 ms); 1024 x 5/6 99 ms (L1 squeezed).  Low error rates keep
+// the band narrow (no row beyond 640 diagonals at --maxerate 0.06 on 5-15 kb reads); at high rates the wide instance runs.
+#ifndef OIC_SW_NARROW
+#define OIC_SW_NARROW 768
 #endif
-constexpr int TASK_BLOCKS_PER_SM = OIC_TASK_BLOCKS;   // resident blocks of the lean task kernel (5 -> 96 registers, small spills, measured slower)
+#ifndef OIC_TASK_BLOCKS
+#define OIC_TASK_BLOCKS 6
+#endif
+constexpr int LSW_NARROW = OIC_SW_NARROW, LSW_WIDE = SW;
+constexpr int TASK_BLOCKS_NARROW = OIC_TASK_BLOCKS, TASK_BLOCKS_WIDE = 4;
 
 struct PairCtx {   // the strings and IDs of one pair
   const uint64_t *S, *T;
@@ -361,7 +370,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
       const Seed lg = seeds[li];
       int s_lo, s_hi, t_lo, t_hi, errors, dlen;
       ext_calls++;
-      const int kind = extend_alignment<false>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
+      const int kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
                                         errors, dlen);
       if (kind < 0) { overflow = true; break; }
       accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
@@ -428,15 +437,16 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
 /*
  * Pass 2: one warp per (pair, remaining seed): a single Extend_Alignment, result + delta list stored for the commit pass.
  * Tasks are taken from the END of the list: heavy pairs start first in pass 1 but finish (and emit their tasks) last.
- * LEAN = true: the shared-memory-only row loop; a task that meets a row wider than SW is queued for the LEAN = false
+ * LSW > 0: the shared-memory-only row loop; a task that meets a row wider than LSW is queued for the LSW = 0
  * instance of the kernel (generic row loop), which runs right after on just those tasks.
  */
-template <bool LEAN>
-__global__ void __launch_bounds__(EXT_WARPS * 32, LEAN ? TASK_BLOCKS_PER_SM : 4) k_extend_tasks(ExtArgs a) {
+template <int LSW, int BLOCKS>
+__global__ void __launch_bounds__(EXT_WARPS * 32, BLOCKS) k_extend_tasks(ExtArgs a) {
+  constexpr bool LEAN = LSW != 0;
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   WarpScratch ws = warp_scratch(a, gw);
-  __shared__ int32_t s_rows[EXT_WARPS][2][LEAN ? LSTRIDE : SW + 4];
+  __shared__ int32_t s_rows[EXT_WARPS][2][LEAN ? LSW + 8 + 32 * LU : SW + 4];
   FastScratch fs;
   fs.row0 = s_rows[threadIdx.x >> 5][0];
   fs.row1 = s_rows[threadIdx.x >> 5][1];
@@ -456,7 +466,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, LEAN ? TASK_BLOCKS_PER_SM : 4)
     ws.cells = ws.words = 0;
     TaskResult r;
     r.pad = 0; r.delta_off = 0;
-    r.kind = extend_alignment<LEAN>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, r.s_lo, r.s_hi, r.t_lo, r.t_hi,
+    r.kind = extend_alignment<LSW>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, r.s_lo, r.s_hi, r.t_lo, r.t_hi,
                                     r.errors, r.dlen);
     if (LEAN && r.kind == LEAN_WIDE) {
       if (l == 0) a.wide_list[atomicAdd(&a.ctr->n_wide_tasks, 1u)] = tidx;

@@ -1,11 +1,11 @@
 /*
- * oic_extend_lean.cuh -- the row loop of the banded prefix edit distance for the common case: every row at most SW
- * diagonals wide, both live rows in shared memory.  Same recurrence, exits, tie-breaks, counters and history layout as
+ * oic_extend_lean.cuh -- the row loop of the banded prefix edit distance for the common case: every row at most LSW
+ * diagonals wide (LSW = the staging width the kernel was instantiated with, <= SW), both live rows in shared memory.  Same recurrence, exits, tie-breaks, counters and history layout as
  * dp_run_fast (oic_extend_fast.cuh; LIBO/prefixEditDistance-forward.C:110-285, -reverse.C:130-300) -- the results are
  * bit-identical -- but written for instruction count: no generic pointers, two chunks of 32 diagonals per iteration with
  * branch-free bookkeeping (selects on ballot words instead of warp-uniform branches), one uniform branch per chunk pair for
  * the rare "a cell reached the end of a string" exit, direction words gathered in registers and stored once per row.
- * Returns -1 when the rows do not fit the warp's history, -2 when a row is wider than SW (the caller reruns the
+ * Returns -1 when the rows do not fit the warp's history, -2 when a row is wider than LSW (the caller reruns the
  * extension with dp_run_fast).
  */
 #ifndef OIC_EXTEND_LEAN_CUH
@@ -20,7 +20,7 @@
 namespace oic {
 
 constexpr int LU = LEAN_U;
-constexpr int LSTRIDE = SW + 8 + 32 * LU;   // ints per live row: 2 margin + SW + idle-lane slack of the last chunk group
+// ints per live row of the lean loop: 2 margin + staging width + idle-lane slack of the last chunk group = LSW + 8 + 32 * LU
 constexpr int LEAN_WIDE = -2;
 constexpr int LEAN_IDLE = (int)0x80000000;
 
@@ -41,6 +41,7 @@ __device__ __forceinline__ int lean_step(const uint32_t *Ap, int pa, const uint3
   return __clz((int)__brev(x)) >> 1;   // clz(0) = 32 -> 16
 }
 
+template <int LSW>
 __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, WarpScratch &ws, int32_t *srow0, int32_t *srow1,
                                            const uint64_t *__restrict__ A, int64_t a0, int m, const uint64_t *__restrict__ T, int64_t t0,
                                            int n, int error_limit, int &a_end, int &t_end, int &leftover, int &to_end, int &delta_len) {
@@ -88,7 +89,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     right = imin(right + 1, e);
     const int width = right - left + 1;
     const int nch = (width + 31) >> 5;
-    if (width > SW) { errors = LEAN_WIDE; break; }
+    if (width > LSW) { errors = LEAN_WIDE; break; }
     if (e > max_e || next_off + width + 4 + 2 * nch > rowcap) { errors = -1; break; }
     const int off = next_off + 2;
     next_off += width + 4 + 2 * nch;
