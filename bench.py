@@ -36,6 +36,8 @@ LEN_MIN, LEN_MAX = 5000, 15000
 SEED = 1003
 MODE = "blocks"                # "blocks": disjoint query block(s) vs one hash block; "self": -h 1-N -r 1-N on one read set
 PARTIAL, MIN_OLAP, SUB_ONLY, HASH_BITS, REF_SCALE_MBP = 0, 500, False, 23, 20
+REPEATS = None                 # c5: dict(frac, families, unit_min, unit_max, div) -- repeat model of tools/gen_reads.c
+SKIP_T = 0                     # c5: K-mers seen >= SKIP_T times in the loaded reads (both strands) go to the -k skip list
 
 # BASELINE.json's named shapes.  The driver's bench line is c3 (the config the metric is quoted on); the others are run by
 # hand (`--workload`) for the per-shape table of DESIGN.md section 7 and are parity-test cases at reduced size in tests/.
@@ -51,6 +53,11 @@ WORKLOADS = {
     "c4": dict(desc="c4: synthetic 100 Mbp genome, 150 bp reads (substitutions only, 0.5%), -G --minlength 40, k=22, --maxerate 0.06, "
                     "100 Mbp hash block (667 k reads, 1x) vs one 100 Mbp query block per GPU",
                LEN_MIN=150, LEN_MAX=150, READ_ERR=0.005, SUB_ONLY=True, PARTIAL=1, MIN_OLAP=40, HASH_BITS=24, SEED=1004, REF_SCALE_MBP=5),
+    "c5": dict(desc="c5: synthetic 1 Gbp repeat-rich genome (30% of it copies of 500 repeat families, 1-6 kb units, 2% divergence), corrected "
+                    "reads 5-15 kb, 2% error, k=22, --maxerate 0.06, frequent k-mers (>= 4 occurrences in the 0.2x of reads loaded, i.e. copy "
+                    "number >~ 30) on a -k skip list, 100 Mbp hash block (0.1x) vs one 100 Mbp query block per GPU",
+               GENOME=1_000_000_000, SEED=1005, REPEATS=dict(frac=0.3, families=500, unit_min=1000, unit_max=6000, div=0.02), SKIP_T=4,
+               REF_SCALE_MBP=300),
 }
 
 
@@ -68,7 +75,11 @@ def gen_blocks(genome_len, n_blocks, block_bases, seed):
     """reads for n_blocks blocks of ~block_bases each, sampled from one genome (each block = block_bases/genome coverage)"""
     import helpers as H
     cov = n_blocks * block_bases / genome_len
-    return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed, sub_only=SUB_ONLY)
+    rep = {}
+    if REPEATS:   # the number of families follows the genome so that copies per family stay the same on a scaled-down sample
+        rep = dict(repeat_frac=REPEATS["frac"], repeat_families=max(1, int(round(REPEATS["families"] * genome_len / GENOME))),
+                   repeat_min=REPEATS["unit_min"], repeat_max=REPEATS["unit_max"], repeat_div=REPEATS["div"])
+    return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed, sub_only=SUB_ONLY, **rep)
 
 
 class ClockSampler(threading.Thread):
@@ -115,11 +126,11 @@ def reference_leg(steps, warmup, scale_mbp=None, cores=None):
         sample = ("reference overlapInCore -t %d, genome %.1f Mbp at the same coverage: %d reads (%.1f Mbp) against themselves (-h 1-N -r 1-N), "
                   "same read model/flags; wall time of the process" % (cores, scale_mbp, reads.n, qbases / 1e6))
     else:
-        reads = gen_blocks(g, 2, g, SEED + 7)
+        reads = gen_blocks(g, 2, int(g * BLOCK_BASES / GENOME), SEED + 7)
         (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
         qbases = int(reads.lengths[qb - 1:qe].sum())
         P = params_for(he - hb + 1, reads.n, threads=cores)
-        sample = ("reference overlapInCore -t %d, genome %.1f Mbp: hash block %d reads (%.1f Mbp, 1x) x query block %d reads (%.1f Mbp, 1x), "
+        sample = ("reference overlapInCore -t %d, genome %.1f Mbp: hash block %d reads (%.1f Mbp) x query block %d reads (%.1f Mbp), "
                   "same read model/flags as the 100 Mbp job; wall time of the process (store open + hash build + search + .ovb)"
                   % (cores, scale_mbp, he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, qe - qb + 1, qbases / 1e6))
     kind = "reference" if H.have_ref() else "port"
@@ -128,6 +139,11 @@ def reference_leg(steps, warmup, scale_mbp=None, cores=None):
         if kind == "reference":
             store = H.make_store(reads, wd)
             args = H.oic_args(P, ERATE)
+            if SKIP_T:
+                import cases
+                sf = os.path.join(wd, "skip.fasta")
+                cases.write_skip_file(H.frequent_kmers_fast(reads, K, SKIP_T), sf)
+                args += ["-k", sf]
             for i in range(warmup + steps):
                 t0 = time.time()
                 ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref%d" % i), args, cores)
@@ -139,7 +155,7 @@ def reference_leg(steps, warmup, scale_mbp=None, cores=None):
             cores = 1
             for i in range(warmup + steps):
                 t0 = time.time()
-                res = H.run_oracle(reads, P)
+                res = H.run_oracle(reads, P, skip_kmers=H.frequent_kmers_fast(reads, K, SKIP_T) if SKIP_T else None)
                 dt = time.time() - t0
                 if i >= warmup:
                     times.append(dt)
@@ -243,6 +259,15 @@ def main():
                            if a.e2e_input == "2bit" else "ASCII reads in pinned host memory -> oic_load_reads")
 
     ov = api.Overlapper(LP, device=local)
+    n_skip = 0
+    if SKIP_T:   # the -k skip list, from the reads this rank holds (its query block + the hash block)
+        class _R:   # the rank's reads in the shape H.frequent_kmers_fast wants
+            pass
+        rr = _R()
+        rr.bases, rr.offsets, rr.lengths, rr.n = pinned.numpy(), np.asarray(offs, dtype=np.uint64), np.asarray(lens, dtype=np.uint32), len(lens)
+        skip = H.frequent_kmers_fast(rr, K, SKIP_T)
+        n_skip = len(skip)
+        config["skip_kmers"] = n_skip
 
     class DevView:
         def __init__(self, ptr, nbytes):
@@ -330,6 +355,8 @@ def main():
         return dt, n
 
     ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
+    if n_skip:
+        ov.set_skip_kmers(skip)
     for _ in range(a.warmup):
         job(False)
     sampler = ClockSampler(local)

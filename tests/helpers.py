@@ -117,6 +117,33 @@ def encode_2bit(reads_bases, offsets, lengths, out=None):
     return out[:total], boff
 
 
+def frequent_kmers_fast(reads, K, threshold):
+    """Frequent canonical K-mers of a read set as strings (tools/gen_reads.c oic_frequent_kmers): the harness's stand-in for the
+    pipeline's `meryl -Dt -n T` skip list at sizes where the pure-Python counter of tests/cases.py is too slow."""
+    gen_so, _ = build_harness_libs()
+    lib = C.CDLL(gen_so)
+    lib.oic_frequent_kmers.restype = C.c_uint64
+    lib.oic_frequent_kmers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64]
+    bases = np.ascontiguousarray(reads.bases, dtype=np.uint8)
+    offsets = np.ascontiguousarray(reads.offsets[:reads.n], dtype=np.uint64)
+    lengths = np.ascontiguousarray(reads.lengths, dtype=np.uint32)
+    cap = 1 << 22
+    while True:
+        out = np.zeros(cap, dtype=np.uint64)
+        n = lib.oic_frequent_kmers(bases.ctypes.data, offsets.ctypes.data, lengths.ctypes.data, reads.n, K, threshold, out.ctypes.data, cap)
+        if n == 2 ** 64 - 1:
+            raise MemoryError("oic_frequent_kmers")
+        if n <= cap:
+            break
+        cap = int(n)
+    keys = np.sort(out[:n])
+    codes = np.zeros((len(keys), K), dtype=np.uint8)
+    for i in range(K):
+        codes[:, i] = (keys >> np.uint64(2 * i)) & np.uint64(3)
+    letters = np.frombuffer(b"acgt", dtype=np.uint8)[codes]
+    return [row.tobytes().decode() for row in letters]
+
+
 # ----------------------------------------------------------------------------- reference tools
 
 def make_store(reads, workdir, minlength=0):

@@ -147,6 +147,61 @@ void oic_gen_fill(const gen_params_t *p, const uint8_t *g, uint64_t nreads, cons
 
 void oic_gen_free(void *p) { free(p); }
 
+/* Frequent k-mer list of a read set (harness only: what `meryl -Dt -n T` feeds `overlapInCore -k <file>` in the pipeline,
+ * Meryl.pm:634): every canonical K-mer (the smaller of a K-mer and its reverse complement as 2-bit keys, first base in the low
+ * bits) whose occurrences on both strands total >= threshold.  Windows with a non-ACGT base are skipped.  Open-addressing
+ * table, OpenMP over reads.  Returns the number of keys found (written to out_keys up to `cap`), or (uint64_t)-1 on allocation failure. */
+static inline uint64_t fk_mix(uint64_t k) { k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33; return k; }
+uint64_t oic_frequent_kmers(const char *bases, const uint64_t *offsets, const uint32_t *lengths, uint64_t nreads, int K, uint32_t threshold,
+                            uint64_t *out_keys, uint64_t cap) {
+  uint64_t windows = 0;
+  for (uint64_t i = 0; i < nreads; i++) if (lengths[i] >= (uint32_t)K) windows += lengths[i] - K + 1;
+  uint64_t slots = 1024;
+  while (slots < 2 * windows) slots <<= 1;
+  const uint64_t mask = slots - 1, kmask = (K == 32) ? ~0ULL : ((1ULL << (2 * K)) - 1);
+  uint64_t *keys = (uint64_t *)malloc(slots * sizeof(uint64_t));
+  uint32_t *cnt = (uint32_t *)calloc(slots, sizeof(uint32_t));
+  if (!keys || !cnt) { free(keys); free(cnt); return (uint64_t)-1; }
+  memset(keys, 0xff, slots * sizeof(uint64_t));
+#pragma omp parallel for schedule(dynamic, 64)
+  for (uint64_t i = 0; i < nreads; i++) {
+    const char *s = bases + offsets[i];
+    const uint32_t len = lengths[i];
+    uint64_t fw = 0, rv = 0;
+    uint32_t good = 0;
+    for (uint32_t j = 0; j < len; j++) {
+      uint64_t c;
+      switch (s[j]) {
+        case 'a': case 'A': c = 0; break;
+        case 'c': case 'C': c = 1; break;
+        case 'g': case 'G': c = 2; break;
+        case 't': case 'T': c = 3; break;
+        default: c = 4; break;
+      }
+      if (c == 4) { good = 0; fw = rv = 0; continue; }
+      fw = (fw >> 2) | (c << (2 * (K - 1)));          /* first base of the window in the low bits */
+      rv = ((rv << 2) | (3 - c)) & kmask;             /* reverse complement of the window, same convention */
+      if (++good < (uint32_t)K) continue;
+      const uint64_t key = fw < rv ? fw : rv;
+      uint64_t h = fk_mix(key) & mask;
+      for (;;) {
+        uint64_t cur = __atomic_load_n(&keys[h], __ATOMIC_RELAXED);
+        if (cur == ~0ULL) {
+          uint64_t expect = ~0ULL;
+          if (__atomic_compare_exchange_n(&keys[h], &expect, key, 0, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) cur = key; else cur = expect;
+        }
+        if (cur == key) { __atomic_fetch_add(&cnt[h], 1u, __ATOMIC_RELAXED); break; }
+        h = (h + 1) & mask;
+      }
+    }
+  }
+  uint64_t n = 0;
+  for (uint64_t h = 0; h < slots; h++)
+    if (cnt[h] >= threshold) { if (n < cap) out_keys[n] = keys[h]; n++; }
+  free(keys); free(cnt);
+  return n;
+}
+
 /* ASCII reads -> the gkpStore 2-bit encoding (4 bases per byte, first base in bits 7-6, a=0 c=1 g=2 t=3, every read on a
  * byte boundary, ceil(len/4) bytes per read) -- what gatekeeperCreate writes into the `2SEQ` chunk of a read blob
  * (reference: src/stores/gkStoreEncode.C:45-78).  Returns the number of bytes written, or (uint64_t)-1 on a non-ACGT base. */
