@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "oic_process_overlaps", "oic_overlap_driver", "oic_last_processed_ref", "oic_num_overlaps", "oic_copy_overlaps",
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
-    "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats",
+    "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
 ]
 
 
@@ -87,6 +87,8 @@ def load_library():
     lib.oic_set_job.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
     lib.oic_reset_stats.argtypes = [vp]
     lib.oic_build_hash_index.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+    lib.oic_count_kmers.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
+    lib.oic_copy_frequent_kmers.argtypes = [vp, vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.oic_process_overlaps.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.oic_overlap_driver.argtypes = [vp]
     lib.oic_last_processed_ref.restype = C.c_uint32
@@ -251,6 +253,17 @@ class Overlapper:
 
     def set_skip_kmers(self, kmers):
         self._check(self.lib.oic_set_skip_kmers(self._h, len(kmers), "".join(kmers).encode()), "oic_set_skip_kmers")
+
+    def count_kmers(self, K, min_count):
+        """canonical K-mers of all loaded reads seen >= min_count times (meryl -B -C + meryl -Dt -n): (keys uint64 ascending, first
+        base in the high bits; counts uint32; info dict with passes / device_ms)"""
+        n, passes, ms = C.c_uint64(0), C.c_uint32(0), C.c_double(0.0)
+        self._check(self.lib.oic_count_kmers(self._h, K, min_count, C.byref(n), C.byref(passes), C.byref(ms)), "oic_count_kmers")
+        keys = np.zeros(n.value, dtype=np.uint64)
+        counts = np.zeros(n.value, dtype=np.uint32)
+        got = C.c_uint64(0)
+        self._check(self.lib.oic_copy_frequent_kmers(self._h, keys.ctypes.data, counts.ctypes.data, n.value, C.byref(got)), "oic_copy_frequent_kmers")
+        return keys[:got.value], counts[:got.value], {"passes": passes.value, "device_ms": ms.value}
 
     def build_hash_index(self, bgn_id, end_id):
         last = C.c_uint32(0)

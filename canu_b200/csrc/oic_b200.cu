@@ -1,7 +1,8 @@
 /*
  * oic_b200.cu -- context, host orchestration and the C ABI (include/oic_b200.h) of the B200-native
  * overlapInCore path.  Kernels live in oic_build.cuh (pack + k-mer index), oic_search.cuh (seed scan, run
- * grouping, Add_Match replay) and oic_extend.cuh (banded prefix edit distance + overlap output).
+ * grouping, Add_Match replay), oic_extend.cuh (banded prefix edit distance + overlap output) and oic_count.cuh (canonical
+ * K-mer counts of the loaded reads: the frequent-k-mer list the pipeline takes from meryl).
  *
  * Reference call stack replaced: OverlapDriver -> Build_Hash_Index -> Process_Overlaps ->
  * Find_Overlaps -> Process_String_Olaps -> Process_Matches -> Extend_Alignment -> Output_Overlap.
@@ -19,6 +20,7 @@
 
 #include "../../include/oic_b200.h"
 #include "oic_extend.cuh"
+#include "oic_count.cuh"
 
 using namespace oic;
 
@@ -143,6 +145,11 @@ struct oic_ctx {
   double ml_erate = -1.0; int ml_rows = -1;   // what d_match_limit was built for
   uint64_t rec_cap = 0;       // run records per batch
   uint64_t batch_bases = 0;
+
+  // canonical K-mer counts (oic_count_kmers)
+  DevBuf d_kc_keys, d_kc_cnt, d_kc_out_keys, d_kc_out_cnt, d_kc_n;
+  std::vector<std::pair<uint64_t, uint32_t>> freq;   // {key (first base high), count}, ascending
+  float kc_ms = 0;
 
   std::vector<oic_ovb_record_t> overlaps;
   oic_stats_t stats = {};
@@ -369,7 +376,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_keys, &c->d_kc_cnt, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
@@ -1096,6 +1103,95 @@ int oic_dump_pairs(oic_ctx_t *c, uint64_t *n_pairs, uint64_t *n_matches, int64_t
 
 
 /* Measured INT32 issue rates of this GPU in Gop/s (thread operations): alu = LOP3/IADD3 chains, imad = IMAD chains. */
+int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_found, uint32_t *n_passes, double *device_ms) {
+  if (!c) return OIC_ERR_ARG;
+  if (K < 2 || K > 31) return c->fail(OIC_ERR_UNSUPPORTED, "oic_count_kmers: K must be 2..31");
+  if (c->n_reads == 0) return c->fail(OIC_ERR_STATE, "oic_count_kmers before oic_load_reads");
+  cudaSetDevice(c->device);
+  if (min_count < 1) min_count = 1;
+  uint64_t windows = 0;
+  for (uint32_t i = 0; i < c->n_reads; i++) if (c->h_len[i] >= K) windows += c->h_len[i] - K + 1;
+  c->freq.clear();
+  if (n_found) *n_found = 0;
+  if (n_passes) *n_passes = 0;
+  if (device_ms) *device_ms = 0.0;
+  if (windows == 0) return OIC_OK;
+  // table of {8-byte key, 4-byte count}, at most half full even if every window is a different K-mer; read sets whose
+  // table does not fit the budget are counted in n_pass passes, each over one hash partition of the K-mers
+  size_t free_b = 0, total_b = 0;
+  cudaMemGetInfo(&free_b, &total_b);
+  unsigned long long budget = (unsigned long long)(free_b + c->d_kc_keys.cap + c->d_kc_cnt.cap) * 6 / 10;
+  uint64_t floor_slots = 1ull << 20;
+  if (const char *e = getenv("OIC_COUNT_BUDGET_MB")) { budget = strtoull(e, nullptr, 10) << 20; floor_slots = 4096; }   // test knob: forces several passes
+  uint32_t n_pass = 1;
+  uint64_t slots = 0;
+  for (;; n_pass++) {
+    slots = 1024;
+    while (slots < 2 * ((windows + n_pass - 1) / n_pass) + 2 * (windows / n_pass / 16)) slots <<= 1;   // + slack for uneven partitions
+    if (slots * 12ull <= budget || slots <= floor_slots) break;
+    if (n_pass > 4096) return c->fail(OIC_ERR_CAPACITY, "oic_count_kmers: no memory for the count table");
+  }
+  CK(c->d_kc_keys.ensure(slots * 8));
+  CK(c->d_kc_cnt.ensure(slots * 4));
+  CK(c->d_kc_n.ensure(8));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, c->stream);
+  CountArgs a;
+  a.fwd = c->d_fwd.as<uint64_t>(); a.n_off = c->n_off; a.rd_pos = c->d_pos.as<int64_t>(); a.rd_len = c->d_len.as<uint32_t>();
+  a.n_reads = c->n_reads; a.n_words = c->stream_words - 4; a.K = (int)K;
+  a.keys = c->d_kc_keys.as<unsigned long long>(); a.cnt = c->d_kc_cnt.as<uint32_t>(); a.slot_mask = slots - 1; a.n_pass = n_pass;
+  int rc = OIC_OK;
+  for (uint32_t pass = 0; pass < n_pass && rc == OIC_OK; pass++) {
+    a.pass = pass;
+    CK(cudaMemsetAsync(c->d_kc_keys.p, 0xff, slots * 8, c->stream));
+    CK(cudaMemsetAsync(c->d_kc_cnt.p, 0, slots * 4, c->stream));
+    k_count_kmers<<<nblocks(a.n_words * 32, 256), 256, 0, c->stream>>>(a);
+    // how many K-mers reach min_count, then collect them
+    unsigned long long n = 0;
+    CK(cudaMemsetAsync(c->d_kc_n.p, 0, 8, c->stream));
+    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.keys, a.cnt, slots, min_count, nullptr, nullptr, 0, c->d_kc_n.as<unsigned long long>());
+    CK(cudaMemcpyAsync(&n, c->d_kc_n.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    c->tm.launches += 2;
+    if (n == 0) continue;
+    CK(c->d_kc_out_keys.ensure(n * 8));
+    CK(c->d_kc_out_cnt.ensure(n * 4));
+    CK(cudaMemsetAsync(c->d_kc_n.p, 0, 8, c->stream));
+    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.keys, a.cnt, slots, min_count, c->d_kc_out_keys.as<unsigned long long>(),
+                                                               c->d_kc_out_cnt.as<uint32_t>(), n, c->d_kc_n.as<unsigned long long>());
+    std::vector<unsigned long long> hk(n);
+    std::vector<uint32_t> hcnt(n);
+    CK(cudaMemcpyAsync(hk.data(), c->d_kc_out_keys.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(hcnt.data(), c->d_kc_out_cnt.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    c->tm.launches += 1;
+    c->tm.d2h_bytes += n * 12;
+    const size_t old = c->freq.size();
+    c->freq.resize(old + n);
+    for (size_t i = 0; i < n; i++) c->freq[old + i] = std::make_pair((uint64_t)hk[i], hcnt[i]);
+  }
+  cudaEventRecord(e1, c->stream);
+  cudaEventSynchronize(e1);
+  cudaEventElapsedTime(&c->kc_ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  std::sort(c->freq.begin(), c->freq.end());   // ascending K-mer order = the order of `meryl -Dt`
+  if (n_found) *n_found = c->freq.size();
+  if (n_passes) *n_passes = n_pass;
+  if (device_ms) *device_ms = c->kc_ms;
+  return rc;
+}
+
+int oic_copy_frequent_kmers(oic_ctx_t *c, uint64_t *keys, uint32_t *counts, uint64_t capacity, uint64_t *n_copied) {
+  if (!c || (capacity && !keys)) return OIC_ERR_ARG;
+  const uint64_t n = std::min<uint64_t>(capacity, c->freq.size());
+  for (uint64_t i = 0; i < n; i++) { keys[i] = c->freq[i].first; if (counts) counts[i] = c->freq[i].second; }
+  if (n_copied) *n_copied = n;
+  return OIC_OK;
+}
+
 int oic_measure_int32_peak(int device, double *alu_gops, double *imad_gops) {
   if (cudaSetDevice(device) != cudaSuccess) return OIC_ERR_CUDA;
   cudaDeviceProp prop;

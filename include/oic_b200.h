@@ -174,6 +174,18 @@ int oic_dump_index(oic_ctx_t *ctx, uint64_t *n_keys, uint64_t *n_occ, uint64_t *
 void oic_set_debug(oic_ctx_t *ctx, uint32_t mask);
 int oic_dump_pairs(oic_ctx_t *ctx, uint64_t *n_pairs, uint64_t *n_matches, int64_t *pairs, int32_t *matches);
 
+/* Canonical K-mer counts of ALL loaded reads -- the step upstream of overlapInCore in the pipeline.
+ * Replaces `meryl -B -C -m K -s <gkpStore>` (src/meryl/meryl-build.C: canonical = the lexicographically smaller of a K-mer and
+ * its reverse complement; windows with a non-ACGT base are skipped) followed by `meryl -Dt -n min_count` (src/meryl/
+ * meryl-dump.C, called at src/pipelines/canu/Meryl.pm:634 to write the `-k` skip list of overlapInCore).  The result stays in
+ * the context, ascending by K-mer; n_passes = hash partitions the count was done in (1 unless the table did not fit),
+ * device_ms = CUDA-event time of the count.  K 2..31. */
+int oic_count_kmers(oic_ctx_t *ctx, uint32_t K, uint32_t min_count, uint64_t *n_found, uint32_t *n_passes, double *device_ms);
+
+/* The K-mers found by oic_count_kmers, in the order `meryl -Dt` prints them.  keys[i] holds the K-mer with its FIRST base in the
+ * HIGH bits (a=0 c=1 g=2 t=3, 2 bits per base); counts may be NULL. */
+int oic_copy_frequent_kmers(oic_ctx_t *ctx, uint64_t *keys, uint32_t *counts, uint64_t capacity, uint64_t *n_copied);
+
 /* Roofline denominator of the extension stage: INT32 issue rates of `device`, measured (thread Gop/s).  alu = chains of
  * LOP3 + IADD3 (the pipe the edit-distance rows live on; reference code measured against: LIBO/prefixEditDistance-forward.C
  * inner loop), imad = chains of IMAD.  Takes a few milliseconds. */

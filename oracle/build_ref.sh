@@ -25,7 +25,7 @@ if [ ! -d "$REF" ]; then
   exit 0
 fi
 if [ -x "$OUT/overlapInCore" ] && [ -x "$OUT/gatekeeperCreate" ] && [ -x "$OUT/overlapConvert" ] \
-   && [ -x "$OUT/overlapInCorePartition" ] && [ "$1" != "-f" ]; then
+   && [ -x "$OUT/overlapInCorePartition" ] && [ -x "$OUT/meryl" ] && [ "$1" != "-f" ]; then
   exit 0
 fi
 
@@ -76,8 +76,19 @@ compile() {  # src -> obj path (echoed)
   echo "$o"
 }
 
+# meryl (the k-mer counter upstream of overlapInCore: `meryl -B -C ...` then `meryl -Dt -n T` writes the -k skip list,
+# Meryl.pm:434-450,634) -- the oracle of the frequent-k-mer row
+MERYL_SRCS="
+meryl/meryl-args.C meryl/meryl-binaryOp.C meryl/meryl-build.C meryl/meryl-dump.C meryl/meryl-estimate.C meryl/meryl-merge.C
+meryl/meryl-unaryOp.C meryl/meryl.C meryl/libmeryl.C
+meryl/libleaff/fastaFile.C meryl/libleaff/fastaStdin.C meryl/libleaff/fastqFile.C meryl/libleaff/fastqStdin.C
+meryl/libleaff/gkStoreFile.C meryl/libleaff/merStream.C meryl/libleaff/seqCache.C meryl/libleaff/seqFactory.C
+meryl/libleaff/seqStore.C meryl/libleaff/seqStream.C meryl/libleaff/sffFile.C
+"
+INC="$INC -I$REF/meryl"
+
 pids=""; LIB_OBJS=""
-for s in $LIB_SRCS $OIC_SRCS stores/gatekeeperCreate.C overlapInCore/overlapConvert.C overlapInCore/overlapInCorePartition.C; do
+for s in $LIB_SRCS $OIC_SRCS $MERYL_SRCS stores/gatekeeperCreate.C overlapInCore/overlapConvert.C overlapInCore/overlapInCorePartition.C; do
   ( compile "$s" >/dev/null ) &
   pids="$pids $!"
   # bound parallelism to 8
@@ -92,4 +103,6 @@ $CXX -o "$OUT/overlapInCore"          $OIC_OBJS $LIB_OBJS $LD
 $CXX -o "$OUT/gatekeeperCreate"       "$(compile stores/gatekeeperCreate.C)" $LIB_OBJS $LD
 $CXX -o "$OUT/overlapConvert"         "$(compile overlapInCore/overlapConvert.C)" $LIB_OBJS $LD
 $CXX -o "$OUT/overlapInCorePartition" "$(compile overlapInCore/overlapInCorePartition.C)" $LIB_OBJS $LD
+MERYL_OBJS=""; for s in $MERYL_SRCS; do MERYL_OBJS="$MERYL_OBJS $(compile $s)"; done
+$CXX -o "$OUT/meryl"                  $MERYL_OBJS $LIB_OBJS $LD
 echo "build_ref.sh: built reference tools in $OUT" >&2

@@ -133,6 +133,10 @@ def write_skip_file(kmers, path):
             f.write(">1\n%s\n" % k)
 
 
+# (case, K, min count) of the frequent-k-mer fixtures (tests/golden/make_golden_kmers.py: reference meryl output)
+KMER_CASES = [("repeats_skip", 22, 40), ("repeats_skip", 17, 14), ("c1_small", 31, 14), ("n_bases", 22, 7), ("c4_short", 14, 12)]
+
+
 # ----------------------------------------------------------------------------- seeded random cases
 ERATES = ["0.03", "0.045", "0.06", "0.1", "0.15"]
 N_FUZZ = 64

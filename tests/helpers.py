@@ -117,31 +117,59 @@ def encode_2bit(reads_bases, offsets, lengths, out=None):
     return out[:total], boff
 
 
-def frequent_kmers_fast(reads, K, threshold):
-    """Frequent canonical K-mers of a read set as strings (tools/gen_reads.c oic_frequent_kmers): the harness's stand-in for the
-    pipeline's `meryl -Dt -n T` skip list at sizes where the pure-Python counter of tests/cases.py is too slow."""
+def count_kmers_cpu(reads, K, threshold):
+    """CPU restatement of `meryl -B -C` + `meryl -Dt -n threshold` (tools/gen_reads.c oic_frequent_kmers): canonical K-mers seen
+    >= threshold times in the read set -> (keys uint64 ascending, first base in the HIGH bits; counts uint32)."""
     gen_so, _ = build_harness_libs()
     lib = C.CDLL(gen_so)
     lib.oic_frequent_kmers.restype = C.c_uint64
-    lib.oic_frequent_kmers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64]
+    lib.oic_frequent_kmers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64]
     bases = np.ascontiguousarray(reads.bases, dtype=np.uint8)
     offsets = np.ascontiguousarray(reads.offsets[:reads.n], dtype=np.uint64)
     lengths = np.ascontiguousarray(reads.lengths, dtype=np.uint32)
     cap = 1 << 22
     while True:
-        out = np.zeros(cap, dtype=np.uint64)
-        n = lib.oic_frequent_kmers(bases.ctypes.data, offsets.ctypes.data, lengths.ctypes.data, reads.n, K, threshold, out.ctypes.data, cap)
+        keys = np.zeros(cap, dtype=np.uint64)
+        counts = np.zeros(cap, dtype=np.uint32)
+        n = lib.oic_frequent_kmers(bases.ctypes.data, offsets.ctypes.data, lengths.ctypes.data, reads.n, K, threshold,
+                                   keys.ctypes.data, counts.ctypes.data, cap)
         if n == 2 ** 64 - 1:
             raise MemoryError("oic_frequent_kmers")
         if n <= cap:
             break
         cap = int(n)
-    keys = np.sort(out[:n])
+    order = np.argsort(keys[:n], kind="stable")
+    return keys[:n][order], counts[:n][order]
+
+
+def kmer_strings(keys, K, upper=False):
+    """uint64 keys (first base in the high bits) -> list of K-letter strings"""
+    keys = np.asarray(keys, dtype=np.uint64)
     codes = np.zeros((len(keys), K), dtype=np.uint8)
     for i in range(K):
-        codes[:, i] = (keys >> np.uint64(2 * i)) & np.uint64(3)
-    letters = np.frombuffer(b"acgt", dtype=np.uint8)[codes]
+        codes[:, i] = (keys >> np.uint64(2 * (K - 1 - i))) & np.uint64(3)
+    letters = np.frombuffer(b"ACGT" if upper else b"acgt", dtype=np.uint8)[codes]
     return [row.tobytes().decode() for row in letters]
+
+
+def meryl_dump_text(keys, counts, K):
+    """the text `meryl -Dt -n T` prints (meryl-dump.C): ">count\nKMER\n" per K-mer, ascending"""
+    return "".join(">%d\n%s\n" % (int(c), k) for c, k in zip(counts, kmer_strings(keys, K, upper=True)))
+
+
+def frequent_kmers_fast(reads, K, threshold):
+    """Frequent canonical K-mers of a read set as strings: the harness's stand-in for the pipeline's `meryl -Dt -n T` skip list
+    at sizes where the pure-Python counter of tests/cases.py is too slow."""
+    return kmer_strings(count_kmers_cpu(reads, K, threshold)[0], K)
+
+
+def run_meryl(store, K, threshold, workdir, threads=4):
+    """reference meryl as the pipeline runs it (Meryl.pm:434-450, 634): build the canonical count database, dump mers >= threshold"""
+    db = os.path.join(workdir, "ref.ms%d" % K)
+    with open(os.path.join(workdir, "meryl.err"), "w") as ef:
+        subprocess.check_call([os.path.join(REF_DIR, "meryl"), "-B", "-C", "-L", "2", "-v", "-m", str(K), "-threads", str(threads),
+                               "-memory", "1024", "-s", store, "-o", db], stdout=ef, stderr=ef)
+        return subprocess.check_output([os.path.join(REF_DIR, "meryl"), "-Dt", "-n", str(threshold), "-s", db], stderr=ef).decode()
 
 
 # ----------------------------------------------------------------------------- reference tools

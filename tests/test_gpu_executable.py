@@ -158,3 +158,20 @@ def test_multi_gpu_executable_equals_single(tmp_path):
     r = subprocess.run([BIN, "-t", "3", "--gpus", str(_n_gpus() + 1)] + common + ["--sweep", prefix, "--sweep-out", os.path.join(wd, "swbad"), store],
                        capture_output=True)
     assert r.returncode != 0
+
+
+@needs_tools
+@pytest.mark.parametrize("name,K,T", [("n_bases", 22, 7), ("c4_short", 14, 12)])
+def test_frequent_mers_tool_vs_meryl(name, K, T, tmp_path):
+    """canu_b200/bin/frequentMers on a gkpStore writes the bytes of the reference's `meryl -Dt -n T` (golden fixture), and of the
+    reference's meryl run on the spot when it is there"""
+    import gzip
+    reads = cases.build_case(name)[0]
+    store = H.make_store(reads, str(tmp_path))
+    out = str(tmp_path / "freq.fasta")
+    subprocess.check_call([os.path.join(os.path.dirname(BIN), "frequentMers"), "-m", str(K), "-n", str(T), "-s", store, "-o", out],
+                          stderr=subprocess.DEVNULL)
+    got = open(out).read()
+    gold = gzip.open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
+    assert got == gold
+    assert got == H.run_meryl(store, K, T, str(tmp_path))

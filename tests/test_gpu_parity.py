@@ -200,3 +200,37 @@ def test_fuzz_vs_oracle(i):
     assert mine == want
     for k in STAT_KEYS + WORK_KEYS:
         assert st[k] == res["stats"][k], k
+
+
+@pytest.mark.parametrize("name,K,T", cases.KMER_CASES)
+@pytest.mark.parametrize("budget_mb", [None, "1"])
+def test_kmer_counts_vs_meryl(name, K, T, budget_mb, monkeypatch):
+    """frequent-k-mer row: oic_count_kmers on the GPU writes the bytes the reference's meryl wrote
+    (`meryl -B -C` + `meryl -Dt -n T`, fixtures of tests/golden/make_golden_kmers.py), in one pass and -- with the table budget
+    forced down to 1 MB -- in many hash-partition passes; the CPU restatement agrees key by key."""
+    if budget_mb:
+        monkeypatch.setenv("OIC_COUNT_BUDGET_MB", budget_mb)
+    reads = cases.build_case(name)[0]
+    P = H.default_params(kmer_len=K, max_hash_strings=reads.n, end_hash_id=reads.n, end_ref_id=reads.n)
+    ov = make_overlapper(reads, P)
+    keys, counts, info = ov.count_kmers(K, T)
+    ov.close()
+    assert (info["passes"] > 1) == bool(budget_mb)
+    gold = gzip.open(os.path.join(GOLDEN, "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
+    assert H.meryl_dump_text(keys, counts, K) == gold
+    ck, cc = H.count_kmers_cpu(reads, K, T)
+    assert (keys == ck).all() and (counts == cc).all()
+
+
+def test_kmer_counts_feed_skip_list():
+    """the GPU-counted list, handed back as the -k skip list, gives the overlaps of the golden repeats_skip job
+    (whose list came from the pure-Python counter of tests/cases.py)"""
+    reads, P, erate, threads, skip = cases.build_case("repeats_skip")
+    ov = make_overlapper(reads, P)
+    keys, counts, _ = ov.count_kmers(P["kmer_len"], 40)
+    ov.set_skip_kmers(H.kmer_strings(keys, P["kmer_len"]))
+    ov.overlap_driver()
+    mine = formatted(ov.overlaps())
+    ov.close()
+    gold = gzip.open(os.path.join(GOLDEN, "repeats_skip.txt.gz")).read().decode().splitlines()
+    assert mine == gold

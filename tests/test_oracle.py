@@ -75,6 +75,30 @@ def test_oracle_vs_live_reference_fuzz(i):
     check_stats(ref_stats, res["stats"], P["partial"])
 
 
+def _kmer_golden(name, K, T):
+    return gzip.open(os.path.join(GOLDEN, "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
+
+
+@pytest.mark.parametrize("name,K,T", cases.KMER_CASES)
+def test_kmer_counter_vs_meryl_golden(name, K, T):
+    """frequent-k-mer row: the CPU restatement of `meryl -B -C` + `meryl -Dt -n T` (tools/gen_reads.c) writes
+    the bytes the reference's meryl wrote (tests/golden/make_golden_kmers.py)."""
+    reads = cases.build_case(name)[0]
+    keys, counts = H.count_kmers_cpu(reads, K, T)
+    assert H.meryl_dump_text(keys, counts, K) == _kmer_golden(name, K, T)
+
+
+@pytest.mark.skipif(not H.have_ref(), reason="reference binary not built (oracle/build_ref.sh)")
+@pytest.mark.parametrize("i", [3, 9, 19])
+def test_kmer_counter_vs_live_meryl(i):
+    reads = cases.fuzz_case(i)[0]
+    K, T = [(15, 2), (22, 2), (27, 3)][i % 3]
+    with tempfile.TemporaryDirectory() as wd:
+        want = H.run_meryl(H.make_store(reads, wd), K, T, wd)
+    keys, counts = H.count_kmers_cpu(reads, K, T)
+    assert H.meryl_dump_text(keys, counts, K) == want
+
+
 def test_host_tables_monotone():
     lib = H.oracle_lib()
     import numpy as np

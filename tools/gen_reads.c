@@ -147,13 +147,15 @@ void oic_gen_fill(const gen_params_t *p, const uint8_t *g, uint64_t nreads, cons
 
 void oic_gen_free(void *p) { free(p); }
 
-/* Frequent k-mer list of a read set (harness only: what `meryl -Dt -n T` feeds `overlapInCore -k <file>` in the pipeline,
- * Meryl.pm:634): every canonical K-mer (the smaller of a K-mer and its reverse complement as 2-bit keys, first base in the low
- * bits) whose occurrences on both strands total >= threshold.  Windows with a non-ACGT base are skipped.  Open-addressing
- * table, OpenMP over reads.  Returns the number of keys found (written to out_keys up to `cap`), or (uint64_t)-1 on allocation failure. */
+/* K-mer counter of a read set -- CPU restatement (test infrastructure) of what the pipeline gets from the reference's meryl:
+ * `meryl -B -C -m K -s store` counts CANONICAL K-mers (the lexicographically smaller of a K-mer and its reverse complement,
+ * meryl-build.C) over every read, skipping windows with a non-ACGT base, and `meryl -Dt -n T` (meryl-dump.C, Meryl.pm:634) lists
+ * those seen >= T times as ">count\nKMER\n" in ascending K-mer order.  Keys here are the K-mer with its FIRST base in the HIGH
+ * bits (a=0 c=1 g=2 t=3), so ascending key order is that order.  Open-addressing table, OpenMP over reads.  Returns the number of
+ * K-mers with count >= threshold (keys/counts written UNSORTED up to `cap`), or (uint64_t)-1 on allocation failure. */
 static inline uint64_t fk_mix(uint64_t k) { k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33; return k; }
 uint64_t oic_frequent_kmers(const char *bases, const uint64_t *offsets, const uint32_t *lengths, uint64_t nreads, int K, uint32_t threshold,
-                            uint64_t *out_keys, uint64_t cap) {
+                            uint64_t *out_keys, uint32_t *out_counts, uint64_t cap) {
   uint64_t windows = 0;
   for (uint64_t i = 0; i < nreads; i++) if (lengths[i] >= (uint32_t)K) windows += lengths[i] - K + 1;
   uint64_t slots = 1024;
@@ -179,8 +181,8 @@ uint64_t oic_frequent_kmers(const char *bases, const uint64_t *offsets, const ui
         default: c = 4; break;
       }
       if (c == 4) { good = 0; fw = rv = 0; continue; }
-      fw = (fw >> 2) | (c << (2 * (K - 1)));          /* first base of the window in the low bits */
-      rv = ((rv << 2) | (3 - c)) & kmask;             /* reverse complement of the window, same convention */
+      fw = ((fw << 2) | c) & kmask;                    /* the window, first base in the high bits */
+      rv = (rv >> 2) | ((3 - c) << (2 * (K - 1)));     /* its reverse complement, same convention */
       if (++good < (uint32_t)K) continue;
       const uint64_t key = fw < rv ? fw : rv;
       uint64_t h = fk_mix(key) & mask;
@@ -197,7 +199,7 @@ uint64_t oic_frequent_kmers(const char *bases, const uint64_t *offsets, const ui
   }
   uint64_t n = 0;
   for (uint64_t h = 0; h < slots; h++)
-    if (cnt[h] >= threshold) { if (n < cap) out_keys[n] = keys[h]; n++; }
+    if (cnt[h] >= threshold && cnt[h] > 0) { if (n < cap) { out_keys[n] = keys[h]; if (out_counts) out_counts[n] = cnt[h]; } n++; }
   free(keys); free(cnt);
   return n;
 }
