@@ -260,15 +260,6 @@ def main():
 
     ov = api.Overlapper(LP, device=local)
     n_skip = 0
-    if SKIP_T:   # the -k skip list, from the reads this rank holds (its query block + the hash block)
-        class _R:   # the rank's reads in the shape H.frequent_kmers_fast wants
-            pass
-        rr = _R()
-        rr.bases, rr.offsets, rr.lengths, rr.n = pinned.numpy(), np.asarray(offs, dtype=np.uint64), np.asarray(lens, dtype=np.uint32), len(lens)
-        skip = H.frequent_kmers_fast(rr, K, SKIP_T)
-        n_skip = len(skip)
-        config["skip_kmers"] = n_skip
-
     class DevView:
         def __init__(self, ptr, nbytes):
             self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
@@ -355,7 +346,12 @@ def main():
         return dt, n
 
     ov.load_reads_ptr(pinned.data_ptr(), offs, lens, first_id=1)
-    if n_skip:
+    if SKIP_T:   # the -k skip list from the reads this rank holds (its query block + the hash block), counted on the GPU
+        keys, _, kinfo = ov.count_kmers(K, SKIP_T)   # what `meryl -B -C` + `meryl -Dt -n T` give the pipeline (oic_count_kmers)
+        skip = H.kmer_strings(keys, K)
+        n_skip = len(skip)
+        config["skip_kmers"] = n_skip
+        config["skip_list"] = "oic_count_kmers on the resident reads: %.1f ms on the GPU, %d pass(es)" % (kinfo["device_ms"], kinfo["passes"])
         ov.set_skip_kmers(skip)
     for _ in range(a.warmup):
         job(False)
