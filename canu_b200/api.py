@@ -22,6 +22,7 @@ ABI_SYMBOLS = [
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
     "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
+    "oic_copy_kmer_histogram",
 ]
 
 
@@ -89,6 +90,7 @@ def load_library():
     lib.oic_build_hash_index.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     lib.oic_count_kmers.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
     lib.oic_copy_frequent_kmers.argtypes = [vp, vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.oic_copy_kmer_histogram.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.oic_process_overlaps.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.oic_overlap_driver.argtypes = [vp]
     lib.oic_last_processed_ref.restype = C.c_uint32
@@ -263,7 +265,11 @@ class Overlapper:
         counts = np.zeros(n.value, dtype=np.uint32)
         got = C.c_uint64(0)
         self._check(self.lib.oic_copy_frequent_kmers(self._h, keys.ctypes.data, counts.ctypes.data, n.value, C.byref(got)), "oic_copy_frequent_kmers")
-        return keys[:got.value], counts[:got.value], {"passes": passes.value, "device_ms": ms.value}
+        hl = C.c_uint64(0)
+        self._check(self.lib.oic_copy_kmer_histogram(self._h, None, 0, C.byref(hl)), "oic_copy_kmer_histogram")
+        hist = np.zeros(hl.value, dtype=np.uint64)
+        self._check(self.lib.oic_copy_kmer_histogram(self._h, hist.ctypes.data, hl.value, C.byref(hl)), "oic_copy_kmer_histogram")
+        return keys[:got.value], counts[:got.value], {"passes": passes.value, "device_ms": ms.value, "histogram": hist}
 
     def build_hash_index(self, bgn_id, end_id):
         last = C.c_uint32(0)

@@ -147,7 +147,8 @@ struct oic_ctx {
   uint64_t batch_bases = 0;
 
   // canonical K-mer counts (oic_count_kmers)
-  DevBuf d_kc_keys, d_kc_cnt, d_kc_out_keys, d_kc_out_cnt, d_kc_n;
+  DevBuf d_kc_keys, d_kc_cnt, d_kc_out_keys, d_kc_out_cnt, d_kc_n, d_kc_hist, d_kc_big;
+  std::vector<uint64_t> kc_hist;   // kc_hist[i] = distinct canonical K-mers seen exactly i times (last oic_count_kmers)
   std::vector<std::pair<uint64_t, uint32_t>> freq;   // {key (first base high), count}, ascending
   float kc_ms = 0;
 
@@ -376,7 +377,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_keys, &c->d_kc_cnt, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_keys, &c->d_kc_cnt, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
@@ -1133,7 +1134,14 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   }
   CK(c->d_kc_keys.ensure(slots * 8));
   CK(c->d_kc_cnt.ensure(slots * 4));
-  CK(c->d_kc_n.ensure(8));
+  CK(c->d_kc_n.ensure(16));
+  const uint32_t HB = 1u << 20, BIG_CAP = 1u << 20;   // histogram bins on the device; rarer, larger counts are listed one by one
+  CK(c->d_kc_hist.ensure((size_t)HB * 8));
+  CK(c->d_kc_big.ensure((size_t)BIG_CAP * 4));
+  CK(cudaMemsetAsync(c->d_kc_hist.p, 0, (size_t)HB * 8, c->stream));
+  CK(cudaMemsetAsync(c->d_kc_n.p, 0, 16, c->stream));
+  c->kc_hist.clear();
+  std::vector<uint32_t> big_counts;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, c->stream);
@@ -1147,6 +1155,22 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     CK(cudaMemsetAsync(c->d_kc_keys.p, 0xff, slots * 8, c->stream));
     CK(cudaMemsetAsync(c->d_kc_cnt.p, 0, slots * 4, c->stream));
     k_count_kmers<<<nblocks(a.n_words * 32, 256), 256, 0, c->stream>>>(a);
+    // histogram of this partition's counts (accumulates over the passes)
+    unsigned int *n_big = reinterpret_cast<unsigned int *>(c->d_kc_n.as<unsigned long long>() + 1);
+    CK(cudaMemsetAsync(n_big, 0, 4, c->stream));
+    k_count_hist<<<148 * 8, 256, 0, c->stream>>>(a.cnt, slots, c->d_kc_hist.as<unsigned long long>(), HB, c->d_kc_big.as<uint32_t>(), BIG_CAP, n_big);
+    {
+      unsigned int nb = 0;
+      CK(cudaMemcpyAsync(&nb, n_big, 4, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      if (nb > BIG_CAP) return c->fail(OIC_ERR_CAPACITY, "oic_count_kmers: more than 2^20 K-mers seen >= 2^20 times");
+      if (nb) {
+        const size_t old_n = big_counts.size();
+        big_counts.resize(old_n + nb);
+        CK(cudaMemcpy(big_counts.data() + old_n, c->d_kc_big.p, (size_t)nb * 4, cudaMemcpyDeviceToHost));
+      }
+    }
+    c->tm.launches += 1;
     // how many K-mers reach min_count, then collect them
     unsigned long long n = 0;
     CK(cudaMemsetAsync(c->d_kc_n.p, 0, 8, c->stream));
@@ -1177,6 +1201,16 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   cudaEventSynchronize(e1);
   cudaEventElapsedTime(&c->kc_ms, e0, e1);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
+  {
+    std::vector<unsigned long long> hh(HB);
+    CK(cudaMemcpy(hh.data(), c->d_kc_hist.p, (size_t)HB * 8, cudaMemcpyDeviceToHost));
+    uint64_t top = 0;
+    for (uint32_t i = 0; i < HB; i++) if (hh[i]) top = i;
+    for (uint32_t b : big_counts) top = std::max<uint64_t>(top, b);
+    c->kc_hist.assign(top + 1, 0);
+    for (uint32_t i = 0; i < HB && i <= top; i++) c->kc_hist[i] = hh[i];
+    for (uint32_t b : big_counts) c->kc_hist[b]++;
+  }
   std::sort(c->freq.begin(), c->freq.end());   // ascending K-mer order = the order of `meryl -Dt`
   if (n_found) *n_found = c->freq.size();
   if (n_passes) *n_passes = n_pass;
@@ -1189,6 +1223,13 @@ int oic_copy_frequent_kmers(oic_ctx_t *c, uint64_t *keys, uint32_t *counts, uint
   const uint64_t n = std::min<uint64_t>(capacity, c->freq.size());
   for (uint64_t i = 0; i < n; i++) { keys[i] = c->freq[i].first; if (counts) counts[i] = c->freq[i].second; }
   if (n_copied) *n_copied = n;
+  return OIC_OK;
+}
+
+int oic_copy_kmer_histogram(oic_ctx_t *c, uint64_t *hist, uint64_t capacity, uint64_t *length) {
+  if (!c) return OIC_ERR_ARG;
+  if (length) *length = c->kc_hist.size();
+  if (hist) for (uint64_t i = 0; i < capacity && i < c->kc_hist.size(); i++) hist[i] = c->kc_hist[i];
   return OIC_OK;
 }
 

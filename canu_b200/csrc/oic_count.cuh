@@ -11,6 +11,7 @@
  *                    on the count.  With n_pass > 1 a pass only takes the keys of its hash partition (reads larger than
  *                    the table budget are counted in several passes over the resident stream).
  *   k_count_collect  one thread per slot: keys with count >= T appended to the output (or only counted: cap == 0)
+ *   k_count_hist     histogram of the counts (`meryl -Dh`)
  */
 #ifndef OIC_COUNT_CUH
 #define OIC_COUNT_CUH
@@ -93,6 +94,31 @@ __global__ void __launch_bounds__(256) k_count_collect(const unsigned long long 
     const unsigned long long w = base + __popc(m & ((1u << l) - 1));
     if (w < cap) { out_keys[w] = keys[i]; out_cnt[w] = c; }
   }
+}
+
+/* Histogram of the counts of one pass (`meryl -Dh`, src/meryl/meryl-dump.C:120-152: how many distinct K-mers were seen exactly
+ * i times): counts below HIST_SMEM are binned in shared memory per block (most K-mers of a read set are seen once or
+ * coverage-many times: a global atomic per slot would serialise on two or three addresses), the rest go to the global bins,
+ * counts >= n_bins - 1 to the last bin's overflow list. */
+constexpr int HIST_SMEM = 1024;
+__global__ void __launch_bounds__(256) k_count_hist(const uint32_t *__restrict__ cnt, uint64_t n_slots, unsigned long long *hist, uint32_t n_bins,
+                                                    uint32_t *big, uint32_t big_cap, unsigned int *n_big) {
+  __shared__ unsigned int sh[HIST_SMEM];
+  for (int i = threadIdx.x; i < HIST_SMEM; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t c = cnt[i];
+    if (c == 0) continue;
+    if (c < HIST_SMEM) atomicAdd(&sh[c], 1u);
+    else if (c < n_bins - 1) atomicAdd(&hist[c], 1ull);
+    else {
+      const unsigned int w = atomicAdd(n_big, 1u);
+      if (w < big_cap) big[w] = c;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < HIST_SMEM; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
 }
 
 }  // namespace oic

@@ -6,9 +6,12 @@
  * This tool writes the same bytes as that second command -- ">count\nKMER\n" for every canonical K-mer seen >= T times in
  * the reads of the store, upper case, ascending -- straight from the store:
  *
- *     frequentMers -m K -n T -s <gkpStore> [-o <file>] [--device d]
+ *     frequentMers -m K -n T -s <gkpStore> [-o <file>] [--histogram <file> [--info <file>]] [--device d]
  *
- * (-o defaults to stdout, like the shell redirection of the pipeline.)  No CPU path: without a CUDA device it exits 1.
+ * (-o defaults to stdout, like the shell redirection of the pipeline.)  --histogram writes what `meryl -Dh -s <db>` prints on
+ * stdout (count, distinct K-mers with that count, cumulative fraction of distinct, cumulative fraction of all; meryl-dump.C:
+ * 120-152 -- the input of estimate-mer-threshold, Meryl.pm:449-470) and --info its four stderr lines; with --histogram, -n may be
+ * omitted (no list is written).  No CPU path: without a CUDA device it exits 1.
  */
 #include <errno.h>
 #include <stdint.h>
@@ -28,7 +31,7 @@ using namespace oichost;
 
 int main(int argc, char **argv) {
   uint32_t K = 0, T = 0;
-  const char *store_path = nullptr, *out_name = nullptr;
+  const char *store_path = nullptr, *out_name = nullptr, *hist_name = nullptr, *info_name = nullptr;
   int device = 0;
   for (int i = 1; i < argc; i++) {
     const char *a = argv[i];
@@ -40,11 +43,13 @@ int main(int argc, char **argv) {
     else if (!strcmp(a, "-n")) T = (uint32_t)strtoul(need(), nullptr, 10);
     else if (!strcmp(a, "-s")) store_path = need();
     else if (!strcmp(a, "-o")) out_name = need();
+    else if (!strcmp(a, "--histogram")) hist_name = need();
+    else if (!strcmp(a, "--info")) info_name = need();
     else if (!strcmp(a, "--device")) device = atoi(need());
     else { fprintf(stderr, "Unknown option '%s'\n", a); return 1; }
   }
-  if (K < 2 || K > 31 || T < 1 || !store_path) {
-    fprintf(stderr, "usage: %s -m <mersize 2..31> -n <min count> -s <gkpStore> [-o file] [--device d]\n", argv[0]);
+  if (K < 2 || K > 31 || (T < 1 && !hist_name) || !store_path) {
+    fprintf(stderr, "usage: %s -m <mersize 2..31> -n <min count> -s <gkpStore> [-o file] [--histogram file [--info file]] [--device d]\n", argv[0]);
     return 1;
   }
 
@@ -90,7 +95,8 @@ int main(int argc, char **argv) {
   uint64_t found = 0;
   uint32_t passes = 0;
   double ms = 0;
-  if (!rc) rc = oic_count_kmers(ctx, K, T, &found, &passes, &ms);
+  const bool want_list = T >= 1;
+  if (!rc) rc = oic_count_kmers(ctx, K, want_list ? T : UINT32_MAX, &found, &passes, &ms);
   if (rc) { fprintf(stderr, "ERROR: %s\n", oic_last_error(ctx)); return 1; }
   std::vector<uint64_t> keys(found);
   std::vector<uint32_t> counts(found);
@@ -98,6 +104,31 @@ int main(int argc, char **argv) {
   oic_copy_frequent_kmers(ctx, keys.data(), counts.data(), found, &got);
   fprintf(stderr, "%llu reads, %llu bases: %llu canonical %u-mers seen >= %u times (%u pass%s, %.1f ms on the GPU)\n", (unsigned long long)n,
           (unsigned long long)total, (unsigned long long)got, K, T, passes, passes == 1 ? "" : "es", ms);
+
+  if (hist_name) {
+    uint64_t hl = 0;
+    oic_copy_kmer_histogram(ctx, nullptr, 0, &hl);
+    std::vector<uint64_t> hist(hl);
+    oic_copy_kmer_histogram(ctx, hist.data(), hl, &hl);
+    uint64_t n_distinct = 0, n_total = 0;
+    for (uint64_t i = 1; i < hl; i++) { n_distinct += hist[i]; n_total += hist[i] * i; }
+    FILE *hf = fopen(hist_name, "w");
+    if (!hf) { fprintf(stderr, "ERROR: cannot write '%s': %s\n", hist_name, strerror(errno)); return 1; }
+    uint64_t distinct = 0, tot = 0;
+    for (uint64_t i = 1; i < hl; i++) {
+      if (hist[i] == 0) continue;
+      distinct += hist[i];
+      tot += hist[i] * i;
+      fprintf(hf, "%u\t%llu\t%.4f\t%.4f\n", (unsigned)i, (unsigned long long)hist[i], distinct / (double)n_distinct, tot / (double)n_total);
+    }
+    fclose(hf);
+    FILE *inf = info_name ? fopen(info_name, "w") : stderr;
+    if (!inf) { fprintf(stderr, "ERROR: cannot write '%s': %s\n", info_name, strerror(errno)); return 1; }
+    fprintf(inf, "Found %llu mers.\nFound %llu distinct mers.\nFound %llu unique mers.\nLargest mercount is %llu.\n", (unsigned long long)n_total,
+            (unsigned long long)n_distinct, (unsigned long long)(hl > 1 ? hist[1] : 0), (unsigned long long)(hl ? hl - 1 : 0));
+    if (inf != stderr) fclose(inf);
+  }
+  if (!want_list) { oic_destroy(ctx); return 0; }
 
   FILE *out = stdout;
   if (out_name) {

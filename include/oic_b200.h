@@ -186,6 +186,12 @@ int oic_count_kmers(oic_ctx_t *ctx, uint32_t K, uint32_t min_count, uint64_t *n_
  * HIGH bits (a=0 c=1 g=2 t=3, 2 bits per base); counts may be NULL. */
 int oic_copy_frequent_kmers(oic_ctx_t *ctx, uint64_t *keys, uint32_t *counts, uint64_t capacity, uint64_t *n_copied);
 
+/* Histogram of the counts of the last oic_count_kmers call: hist[i] = distinct canonical K-mers seen exactly i times, i <
+ * *length = largest count + 1 (hist may be NULL to ask for the length).  What `meryl -Dh` prints (src/meryl/meryl-dump.C:120-152;
+ * the pipeline feeds it to estimate-mer-threshold, src/pipelines/canu/Meryl.pm:449-470): distinct = sum hist[i], unique = hist[1],
+ * total = sum i * hist[i]. */
+int oic_copy_kmer_histogram(oic_ctx_t *ctx, uint64_t *hist, uint64_t capacity, uint64_t *length);
+
 /* Roofline denominator of the extension stage: INT32 issue rates of `device`, measured (thread Gop/s).  alu = chains of
  * LOP3 + IADD3 (the pipe the edit-distance rows live on; reference code measured against: LIBO/prefixEditDistance-forward.C
  * inner loop), imad = chains of IMAD.  Takes a few milliseconds. */

@@ -3,7 +3,8 @@
 
     python tests/golden/make_golden_kmers.py
 
-For each (case, K, T) of cases.KMER_CASES: kmers_<case>_<K>_<T>.txt.gz = the bytes of `meryl -Dt -n T -s <db>`.
+For each (case, K, T) of cases.KMER_CASES: kmers_<case>_<K>_<T>.txt.gz = the bytes of `meryl -Dt -n T -s <db>`;
+khist_<case>_<K>.txt.gz = stdout of `meryl -Dh -s <db>`, a line `--info--`, then its stderr.
 """
 import gzip
 import os
@@ -23,6 +24,9 @@ def main():
         with tempfile.TemporaryDirectory() as wd:
             store = H.make_store(reads, wd)
             text = H.run_meryl(store, K, T, wd)
+            hout, herr = H.run_meryl_hist(store, K, wd)
+        with gzip.GzipFile(os.path.join(HERE, "khist_%s_%d.txt.gz" % (name, K)), "wb", mtime=0) as f:
+            f.write((hout + "--info--\n" + herr).encode())
         with gzip.GzipFile(os.path.join(HERE, "kmers_%s_%d_%d.txt.gz" % (name, K, T)), "wb", mtime=0) as f:
             f.write(text.encode())
         print(name, K, T, text.count(">"))

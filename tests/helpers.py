@@ -157,6 +157,38 @@ def meryl_dump_text(keys, counts, K):
     return "".join(">%d\n%s\n" % (int(c), k) for c, k in zip(counts, kmer_strings(keys, K, upper=True)))
 
 
+def meryl_hist_text(hist):
+    """the text of `meryl -Dh` (meryl-dump.C:120-152) from hist[i] = distinct K-mers seen exactly i times -> (stdout, stderr)"""
+    hist = [int(x) for x in hist]
+    n_distinct = sum(hist[1:])
+    n_total = sum(i * h for i, h in enumerate(hist))
+    out, distinct, total = [], 0, 0
+    for i in range(1, len(hist)):
+        if hist[i]:
+            distinct += hist[i]
+            total += hist[i] * i
+            out.append("%d\t%d\t%.4f\t%.4f\n" % (i, hist[i], distinct / float(n_distinct), total / float(n_total)))
+    info = "Found %d mers.\nFound %d distinct mers.\nFound %d unique mers.\nLargest mercount is %d.\n" % (
+        n_total, n_distinct, hist[1] if len(hist) > 1 else 0, len(hist) - 1)
+    return "".join(out), info
+
+
+def kmer_histogram_cpu(reads, K):
+    """hist[i] = distinct canonical K-mers seen exactly i times, from the CPU restatement"""
+    _, counts = count_kmers_cpu(reads, K, 1)
+    return np.bincount(counts.astype(np.int64)) if len(counts) else np.zeros(1, dtype=np.int64)
+
+
+def run_meryl_hist(store, K, workdir, threads=4):
+    """`meryl -Dh` on a database built as the pipeline builds it (Meryl.pm:434-455) -> (stdout, stderr)"""
+    db = os.path.join(workdir, "refh.ms%d" % K)
+    with open(os.path.join(workdir, "merylh.err"), "w") as ef:
+        subprocess.check_call([os.path.join(REF_DIR, "meryl"), "-B", "-C", "-L", "2", "-v", "-m", str(K), "-threads", str(threads),
+                               "-memory", "1024", "-s", store, "-o", db], stdout=ef, stderr=ef)
+    r = subprocess.run([os.path.join(REF_DIR, "meryl"), "-Dh", "-s", db], capture_output=True, check=True)
+    return r.stdout.decode(), r.stderr.decode()
+
+
 def frequent_kmers_fast(reads, K, threshold):
     """Frequent canonical K-mers of a read set as strings: the harness's stand-in for the pipeline's `meryl -Dt -n T` skip list
     at sizes where the pure-Python counter of tests/cases.py is too slow."""

@@ -169,8 +169,11 @@ def test_frequent_mers_tool_vs_meryl(name, K, T, tmp_path):
     reads = cases.build_case(name)[0]
     store = H.make_store(reads, str(tmp_path))
     out = str(tmp_path / "freq.fasta")
-    subprocess.check_call([os.path.join(os.path.dirname(BIN), "frequentMers"), "-m", str(K), "-n", str(T), "-s", store, "-o", out],
-                          stderr=subprocess.DEVNULL)
+    hist, info = str(tmp_path / "hist"), str(tmp_path / "hist.info")
+    subprocess.check_call([os.path.join(os.path.dirname(BIN), "frequentMers"), "-m", str(K), "-n", str(T), "-s", store, "-o", out,
+                           "--histogram", hist, "--info", info], stderr=subprocess.DEVNULL)
+    gold_h = gzip.open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "khist_%s_%d.txt.gz" % (name, K))).read().decode()
+    assert open(hist).read() + "--info--\n" + open(info).read() == gold_h
     got = open(out).read()
     gold = gzip.open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
     assert got == gold

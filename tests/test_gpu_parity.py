@@ -220,6 +220,9 @@ def test_kmer_counts_vs_meryl(name, K, T, budget_mb, monkeypatch):
     assert H.meryl_dump_text(keys, counts, K) == gold
     ck, cc = H.count_kmers_cpu(reads, K, T)
     assert (keys == ck).all() and (counts == cc).all()
+    # the count histogram = what `meryl -Dh` printed
+    out, hinfo = H.meryl_hist_text(info["histogram"])
+    assert out + "--info--\n" + hinfo == gzip.open(os.path.join(GOLDEN, "khist_%s_%d.txt.gz" % (name, K))).read().decode()
 
 
 def test_kmer_counts_feed_skip_list():

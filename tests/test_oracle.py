@@ -88,6 +88,14 @@ def test_kmer_counter_vs_meryl_golden(name, K, T):
     assert H.meryl_dump_text(keys, counts, K) == _kmer_golden(name, K, T)
 
 
+@pytest.mark.parametrize("name,K", sorted({(n, k) for n, k, _ in cases.KMER_CASES}))
+def test_kmer_histogram_vs_meryl_golden(name, K):
+    """the count histogram of the CPU restatement prints as the reference's `meryl -Dh` did (stdout and the four stderr lines)"""
+    reads = cases.build_case(name)[0]
+    out, info = H.meryl_hist_text(H.kmer_histogram_cpu(reads, K))
+    assert out + "--info--\n" + info == gzip.open(os.path.join(GOLDEN, "khist_%s_%d.txt.gz" % (name, K))).read().decode()
+
+
 @pytest.mark.skipif(not H.have_ref(), reason="reference binary not built (oracle/build_ref.sh)")
 @pytest.mark.parametrize("i", [3, 9, 19])
 def test_kmer_counter_vs_live_meryl(i):
