@@ -67,10 +67,6 @@ __device__ __forceinline__ uint64_t ext32(const uint64_t *__restrict__ W, int64_
   return (lo >> s) | (hi << (64 - s));
 }
 
-__device__ __forceinline__ uint32_t base_at(const uint64_t *__restrict__ W, int64_t p) {
-  return (uint32_t)(W[p >> 5] >> ((p & 31) * 2)) & 3u;
-}
-
 /* number of equal bases comparing A[pa + i] with T[pt + i], i = 0.. , at most `limit` */
 __device__ __forceinline__ int match_fwd(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T,
                                          int64_t pt, int limit) {
@@ -78,19 +74,6 @@ __device__ __forceinline__ int match_fwd(const uint64_t *__restrict__ A, int64_t
   while (r < limit) {
     uint64_t x = ext32(A, pa + r) ^ ext32(T, pt + r);
     if (x) { r += (__ffsll((long long)x) - 1) >> 1; break; }
-    r += 32;
-  }
-  return r < limit ? r : limit;
-}
-
-/* number of equal bases comparing A[pa - i] with T[pt - i], i = 0.. , at most `limit` (pa - limit + 1 >= -31 is safe:
- * the stream has READ_LEAD_BASES of padding in front) */
-__device__ __forceinline__ int match_rev(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T,
-                                         int64_t pt, int limit) {
-  int r = 0;
-  while (r < limit) {
-    uint64_t x = ext32(A, pa - r - 31) ^ ext32(T, pt - r - 31);
-    if (x) { r += __clzll((long long)x) >> 1; break; }
     r += 32;
   }
   return r < limit ? r : limit;

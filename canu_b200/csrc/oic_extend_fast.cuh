@@ -133,25 +133,6 @@ __device__ __forceinline__ int traceback_fast(const WarpScratch &ws, int fin_e, 
   return nev;
 }
 
-/* 32-base compare step in either direction: number of equal bases starting at A[pa], T[pt] and walking by DIR
- * (32 if all equal).  The reverse direction bit-reverses the XOR so one find-first-set serves both: the two bits of
- * a base swap places, which does not matter for "first base that differs". */
-__device__ __forceinline__ int step32(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T, int64_t pt, int DIR) {
-  const int back = DIR > 0 ? 0 : 31;
-  uint64_t x = ext32(A, pa - back) ^ ext32(T, pt - back);
-  if (DIR < 0) x = __brevll(x);
-  return x ? ((__ffsll((long long)x) - 1) >> 1) : 32;
-}
-__device__ __forceinline__ int match_dir(const uint64_t *__restrict__ A, int64_t pa, const uint64_t *__restrict__ T, int64_t pt, int limit, int DIR) {
-  int r = 0;
-  while (r < limit) {
-    const int adv = step32(A, pa + DIR * r, T, pt + DIR * r, DIR);
-    r += adv;
-    if (adv < 32) break;
-  }
-  return r < limit ? r : limit;
-}
-
 /* After the row loop of one direction: pick the exit cell (or fall back to the best cell seen), trace back, build the
  * delta list (Set_Right_Delta / Set_Left_Delta).  Shared by the generic and the lean row loops. */
 __device__ __forceinline__ int dp_finish(const int DIR, WarpScratch &ws, int n, int row0, int fin_e, int fin_d, int fin_val, int from0, int errors,

@@ -11,9 +11,6 @@
 #ifndef OIC_EXTEND_LEAN_CUH
 #define OIC_EXTEND_LEAN_CUH
 
-#ifndef LEAN_V2
-#define LEAN_V2 1   /* branch-free first slides, merged continuation loop, lane-local best cell (0 = the round-1c loop, kept for A/B builds) */
-#endif
 #ifndef LEAN_U
 #define LEAN_U 2   /* chunks of 32 diagonals in flight together */
 #endif
@@ -122,7 +119,6 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         cap[u] = (i < width) ? imin(m, n - d) : LEAN_IDLE;
       }
       int more = 0;                                      // bit u: the slide of chunk u goes on
-#if LEAN_V2
       // Branch-free: a cell that does not slide (idle lane, or already at the end of a string) compares the first windows
       // of the two strings instead and discards the result, so the 4*LU loads of a chunk group issue back to back.
 #pragma unroll
@@ -150,27 +146,6 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         r[1] = s1 ? rr : r[1];
         more &= (has && stop) ? (s1 ? ~2 : ~1) : ~0;
       }
-#else
-#pragma unroll
-      for (int u = 0; u < LU; u++) {                     // first 16 bases of every slide, loads back to back
-        r[u] = r0[u];
-        if (r0[u] < cap[u]) {
-          const int adv = lean_step(Ap, aph + r0[u], Tp, tph + r0[u] + dd[u]);
-          r[u] = r0[u] + adv;
-          more |= ((adv == 16) && (r[u] < cap[u])) ? (1 << u) : 0;
-        }
-      }
-      while (__any_sync(FULL, more != 0)) {              // slides longer than 16 bases (the cells on the alignment path)
-#pragma unroll
-        for (int u = 0; u < LU; u++) {
-          if (more & (1 << u)) {
-            const int adv = lean_step(Ap, aph + r[u], Tp, tph + r[u] + dd[u]);
-            r[u] += adv;
-            if (!((adv == 16) && (r[u] < cap[u]))) more &= ~(1 << u);
-          }
-        }
-      }
-#endif
       unsigned em[LU], wc[LU], any_em = 0;
 #pragma unroll
       for (int u = 0; u < LU; u++) {
@@ -182,14 +157,8 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         any_em |= em[u];
         wc[u] = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
-#if LEAN_V2
         if (l == c) my_ok = ok;
         if (r[u] > my_mx) { my_mx = r[u]; my_pm = (unsigned)i; }   // this lane's highest cell, lowest chunk on ties
-#else
-        const int mx = __reduce_max_sync(FULL, r[u]);
-        const unsigned pm = __ballot_sync(FULL, r[u] == mx);
-        if (l == c) { my_ok = ok; my_mx = mx; my_pm = pm; }
-#endif
       }
       if (any_em) {                                      // a cell reached the end of A or T: the row stops at the first one
         int uu = 0;
@@ -268,12 +237,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     int gmax = __reduce_max_sync(FULL, my_mx);           // highest cell of the row, lowest diagonal on ties
     int gpos = 0;
     if (gmax > longest) {
-#if LEAN_V2
       gpos = left + (int)__reduce_min_sync(FULL, (my_mx == gmax) ? my_pm : 0x7fffffffu);
-#else
-      const int cw = __ffs(__ballot_sync(FULL, my_mx == gmax)) - 1;
-      gpos = left + 32 * cw + __ffs(__shfl_sync(FULL, my_pm, cw)) - 1;
-#endif
     }
 
     // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
