@@ -25,10 +25,28 @@ constexpr int LEAN_IDLE = (int)0x80000000;
  * only walks forward: the reverse direction is run on the reverse-complement streams (same comparisons, mirrored). */
 __device__ __forceinline__ uint32_t ldg_nc(const uint32_t *p) {   // the bases are "laundered" 64-bit registers: say they are global
   uint32_t v;
+#if OIC_SEQ_LD == 1
+  asm("ld.global.nc.L1::evict_last.u32 %0, [%1];" : "=r"(v) : "l"(p));
+#else
   asm("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+#endif
   return v;
 }
-__device__ __forceinline__ void stg_s32(int32_t *p, int32_t v) { asm volatile("st.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+#ifndef OIC_SEQ_LD
+#define OIC_SEQ_LD 0    /* 1: sequence window loads ask L1 to keep their lines (evict_last); measured: no change (88.38 vs 88.37 ms) */
+#endif
+#ifndef OIC_HIST_ST
+#define OIC_HIST_ST 2   /* cache operator of the row-history stores: 0 default, 1 .cg (L2 only), 2 .cs (streaming: written once, read once by the traceback); measured 88.37 / 88.34 / 88.03 ms */
+#endif
+__device__ __forceinline__ void stg_s32(int32_t *p, int32_t v) {
+#if OIC_HIST_ST == 1
+  asm volatile("st.global.cg.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#elif OIC_HIST_ST == 2
+  asm volatile("st.global.cs.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#else
+  asm volatile("st.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#endif
+}
 __device__ __forceinline__ uint32_t lean_ext16(const uint32_t *Wp, int p) {
   const uint32_t *q = Wp + (p >> 4);
   return __funnelshift_r(ldg_nc(q), ldg_nc(q + 1), (p & 15) * 2);
