@@ -62,7 +62,10 @@ struct ScanArgs {
 
 constexpr int SCAN_WARPS = 4;
 
-__global__ void __launch_bounds__(SCAN_WARPS * 32) k_seed_scan(ScanArgs a) {
+#ifndef OIC_SCAN_BLOCKS
+#define OIC_SCAN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(SCAN_WARPS * 32, OIC_SCAN_BLOCKS) k_seed_scan(ScanArgs a) {
   __shared__ uint32_t s_pref[SCAN_WARPS][33];
   __shared__ unsigned long long s_pay[SCAN_WARPS][32];
   const int wib = threadIdx.x >> 5, l = lane_id();
