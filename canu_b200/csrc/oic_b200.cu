@@ -1117,11 +1117,11 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   if (n_passes) *n_passes = 0;
   if (device_ms) *device_ms = 0.0;
   if (windows == 0) return OIC_OK;
-  // table of {8-byte key, 4-byte count}, at most half full even if every window is a different K-mer; read sets whose
+  // table of 16-byte {key, count} slots, at most half full even if every window is a different K-mer; read sets whose
   // table does not fit the budget are counted in n_pass passes, each over one hash partition of the K-mers
   size_t free_b = 0, total_b = 0;
   cudaMemGetInfo(&free_b, &total_b);
-  unsigned long long budget = (unsigned long long)(free_b + c->d_kc_keys.cap + c->d_kc_cnt.cap) * 6 / 10;
+  unsigned long long budget = (unsigned long long)(free_b + c->d_kc_keys.cap) * 6 / 10;
   uint64_t floor_slots = 1ull << 20;
   if (const char *e = getenv("OIC_COUNT_BUDGET_MB")) { budget = strtoull(e, nullptr, 10) << 20; floor_slots = 4096; }   // test knob: forces several passes
   uint32_t n_pass = 1;
@@ -1129,11 +1129,10 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   for (;; n_pass++) {
     slots = 1024;
     while (slots < 2 * ((windows + n_pass - 1) / n_pass) + 2 * (windows / n_pass / 16)) slots <<= 1;   // + slack for uneven partitions
-    if (slots * 12ull <= budget || slots <= floor_slots) break;
+    if (slots * 16ull <= budget || slots <= floor_slots) break;
     if (n_pass > 4096) return c->fail(OIC_ERR_CAPACITY, "oic_count_kmers: no memory for the count table");
   }
-  CK(c->d_kc_keys.ensure(slots * 8));
-  CK(c->d_kc_cnt.ensure(slots * 4));
+  CK(c->d_kc_keys.ensure(slots * sizeof(Slot)));
   CK(c->d_kc_n.ensure(16));
   const uint32_t HB = 1u << 20, BIG_CAP = 1u << 20;   // histogram bins on the device; rarer, larger counts are listed one by one
   CK(c->d_kc_hist.ensure((size_t)HB * 8));
@@ -1148,17 +1147,16 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   CountArgs a;
   a.fwd = c->d_fwd.as<uint64_t>(); a.n_off = c->n_off; a.rd_pos = c->d_pos.as<int64_t>(); a.rd_len = c->d_len.as<uint32_t>();
   a.n_reads = c->n_reads; a.n_words = c->stream_words - 4; a.K = (int)K;
-  a.keys = c->d_kc_keys.as<unsigned long long>(); a.cnt = c->d_kc_cnt.as<uint32_t>(); a.slot_mask = slots - 1; a.n_pass = n_pass;
+  a.table = c->d_kc_keys.as<Slot>(); a.slot_mask = slots - 1; a.n_pass = n_pass;
   int rc = OIC_OK;
   for (uint32_t pass = 0; pass < n_pass && rc == OIC_OK; pass++) {
     a.pass = pass;
-    CK(cudaMemsetAsync(c->d_kc_keys.p, 0xff, slots * 8, c->stream));
-    CK(cudaMemsetAsync(c->d_kc_cnt.p, 0, slots * 4, c->stream));
+    k_table_init<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.table, slots);
     k_count_kmers<<<nblocks(a.n_words * 32, 256), 256, 0, c->stream>>>(a);
     // histogram of this partition's counts (accumulates over the passes)
     unsigned int *n_big = reinterpret_cast<unsigned int *>(c->d_kc_n.as<unsigned long long>() + 1);
     CK(cudaMemsetAsync(n_big, 0, 4, c->stream));
-    k_count_hist<<<148 * 8, 256, 0, c->stream>>>(a.cnt, slots, c->d_kc_hist.as<unsigned long long>(), HB, c->d_kc_big.as<uint32_t>(), BIG_CAP, n_big);
+    k_count_hist<<<148 * 8, 256, 0, c->stream>>>(a.table, slots, c->d_kc_hist.as<unsigned long long>(), HB, c->d_kc_big.as<uint32_t>(), BIG_CAP, n_big);
     {
       unsigned int nb = 0;
       CK(cudaMemcpyAsync(&nb, n_big, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1174,7 +1172,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     // how many K-mers reach min_count, then collect them
     unsigned long long n = 0;
     CK(cudaMemsetAsync(c->d_kc_n.p, 0, 8, c->stream));
-    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.keys, a.cnt, slots, min_count, nullptr, nullptr, 0, c->d_kc_n.as<unsigned long long>());
+    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.table, slots, min_count, nullptr, nullptr, 0, c->d_kc_n.as<unsigned long long>());
     CK(cudaMemcpyAsync(&n, c->d_kc_n.p, 8, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaGetLastError());
@@ -1183,7 +1181,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     CK(c->d_kc_out_keys.ensure(n * 8));
     CK(c->d_kc_out_cnt.ensure(n * 4));
     CK(cudaMemsetAsync(c->d_kc_n.p, 0, 8, c->stream));
-    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.keys, a.cnt, slots, min_count, c->d_kc_out_keys.as<unsigned long long>(),
+    k_count_collect<<<nblocks(slots, 256), 256, 0, c->stream>>>(a.table, slots, min_count, c->d_kc_out_keys.as<unsigned long long>(),
                                                                c->d_kc_out_cnt.as<uint32_t>(), n, c->d_kc_n.as<unsigned long long>());
     std::vector<unsigned long long> hk(n);
     std::vector<uint32_t> hcnt(n);
