@@ -147,7 +147,7 @@ struct oic_ctx {
   uint64_t batch_bases = 0;
 
   // canonical K-mer counts (oic_count_kmers)
-  DevBuf d_kc_keys, d_kc_cnt, d_kc_out_keys, d_kc_out_cnt, d_kc_n, d_kc_hist, d_kc_big;
+  DevBuf d_kc_table, d_kc_out_keys, d_kc_out_cnt, d_kc_n, d_kc_hist, d_kc_big;
   std::vector<uint64_t> kc_hist;   // kc_hist[i] = distinct canonical K-mers seen exactly i times (last oic_count_kmers)
   std::vector<std::pair<uint64_t, uint32_t>> freq;   // {key (first base high), count}, ascending
   float kc_ms = 0;
@@ -377,7 +377,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_keys, &c->d_kc_cnt, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big};
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
@@ -1121,7 +1121,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   // table does not fit the budget are counted in n_pass passes, each over one hash partition of the K-mers
   size_t free_b = 0, total_b = 0;
   cudaMemGetInfo(&free_b, &total_b);
-  unsigned long long budget = (unsigned long long)(free_b + c->d_kc_keys.cap) * 6 / 10;
+  unsigned long long budget = (unsigned long long)(free_b + c->d_kc_table.cap) * 6 / 10;
   uint64_t floor_slots = 1ull << 20;
   if (const char *e = getenv("OIC_COUNT_BUDGET_MB")) { budget = strtoull(e, nullptr, 10) << 20; floor_slots = 4096; }   // test knob: forces several passes
   uint32_t n_pass = 1;
@@ -1132,7 +1132,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     if (slots * 16ull <= budget || slots <= floor_slots) break;
     if (n_pass > 4096) return c->fail(OIC_ERR_CAPACITY, "oic_count_kmers: no memory for the count table");
   }
-  CK(c->d_kc_keys.ensure(slots * sizeof(Slot)));
+  CK(c->d_kc_table.ensure(slots * sizeof(Slot)));
   CK(c->d_kc_n.ensure(16));
   const uint32_t HB = 1u << 20, BIG_CAP = 1u << 20;   // histogram bins on the device; rarer, larger counts are listed one by one
   CK(c->d_kc_hist.ensure((size_t)HB * 8));
@@ -1147,7 +1147,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   CountArgs a;
   a.fwd = c->d_fwd.as<uint64_t>(); a.n_off = c->n_off; a.rd_pos = c->d_pos.as<int64_t>(); a.rd_len = c->d_len.as<uint32_t>();
   a.n_reads = c->n_reads; a.n_words = c->stream_words - 4; a.K = (int)K;
-  a.table = c->d_kc_keys.as<Slot>(); a.slot_mask = slots - 1; a.n_pass = n_pass;
+  a.table = c->d_kc_table.as<Slot>(); a.slot_mask = slots - 1; a.n_pass = n_pass;
   int rc = OIC_OK;
   for (uint32_t pass = 0; pass < n_pass && rc == OIC_OK; pass++) {
     a.pass = pass;
