@@ -52,3 +52,24 @@ def test_unsupported_options_fail_loudly():
         api.Overlapper(api.default_params(kmer_len=32))
     with pytest.raises(api.OicError):
         api.Overlapper(api.default_params(frag_olap_limit=5))
+
+
+def test_tools_fail_without_device(tmp_path):
+    """the executables have no CPU path either: without a CUDA device they exit 1 with a message, they do not compute"""
+    import subprocess
+    import torch
+    import cases
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    if not H.have_ref():
+        pytest.skip("reference tools not built (no gatekeeperCreate to make a store)")
+    bindir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "canu_b200", "bin")
+    reads = cases.build_case("ragged_tiny")[0]
+    store = H.make_store(reads, str(tmp_path))
+    r = subprocess.run([os.path.join(bindir, "frequentMers"), "-m", "22", "-n", "3", "-s", store, "-o", str(tmp_path / "f.fasta")], capture_output=True)
+    assert r.returncode == 1 and b"no CUDA device" in r.stderr and not os.path.exists(tmp_path / "f.fasta")
+    r = subprocess.run([os.path.join(bindir, "overlapInCore"), "-k", "22", "--hashstrings", "100", "-o", str(tmp_path / "x.ovb"), store], capture_output=True)
+    assert r.returncode == 1 and b"no CUDA device" in r.stderr
+    # argument errors are caught before anything else (OIC/overlapInCore.C:423-483)
+    r = subprocess.run([os.path.join(bindir, "frequentMers"), "-m", "40", "-n", "3", "-s", store], capture_output=True)
+    assert r.returncode == 1 and b"usage" in r.stderr
