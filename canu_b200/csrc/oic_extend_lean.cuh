@@ -91,7 +91,8 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   int next_off = 5;
   int fin_e = -1, fin_d = 0, fin_val = 0, from0 = FROM_NONE;
   int errors = 0;
-  unsigned wsum = 0;    // per-lane count of 16-base compare words (W)
+  unsigned wsum = 0;    // per-lane count of 16-base compare words (W), without the first word of the cells that ncell counts
+  unsigned w_adj = 0;   // cells of the chunk group that ended the run (their words are counted in full by wsum)
   unsigned ncell = 0;   // warp-uniform count of cells (C)
   to_end = 0;
   int lim_next = ws.match_limit[1];
@@ -150,9 +151,11 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       }
       // Slides longer than 16 bases (the cells on the alignment path): few lanes, seldom both chunks of a lane, so every
       // pass advances ONE chunk per lane (the lowest one still sliding) through a single copy of the compare.
+      unsigned nst = 0;                                  // continuation steps of this lane in this chunk group
       while (__any_sync(FULL, more != 0)) {
         static_assert(LU == 2, "the merged continuation loop is written for two chunks in flight");
         const bool has = more != 0, s1 = (more == 2);
+        nst += has ? 1u : 0u;
         int rr = s1 ? r[1] : r[0];
         const int ds = s1 ? dd[1] : dd[0], cs = s1 ? cap[1] : cap[0];
         const int p = has ? rr : 0, q = has ? rr + ds : 0;
@@ -164,7 +167,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         r[1] = s1 ? rr : r[1];
         more &= (has && stop) ? (s1 ? ~2 : ~1) : ~0;
       }
-      unsigned em[LU], wc[LU], any_em = 0;
+      unsigned em[LU], any_em = 0;
 #pragma unroll
       for (int u = 0; u < LU; u++) {
         const int c = c0 + u, i = 32 * c + l;
@@ -173,12 +176,15 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         if (act) { cp[32 * c] = r[u]; stg_s32(hp + 32 * c, r[u]); }
         em[u] = __ballot_sync(FULL, act && r[u] == cap[u]);            // reached the end of A (r == m) or of T (r + d == n)
         any_em |= em[u];
-        wc[u] = act ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
         if (l == c) my_ok = ok;
         if (r[u] > my_mx) { my_mx = r[u]; my_pm = (unsigned)i; }   // this lane's highest cell, lowest chunk on ties
       }
       if (any_em) {                                      // a cell reached the end of A or T: the row stops at the first one
+        // W of this chunk group from the slide lengths: ceil((run + 1) / 16) compare words per cell
+        unsigned wc[LU];
+#pragma unroll
+        for (int u = 0; u < LU; u++) wc[u] = (32 * (c0 + u) + l < width) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         int uu = 0;
 #pragma unroll
         for (int u = LU - 1; u >= 0; u--) if (em[u]) uu = u;
@@ -192,13 +198,15 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         const int first = __ffs(emu) - 1;
         if (l <= first) wsum += wcu;
         ncell += 32 * (c0 + uu) + first + 1;
+        w_adj = 32 * uu + first + 1;                     // the cells of this chunk group are counted by wc above, not by ncell
         d_end = left + 32 * (c0 + uu) + first;
         r_end = __shfl_sync(FULL, ru, first);
         ended = true;
         break;
       }
-#pragma unroll
-      for (int u = 0; u < LU; u++) wsum += wc[u];
+      // no cell of the group reached the end of a string: a cell slid 16 * (its continuation steps) + less than 16 bases, i.e.
+      // it cost 1 + steps compare words; the "1" of every cell is added once per run from the cell count (below)
+      wsum += nst;
     }
     int32_t *hist = ws.vals + off;
     {   // direction words of the row: two per chunk, right behind the values (and their 2-int margin)
@@ -289,7 +297,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     __syncwarp();
   }
   ws.cells += (l == 0) ? ncell : 0;
-  ws.words += wsum;
+  ws.words += wsum + ((l == 0) ? ncell - w_adj : 0u);
   if (errors < 0) return errors;
   return dp_finish(DIR, ws, n, row0, fin_e, fin_d, fin_val, from0, errors, max_score_len, max_score_best_d, max_score_best_e, a_end, t_end,
                    leftover, to_end, delta_len);
