@@ -36,6 +36,7 @@ LEN_MIN, LEN_MAX = 5000, 15000
 SEED = 1003
 MODE = "blocks"                # "blocks": disjoint query block(s) vs one hash block; "self": -h 1-N -r 1-N on one read set
 PARTIAL, MIN_OLAP, SUB_ONLY, HASH_BITS, REF_SCALE_MBP = 0, 500, False, 23, 20
+REF_FULL = True                # reference arm / cpu_baseline run the FULL job of the step (False: a REF_SCALE_MBP-genome sample, c2 only)
 REPEATS = None                 # c5: dict(frac, families, unit_min, unit_max, div) -- repeat model of tools/gen_reads.c
 SKIP_T = 0                     # c5: K-mers seen >= SKIP_T times in the loaded reads (both strands) go to the -k skip list
 
@@ -47,7 +48,8 @@ WORKLOADS = {
                GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.06", READ_ERR=0.02, SEED=1001, MODE="self", REF_SCALE_MBP=0.3),
     "c2": dict(desc="c2: synthetic 4.6 Mbp genome, 30x raw-noise reads 5-15 kb, 6% per read = 12% pairwise, k=22, --maxerate 0.15 "
                     "(wide-band extension), -h 1-N -r 1-N",
-               GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.15", READ_ERR=0.06, SEED=1002, MODE="self", REF_SCALE_MBP=0.1),
+               GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.15", READ_ERR=0.06, SEED=1002, MODE="self", REF_SCALE_MBP=0.1,
+               REF_FULL=False),   # the full c2 job takes the reference ~20 min on 16 cores
     "c3": dict(desc="c3: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, "
                     "100 Mbp hash block (1x) broadcast, one 100 Mbp query block per GPU"),
     "c4": dict(desc="c4: synthetic 100 Mbp genome, 150 bp reads (substitutions only, 0.5%), -G --minlength 40, k=22, --maxerate 0.06, "
@@ -59,6 +61,21 @@ WORKLOADS = {
                GENOME=1_000_000_000, SEED=1005, REPEATS=dict(frac=0.3, families=500, unit_min=1000, unit_max=6000, div=0.02), SKIP_T=4,
                REF_SCALE_MBP=300),
 }
+
+
+_DEFAULTS = None
+
+
+def set_workload(name):
+    """make `name` (a key of WORKLOADS) the module's current shape: the generator / flag globals above"""
+    global _DEFAULTS
+    g = globals()
+    if _DEFAULTS is None:
+        _DEFAULTS = {k: g[k] for k in ("GENOME", "BLOCK_BASES", "ERATE", "READ_ERR", "LEN_MIN", "LEN_MAX", "SEED", "MODE", "PARTIAL", "MIN_OLAP",
+                                       "SUB_ONLY", "HASH_BITS", "REF_SCALE_MBP", "REF_FULL", "REPEATS", "SKIP_T")}
+    g.update(_DEFAULTS)
+    g.update({k: v for k, v in WORKLOADS[name].items() if k != "desc"})
+    return WORKLOADS[name]
 
 
 def params_for(n_hash_reads, n_total, threads=1):
@@ -110,32 +127,50 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def reference_leg(steps, warmup, scale_mbp=None, cores=None):
-    """The reference's own CPU overlapInCore (oracle/_ref, built from /root/reference/src by oracle/build_ref.sh) on a
-    bounded sample of the same workload: same read/error model and the same 1x-hash-block vs 1x-query-block density,
-    on a genome of `scale_mbp` Mbp (default: the workload's REF_SCALE_MBP) instead of the full one (so one step ends in tens of seconds)."""
+def reference_records(store, ovb):
+    """sorted `overlapConvert -raw` lines of a reference .ovb (the parity comparator of SURVEY.md 8(c))"""
+    import helpers as H
+    return H.dump_ovb_sorted(store, ovb)
+
+
+def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=None):
+    """The reference's own CPU overlapInCore (oracle/_ref, built from /root/reference/src by oracle/build_ref.sh) on the SAME job
+    the GPU arm times at `world` GPUs: same generator seed, the full hash block, and the same `world` query blocks searched
+    by ONE reference process (-h <hash block> -r 1-<hash block - 1>), -t <all host cores>; wall time of the process (store open
+    + hash build + search + .ovb/.counts written).  The steps/warm-ups actually run are bounded by `budget_s` of host time
+    (default 420 s, OIC_REF_BUDGET_S) and REPORTED: the first run always counts unless two more fit the budget, in which case it
+    is the warm-up.  Workloads with REF_FULL = False (c2) run a REF_SCALE_MBP-genome sample of the same read model instead.
+    keep: optional dict that receives store / ovb paths of the last run (bench.py --check); the work directory then stays."""
     import helpers as H
     cores = cores or os.cpu_count()
-    scale_mbp = REF_SCALE_MBP if scale_mbp is None else scale_mbp
-    g = int(scale_mbp * 1_000_000)
+    budget_s = float(os.environ.get("OIC_REF_BUDGET_S", "420")) if budget_s is None else budget_s
     from canu_b200 import shard
+    t_start = time.time()
+    full = bool(REF_FULL)
+    g = GENOME if full else int(REF_SCALE_MBP * 1_000_000)
+    blk = BLOCK_BASES if full else int(g * BLOCK_BASES / GENOME)
+    seed = SEED if full else SEED + 7
     if MODE == "self":
-        reads = gen_blocks(g, 1, int(g * BLOCK_BASES / GENOME), SEED + 7)
+        reads = gen_blocks(g, 1, blk, seed)
         qbases = int(reads.lengths.sum())
         P = params_for(reads.n, reads.n, threads=cores)
-        sample = ("reference overlapInCore -t %d, genome %.1f Mbp at the same coverage: %d reads (%.1f Mbp) against themselves (-h 1-N -r 1-N), "
-                  "same read model/flags; wall time of the process" % (cores, scale_mbp, reads.n, qbases / 1e6))
+        sample = ("reference overlapInCore -t %d, %s: %d reads (%.1f Mbp) against themselves (-h 1-N -r 1-N)"
+                  % (cores, "the full job of the step" if full else "genome %.1f Mbp at the same coverage, same read model/flags" % (g / 1e6),
+                     reads.n, qbases / 1e6))
     else:
-        reads = gen_blocks(g, 2, int(g * BLOCK_BASES / GENOME), SEED + 7)
-        (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
-        qbases = int(reads.lengths[qb - 1:qe].sum())
+        reads = gen_blocks(g, world + 1, blk, seed)
+        blocks = shard.split_blocks(reads.n, world + 1)
+        hb, he = blocks[-1]
+        qbases = int(reads.lengths[:hb - 1].sum())
         P = params_for(he - hb + 1, reads.n, threads=cores)
-        sample = ("reference overlapInCore -t %d, genome %.1f Mbp: hash block %d reads (%.1f Mbp) x query block %d reads (%.1f Mbp), "
-                  "same read model/flags as the 100 Mbp job; wall time of the process (store open + hash build + search + .ovb)"
-                  % (cores, scale_mbp, he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, qe - qb + 1, qbases / 1e6))
+        sample = ("reference overlapInCore -t %d, %s: hash block %d reads (%.1f Mbp) x %d query block(s) %d reads (%.1f Mbp) in one process "
+                  "(-h %d-%d -r 1-%d)" % (cores, "the full job of the step (same seed, same reads as the GPU arm)" if full else
+                                          "genome %.1f Mbp sample, same read model/flags" % (g / 1e6),
+                                          he - hb + 1, reads.lengths[hb - 1:he].sum() / 1e6, world, hb - 1, qbases / 1e6, hb, he, hb - 1))
     kind = "reference" if H.have_ref() else "port"
-    times, n_ovl = [], 0
-    with tempfile.TemporaryDirectory() as wd:
+    times, n_ovl, n_warm = [], 0, 0
+    wd = tempfile.mkdtemp(prefix="oic_ref_")
+    try:
         if kind == "reference":
             store = H.make_store(reads, wd)
             args = H.oic_args(P, ERATE)
@@ -144,25 +179,39 @@ def reference_leg(steps, warmup, scale_mbp=None, cores=None):
                 sf = os.path.join(wd, "skip.fasta")
                 cases.write_skip_file(H.frequent_kmers_fast(reads, K, SKIP_T), sf)
                 args += ["-k", sf]
-            for i in range(warmup + steps):
+            prep_s = time.time() - t_start
+
+            def one(i):
                 t0 = time.time()
                 ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref%d" % i), args, cores)
-                dt = time.time() - t0
-                if i >= warmup:
-                    times.append(dt)
-                n_ovl = H.parse_stats(st).get("Total overlaps produced", 0)
+                return time.time() - t0, ovb, st
+            dt, ovb, st = one(0)
+            times.append(dt)
+            # how many more runs fit the budget (projected from the first)
+            more = int(max(0.0, budget_s - (time.time() - t_start)) // max(dt, 1e-3))
+            more = min(more, max(0, steps - 1) + (1 if warmup > 0 else 0))
+            for i in range(more):
+                dt, ovb, st = one(i + 1)
+                times.append(dt)
+            if warmup > 0 and len(times) >= 3:
+                n_warm, times = 1, times[1:]
+            times = times[:max(1, steps)]
+            n_ovl = H.parse_stats(st).get("Total overlaps produced", 0)
+            if keep is not None:
+                keep.update(store=store, ovb=ovb, stats=st, workdir=wd)
         else:
-            cores = 1
-            for i in range(warmup + steps):
-                t0 = time.time()
-                res = H.run_oracle(reads, P, skip_kmers=H.frequent_kmers_fast(reads, K, SKIP_T) if SKIP_T else None)
-                dt = time.time() - t0
-                if i >= warmup:
-                    times.append(dt)
-                n_ovl = len(res["overlaps"])
+            cores, prep_s = 1, 0.0
+            t0 = time.time()
+            res = H.run_oracle(reads, P, skip_kmers=H.frequent_kmers_fast(reads, K, SKIP_T) if SKIP_T else None)
+            times.append(time.time() - t0)
+            n_ovl = len(res["overlaps"])
+    finally:
+        if keep is None:
+            subprocess.call(["rm", "-rf", wd])
     t = float(np.mean(times))
-    return dict(value=qbases / 1e6 / t, unit="query Mbp/s", cores=cores, kind=kind, sample=sample,
-                seconds_per_step=t, overlaps_per_sec=n_ovl / t, overlaps=int(n_ovl))
+    sample += "; %d timed run(s) after %d warm-up, %.1f s each (store written in %.1f s, not timed)" % (len(times), n_warm, t, prep_s)
+    return dict(value=qbases / 1e6 / t, unit="query Mbp/s", cores=cores, kind=kind, sample=sample, full_job=full,
+                seconds_per_step=t, overlaps_per_sec=n_ovl / t, overlaps=int(n_ovl), steps=len(times), warmup=n_warm)
 
 
 def main():
@@ -175,16 +224,19 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-input", default="2bit", choices=["2bit", "ascii"],
                     help="host buffers of the end-to-end leg: the gkpStore's 2-bit read encoding (oic_load_reads_2bit) or ASCII (oic_load_reads)")
-    ap.add_argument("--replicate", default="broadcast", choices=["broadcast", "rebuild"],
-                    help="N > 1: rank 0 builds the hash block and NCCL-broadcasts it (north star), or every rank builds its own copy")
+    ap.add_argument("--replicate", default="sharded", choices=["sharded", "broadcast", "rebuild"],
+                    help="N > 1: every rank builds 1/N of the hash table and the slices are exchanged by ncclAllGather (default); rank 0 "
+                         "builds and ncclBroadcasts the block; or every rank builds its own copy (no collective)")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json shape; c3 is the bench line")
+    ap.add_argument("--check", action="store_true",
+                    help="after the timed runs: gather every rank's records on the host of rank 0 and compare the multiset (all stored fields) "
+                         "with the reference binary run on the same job (exit 1 on any difference)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
-    wl = WORKLOADS[a.workload]
-    globals().update({k: v for k, v in wl.items() if k != "desc"})
+    wl = set_workload(a.workload)
     if MODE == "self" and world > 1:
         raise SystemExit("workload %s is a single-GPU shape (one hash block vs one query block)" % a.workload)
     metric = "overlapInCore query Mbp/sec (+overlaps/sec), 30x 100 Mbp genome, one hash block x one query block per GPU per step"
@@ -193,17 +245,30 @@ def main():
     config = {"workload": wl["desc"],
               "hash_block_mbp": BLOCK_BASES * a.scale / 1e6, "query_block_mbp_per_gpu": BLOCK_BASES * a.scale / 1e6,
               "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (
-                  world, "" if world == 1 else (" by NCCL broadcast" if a.replicate == "broadcast" else " by rebuilding it on every rank (no collective)")),
-              "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed"}
+                  world, "" if world == 1 else {"sharded": " by NCCL: every rank builds 1/N of the table, ncclAllGather of the slices (oic_build_hash_index_sharded)",
+                                                "broadcast": " by ncclBroadcast from rank 0 (oic_hash_block_replicate)",
+                                                "rebuild": " by rebuilding it on every rank (no collective)"}[a.replicate]),
+              "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed",
+              "e2e_input": ("gkpStore 2-bit encoded reads (2SEQ chunks, ST/gkStoreEncode.C) in pinned host memory -> oic_load_reads_2bit"
+                            if a.e2e_input == "2bit" else "ASCII reads in pinned host memory -> oic_load_reads")}
+    if a.scale != 1.0:
+        config["scale"] = a.scale
 
     if a.impl == "reference":
+        # the reference's own CPU program on the SAME job (same seed, full blocks, the same a.gpus query blocks in one process);
+        # rank 0 alone runs it.  A step is ~30-250 s of host time, so the runs that fit OIC_REF_BUDGET_S are made and the counts
+        # actually run are what the line reports (steps_requested / warmup_requested keep the command line's).
         if rank != 0:
             return
-        r = reference_leg(max(1, min(a.steps, 2)), min(a.warmup, 1))
-        line = {"impl": "reference", "metric": metric, "value": r["value"], "unit": r["unit"], "n_gpus": a.gpus, "steps": a.steps,
-                "warmup": a.warmup, "ms_per_step": 1000 * r["seconds_per_step"], "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic", "config": config,
-                "overlaps_per_sec": r["overlaps_per_sec"],
+        if a.scale != 1.0:
+            globals().update(GENOME=int(GENOME * a.scale), BLOCK_BASES=int(BLOCK_BASES * a.scale))
+        r = reference_leg(max(a.gpus, 1), max(1, min(a.steps, 2)), min(a.warmup, 1))
+        line = {"impl": "reference", "metric": metric, "value": r["value"], "unit": r["unit"], "n_gpus": a.gpus, "steps": r["steps"],
+                "warmup": r["warmup"], "steps_requested": a.steps, "warmup_requested": a.warmup,
+                "ms_per_step": 1000 * r["seconds_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8/int32 (2-bit packed bases, int32 edit rows, f64 branch score)", "data": "synthetic",
+                "config": config, "same_config": bool(r["full_job"]),
+                "overlaps_per_sec": r["overlaps_per_sec"], "overlaps_per_step": r["overlaps"],
                 "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": r["value"], "unit": r["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
@@ -214,10 +279,11 @@ def main():
     from canu_b200 import api
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
     torch.cuda.set_device(local)
-    dist = None
+    dist, host_group = None, None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        host_group = dist.new_group(backend="gloo")   # host-side gather of the overlap records (no GPU collective on them)
 
     genome = int(GENOME * a.scale)
     block = int(BLOCK_BASES * a.scale)
@@ -255,42 +321,19 @@ def main():
     lens64 = np.asarray(lens, dtype=np.int64)
     pinned2 = torch.empty(int(((lens64 + 3) // 4).sum()) + 8, dtype=torch.uint8).pin_memory()
     _, boffs = H.encode_2bit(pinned.numpy(), offs, lens, out=pinned2.numpy())
-    config["e2e_input"] = ("gkpStore 2-bit encoded reads (2SEQ chunks, ST/gkStoreEncode.C) in pinned host memory -> oic_load_reads_2bit"
-                           if a.e2e_input == "2bit" else "ASCII reads in pinned host memory -> oic_load_reads")
 
     ov = api.Overlapper(LP, device=local)
-    n_skip = 0
-    class DevView:
-        def __init__(self, ptr, nbytes):
-            self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
-
-    def replicate_hash_block():
-        """rank 0 has built the block: broadcast meta, then the three device buffers in place (NCCL over NVLink)."""
-        meta = api.HashMeta()
+    n_skip, skip_info = 0, {}
+    if world > 1 and a.replicate != "rebuild":
+        # the library's own NCCL communicator (oic_comm_init_rank): rank 0 draws the id, torch.distributed only ships its 128 bytes
+        idt = torch.zeros(api.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
         if rank == 0:
-            meta = ov.hash_block_meta()
-        mt = torch.tensor([meta.table_slots, meta.n_occ, meta.n_strings, meta.bgn_id, meta.last_id, meta.has_empty, meta.n_distinct],
-                          dtype=torch.int64, device="cuda")
-        dist.broadcast(mt, 0)
-        if rank != 0:
-            v = [int(x) for x in mt.tolist()]
-            meta = api.HashMeta(v[0], v[1], v[2], v[3], v[4], v[5], v[6])
-            ov.hash_block_reserve(meta)
-        for ptr, nbytes in buffers_of(meta):
-            t = torch.as_tensor(DevView(ptr, nbytes), device="cuda")
-            dist.broadcast(t, 0)
-        # the library works on its own stream: the broadcast (NCCL's stream) must have landed before it reads the block
-        torch.cuda.synchronize()
-        if rank != 0:
-            ov.hash_block_commit(meta)
-
-    def buffers_of(meta):
-        # buffer sizes follow from meta on every rank (the library reports the sizes of the CURRENT block on rank 0)
-        bufs = ov.hash_block_buffers()
-        sizes = [meta.table_slots * 16, (meta.n_occ + 32) * 8, (meta.n_strings + 8) & ~3]
-        return [(bufs[i][0], sizes[i]) for i in range(3)]
+            idt.copy_(torch.frombuffer(bytearray(api.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        ov.comm_init_rank(bytes(idt.cpu().numpy().tobytes()), world, rank)
 
     trace = os.environ.get("OIC_BENCH_TRACE")
+    last_records = [None]   # rank 0: the gathered records of the last end-to-end step (bench.py --check)
 
     def job(load):
         """one step; returns number of overlap records of this rank"""
@@ -304,19 +347,23 @@ def main():
         t.append(time.perf_counter())
         if world == 1 or a.replicate == "rebuild":
             ov.build_hash_index(*hash_range)
+        elif a.replicate == "sharded":
+            ov.build_hash_index_sharded(*hash_range)      # every rank builds 1/N of the table; ncclAllGather inside the library
         else:
             if rank == 0:
                 ov.build_hash_index(*hash_range)
             t.append(time.perf_counter())
-            replicate_hash_block()
+            ov.hash_block_replicate(0)                    # ncclBroadcast of the built block inside the library
         t.append(time.perf_counter())
         ov.process_overlaps(*query_range)
         n = ov.num_overlaps()
         t.append(time.perf_counter())
         if load:
-            rec = ov.overlaps()   # records back in a host buffer
-            if world > 1:         # per-GPU records gathered on the host side, in store IDs
-                shard.gather_records(rj.to_global(rec), dist, device="cuda")
+            rec = ov.overlaps()   # records back in a host buffer (D2H inside the library)
+            if world > 1:         # per-GPU records merged on the HOST of rank 0, in store IDs (gloo; nothing goes back to a GPU)
+                last_records[0] = shard.gather_records(rj.to_global(rec), dist, group=host_group, dst=0)
+            else:
+                last_records[0] = rj.to_global(rec) if rj is not None else rec
         t.append(time.perf_counter())
         if trace:
             sys.stderr.write("[rank %d] step phases ms: %s\n" % (rank, " ".join("%.1f" % (1000 * (b - a_)) for a_, b in zip(t, t[1:]))))
@@ -350,8 +397,8 @@ def main():
         keys, _, kinfo = ov.count_kmers(K, SKIP_T)   # what `meryl -B -C` + `meryl -Dt -n T` give the pipeline (oic_count_kmers)
         skip = H.kmer_strings(keys, K)
         n_skip = len(skip)
-        config["skip_kmers"] = n_skip
-        config["skip_list"] = "oic_count_kmers on the resident reads: %.1f ms on the GPU, %d pass(es)" % (kinfo["device_ms"], kinfo["passes"])
+        skip_info = {"skip_kmers": n_skip,
+                     "skip_list": "oic_count_kmers on the resident reads: %.1f ms on the GPU, %d pass(es)" % (kinfo["device_ms"], kinfo["passes"])}
         ov.set_skip_kmers(skip)
     for _ in range(a.warmup):
         job(False)
@@ -409,17 +456,25 @@ def main():
     # dram read+write bytes per launch and pipe utilisation: from the committed summary of the newest `ncu --set full`
     # capture of this command (profiles/*_kernels.json, written by tools/ncu_summary.py)
     traffic, ncu_k, ncu_src = None, {}, None
+    narrow = not (H.strtof(ERATE) > 0.06) and os.environ.get("OIC_LEAN_WIDE") is None
+    lean_prefix = "k_extend_tasks<"
+    lean_name = None
     try:
         import glob
-        ncu_src = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")))[-1]
-        for k in json.load(open(ncu_src))["kernels"]:
-            ncu_k.setdefault(k["kernel"], k)
-        # the lean instance of the task kernel (k_extend_tasks<staging width, blocks per SM>; <0, 4> is the generic one)
-        lean_name = max((n for n in ncu_k if n.startswith("k_extend_tasks<") and not n.startswith("k_extend_tasks<0")),
-                        key=lambda n: ncu_k[n].get("ms", 0.0))
-        traffic = ncu_k[lean_name]["dram_bytes_per_launch"]
+        # the newest committed summary (files are named per round: r1e_, r2a_, ... sort in that order) that CONTAINS the lean task kernel
+        for cand in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), reverse=True):
+            ks = {}
+            for k in json.load(open(cand)).get("kernels", []):
+                ks.setdefault(k["kernel"], k)
+            names = [n for n in ks if n.startswith(lean_prefix) and not n.startswith("k_extend_tasks<0")]
+            if names:
+                ncu_k, ncu_src = ks, cand
+                lean_name = max(names, key=lambda n: ks[n].get("ms", 0.0))
+                traffic = ks[lean_name]["dram_bytes_per_launch"]
+                break
     except Exception:
-        lean_name = "k_extend_tasks<1>"
+        pass
+    kernel_label = lean_name or ("k_extend_tasks (lean row loop, %s staging instance)" % ("narrow" if narrow else "wide"))
 
     def ncu_of(name):
         k = ncu_k.get(name)
@@ -427,7 +482,7 @@ def main():
             return None
         return {x: k.get(x) for x in ("ms", "dram_bytes_per_launch", "dram_GBps", "issue_active_pct", "alu_pipe_pct", "lsu_pipe_pct",
                                       "warps_active_pct", "l1_hit_pct", "l2_hit_pct", "sectors_per_ld_request")}
-    roof = {"kernel": "k_extend_tasks<768, 6> (lean row loop, rows <= 768 diagonals staged in shared memory, 6 blocks per SM)", "bound": "int32", "achieved": tasks_gops, "peak": alu_peak, "unit": "Gop/s",
+    roof = {"kernel": kernel_label + " (lean row loop: rows staged in shared memory, template args = staging width, blocks per SM)", "bound": "int32", "achieved": tasks_gops, "peak": alu_peak, "unit": "Gop/s",
             "frac": tasks_gops / alu_peak if alu_peak else None, "traffic": traffic, "peak_source": int_src,
             "algorithmic_ops_per_launch": i_tasks, "ms_per_launch": ms_tasks,
             "formula": "6*C + 4*W (C = DP cells, W = 16-base compare words) x share of extension calls run by this kernel; "
@@ -462,11 +517,30 @@ def main():
             "gpu_launches": int(tm["launches"]), "roofline": roof, "stages": stages,
             "work_per_step_rank0": {k: d[k] // steps for k in ("n_inserts", "n_distinct", "n_windows", "n_found", "n_refs", "n_add_ref",
                                                                  "n_runs", "n_pairs", "ext_calls", "ext_cells", "ext_words")}}
-    if world == 1 and not a.no_cpu:
-        r = reference_leg(1, 0)
+    line.update(skip_info)
+    keep = {} if a.check else None
+    if (world == 1 and not a.no_cpu) or a.check:
+        if a.scale != 1.0:
+            globals().update(GENOME=genome, BLOCK_BASES=block)
+        r = reference_leg(world, 1, 0, keep=keep)   # the same job, one run of the reference binary on this box's host cores
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         line["cpu_baseline"]["overlaps_per_sec"] = r["overlaps_per_sec"]
+        line["cpu_baseline"]["overlaps"] = r["overlaps"]
+    if a.check:
+        # record-for-record: the gathered records of the last end-to-end step (all ranks, store IDs) against the reference's .ovb
+        from canu_b200 import api as _api
+        dd = _api.decode_records(last_records[0])
+        mine = sorted(H.format_raw({k: int(dd[k][i]) for k in dd}) for i in range(len(dd["a_iid"])))
+        want = reference_records(keep["store"], keep["ovb"])
+        ok = mine == want
+        line["check"] = {"records": len(mine), "reference_records": len(want), "equal": ok,
+                         "what": "every stored field of every overlap gathered from %d rank(s) vs oracle/_ref/overlapInCore on the same job" % world}
+        subprocess.call(["rm", "-rf", keep["workdir"]])
     print(json.dumps(line))
+    if a.check and not line["check"]["equal"]:
+        if dist is not None:
+            dist.destroy_process_group()
+        raise SystemExit("bench.py --check: records differ from the reference (%d vs %d)" % (line["check"]["records"], line["check"]["reference_records"]))
     if dist is not None:
         dist.destroy_process_group()
 

@@ -22,7 +22,8 @@ ABI_SYMBOLS = [
     "oic_clear_overlaps", "oic_get_stats", "oic_get_timings", "oic_reset_timings", "oic_hash_block_meta",
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
     "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
-    "oic_copy_kmer_histogram",
+    "oic_copy_kmer_histogram", "oic_comm_unique_id", "oic_comm_init_rank", "oic_comm_init_all", "oic_comm_info",
+    "oic_hash_block_replicate", "oic_build_hash_index_sharded",
 ]
 
 
@@ -59,7 +60,12 @@ class Timings(C.Structure):
 
 class HashMeta(C.Structure):
     _fields_ = [("table_slots", C.c_uint64), ("n_occ", C.c_uint64), ("n_strings", C.c_uint32), ("bgn_id", C.c_uint32),
-                ("last_id", C.c_uint32), ("has_empty", C.c_uint32), ("n_distinct", C.c_uint64)]
+                ("last_id", C.c_uint32), ("has_empty", C.c_uint32), ("n_distinct", C.c_uint64),
+                ("n_slices", C.c_uint32), ("slice_bits", C.c_uint32), ("filter_words", C.c_uint64)]
+
+
+HASH_BLOCK_NBUF = 4
+COMM_ID_BYTES = 128
 
 
 class DevBuffer(C.Structure):
@@ -106,6 +112,12 @@ def load_library():
     lib.oic_hash_block_reserve.argtypes = [vp, C.POINTER(HashMeta)]
     lib.oic_hash_block_buffers.argtypes = [vp, C.POINTER(DevBuffer)]
     lib.oic_hash_block_commit.argtypes = [vp, C.POINTER(HashMeta)]
+    lib.oic_comm_unique_id.argtypes = [vp]
+    lib.oic_comm_init_rank.argtypes = [vp, vp, C.c_int, C.c_int]
+    lib.oic_comm_init_all.argtypes = [C.POINTER(vp), C.c_int]
+    lib.oic_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.oic_hash_block_replicate.argtypes = [vp, vp, C.c_int]
+    lib.oic_build_hash_index_sharded.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     lib.oic_dump_index.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp, vp, vp]
     lib.oic_set_debug.argtypes = [vp, C.c_uint32]
     lib.oic_dump_pairs.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp]
@@ -322,12 +334,31 @@ class Overlapper:
         self._check(self.lib.oic_hash_block_reserve(self._h, C.byref(meta)), "oic_hash_block_reserve")
 
     def hash_block_buffers(self):
-        b = (DevBuffer * 3)()
+        b = (DevBuffer * HASH_BLOCK_NBUF)()
         self._check(self.lib.oic_hash_block_buffers(self._h, b), "oic_hash_block_buffers")
         return [(x.ptr, x.bytes) for x in b]
 
     def hash_block_commit(self, meta):
         self._check(self.lib.oic_hash_block_commit(self._h, C.byref(meta)), "oic_hash_block_commit")
+
+    # ---- the collective inside the library (NCCL)
+    def comm_init_rank(self, unique_id, n_ranks, rank):
+        """attach an NCCL communicator: `unique_id` = the 128 bytes rank 0 got from comm_unique_id(), shipped by the launcher"""
+        buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
+        self._check(self.lib.oic_comm_init_rank(self._h, buf, n_ranks, rank), "oic_comm_init_rank")
+
+    def comm_info(self):
+        n, r = C.c_int(0), C.c_int(0)
+        self._check(self.lib.oic_comm_info(self._h, C.byref(n), C.byref(r)), "oic_comm_info")
+        return n.value, r.value
+
+    def hash_block_replicate(self, root=0, comm=None):
+        self._check(self.lib.oic_hash_block_replicate(self._h, comm, root), "oic_hash_block_replicate")
+
+    def build_hash_index_sharded(self, bgn_id, end_id, comm=None):
+        last = C.c_uint32(0)
+        self._check(self.lib.oic_build_hash_index_sharded(self._h, comm, bgn_id, end_id, C.byref(last)), "oic_build_hash_index_sharded")
+        return last.value
 
     # ---- stage dumps (tests)
     def set_debug(self, mask):
@@ -352,6 +383,25 @@ class Overlapper:
         self._check(self.lib.oic_dump_pairs(self._h, C.byref(npair), C.byref(nm), pairs.ctypes.data, matches.ctypes.data),
                     "oic_dump_pairs")
         return pairs, matches
+
+
+def comm_unique_id():
+    """ncclGetUniqueId through the library: 128 bytes for the launcher to ship to every rank"""
+    lib = load_library()
+    buf = (C.c_uint8 * COMM_ID_BYTES)()
+    rc = lib.oic_comm_unique_id(buf)
+    if rc != 0:
+        raise OicError("oic_comm_unique_id failed (%d): %s" % (rc, lib.oic_last_error(None).decode()))
+    return bytes(buf)
+
+
+def comm_init_all(overlappers):
+    """one process, one context per GPU: ncclCommInitAll over the contexts' devices"""
+    lib = load_library()
+    arr = (C.c_void_p * len(overlappers))(*[o._h for o in overlappers])
+    rc = lib.oic_comm_init_all(arr, len(overlappers))
+    if rc != 0:
+        raise OicError("oic_comm_init_all failed (%d): %s" % (rc, lib.oic_last_error(overlappers[0]._h).decode()))
 
 
 def measure_int32_peak(device=0):

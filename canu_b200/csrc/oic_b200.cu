@@ -8,13 +8,16 @@
  * Find_Overlaps -> Process_String_Olaps -> Process_Matches -> Extend_Alignment -> Output_Overlap.
  * There is no CPU implementation of any stage in this library: every entry point needs a CUDA device.
  */
+#include <dlfcn.h>
 #include <math.h>
+#include <nccl.h>   /* types and prototypes only: the library is dlopen'ed at the first communicator call */
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -26,7 +29,7 @@ using namespace oic;
 
 namespace {
 
-std::string g_create_error;
+thread_local std::string g_create_error;   // error text of the last failed context-less call on THIS thread (oic_last_error(NULL))
 
 struct DevBuf {
   void *p = nullptr;
@@ -127,15 +130,23 @@ struct oic_ctx {
   std::vector<uint64_t> skip_keys;
   DevBuf d_skip_keys;
 
+  int sm_count = 148;
+
+  // communicator (NCCL), attached by oic_comm_init_rank / oic_comm_init_all
+  ncclComm_t comm = nullptr;
+  int comm_n = 0, comm_rank = 0;
+  DevBuf d_xchg;               // small device staging of the collectives (meta, per-rank counts)
+
   // hash block
   bool hash_ready = false;
   oic_hash_meta_t hb = {};
+  TableGeom geom = {};
   DevBuf d_table, d_occ, d_str_flags, d_str_use, d_filter, d_ovf_slot, d_ovf_occ, d_multi_list, d_first_occ, d_cnt, d_mid_list, d_blk, d_big_list, d_occ_tmp, d_hist;
   // identity of the block in the table (oic_set_job sweeps reuse it): requested range + the two load limits
   uint32_t hbk_bgn = 0, hbk_end = 0, hbk_strings = 0; uint64_t hbk_datalen = 0;
   bool job_mode = false;   // set by oic_set_job: only a job sweep reuses a block; a plain oic_build_hash_index always builds
   unsigned long long mem_avail = 0;   // device memory the pair stage may plan with (free + what it already holds)
-  bool have_occupancy = false;   // occupancy bitmap of the current hash block is valid
+  bool have_filter = false;      // Bloom filter of the current hash block is valid
 
   // search buffers
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
@@ -156,6 +167,7 @@ struct oic_ctx {
   oic_stats_t stats = {};
   oic_timings_t tm = {};
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  cudaEvent_t ev_call[2] = {nullptr, nullptr};   // whole-call timers (oic_process_overlaps, oic_count_kmers)
   cudaEvent_t ev_k[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // inner kernel timers of the pair stage
 
   // debug dumps of the last oic_process_overlaps call
@@ -183,16 +195,19 @@ namespace {
 
 inline unsigned nblocks(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
 
-struct StageTimer {
+struct StageTimer {   // stops itself on every exit path (early error returns included)
   oic_ctx *c;
   float *acc;
+  bool running = true;
   StageTimer(oic_ctx *c_, float *acc_) : c(c_), acc(acc_) { cudaEventRecord(c->ev[0], c->stream); }
+  ~StageTimer() { stop(); }
   void stop() {
+    if (!running) return;
+    running = false;
     cudaEventRecord(c->ev[1], c->stream);
-    cudaEventSynchronize(c->ev[1]);
+    if (cudaEventSynchronize(c->ev[1]) != cudaSuccess) return;
     float ms = 0;
-    cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
-    *acc += ms;
+    if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) *acc += ms;
   }
 };
 
@@ -207,19 +222,32 @@ int zero_counters(oic_ctx *c) {
   return 0;
 }
 
-// occupancy bitmap of the table (oic_build.cuh k_occupancy); OIC_OCCUPANCY=0 turns it off
-bool use_occupancy() {
-  static const char *env = getenv("OIC_OCCUPANCY");
+// Bloom filter of the block's k-mers (oic_dev_common.cuh TableGeom), filled by k_insert; OIC_FILTER=0 makes the scan ignore it
+bool use_filter() {
+  static const char *env = getenv("OIC_FILTER");
   return !(env && env[0] == '0');
 }
-int build_occupancy(oic_ctx *c, uint64_t slots) {
-  c->have_occupancy = false;
-  if (!use_occupancy()) return 0;
-  CK(c->d_filter.ensure(slots / 8 + 64));
-  k_occupancy<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots, c->d_filter.as<uint32_t>());
-  c->tm.launches += 1;
-  c->have_occupancy = true;
-  return 0;
+
+// Table geometry for a block of n_keys k-mer windows (+ skip k-mers): slots ~ factor x windows in steps of one slice
+// (32..63 slices, a multiple of FILTER_REGIONS = 8 so that 1, 2, 4 or 8 GPUs own whole slices and whole filter regions;
+// slices of at least 4096 slots so that the load of a single slice cannot stray far from the mean), filter ~ 4 bits per window.
+TableGeom table_geometry(uint64_t n_keys) {
+  static const char *tf = getenv("OIC_TABLE_FACTOR");   // slots per k-mer window (default 1.5: load ~0.55 on a 1x block)
+  static const char *ff = getenv("OIC_FILTER_BITS");    // filter bits per k-mer window before rounding up to a power of two (default 4)
+  const double factor = tf ? std::max(1.1, atof(tf)) : 1.5;
+  const double fbits = ff ? std::max(1.0, atof(ff)) : 4.0;
+  const uint64_t want = (uint64_t)(factor * (double)n_keys) + 16;
+  TableGeom g;
+  g.slice_bits = 12;
+  while ((want >> g.slice_bits) >= 64) g.slice_bits++;
+  g.slice_mask = (1ULL << g.slice_bits) - 1;
+  uint64_t ns = (want + g.slice_mask) >> g.slice_bits;
+  ns = std::max<uint64_t>(FILTER_REGIONS, (ns + FILTER_REGIONS - 1) / FILTER_REGIONS * FILTER_REGIONS);
+  g.n_slices = (uint32_t)ns;
+  const uint64_t fwords = (uint64_t)(fbits * (double)n_keys / 32.0) + 1;
+  g.region_bits = 6;
+  while (((uint64_t)FILTER_REGIONS << g.region_bits) < fwords && g.region_bits < 28) g.region_bits++;
+  return g;
 }
 
 __global__ void k_table_init(Slot *t, uint64_t n) {
@@ -228,22 +256,31 @@ __global__ void k_table_init(Slot *t, uint64_t n) {
 }
 
 // ---- hash build ------------------------------------------------------------------------------------------
+uint64_t block_windows(const oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vector<uint8_t> &use) {
+  const uint32_t K = (uint32_t)c->P.kmer_len;
+  uint64_t n = 0;
+  for (uint32_t s = 0; s < n_strings; s++)
+    if (use[s] && c->h_len[ri_bgn + s] >= K) n += c->h_len[ri_bgn + s] - K + 1;
+  return n;
+}
+
 // Builds the index over string slots [0, n_strings) starting at read index ri_bgn; use[] says which are loaded.
-int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vector<uint8_t> &use, DevCounters &hc) {
+// part / n_parts: only the k-mers whose home slice belongs to share `part` of `n_parts` are inserted (the sharded build of a
+// GPU group; 0 / 1 = everything).  The slices of the other shares stay empty, the occurrence lists built are those of this share.
+int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vector<uint8_t> &use, DevCounters &hc, uint32_t part = 0,
+                uint32_t n_parts = 1) {
   const oic_params_t &P = c->P;
   const int K = P.kmer_len;
-  uint64_t n_windows = 0;
-  for (uint32_t s = 0; s < n_strings; s++)
-    if (use[s] && c->h_len[ri_bgn + s] >= (uint32_t)K) n_windows += c->h_len[ri_bgn + s] - K + 1;
+  const uint64_t n_windows = block_windows(c, ri_bgn, n_strings, use);
   if (n_windows >= (1ull << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %llu k-mers (limit 2^30)", (unsigned long long)n_windows);
   if (n_strings >= (1u << 30)) return c->fail(OIC_ERR_CAPACITY, "hash block has %u reads (limit 2^30)", n_strings);
-  static const char *tf = getenv("OIC_TABLE_FACTOR");   // slots per k-mer window before rounding up to a power of two (default 2)
-  const double factor = tf ? std::max(1.1, atof(tf)) : 2.0;
-  uint64_t want = (uint64_t)(factor * (double)(n_windows + c->skip_keys.size())) + 16;
-  uint64_t slots = 1024;
-  while (slots < want) slots <<= 1;
+  const TableGeom geom = table_geometry(n_windows + c->skip_keys.size());
+  const uint64_t slots = geom_slots(geom), fwords = geom_filter_words(geom);
+  if (geom.n_slices % n_parts) return c->fail(OIC_ERR_ARG, "internal: %u table slices do not split over %u ranks", geom.n_slices, n_parts);
+  const uint64_t share = n_windows;   // list scratch: the worst case (every window a repeat, all of them in this share)
 
   CK(c->d_table.ensure(slots * sizeof(Slot)));
+  CK(c->d_filter.ensure(fwords * 4));
   CK(c->d_str_flags.ensure(((size_t)n_strings + 8) & ~(size_t)3));
   CK(c->d_str_use.ensure((size_t)n_strings + 4));
   const int64_t region_pos = c->h_pos[ri_bgn];
@@ -251,17 +288,18 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   const int64_t region_end = c->h_pos[ri_last] + c->h_len[ri_last];
   const uint64_t region_words = (uint64_t)((region_end - region_pos + 31) >> 5);
   // worst case: every window belongs to a repeated k-mer
-  CK(c->d_ovf_slot.ensure((n_windows + 32) * sizeof(uint32_t)));
-  CK(c->d_ovf_occ.ensure((n_windows + 32) * sizeof(uint64_t)));
-  CK(c->d_multi_list.ensure((n_windows / 2 + 32) * sizeof(uint32_t)));
-  CK(c->d_first_occ.ensure((n_windows / 2 + 32) * sizeof(uint64_t)));
-  CK(c->d_cnt.ensure((n_windows / 2 + 32) * sizeof(uint32_t)));
-  CK(c->d_mid_list.ensure((n_windows / (SMALL_LIST + 1) + 32) * sizeof(uint32_t)));
-  CK(c->d_big_list.ensure((n_windows / 33 + 32) * sizeof(uint32_t)));
+  CK(c->d_ovf_slot.ensure((share + 32) * sizeof(uint32_t)));
+  CK(c->d_ovf_occ.ensure((share + 32) * sizeof(uint64_t)));
+  CK(c->d_multi_list.ensure((share / 2 + 32) * sizeof(uint32_t)));
+  CK(c->d_first_occ.ensure((share / 2 + 32) * sizeof(uint64_t)));
+  CK(c->d_cnt.ensure((share / 2 + 32) * sizeof(uint32_t)));
+  CK(c->d_mid_list.ensure((share / (SMALL_LIST + 1) + 32) * sizeof(uint32_t)));
+  CK(c->d_big_list.ensure((share / 33 + 32) * sizeof(uint32_t)));
   CK(c->d_occ.ensure((n_windows + 32) * sizeof(uint64_t)));
 
   if (zero_counters(c)) return OIC_ERR_CUDA;
   k_table_init<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots);
+  CK(cudaMemsetAsync(c->d_filter.p, 0, fwords * 4, c->stream));
   CK(cudaMemsetAsync(c->d_str_flags.p, 0, ((size_t)n_strings + 8) & ~(size_t)3, c->stream));
   CK(cudaMemcpyAsync(c->d_str_use.p, use.data(), n_strings, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += n_strings;
@@ -278,7 +316,10 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   a.region_words = region_words;
   a.K = K;
   a.table = c->d_table.as<Slot>();
-  a.slot_mask = slots - 1;
+  a.geom = geom;
+  a.slice_lo = geom.n_slices / n_parts * part;
+  a.slice_hi = geom.n_slices / n_parts * (part + 1);
+  a.filter = c->d_filter.as<uint32_t>();
   a.ovf_slot = c->d_ovf_slot.as<uint32_t>();
   a.ovf_occ = c->d_ovf_occ.as<uint64_t>();
   a.multi_list = c->d_multi_list.as<uint32_t>();
@@ -299,22 +340,276 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   k_sort_mid<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   c->tm.launches += 8;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
-  if (c->n_off ? hc.n_inserts > n_windows : hc.n_inserts != n_windows) return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
+  if (n_parts == 1 && (c->n_off ? hc.n_inserts > n_windows : hc.n_inserts != n_windows))
+    return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
   const uint32_t n_occ = hc.n_ovf + hc.n_multi;
   if (hc.occ_cursor != n_occ) return c->fail(OIC_ERR_STATE, "internal: %u list entries allocated, %u on the overflow list", hc.occ_cursor, n_occ);
   if (hc.n_big_lists) {
     CK(c->d_occ_tmp.ensure(((size_t)n_occ + 32) * sizeof(uint64_t)));
-    unsigned grid = std::min<unsigned>(hc.n_big_lists, 148 * 8);
+    unsigned grid = std::min<unsigned>(hc.n_big_lists, c->sm_count * 8);
     k_sort_big<<<grid, BIG_THREADS, 0, c->stream>>>(c->d_table.as<Slot>(), c->d_big_list.as<uint32_t>(), c->d_ctr.as<DevCounters>(), c->d_occ.as<uint64_t>(),
                                                     c->d_occ_tmp.as<uint64_t>());
     c->tm.launches += 1;
   }
+  c->geom = geom;
   c->hb.table_slots = slots;
+  c->hb.n_slices = geom.n_slices;
+  c->hb.slice_bits = geom.slice_bits;
+  c->hb.filter_words = fwords;
   c->hb.n_occ = n_occ;
   c->hb.n_strings = n_strings;
   c->hb.n_distinct = hc.n_distinct;
+  c->have_filter = true;
   CK(cudaGetLastError());
   return 0;
+}
+
+// ---- NCCL, loaded on demand ------------------------------------------------------------------------------
+struct NcclApi {
+  void *handle = nullptr;
+  decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+  decltype(&ncclCommInitRank) CommInitRank = nullptr;
+  decltype(&ncclCommInitAll) CommInitAll = nullptr;
+  decltype(&ncclCommDestroy) CommDestroy = nullptr;
+  decltype(&ncclCommCount) CommCount = nullptr;
+  decltype(&ncclCommUserRank) CommUserRank = nullptr;
+  decltype(&ncclBroadcast) Broadcast = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclGroupStart) GroupStart = nullptr;
+  decltype(&ncclGroupEnd) GroupEnd = nullptr;
+  decltype(&ncclGetErrorString) GetErrorString = nullptr;
+  std::string err;
+};
+NcclApi *nccl_api() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, []() {
+    // a copy the process already holds (e.g. the one torch brought) first: two NCCL copies in one process do not share state
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) { api.err = std::string("cannot load libnccl.so.2: ") + dlerror(); return; }
+    api.handle = h;
+#define OIC_NCCL_SYM(name) \
+    api.name = reinterpret_cast<decltype(api.name)>(dlsym(h, "nccl" #name)); \
+    if (!api.name) { api.err = "libnccl.so.2 lacks nccl" #name; api.handle = nullptr; return; }
+    OIC_NCCL_SYM(GetUniqueId) OIC_NCCL_SYM(CommInitRank) OIC_NCCL_SYM(CommInitAll) OIC_NCCL_SYM(CommDestroy) OIC_NCCL_SYM(CommCount)
+    OIC_NCCL_SYM(CommUserRank) OIC_NCCL_SYM(Broadcast) OIC_NCCL_SYM(AllGather) OIC_NCCL_SYM(GroupStart) OIC_NCCL_SYM(GroupEnd)
+    OIC_NCCL_SYM(GetErrorString)
+#undef OIC_NCCL_SYM
+  });
+  return api.handle ? &api : nullptr;
+}
+#define NK(call)                                                                                              \
+  do {                                                                                                        \
+    ncclResult_t r_ = (call);                                                                                 \
+    if (r_ != ncclSuccess) return c->fail(OIC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, nccl_api()->GetErrorString(r_)); \
+  } while (0)
+
+// the communicator a collective call works on: the caller's ncclComm_t, or the one attached to the context
+int resolve_comm(oic_ctx *c, void *arg, ncclComm_t &comm, int &n, int &rank) {
+  NcclApi *api = nccl_api();
+  if (!api) return c->fail(OIC_ERR_CUDA, "NCCL unavailable: %s", nccl_api() ? "" : "libnccl.so.2 could not be loaded");
+  if (arg) {
+    comm = reinterpret_cast<ncclComm_t>(arg);
+    NK(api->CommCount(comm, &n));
+    NK(api->CommUserRank(comm, &rank));
+    return 0;
+  }
+  if (!c->comm) return c->fail(OIC_ERR_STATE, "no communicator: call oic_comm_init_rank / oic_comm_init_all first, or pass an ncclComm_t");
+  comm = c->comm; n = c->comm_n; rank = c->comm_rank;
+  return 0;
+}
+
+// which reads the reference's load loop would take, ignoring the hash-load limit (Build_Hash_Index.C:538-616)
+void hash_load_plan(const oic_ctx *c, uint32_t bgn_id, uint32_t end_id, std::vector<uint8_t> &use) {
+  const oic_params_t &P = c->P;
+  use.clear();
+  uint64_t total_len = 0;
+  uint32_t cur = bgn_id;
+  while (use.size() < P.max_hash_strings && total_len < P.max_hash_data_len && cur <= end_id) {
+    const uint32_t ri = cur - c->first_id;
+    uint8_t u = c->h_hash_ok[ri] && (int64_t)c->h_len[ri] >= (int64_t)P.min_olap_len;
+    if (u) total_len += c->h_len[ri] + 1;
+    use.push_back(u);
+    cur++;
+  }
+}
+
+// Mark_Skip_Kmers on the finished table (Empty bits, screened ends, absent k-mers): every rank of a group runs it on its own copy
+int mark_skip(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, unsigned int &has_empty) {
+  const oic_params_t &P = c->P;
+  has_empty = 0;
+  if (c->skip_keys.empty()) return 0;
+  CK(c->d_skip_keys.ensure(c->skip_keys.size() * 8));
+  CK(c->d_flag.ensure(16));
+  CK(cudaMemsetAsync(c->d_flag.p, 0, 16, c->stream));
+  CK(cudaMemcpyAsync(c->d_skip_keys.p, c->skip_keys.data(), c->skip_keys.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += c->skip_keys.size() * 8;
+  k_mark_skip<<<nblocks(c->skip_keys.size(), 128), 128, 0, c->stream>>>(
+      c->d_table.as<Slot>(), c->geom, c->d_filter.as<uint32_t>(), c->d_skip_keys.as<uint64_t>(), c->skip_keys.size(), c->d_occ.as<uint64_t>(),
+      c->d_len.as<uint32_t>(), ri_bgn, n_strings, c->d_str_flags.as<uint8_t>(), P.kmer_len, P.use_hopeless_check, c->d_flag.as<unsigned int>());
+  c->tm.launches += 1;
+  CK(cudaMemcpyAsync(&has_empty, c->d_flag.p, 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// lists of this rank's slices were allocated from 0: shift their start indices to the rank's segment of the gathered occ array
+__global__ void k_rebase_lists(Slot *table, uint64_t slot_lo, uint64_t slot_hi, uint32_t base) {
+  const uint64_t i = slot_lo + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= slot_hi) return;
+  const unsigned long long p = table[i].pay;
+  if (table[i].key != EMPTY_KEY && pay_is_list(p)) table[i].pay = p + base;   // start lives in the low 32 bits and cannot carry out (n_occ < 2^30)
+}
+
+struct ShardCounts { unsigned long long n_inserts, n_distinct, n_occ, pad; };
+
+int replicate_impl(oic_ctx *c, ncclComm_t comm, int n, int rank, int root);
+
+/* Build_Hash_Index for one context (comm_arg == nullptr and no group) or collectively for a GPU group (sharded = true). */
+int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id, bool sharded = false) {
+  if (!c) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  const oic_params_t &P = c->P;
+  ncclComm_t comm = nullptr;
+  int n_ranks = 1, rank = 0;
+  if (sharded) {
+    int rc = resolve_comm(c, comm_arg, comm, n_ranks, rank);
+    if (rc) return rc;
+  }
+  if (c->job_mode && c->hash_ready && c->hbk_bgn == bgn_id && c->hbk_end == end_id && c->hbk_strings == P.max_hash_strings && c->hbk_datalen == P.max_hash_data_len) {
+    if (last_id) *last_id = c->hb.last_id;   // the same request as the block in the table: nothing to do (every rank of a group agrees)
+    return OIC_OK;
+  }
+  c->hash_ready = false;
+  if (bgn_id < c->first_id || end_id >= c->first_id + c->n_reads || c->n_reads == 0)
+    return c->fail(OIC_ERR_ARG, "hash range %u-%u outside the loaded reads %u-%u", bgn_id, end_id, c->first_id, c->first_id + c->n_reads - 1);
+  StageTimer t(c, &c->tm.ms_build);
+  std::vector<uint8_t> use;
+  hash_load_plan(c, bgn_id, end_id, use);
+  uint32_t n_strings = (uint32_t)use.size();
+  if (n_strings == 0) { if (last_id) *last_id = end_id; return c->fail(OIC_ERR_ARG, "empty hash range"); }
+  const uint64_t hash_entry_limit = (uint64_t)(P.hash_load * (double)((uint64_t)1 << P.hash_bits) * 21);   // Build_Hash_Index.C:474
+  const uint32_t ri_bgn = bgn_id - c->first_id;
+  NcclApi *api = n_ranks > 1 ? nccl_api() : nullptr;
+
+  DevCounters hc;
+  unsigned long long tot_inserts = 0, tot_distinct = 0;
+  bool root_path = false;   // group only: build on rank 0 and broadcast (rank count does not divide the slices, or the load limit trips)
+  if (n_ranks > 1) {
+    const TableGeom g = table_geometry(block_windows(c, ri_bgn, n_strings, use) + c->skip_keys.size());
+    root_path = (g.n_slices % (uint32_t)n_ranks) != 0 || (FILTER_REGIONS % (uint32_t)n_ranks) != 0 || getenv("OIC_SHARDED_BUILD_OFF") != nullptr;
+  }
+  if (n_ranks > 1 && !root_path) {
+    // ---- every rank builds the slices it owns, then the slices / list segments / filter regions are exchanged
+    int rcode = build_block(c, ri_bgn, n_strings, use, hc, (uint32_t)rank, (uint32_t)n_ranks);
+    if (rcode) return rcode;
+    CK(c->d_xchg.ensure(sizeof(ShardCounts) * (size_t)n_ranks + 256));
+    std::vector<ShardCounts> cnt(n_ranks);
+    ShardCounts mine = {hc.n_inserts, hc.n_distinct, c->hb.n_occ, 0};
+    ShardCounts *dx = c->d_xchg.as<ShardCounts>();
+    CK(cudaMemcpyAsync(dx + rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, c->stream));
+    NK(api->AllGather(dx + rank, dx, sizeof(ShardCounts), ncclChar, comm, c->stream));
+    CK(cudaMemcpyAsync(cnt.data(), dx, sizeof(ShardCounts) * n_ranks, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    unsigned long long base = 0, tot_occ = 0;
+    for (int q = 0; q < n_ranks; q++) {
+      if (q < rank) base += cnt[q].n_occ;
+      tot_occ += cnt[q].n_occ; tot_inserts += cnt[q].n_inserts; tot_distinct += cnt[q].n_distinct;
+    }
+    if (tot_distinct >= hash_entry_limit) root_path = true;   // the cut needs the global first-occurrence histogram: rare, done on one rank
+    else {
+      const uint64_t slots = c->hb.table_slots, per = slots / n_ranks;
+      const uint64_t fper = c->hb.filter_words / n_ranks;
+      const uint64_t my_occ = c->hb.n_occ;
+      // own list segment out of the way (segments land at their global offsets), own list starts shifted to the segment
+      CK(c->d_occ_tmp.ensure((my_occ + 32) * 8));
+      if (my_occ) CK(cudaMemcpyAsync(c->d_occ_tmp.p, c->d_occ.p, my_occ * 8, cudaMemcpyDeviceToDevice, c->stream));
+      if (base) k_rebase_lists<<<nblocks(per, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), per * rank, per * (rank + 1), (uint32_t)base);
+      NK(api->GroupStart());
+      NK(api->AllGather(c->d_table.as<Slot>() + per * rank, c->d_table.p, per * sizeof(Slot), ncclChar, comm, c->stream));
+      NK(api->AllGather(c->d_filter.as<uint32_t>() + fper * rank, c->d_filter.p, fper * 4, ncclChar, comm, c->stream));
+      unsigned long long off = 0;
+      for (int q = 0; q < n_ranks; q++) {
+        if (cnt[q].n_occ) NK(api->Broadcast(c->d_occ_tmp.p, c->d_occ.as<uint64_t>() + off, cnt[q].n_occ * 8, ncclChar, q, comm, c->stream));
+        off += cnt[q].n_occ;
+      }
+      NK(api->GroupEnd());
+      c->tm.launches += 1;
+      c->hb.n_occ = tot_occ;
+      c->hb.n_distinct = tot_distinct;
+      const uint64_t n_windows = block_windows(c, ri_bgn, n_strings, use);
+      if (c->n_off ? tot_inserts > n_windows : tot_inserts != n_windows)
+        return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted by the group, %llu expected", tot_inserts, (unsigned long long)n_windows);
+    }
+  }
+  if (n_ranks > 1 && root_path) {
+    // ---- rank 0 builds alone (load cut-off included), the others receive
+    int rcode = 0;
+    uint32_t last = 0;
+    if (rank == 0) {
+      t.stop();
+      rcode = build_hash_index_impl(c, nullptr, bgn_id, end_id, &last, false);
+    }
+    // (a failed root still enters the collective so that nobody hangs; the meta carries the failure)
+    if (rank == 0 && rcode) c->hash_ready = false;
+    const int r2 = replicate_impl(c, comm, n_ranks, rank, 0);
+    if (rcode) return rcode;
+    if (r2) return r2;
+    c->hbk_bgn = bgn_id; c->hbk_end = end_id; c->hbk_strings = P.max_hash_strings; c->hbk_datalen = P.max_hash_data_len;
+    if (last_id) *last_id = c->hb.last_id;
+    return OIC_OK;
+  }
+  if (n_ranks == 1) {
+    int rcode = build_block(c, ri_bgn, n_strings, use, hc);
+    if (rcode) return rcode;
+    if (hc.n_distinct >= hash_entry_limit) {
+      // the load loop stops taking reads once Hash_Entries >= limit: find the read at which that happens
+      CK(c->d_hist.ensure((size_t)n_strings * 4));
+      CK(cudaMemsetAsync(c->d_hist.p, 0, (size_t)n_strings * 4, c->stream));
+      k_first_occ<<<nblocks(c->hb.table_slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), c->hb.table_slots, c->d_occ.as<uint64_t>(),
+                                                                          c->d_hist.as<uint32_t>());
+      c->tm.launches += 1;
+      std::vector<uint32_t> hist(n_strings);
+      CK(cudaMemcpyAsync(hist.data(), c->d_hist.p, (size_t)n_strings * 4, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      c->tm.d2h_bytes += (uint64_t)n_strings * 4;
+      uint64_t cum = 0;
+      uint32_t cut = n_strings;
+      for (uint32_t s = 0; s < n_strings; s++) {
+        cum += hist[s];
+        if (cum >= hash_entry_limit) { cut = s + 1; break; }
+      }
+      if (cut < n_strings) {
+        n_strings = cut;
+        use.resize(n_strings);
+        rcode = build_block(c, ri_bgn, n_strings, use, hc);
+        if (rcode) return rcode;
+      }
+    }
+    tot_inserts = hc.n_inserts; tot_distinct = hc.n_distinct;
+  }
+  // screened k-mers
+  unsigned int has_empty = 0;
+  if (mark_skip(c, ri_bgn, n_strings, has_empty)) return OIC_ERR_CUDA;
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  t.stop();
+  c->hb.bgn_id = bgn_id;
+  c->hb.last_id = bgn_id + n_strings - 1;
+  c->hb.has_empty = has_empty;
+  c->hash_ready = true;
+  c->hbk_bgn = bgn_id; c->hbk_end = end_id; c->hbk_strings = P.max_hash_strings; c->hbk_datalen = P.max_hash_data_len;
+  for (uint32_t s = 0; s < n_strings; s++)
+    if (use[s]) c->stats.n_hash_bases += c->h_len[ri_bgn + s];
+  c->stats.n_inserts += tot_inserts;
+  c->stats.n_distinct += tot_distinct;
+  c->stats.n_hash_blocks++;
+  c->stats.last_end_hash_id = c->hb.last_id;
+  c->mem_avail = 0;   // the pair stage re-plans its scratch against what is free now
+  if (last_id) *last_id = c->hb.last_id;
+  return OIC_OK;
 }
 
 }  // namespace
@@ -339,20 +634,17 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   }
   if (device < 0 || device >= ndev) { g_create_error = "bad device index"; return OIC_ERR_ARG; }
   if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OIC_ERR_CUDA; }
-  {
-    // the index is probed with independent random 16-byte loads: ask L2 to fetch single 32-byte sectors from HBM instead
-    // of promoting every miss to a 64/128-byte fetch (a hint; OIC_L2_FETCH=64|128 restores larger fetches)
-    const char *fg = getenv("OIC_L2_FETCH");
-    const size_t gran = fg ? strtoull(fg, nullptr, 10) : 32;
-    if (gran) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, gran);
-    cudaGetLastError();
-  }
   oic_ctx *c = new oic_ctx();
   c->P = *p;
   if (c->P.max_erate > 0.06) c->P.use_hopeless_check = 0;   // OIC/overlapInCore.C:416-421
   c->device = device;
+  {
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0) c->sm_count = sms;
+  }
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev_call[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev_call[1])) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev_k[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[1])) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev_k[2])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[3])) != cudaSuccess ||
       (e = cudaEventCreate(&c->ev_k[4])) != cudaSuccess || (e = cudaEventCreate(&c->ev_k[5])) != cudaSuccess ||
@@ -377,10 +669,13 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg};
+  if (c->comm && nccl_api()) nccl_api()->CommDestroy(c->comm);
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  if (c->ev_call[0]) cudaEventDestroy(c->ev_call[0]);
+  if (c->ev_call[1]) cudaEventDestroy(c->ev_call[1]);
   for (int i = 0; i < 6; i++) if (c->ev_k[i]) cudaEventDestroy(c->ev_k[i]);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -395,6 +690,7 @@ static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const ui
   if (!c || (n && (!offsets || !lengths || !bases)) || first_id < 1) return c ? c->fail(OIC_ERR_ARG, "oic_load_reads: bad argument") : OIC_ERR_ARG;
   cudaSetDevice(c->device);
   c->hash_ready = false;
+  c->mem_avail = 0;
   c->first_id = first_id;
   c->n_reads = n;
   c->h_pos.resize(n + 1);
@@ -518,97 +814,49 @@ int oic_set_skip_kmers(oic_ctx_t *c, uint64_t n, const char *kmers) {
 }
 
 int oic_build_hash_index(oic_ctx_t *c, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id) {
-  if (!c) return OIC_ERR_ARG;
-  cudaSetDevice(c->device);
-  const oic_params_t &P = c->P;
-  if (c->job_mode && c->hash_ready && c->hbk_bgn == bgn_id && c->hbk_end == end_id && c->hbk_strings == P.max_hash_strings && c->hbk_datalen == P.max_hash_data_len) {
-    if (last_id) *last_id = c->hb.last_id;   // the same request as the block in the table: nothing to do
-    return OIC_OK;
-  }
-  c->hash_ready = false;
-  if (bgn_id < c->first_id || end_id >= c->first_id + c->n_reads || c->n_reads == 0)
-    return c->fail(OIC_ERR_ARG, "hash range %u-%u outside the loaded reads %u-%u", bgn_id, end_id, c->first_id, c->first_id + c->n_reads - 1);
-  StageTimer t(c, &c->tm.ms_build);
-  // which reads the reference's load loop would take, ignoring the hash-load limit (Build_Hash_Index.C:538-616)
-  std::vector<uint8_t> use;
-  uint64_t total_len = 0;
-  uint32_t cur = bgn_id;
-  while (use.size() < P.max_hash_strings && total_len < P.max_hash_data_len && cur <= end_id) {
-    const uint32_t ri = cur - c->first_id;
-    uint8_t u = c->h_hash_ok[ri] && (int64_t)c->h_len[ri] >= (int64_t)P.min_olap_len;
-    if (u) total_len += c->h_len[ri] + 1;
-    use.push_back(u);
-    cur++;
-  }
-  uint32_t n_strings = (uint32_t)use.size();
-  if (n_strings == 0) { if (last_id) *last_id = end_id; t.stop(); return c->fail(OIC_ERR_ARG, "empty hash range"); }
-  const uint64_t hash_entry_limit = (uint64_t)(P.hash_load * (double)((uint64_t)1 << P.hash_bits) * 21);   // Build_Hash_Index.C:474
-  const uint32_t ri_bgn = bgn_id - c->first_id;
-
-  DevCounters hc;
-  int rcode = build_block(c, ri_bgn, n_strings, use, hc);
-  if (rcode) return rcode;
-  if (hc.n_distinct >= hash_entry_limit) {
-    // the load loop stops taking reads once Hash_Entries >= limit: find the read at which that happens
-    CK(c->d_hist.ensure((size_t)n_strings * 4));
-    CK(cudaMemsetAsync(c->d_hist.p, 0, (size_t)n_strings * 4, c->stream));
-    k_first_occ<<<nblocks(c->hb.table_slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), c->hb.table_slots, c->d_occ.as<uint64_t>(),
-                                                                        c->d_hist.as<uint32_t>());
-    c->tm.launches += 1;
-    std::vector<uint32_t> hist(n_strings);
-    CK(cudaMemcpyAsync(hist.data(), c->d_hist.p, (size_t)n_strings * 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    c->tm.d2h_bytes += (uint64_t)n_strings * 4;
-    uint64_t cum = 0;
-    uint32_t cut = n_strings;
-    for (uint32_t s = 0; s < n_strings; s++) {
-      cum += hist[s];
-      if (cum >= hash_entry_limit) { cut = s + 1; break; }
-    }
-    if (cut < n_strings) {
-      n_strings = cut;
-      use.resize(n_strings);
-      rcode = build_block(c, ri_bgn, n_strings, use, hc);
-      if (rcode) return rcode;
-    }
-  }
-  // screened k-mers
-  unsigned int has_empty = 0;
-  if (!c->skip_keys.empty()) {
-    CK(c->d_skip_keys.ensure(c->skip_keys.size() * 8));
-    CK(c->d_flag.ensure(16));
-    CK(cudaMemsetAsync(c->d_flag.p, 0, 16, c->stream));
-    CK(cudaMemcpyAsync(c->d_skip_keys.p, c->skip_keys.data(), c->skip_keys.size() * 8, cudaMemcpyHostToDevice, c->stream));
-    c->tm.h2d_bytes += c->skip_keys.size() * 8;
-    k_mark_skip<<<nblocks(c->skip_keys.size(), 128), 128, 0, c->stream>>>(
-        c->d_table.as<Slot>(), c->hb.table_slots - 1, c->d_skip_keys.as<uint64_t>(), c->skip_keys.size(), c->d_occ.as<uint64_t>(),
-        c->d_len.as<uint32_t>(), ri_bgn, n_strings, c->d_str_flags.as<uint8_t>(), P.kmer_len, P.use_hopeless_check, c->d_flag.as<unsigned int>());
-    c->tm.launches += 1;
-    CK(cudaMemcpyAsync(&has_empty, c->d_flag.p, 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-  }
-  if (build_occupancy(c, c->hb.table_slots)) return OIC_ERR_CUDA;
-  CK(cudaStreamSynchronize(c->stream));
-  CK(cudaGetLastError());
-  t.stop();
-  c->hb.bgn_id = bgn_id;
-  c->hb.last_id = bgn_id + n_strings - 1;
-  c->hb.has_empty = has_empty;
-  c->hash_ready = true;
-  c->hbk_bgn = bgn_id; c->hbk_end = end_id; c->hbk_strings = P.max_hash_strings; c->hbk_datalen = P.max_hash_data_len;
-  for (uint32_t s = 0; s < n_strings; s++)
-    if (use[s]) c->stats.n_hash_bases += c->h_len[ri_bgn + s];
-  c->stats.n_inserts += hc.n_inserts;
-  c->stats.n_distinct += hc.n_distinct;
-  c->stats.n_hash_blocks++;
-  c->stats.last_end_hash_id = c->hb.last_id;
-  if (last_id) *last_id = c->hb.last_id;
-  return OIC_OK;
+  return build_hash_index_impl(c, nullptr, bgn_id, end_id, last_id);
 }
 
 }  // extern "C"
 
 namespace {
+
+/* Root holds a built block: meta first (the receivers size their buffers from it), then the four buffers, all on the
+ * context's stream.  meta.table_slots == 0 tells the receivers that the root failed (nobody hangs in the collective). */
+int replicate_impl(oic_ctx *c, ncclComm_t comm, int n, int rank, int root) {
+  NcclApi *api = nccl_api();
+  if (n == 1) return c->hash_ready ? OIC_OK : c->fail(OIC_ERR_STATE, "oic_hash_block_replicate: no hash block on the root");
+  StageTimer t(c, &c->tm.ms_build);
+  CK(c->d_xchg.ensure(sizeof(ShardCounts) * (size_t)n + 256));
+  oic_hash_meta_t meta;
+  memset(&meta, 0, sizeof(meta));
+  if (rank == root && c->hash_ready) meta = c->hb;
+  if (rank == root) CK(cudaMemcpyAsync(c->d_xchg.p, &meta, sizeof(meta), cudaMemcpyHostToDevice, c->stream));
+  NK(api->Broadcast(c->d_xchg.p, c->d_xchg.p, sizeof(meta), ncclChar, root, comm, c->stream));
+  if (rank != root) {
+    CK(cudaMemcpyAsync(&meta, c->d_xchg.p, sizeof(meta), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  if (meta.table_slots == 0) return c->fail(OIC_ERR_STATE, "oic_hash_block_replicate: the root rank has no hash block");
+  if (rank != root) {
+    const int rc = oic_hash_block_reserve(c, &meta);
+    if (rc) return rc;   // (the peers would wait in the broadcasts below: a receiver that cannot allocate is fatal for the job)
+  }
+  const oic_hash_meta_t keep = c->hb;
+  c->hb = meta;   // oic_hash_block_buffers sizes the buffers from the meta
+  oic_dev_buffer_t b[OIC_HASH_BLOCK_NBUF];
+  oic_hash_block_buffers(c, b);
+  c->hb = keep;
+  NK(api->GroupStart());
+  for (int i = 0; i < OIC_HASH_BLOCK_NBUF; i++) NK(api->Broadcast(b[i].ptr, b[i].ptr, b[i].bytes, ncclChar, root, comm, c->stream));
+  NK(api->GroupEnd());
+  c->tm.launches += 1;
+  if (rank != root) {
+    const int rc = oic_hash_block_commit(c, &meta);
+    if (rc) return rc;
+  } else CK(cudaStreamSynchronize(c->stream));
+  return OIC_OK;
+}
 
 int ensure_pair_scratch(oic_ctx *c, unsigned n_warps, unsigned long long rowcap) {
   CK(c->d_vals.ensure((size_t)n_warps * rowcap * 4));
@@ -658,8 +906,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   sa.rd_pos = c->d_pos.as<int64_t>(); sa.rd_len = c->d_len.as<uint32_t>();
   sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.n_queries = nq;
   sa.first_id = c->first_id; sa.hash_bgn_id = c->hb.bgn_id; sa.K = P.kmer_len;
-  sa.table = c->d_table.as<Slot>(); sa.slot_mask = c->hb.table_slots - 1; sa.occ = c->d_occ.as<uint64_t>();
-  sa.occupancy = c->have_occupancy ? c->d_filter.as<uint32_t>() : nullptr;
+  sa.table = c->d_table.as<Slot>(); sa.geom = c->geom; sa.occ = c->d_occ.as<uint64_t>();
+  sa.filter = (c->have_filter && use_filter()) ? c->d_filter.as<uint32_t>() : nullptr;
   sa.has_empty = (int)c->hb.has_empty;
   sa.recs = c->d_recs.as<Seed>(); sa.max_chunks = max_chunks;
   sa.chunk_next = c->d_chunk_next.as<uint32_t>(); sa.chunk_cnt = c->d_chunk_cnt.as<uint32_t>(); sa.chunk_qs = c->d_chunk_qs.as<uint32_t>();
@@ -749,24 +997,38 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       StageTimer t3(c, &c->tm.ms_extend);
       // lean task kernel: the narrow-staging instance (more resident warps) unless the error rate makes wide bands the rule
       const bool narrow = !(P.max_erate > 0.06) && getenv("OIC_LEAN_WIDE") == nullptr;
-      const unsigned grid = 148 * 4, grid_tasks = 148 * (narrow ? TASK_BLOCKS_NARROW : TASK_BLOCKS_WIDE);
+      const unsigned sms = (unsigned)c->sm_count;
+      const unsigned grid = sms * 4, grid_tasks = sms * (narrow ? TASK_BLOCKS_NARROW : TASK_BLOCKS_WIDE);
       const unsigned n_warps = grid_tasks * EXT_WARPS;
       // edit-row history per warp: the worst case (every row 2e+1 wide) if it fits the budget, else what fits
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
       const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
-      // memory budgets follow the device: a B200 has 180 GB, the c3 job needs 8 GB of history, the wide-band c2 job 51 GB
-      if (c->mem_avail == 0) {   // asked once per context: cudaMemGetInfo costs about a millisecond
+      // memory budgets follow the device: a B200 has 180 GB, the c3 job needs 8 GB of history, the wide-band c2 job 51 GB.
+      // mem_avail = what is free now + what the two big scratch buffers already hold; it is asked again whenever the loaded
+      // reads or the hash block changed (they zero it) and after a failed allocation (cudaMemGetInfo costs about a millisecond).
+      if (c->mem_avail == 0) {
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
         c->mem_avail = (unsigned long long)free_b + c->d_vals.cap + c->d_dpool.cap;
       }
-      const unsigned long long avail = c->mem_avail;
-      unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::max<unsigned long long>(12ull << 30, avail * 45 / 100));
+      unsigned long long avail = c->mem_avail;
+      unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::min<unsigned long long>(std::max<unsigned long long>(12ull << 30, avail * 45 / 100), avail * 60 / 100));
       // test knobs: shrink the first-pass history / the delta pool so that the overflow -> serial retry path runs on small inputs
       if (const char *e = getenv("OIC_VALS_BUDGET_MB")) vals_bytes = strtoull(e, nullptr, 10) << 20;
-      const unsigned long long budget = vals_bytes / 4 / n_warps;
-      const unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
-      if (ensure_pair_scratch(c, n_warps, rowcap)) return OIC_ERR_CUDA;
+      unsigned long long budget = vals_bytes / 4 / n_warps;
+      unsigned long long rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
+      // an allocation that fails (another context, a K-mer count table, a larger block took the memory since the plan): halve the
+      // history and try again -- pairs whose rows no longer fit take the retry path below -- instead of failing the call
+      for (int attempt = 0; ensure_pair_scratch(c, n_warps, rowcap) != 0; attempt++) {
+        cudaGetLastError();
+        if (attempt >= 6 || rowcap <= (unsigned long long)c->max_rows * 64 + 1024) return OIC_ERR_CUDA;
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        c->mem_avail = avail = (unsigned long long)free_b + c->d_vals.cap + c->d_dpool.cap;
+        vals_bytes = std::min(vals_bytes / 2, avail * 45 / 100);
+        budget = vals_bytes / 4 / n_warps;
+        rowcap = std::min(worst, std::max(budget, (unsigned long long)c->max_rows * 64 + 1024));
+      }
       // longest-processing-time-first order
       CK(c->d_order.ensure((size_t)n_pairs * 4 + 4));
       CK(c->d_hist2.ensure(ORDER_BINS * 4));
@@ -803,7 +1065,11 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       CK(c->d_results.ensure((size_t)n_runs * sizeof(TaskResult)));
       CK(c->d_alive.ensure((size_t)n_runs + 4));
       CK(c->d_wide.ensure((size_t)n_runs * 4 + 4));
-      CK(c->d_dpool.ensure((size_t)dpool_cap * 4));
+      while (c->d_dpool.ensure((size_t)dpool_cap * 4) != cudaSuccess) {   // a pool that is too small only sends pairs to the retry path
+        cudaGetLastError();
+        if (dpool_cap <= (1ull << 24)) return c->fail(OIC_ERR_CUDA, "no device memory for the delta pool");
+        dpool_cap /= 2;
+      }
       // (pairs with an N in either read are never handed over: the lean loop of pass 2 knows no wildcards)
       ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
@@ -818,7 +1084,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         else k_extend_tasks<LSW_WIDE, TASK_BLOCKS_WIDE><<<grid_tasks, EXT_WARPS * 32, 0, c->stream>>>(ea);
         cudaEventRecord(c->ev_k[2], c->stream);
         k_extend_tasks<0, 4><<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
-        k_commit_pairs<<<148 * 4, 128, 0, c->stream>>>(ea);
+        k_commit_pairs<<<sms * 4, 128, 0, c->stream>>>(ea);
         cudaEventRecord(c->ev_k[3], c->stream);
         c->tm.launches += 3;
       }
@@ -839,7 +1105,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         const uint32_t nr = hc.n_retry;
         k_replay<<<nblocks(n_pairs, 128), 128, 0, c->stream>>>(rp);
         const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
-        const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(148 * 4, std::max<unsigned long long>(24ull << 30, vals_bytes) / 4 / big / EXT_WARPS));
+        const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(sms * 4, std::max<unsigned long long>(24ull << 30, vals_bytes) / 4 / big / EXT_WARPS));
         cudaEventRecord(c->ev_k[4], c->stream);
         DevBuf keep_retry;
         CK(keep_retry.ensure((size_t)nr * 4));
@@ -919,9 +1185,7 @@ int oic_process_overlaps(oic_ctx_t *c, uint32_t bgn_ref_id, uint32_t end_ref_id)
   if (end_ref_id < bgn_ref_id) return OIC_OK;
   if (bgn_ref_id < c->first_id || end_ref_id >= c->first_id + c->n_reads)
     return c->fail(OIC_ERR_ARG, "query range %u-%u outside the loaded reads", bgn_ref_id, end_ref_id);
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0); cudaEventCreate(&e1);
-  cudaEventRecord(e0, c->stream);
+  cudaEventRecord(c->ev_call[0], c->stream);
   const oic_params_t &P = c->P;
   uint32_t id = bgn_ref_id;
   uint64_t batch_bases = c->batch_bases;
@@ -946,12 +1210,10 @@ int oic_process_overlaps(oic_ctx_t *c, uint32_t bgn_ref_id, uint32_t end_ref_id)
     }
     id = j;
   }
-  cudaEventRecord(e1, c->stream);
-  cudaEventSynchronize(e1);
+  cudaEventRecord(c->ev_call[1], c->stream);
   float ms = 0;
-  cudaEventElapsedTime(&ms, e0, e1);
-  c->tm.ms_total_search += ms;
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (cudaEventSynchronize(c->ev_call[1]) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev_call[0], c->ev_call[1]) == cudaSuccess)
+    c->tm.ms_total_search += ms;
   return rc;
 }
 
@@ -1034,9 +1296,13 @@ int oic_hash_block_reserve(oic_ctx_t *c, const oic_hash_meta_t *m) {
   if (!c || !m) return OIC_ERR_ARG;
   cudaSetDevice(c->device);
   c->hash_ready = false;
+  if (m->n_slices == 0 || m->table_slots != ((uint64_t)m->n_slices << m->slice_bits) || m->filter_words == 0 ||
+      (m->filter_words & (m->filter_words - 1)) != 0 || m->filter_words < FILTER_REGIONS)
+    return c->fail(OIC_ERR_ARG, "oic_hash_block_reserve: inconsistent table geometry in the meta");
   CK(c->d_table.ensure(m->table_slots * sizeof(Slot)));
   CK(c->d_occ.ensure(((size_t)m->n_occ + 32) * 8));
   CK(c->d_str_flags.ensure(((size_t)m->n_strings + 8) & ~(size_t)3));
+  CK(c->d_filter.ensure(m->filter_words * 4));
   return OIC_OK;
 }
 int oic_hash_block_buffers(const oic_ctx_t *c, oic_dev_buffer_t b[OIC_HASH_BLOCK_NBUF]) {
@@ -1044,20 +1310,84 @@ int oic_hash_block_buffers(const oic_ctx_t *c, oic_dev_buffer_t b[OIC_HASH_BLOCK
   b[0].ptr = c->d_table.p; b[0].bytes = c->hb.table_slots * sizeof(Slot);
   b[1].ptr = c->d_occ.p; b[1].bytes = ((uint64_t)c->hb.n_occ + 32) * 8;
   b[2].ptr = c->d_str_flags.p; b[2].bytes = ((uint64_t)c->hb.n_strings + 8) & ~(uint64_t)3;
+  b[3].ptr = c->d_filter.p; b[3].bytes = c->hb.filter_words * 4;
   return OIC_OK;
 }
 int oic_hash_block_commit(oic_ctx_t *c, const oic_hash_meta_t *m) {
   if (!c || !m) return OIC_ERR_ARG;
   cudaSetDevice(c->device);
   c->hb = *m;
-  // the occupancy bitmap is not shipped: rebuilt here from the table that arrived
-  if (build_occupancy(c, m->table_slots)) return OIC_ERR_CUDA;
+  c->geom.n_slices = m->n_slices;
+  c->geom.slice_bits = m->slice_bits;
+  c->geom.slice_mask = (1ULL << m->slice_bits) - 1;
+  c->geom.region_bits = 0;
+  while (((uint64_t)FILTER_REGIONS << c->geom.region_bits) < m->filter_words) c->geom.region_bits++;
+  c->have_filter = true;   // the filter travels with the block
   CK(cudaStreamSynchronize(c->stream));
   c->hash_ready = true;
-  c->hbk_bgn = c->hbk_end = 0;   // a block that arrived by broadcast is never mistaken for a local build
+  c->hbk_bgn = c->hbk_end = 0;   // a block that arrived from another rank is never mistaken for a local build
   c->stats.n_hash_blocks++;
   c->stats.last_end_hash_id = m->last_id;
+  c->mem_avail = 0;
   return OIC_OK;
+}
+
+// ---- the collective inside the library -------------------------------------------------------------------
+int oic_comm_unique_id(uint8_t id[OIC_COMM_ID_BYTES]) {
+  static_assert(OIC_COMM_ID_BYTES == NCCL_UNIQUE_ID_BYTES, "ncclUniqueId size");
+  NcclApi *api = nccl_api();
+  if (!api || !id) { g_create_error = "NCCL unavailable (libnccl.so.2 could not be loaded)"; return OIC_ERR_CUDA; }
+  ncclUniqueId u;
+  const ncclResult_t r = api->GetUniqueId(&u);
+  if (r != ncclSuccess) { g_create_error = api->GetErrorString(r); return OIC_ERR_CUDA; }
+  memcpy(id, u.internal, OIC_COMM_ID_BYTES);
+  return OIC_OK;
+}
+int oic_comm_init_rank(oic_ctx_t *c, const uint8_t id[OIC_COMM_ID_BYTES], int n_ranks, int rank) {
+  if (!c || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return c ? c->fail(OIC_ERR_ARG, "oic_comm_init_rank: bad argument") : OIC_ERR_ARG;
+  NcclApi *api = nccl_api();
+  if (!api) return c->fail(OIC_ERR_CUDA, "NCCL unavailable (libnccl.so.2 could not be loaded)");
+  if (c->comm) return c->fail(OIC_ERR_STATE, "the context already has a communicator");
+  cudaSetDevice(c->device);
+  ncclUniqueId u;
+  memcpy(u.internal, id, OIC_COMM_ID_BYTES);
+  NK(api->CommInitRank(&c->comm, n_ranks, u, rank));
+  c->comm_n = n_ranks; c->comm_rank = rank;
+  return OIC_OK;
+}
+int oic_comm_init_all(oic_ctx_t *const *ctxs, int n) {
+  if (!ctxs || n < 1) return OIC_ERR_ARG;
+  NcclApi *api = nccl_api();
+  oic_ctx *c = ctxs[0];
+  if (!api) return c->fail(OIC_ERR_CUDA, "NCCL unavailable (libnccl.so.2 could not be loaded)");
+  std::vector<int> devs(n);
+  std::vector<ncclComm_t> comms(n);
+  for (int i = 0; i < n; i++) {
+    if (!ctxs[i] || ctxs[i]->comm) return c->fail(OIC_ERR_STATE, "oic_comm_init_all: null context or communicator already attached");
+    devs[i] = ctxs[i]->device;
+  }
+  NK(api->CommInitAll(comms.data(), n, devs.data()));
+  for (int i = 0; i < n; i++) { ctxs[i]->comm = comms[i]; ctxs[i]->comm_n = n; ctxs[i]->comm_rank = i; }
+  return OIC_OK;
+}
+int oic_comm_info(const oic_ctx_t *c, int *n_ranks, int *rank) {
+  if (!c) return OIC_ERR_ARG;
+  if (n_ranks) *n_ranks = c->comm ? c->comm_n : 0;
+  if (rank) *rank = c->comm_rank;
+  return OIC_OK;
+}
+int oic_hash_block_replicate(oic_ctx_t *c, void *nccl_comm, int root) {
+  if (!c) return OIC_ERR_ARG;
+  cudaSetDevice(c->device);
+  ncclComm_t comm;
+  int n = 1, rank = 0;
+  int rc = resolve_comm(c, nccl_comm, comm, n, rank);
+  if (rc) return rc;
+  if (root < 0 || root >= n) return c->fail(OIC_ERR_ARG, "oic_hash_block_replicate: bad root");
+  return replicate_impl(c, comm, n, rank, root);
+}
+int oic_build_hash_index_sharded(oic_ctx_t *c, void *nccl_comm, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id) {
+  return build_hash_index_impl(c, nccl_comm, bgn_id, end_id, last_id, true);
 }
 
 // ---- stage dumps ---------------------------------------------------------------------------------------
@@ -1103,8 +1433,23 @@ int oic_dump_pairs(oic_ctx_t *c, uint64_t *n_pairs, uint64_t *n_matches, int64_t
 }
 
 
-/* Measured INT32 issue rates of this GPU in Gop/s (thread operations): alu = LOP3/IADD3 chains, imad = IMAD chains. */
+static int count_kmers_impl(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_found, uint32_t *n_passes, double *device_ms);
+
+/* Canonical K-mer counts of the loaded reads (oic_count.cuh).  The count table (up to 60 % of the free memory) and its output
+ * buffers are released before returning -- the overlap stage plans its own scratch against what is free -- and a failed
+ * count leaves no partial result behind. */
 int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_found, uint32_t *n_passes, double *device_ms) {
+  const int rc = count_kmers_impl(c, K, min_count, n_found, n_passes, device_ms);
+  if (c) {
+    cudaSetDevice(c->device);
+    c->d_kc_table.release(); c->d_kc_out_keys.release(); c->d_kc_out_cnt.release(); c->d_kc_big.release(); c->d_kc_hist.release();
+    c->mem_avail = 0;
+    if (rc != OIC_OK) { c->freq.clear(); c->kc_hist.clear(); if (n_found) *n_found = 0; }
+  }
+  return rc;
+}
+
+static int count_kmers_impl(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_found, uint32_t *n_passes, double *device_ms) {
   if (!c) return OIC_ERR_ARG;
   if (K < 2 || K > 31) return c->fail(OIC_ERR_UNSUPPORTED, "oic_count_kmers: K must be 2..31");
   if (c->n_reads == 0) return c->fail(OIC_ERR_STATE, "oic_count_kmers before oic_load_reads");
@@ -1141,9 +1486,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   CK(cudaMemsetAsync(c->d_kc_n.p, 0, 16, c->stream));
   c->kc_hist.clear();
   std::vector<uint32_t> big_counts;
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0); cudaEventCreate(&e1);
-  cudaEventRecord(e0, c->stream);
+  cudaEventRecord(c->ev_call[0], c->stream);
   CountArgs a;
   a.fwd = c->d_fwd.as<uint64_t>(); a.n_off = c->n_off; a.rd_pos = c->d_pos.as<int64_t>(); a.rd_len = c->d_len.as<uint32_t>();
   a.n_reads = c->n_reads; a.n_words = c->stream_words - 4; a.K = (int)K;
@@ -1156,7 +1499,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     // histogram of this partition's counts (accumulates over the passes)
     unsigned int *n_big = reinterpret_cast<unsigned int *>(c->d_kc_n.as<unsigned long long>() + 1);
     CK(cudaMemsetAsync(n_big, 0, 4, c->stream));
-    k_count_hist<<<148 * 8, 256, 0, c->stream>>>(a.table, slots, c->d_kc_hist.as<unsigned long long>(), HB, c->d_kc_big.as<uint32_t>(), BIG_CAP, n_big);
+    k_count_hist<<<c->sm_count * 8, 256, 0, c->stream>>>(a.table, slots, c->d_kc_hist.as<unsigned long long>(), HB, c->d_kc_big.as<uint32_t>(), BIG_CAP, n_big);
     {
       unsigned int nb = 0;
       CK(cudaMemcpyAsync(&nb, n_big, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1195,10 +1538,9 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
     c->freq.resize(old + n);
     for (size_t i = 0; i < n; i++) c->freq[old + i] = std::make_pair((uint64_t)hk[i], hcnt[i]);
   }
-  cudaEventRecord(e1, c->stream);
-  cudaEventSynchronize(e1);
-  cudaEventElapsedTime(&c->kc_ms, e0, e1);
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaEventRecord(c->ev_call[1], c->stream);
+  CK(cudaEventSynchronize(c->ev_call[1]));
+  cudaEventElapsedTime(&c->kc_ms, c->ev_call[0], c->ev_call[1]);
   {
     std::vector<unsigned long long> hh(HB);
     CK(cudaMemcpy(hh.data(), c->d_kc_hist.p, (size_t)HB * 8, cudaMemcpyDeviceToHost));
@@ -1231,6 +1573,7 @@ int oic_copy_kmer_histogram(oic_ctx_t *c, uint64_t *hist, uint64_t capacity, uin
   return OIC_OK;
 }
 
+/* Measured INT32 issue rates of this GPU in Gop/s (thread operations): alu = LOP3/IADD3 chains, imad = IMAD chains. */
 int oic_measure_int32_peak(int device, double *alu_gops, double *imad_gops) {
   if (cudaSetDevice(device) != cudaSuccess) return OIC_ERR_CUDA;
   cudaDeviceProp prop;

@@ -14,7 +14,7 @@
  *                  occurrence array (bump allocator), scatter the entries into it
  *   k_multi_sort   runs of 2..6 entries: one thread each (sorting network in registers, descending);
  *   k_sort_mid     7..32 entries: one warp per run (bitonic);  k_sort_big: longer runs, one block each (LSD radix)
- *   k_occupancy    bitmap of occupied slots (L2-resident), tested by the seed scan before it touches the table
+ *                  (the Bloom filter the seed scan tests first is filled by the arrival that claims a slot)
  *   k_first_occ    histogram of "read in which a k-mer first appears" -> hash-load cut-off on the host
  *   k_mark_skip    Empty bit + screened ends for the -k skip list (and absent k-mers when the hopeless check is on)
  */
@@ -141,7 +141,9 @@ struct BuildArgs {
   uint64_t region_words;     // words from region_pos to the end of the last string
   int K;
   Slot *table;
-  uint64_t slot_mask;
+  TableGeom geom;
+  uint32_t slice_lo, slice_hi;   // only k-mers whose home slice is in [slice_lo, slice_hi) are inserted (sharded build: this rank's slices)
+  uint32_t *filter;          // Bloom filter words (zeroed before the insert)
   uint32_t *ovf_slot;        // overflow list: every occurrence of a k-mer that occurs more than once ...
   uint64_t *ovf_occ;         // ... {slot, occurrence word}
   uint32_t *multi_list;      // slots of those k-mers
@@ -175,15 +177,15 @@ __device__ __forceinline__ unsigned long long ld_key(const Slot *sl) {
   asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(&sl->key) : "memory");
   return v;
 }
-__device__ __forceinline__ bool table_find(const Slot *__restrict__ table, uint64_t mask, uint64_t h, unsigned long long key, uint32_t &slot,
+__device__ __forceinline__ bool table_find(const Slot *__restrict__ table, const TableGeom &g, uint64_t hk, unsigned long long key, uint32_t &slot,
                                            unsigned long long &pay) {
-  h &= mask;
+  uint64_t h = geom_home(g, hk);
   while (true) {
     uint4 v = __ldg(reinterpret_cast<const uint4 *>(table + h));
     unsigned long long cur = ((unsigned long long)v.y << 32) | v.x;
     if (cur == key) { slot = (uint32_t)h; pay = ((unsigned long long)v.w << 32) | v.z; return true; }
     if (cur == EMPTY_KEY) return false;
-    h = (h + 1) & mask;
+    h = geom_next(g, h);
   }
 }
 
@@ -217,7 +219,7 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
     if (mk) valid_n = false;
     prev_n = l ? ((M0 >> (2 * (l - 1))) & 3u) != 0 : (o > 0 && ((a.fwd[(p0 >> 5) - 1 + a.n_off] >> 62) & 3u) != 0);
   }
-  bool claimed = false, conv = false, later = false;
+  bool claimed = false, conv = false, later = false, mine = false;
   unsigned long long my_occ = 0;
   uint32_t my_slot = 0;
   const bool valid = valid_n && a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
@@ -225,15 +227,21 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
     const uint32_t pv = o > 0 && !prev_n;   // the window one base earlier holds an N: it is not in the table, a run starts here
     const uint32_t pb = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : (pv ? (uint32_t)(a.fwd[(p0 >> 5) - 1] >> 62) & 3u : 0u);
     my_occ = occ_pack(s, (uint32_t)o, pv, pb);
-    uint64_t h = hash_key(key) & a.slot_mask;
+    const uint64_t hk = hash_key(key);
+    const uint32_t slice = geom_slice(a.geom, hk);
+    mine = slice >= a.slice_lo && slice < a.slice_hi;
+    uint64_t h = geom_home(a.geom, hk);
     // a plain load first: it brings the line into L2 with the memory-level parallelism of loads; an atomic that misses
     // L2 is several times slower (measured on B200: CAS-first insert 25 ms, load-first 6 ms for 99 M windows)
-    unsigned long long cur = ld_key(a.table + h);
-    while (true) {
+    unsigned long long cur = mine ? ld_key(a.table + h) : 0ULL;
+    while (mine) {
       if (cur == EMPTY_KEY) cur = atomicCAS(&a.table[h].key, EMPTY_KEY, key);
       if (cur == EMPTY_KEY) {
         if (my_occ) atomicOr(&a.table[h].pay, my_occ);
         claimed = true;
+        uint32_t fw, fb;   // first arrival of the k-mer: its two filter bits (a fire-and-forget reduction into an L2-resident array)
+        geom_filter(a.geom, hk, fw, fb);
+        atomicOr(a.filter + fw, fb);
         break;
       }
       if (cur == key) {
@@ -242,7 +250,7 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
         later = true;
         break;
       }
-      h = (h + 1) & a.slot_mask;
+      h = geom_next(a.geom, h);
       cur = ld_key(a.table + h);
     }
   }
@@ -260,7 +268,7 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
     if (later) { const uint32_t w = base + __popc(lm & below); a.ovf_slot[w] = my_slot; a.ovf_occ[w] = my_occ; }
     if (conv) a.multi_list[mbase + __popc(cm & below)] = my_slot;
   }
-  const uint32_t nv = __popc(__ballot_sync(FULL, valid)), nc = __popc(__ballot_sync(FULL, claimed));
+  const uint32_t nv = __popc(__ballot_sync(FULL, valid && mine)), nc = __popc(__ballot_sync(FULL, claimed));
   if (l == 0) {
     if (nv) atomicAdd(&a.ctr->n_inserts, (unsigned long long)nv);
     if (nc) atomicAdd(&a.ctr->n_distinct, (unsigned long long)nc);
@@ -521,27 +529,16 @@ __global__ void k_first_occ(const Slot *__restrict__ table, uint64_t n_slots, co
   if (n) atomicAdd(&hist[occ_str(occ[pay_start(sl.pay) + n - 1])], 1u);
 }
 
-// Occupancy bitmap of the finished table: bit i = slot i holds a k-mer.  32 MB for a 100 Mbp block (the table is 4.3 GB), so
-// it stays in L2 while the seed scan streams table lines through it: a window whose home slot is free -- two thirds of the
-// windows that are absent from the block -- is answered by an L2 hit instead of a 128-byte HBM fetch.  One warp per 32
-// slots, coalesced, no atomics.
-__global__ void __launch_bounds__(256) k_occupancy(const Slot *__restrict__ table, uint64_t n_slots, uint32_t *bitmap) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool occ = i < n_slots && table[i].key != EMPTY_KEY;
-  const unsigned m = __ballot_sync(FULL, occ);
-  if (lane_id() == 0 && i < n_slots) bitmap[i >> 5] = m;
-}
-
 // Mark_Skip_Kmers: one thread per (k-mer, orientation) key.
 // str_flags: bit0 = left end screened, bit1 = right end screened  (Hash_Frag_Info_t, OIC/overlapInCore.H)
-__global__ void k_mark_skip(Slot *table, uint64_t mask, const uint64_t *__restrict__ keys, uint64_t n_keys,
+__global__ void k_mark_skip(Slot *table, TableGeom geom, uint32_t *filter, const uint64_t *__restrict__ keys, uint64_t n_keys,
                             const uint64_t *__restrict__ occ, const uint32_t *__restrict__ rd_len, uint32_t ri_bgn,
                             uint32_t n_strings, uint8_t *str_flags8, int K, int add_absent, unsigned int *has_empty) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_keys) return;
   const unsigned long long key = keys[i];
   const uint64_t hk = hash_key(key);
-  uint64_t h = hk & mask;
+  uint64_t h = geom_home(geom, hk);
   unsigned long long pay = 0;
   while (true) {
     Slot cur = table[h];
@@ -551,13 +548,16 @@ __global__ void k_mark_skip(Slot *table, uint64_t mask, const uint64_t *__restri
       unsigned long long ok, op;
       slot_cas(table + h, EMPTY_KEY, 0ULL, key, PAY_MULTI | PAY_MULTI_EMPTY, ok, op);
       if (ok == EMPTY_KEY) {
+        uint32_t fw, fb;   // the scan must reach this entry: it screens the query's ends (Find_Overlaps.C:323-325)
+        geom_filter(geom, hk, fw, fb);
+        atomicOr(filter + fw, fb);
         *has_empty = 1;
         return;
       }
       cur.key = ok; cur.pay = op;
     }
     if (cur.key == key) { pay = cur.pay; break; }
-    h = (h + 1) & mask;
+    h = geom_next(geom, h);
   }
   atomicOr(&table[h].pay, pay_is_list(pay) ? PAY_MULTI_EMPTY : PAY_SINGLE_EMPTY);
   *has_empty = 1;

@@ -43,6 +43,37 @@ OIC_HD uint32_t pay_len(unsigned long long p) { return pay_is_list(p) ? (uint32_
 OIC_HD uint32_t pay_start(unsigned long long p) { return (uint32_t)p; }
 OIC_HD bool pay_empty(unsigned long long p) { return pay_is_list(p) ? ((p >> 62) & 1) != 0 : ((p >> 4) & 1) != 0; }
 
+/* Geometry of the k-mer table.  The table is cut into n_slices slices of 2^slice_bits slots; a k-mer's home slot is
+ * (slice picked by the HIGH hash bits, offset by the LOW hash bits) and linear probing wraps INSIDE the slice, so slices are
+ * independent hash tables: the table size follows the load factor in steps of one slice instead of doubling, a slice can be
+ * built by one GPU of a group and exchanged as a plain byte range, and a slice-ordered insert keeps its lines in L2.
+ * filter: a blocked Bloom filter over the k-mers of the block (two bits in one 32-bit word per k-mer), tested by the seed
+ * scan before it touches the table -- the role of the reference's Hash_Check_Array (OIC/overlapInCore.H:329).  Like it, it
+ * never changes a result: a false positive costs one probe.  The filter is cut into FILTER_REGIONS regions that follow the
+ * slices (region = slice * FILTER_REGIONS / n_slices; n_slices is a multiple of FILTER_REGIONS), so the GPU that owns a
+ * range of slices also owns whole regions of the filter. */
+constexpr uint32_t FILTER_REGIONS = 8;
+struct TableGeom {
+  uint32_t n_slices;                // multiple of FILTER_REGIONS
+  uint32_t slice_bits;
+  unsigned long long slice_mask;    // 2^slice_bits - 1
+  uint32_t region_bits;             // log2(filter words per region)
+};
+__host__ __device__ __forceinline__ uint64_t geom_slots(const TableGeom &g) { return (uint64_t)g.n_slices << g.slice_bits; }
+__device__ __forceinline__ uint32_t geom_slice(const TableGeom &g, uint64_t h) { return __umulhi((uint32_t)(h >> 32), g.n_slices); }
+__device__ __forceinline__ uint64_t geom_home(const TableGeom &g, uint64_t h) {
+  return ((uint64_t)geom_slice(g, h) << g.slice_bits) | (h & g.slice_mask);
+}
+__device__ __forceinline__ uint64_t geom_next(const TableGeom &g, uint64_t s) { return (s & ~g.slice_mask) | ((s + 1) & g.slice_mask); }
+/* filter word and the two bits of a k-mer (from a second mix of the hash, so the bits are independent of the slot) */
+__host__ __device__ __forceinline__ uint64_t geom_filter_words(const TableGeom &g) { return (uint64_t)FILTER_REGIONS << g.region_bits; }
+__device__ __forceinline__ void geom_filter(const TableGeom &g, uint64_t h, uint32_t &word, uint32_t &bits) {
+  const uint64_t h2 = h * 0x9e3779b97f4a7c15ULL;
+  const uint32_t region = (uint32_t)(h >> 61);   // = slice * FILTER_REGIONS / n_slices, because n_slices is a multiple of FILTER_REGIONS = 8
+  word = (region << g.region_bits) | ((uint32_t)(h2 >> 32) & ((1u << g.region_bits) - 1u));
+  bits = (1u << ((uint32_t)h2 & 31u)) | (1u << (((uint32_t)h2 >> 5) & 31u));
+}
+
 constexpr int READ_PAD_BASES = 64;   // zero bases after every read
 constexpr int READ_LEAD_BASES = 64;  // zero bases before the first read
 

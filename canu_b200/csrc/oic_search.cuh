@@ -45,9 +45,9 @@ struct ScanArgs {
   uint32_t hash_bgn_id;           // read ID of string 0
   int K;
   const Slot *table;
-  uint64_t slot_mask;
+  TableGeom geom;
   const uint64_t *occ;
-  const uint32_t *occupancy;      // bit i = slot i of the table is occupied (nullptr = none)
+  const uint32_t *filter;         // Bloom filter of the block's k-mers (nullptr = none)
   int has_empty;
   // outputs
   Seed *recs;                     // [max_chunks * CHUNK]
@@ -119,16 +119,17 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, OIC_SCAN_BLOCKS) k_seed_scan(
       const uint64_t M1 = W[wbase + (t0 >> 5) + 1 + a.n_off];
       if ((l ? ((M0 >> (2 * l)) | (M1 << (64 - 2 * l))) : M0) & kmask) valid = false;
     }
-    // occupancy bitmap first (an L2 hit): a window whose home slot is free is absent from the block
+    // Bloom filter first (an L2 hit): most windows of a query are absent from the block and never touch the table
     const uint64_t hk = hash_key(key);
     bool maybe = valid;
-    if (a.occupancy) {
-      const uint64_t h0 = hk & a.slot_mask;
-      maybe = valid && ((__ldg(a.occupancy + (h0 >> 5)) >> (h0 & 31)) & 1u);
+    if (a.filter) {
+      uint32_t fw, fb;
+      geom_filter(a.geom, hk, fw, fb);
+      maybe = valid && ((__ldg(a.filter + fw) & fb) == fb);
     }
     uint32_t slot;
     unsigned long long pay = 0;
-    bool found = maybe && table_find(a.table, a.slot_mask, hk, key, slot, pay);
+    bool found = maybe && table_find(a.table, a.geom, hk, key, slot, pay);
     bool empty = found && pay_empty(pay);
     if (found) c_found++;
     if (empty) {   // hi_hits: OIC/overlapInCore-Find_Overlaps.C:323-325, 359-366

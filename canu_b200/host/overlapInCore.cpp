@@ -4,9 +4,10 @@
  * by liboic_b200.so (CUDA, include/oic_b200.h); this file is argv, file formats and the OverlapDriver loop.
  *
  * Additive options (ignored by nothing in the pipeline because the reference does not have them):
- *   --gpus N      shard the query range of every hash sub-block over N GPUs (one host thread + one context per GPU;
- *                 every GPU builds the same hash block from the same reads -- deterministic, no collective needed here;
- *                 the NCCL-broadcast variant lives in bench.py where torch.distributed provides the communicator)
+ *   --gpus N      shard the query range of every hash sub-block over N GPUs (one host thread + one context per GPU).  The hash
+ *                 block is built ONCE by the group: every GPU inserts the k-mers of the table slices it owns and the slices are
+ *                 exchanged with NCCL over NVLink (oic_comm_init_all + oic_build_hash_index_sharded); overlap records are
+ *                 gathered on the host (one writer).  --replicate rebuild: every GPU builds the whole block itself, no collective.
  *   --device D    first CUDA device to use (default 0)
  *   --sweep PFX   run EVERY job of an overlapInCorePartition job list (PFX.ovlbat / .ovljob / .ovlopt) in this one process:
  *                 the store is opened and its reads sent to the GPU once, consecutive query blocks of a hash block reuse
@@ -74,6 +75,7 @@ void usage(const char *argv0) {
   fprintf(stderr, "--maxreadlen n     accepted, no effect on results\n\n");
   fprintf(stderr, "--gpus n           B200s to shard the query reads over (default 1)\n");
   fprintf(stderr, "--device d         first CUDA device (default 0)\n");
+  fprintf(stderr, "--replicate how    --gpus > 1: 'sharded' (default: the group builds the hash block once, NCCL exchange) or 'rebuild'\n");
   fprintf(stderr, "--sweep prefix     run all jobs of prefix.ovlbat/.ovljob/.ovlopt (overlapInCorePartition) in this process\n");
   fprintf(stderr, "--sweep-out dir    directory of the per-job outputs <dir>/<batch>/<job>.ovb/.counts/.stats (default .)\n");
 }
@@ -107,6 +109,7 @@ int main(int argc, char **argv) {
   const char *skip_file = nullptr, *out_name = nullptr, *stat_name = nullptr, *store_path = nullptr;
   bool window_filter = false;
   int n_gpus = 1, device0 = 0;
+  bool sharded_build = true;
   const char *sweep_prefix = nullptr, *sweep_out = ".";
   uint64_t max_string_num = (1ull << 31) - 1;
 
@@ -158,6 +161,12 @@ int main(int argc, char **argv) {
     else if (strcmp(a, "-z") == 0) P.use_hopeless_check = 0;
     else if (strcmp(a, "--gpus") == 0) n_gpus = atoi(need());
     else if (strcmp(a, "--device") == 0) device0 = atoi(need());
+    else if (strcmp(a, "--replicate") == 0) {
+      const char *v = need();
+      if (strcmp(v, "sharded") == 0) sharded_build = true;
+      else if (strcmp(v, "rebuild") == 0) sharded_build = false;
+      else { fprintf(stderr, "ERROR: --replicate takes 'sharded' or 'rebuild'\n"); err++; }
+    }
     else if (strcmp(a, "--sweep") == 0) sweep_prefix = need();
     else if (strcmp(a, "--sweep-out") == 0) sweep_out = need();
     else if (store_path == nullptr) store_path = a;
@@ -297,6 +306,18 @@ int main(int argc, char **argv) {
     for (int g = 0; g < n_gpus; g++)
       if (sh[g].rc) { fprintf(stderr, "ERROR (GPU %d): %s\n", device0 + g, sh[g].err.c_str()); return 1; }
   }
+  // a plain job on several GPUs: one NCCL communicator over the contexts (a sweep hands WHOLE jobs to the GPUs: no group there)
+  bool have_comm = false;
+  if (n_gpus > 1 && !sweep_prefix && sharded_build) {
+    std::vector<oic_ctx_t *> ctxs(n_gpus);
+    for (int g = 0; g < n_gpus; g++) ctxs[g] = sh[g].ctx;
+    if (oic_comm_init_all(ctxs.data(), n_gpus) != 0) {
+      fprintf(stderr, "ERROR: NCCL communicator over %d GPUs: %s (use --replicate rebuild to run without one)\n", n_gpus, oic_last_error(sh[0].ctx));
+      return 1;
+    }
+    have_comm = true;
+    fprintf(stderr, "NCCL communicator over %d GPUs  [%.2f s]\n", n_gpus, elapsed());
+  }
 
   // One job = what one process of the reference does with its -h / -r / --hashstrings / --hashdatalen.
   // It runs on the contexts g0 .. g0+ng-1: the query range of every hash sub-block is split over them.
@@ -314,7 +335,10 @@ int main(int argc, char **argv) {
     while (bgn < J.end_hash_id) {
       if (end > J.end_hash_id) end = J.end_hash_id;
       std::vector<uint32_t> last(n_gpus, 0);
-      if (!on_all([&](int g) { return oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g - g0]); })) return 1;
+      if (!on_all([&](int g) {
+            return (have_comm && ng > 1) ? oic_build_hash_index_sharded(sh[g].ctx, nullptr, (uint32_t)bgn, (uint32_t)end, &last[g - g0])
+                                         : oic_build_hash_index(sh[g].ctx, (uint32_t)bgn, (uint32_t)end, &last[g - g0]);
+          })) return 1;
       fprintf(stderr, "Hash block %llu-%u built\n", (unsigned long long)bgn, last[0]);
       const uint32_t last_ref = oic_last_processed_ref(J.bgn_ref_id, J.end_ref_id, J.num_threads);
       if (last_ref >= J.bgn_ref_id) {

@@ -58,21 +58,25 @@ class RankJob:
         return rec
 
 
-def gather_records(rec, dist, device="cpu"):
-    """All ranks call; every rank gets the concatenation (rank order) of the (n, 6) uint32 record arrays.  Works on gloo
-    (CPU tensors) and NCCL (device='cuda'): two all_gathers, sizes then padded payloads."""
+def gather_records(rec, dist, group=None, dst=0, device="cpu"):
+    """Host-side merge of the per-rank overlap records ("gathered on host"): every rank calls with its (n, 6)
+    uint32 records already in host memory; rank `dst` gets the concatenation in rank order, the others None.  `group` should be
+    a gloo group (CPU tensors: nothing goes back through a GPU); with the default group of an NCCL job pass device='cuda'."""
     import torch
-    world = dist.get_world_size()
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
     rec = np.ascontiguousarray(rec, dtype=np.uint32).reshape(-1, 6)
     n = torch.tensor([rec.shape[0]], dtype=torch.int64, device=device)
     sizes = [torch.zeros_like(n) for _ in range(world)]
-    dist.all_gather(sizes, n)
+    dist.all_gather(sizes, n, group=group)
     sizes = [int(s.item()) for s in sizes]
     cap = max(max(sizes), 1)
     pad = np.zeros((cap, 6), dtype=np.int32)
     pad[:rec.shape[0]] = rec.view(np.int32)
     mine = torch.from_numpy(pad).to(device)
-    parts = [torch.zeros_like(mine) for _ in range(world)]
-    dist.all_gather(parts, mine)
+    parts = [torch.zeros_like(mine) for _ in range(world)] if rank == dst else None
+    dist.gather(mine, parts, dst=dst, group=group)
+    if rank != dst:
+        return None
     out = [p.cpu().numpy().view(np.uint32)[:sizes[r]] for r, p in enumerate(parts)]
     return np.concatenate(out, axis=0)

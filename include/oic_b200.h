@@ -144,24 +144,56 @@ void oic_reset_timings(oic_ctx_t *ctx);
 
 /* ---- multi-GPU: the immutable product of a hash build, for replication by NCCL broadcast ------------
  * After oic_build_hash_index on the root rank, oic_hash_block_meta/oic_hash_block_buffers expose the
- * device buffers (table, occurrence array, string flags); non-root ranks call oic_hash_block_reserve with
+ * device buffers (table, occurrence array, string flags, Bloom filter); non-root ranks call oic_hash_block_reserve with
  * the root's meta to allocate identically sized buffers, the caller broadcasts each buffer in place
  * (ncclBroadcast / torch.distributed.broadcast over NVLink), then oic_hash_block_commit makes the block
  * current.  Reads must already be loaded identically on every rank. */
 typedef struct {
-  uint64_t table_slots;      /* power of two                                */
+  uint64_t table_slots;      /* n_slices << slice_bits                      */
   uint64_t n_occ;            /* occurrence entries                          */
   uint32_t n_strings;        /* string slots in the block                   */
   uint32_t bgn_id, last_id;  /* read IDs covered                            */
   uint32_t has_empty;        /* any screened (Empty) k-mer present          */
   uint64_t n_distinct;
+  uint32_t n_slices;         /* table = n_slices independent slices ...     */
+  uint32_t slice_bits;       /* ... of 2^slice_bits slots (probing wraps inside a slice) */
+  uint64_t filter_words;     /* 32-bit words of the Bloom filter (power of two) */
 } oic_hash_meta_t;
 typedef struct { void *ptr; uint64_t bytes; } oic_dev_buffer_t;
-#define OIC_HASH_BLOCK_NBUF 3
+#define OIC_HASH_BLOCK_NBUF 4   /* table, occurrence array, string flags, filter */
 int oic_hash_block_meta(const oic_ctx_t *ctx, oic_hash_meta_t *meta);
 int oic_hash_block_reserve(oic_ctx_t *ctx, const oic_hash_meta_t *meta);
 int oic_hash_block_buffers(const oic_ctx_t *ctx, oic_dev_buffer_t bufs[OIC_HASH_BLOCK_NBUF]);
 int oic_hash_block_commit(oic_ctx_t *ctx, const oic_hash_meta_t *meta);
+
+/* ---- multi-GPU: the collective inside the library (NCCL over NVLink / NVSwitch) -----------------------
+ * The reference parallelises with threads over ONE hash table in host memory (OIC/overlapInCore.C:271-273) and with
+ * independent grid jobs (OIC/overlapInCorePartition.C:298-349); it has no collective to cite.  Here every GPU needs the hash
+ * block in its own HBM.  A communicator is attached to a context either by the multi-process route (rank 0 calls
+ * oic_comm_unique_id, the launcher ships the 128 bytes -- torch.distributed, MPI, a file -- and every rank calls
+ * oic_comm_init_rank) or, inside ONE process with one context per GPU, by oic_comm_init_all.  NCCL is loaded with dlopen
+ * ("libnccl.so.2", reusing a copy the process already holds) at the first of these calls; the library has no link-time
+ * dependency on it.
+ *
+ * oic_hash_block_replicate: rank `root` has built the block (oic_build_hash_index); every rank of the communicator calls
+ * this, the meta and the three buffers travel by ncclBroadcast on the context's own stream (no host synchronisation between
+ * them), non-root ranks commit the block (occupancy bitmap rebuilt locally).  nccl_comm: a caller-owned ncclComm_t, or NULL
+ * for the communicator attached to the context.
+ *
+ * oic_build_hash_index_sharded: the collective build.  Every rank calls it with the same arguments (the same reads must be
+ * resident everywhere); rank r inserts only the k-mers whose home slot lies in slice r of the table (the table is cut into
+ * n_ranks slices, linear probing wraps inside a slice, so slices are independent), builds the occurrence lists of its slice,
+ * and the slices / list segments are exchanged with ncclAllGather / grouped ncclBroadcast.  Afterwards every rank holds the
+ * identical, complete block: the serial build and the broadcast of a mostly empty table leave the critical path.  Falls
+ * back to build-on-root + oic_hash_block_replicate when the rank count is not a power of two or the hash-load cut-off
+ * trips (the cut needs the global first-occurrence histogram). */
+#define OIC_COMM_ID_BYTES 128
+int oic_comm_unique_id(uint8_t id[OIC_COMM_ID_BYTES]);
+int oic_comm_init_rank(oic_ctx_t *ctx, const uint8_t id[OIC_COMM_ID_BYTES], int n_ranks, int rank);
+int oic_comm_init_all(oic_ctx_t *const *ctxs, int n_ctx);
+int oic_comm_info(const oic_ctx_t *ctx, int *n_ranks, int *rank);   /* n_ranks = 0: no communicator attached */
+int oic_hash_block_replicate(oic_ctx_t *ctx, void *nccl_comm, int root);
+int oic_build_hash_index_sharded(oic_ctx_t *ctx, void *nccl_comm, uint32_t bgn_id, uint32_t end_id, uint32_t *last_id);
 
 /* ---- stage dumps for parity tests (not used by the product path) -----------------------------------
  * k-mer index of the current hash block as sorted CSR: keys ascending, occ (string<<32 | offset) DESCENDING
