@@ -338,7 +338,11 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   k_multi_fill<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_sort<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_sort_mid<<<MULTI_GRID, 256, 0, c->stream>>>(a);
-  c->tm.launches += 8;
+  {
+    const uint64_t per = slots / n_parts;   // the filter regions of this share follow its slices
+    k_filter_build<<<nblocks(per, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), per * part, per * (part + 1), geom, c->d_filter.as<uint32_t>());
+  }
+  c->tm.launches += 9;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
   if (n_parts == 1 && (c->n_off ? hc.n_inserts > n_windows : hc.n_inserts != n_windows))
     return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);

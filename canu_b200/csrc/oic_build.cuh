@@ -14,7 +14,7 @@
  *                  occurrence array (bump allocator), scatter the entries into it
  *   k_multi_sort   runs of 2..6 entries: one thread each (sorting network in registers, descending);
  *   k_sort_mid     7..32 entries: one warp per run (bitonic);  k_sort_big: longer runs, one block each (LSD radix)
- *                  (the Bloom filter the seed scan tests first is filled by the arrival that claims a slot)
+ *   k_filter_build Bloom filter of the block's k-mers (L2-resident), tested by the seed scan before it touches the table
  *   k_first_occ    histogram of "read in which a k-mer first appears" -> hash-load cut-off on the host
  *   k_mark_skip    Empty bit + screened ends for the -k skip list (and absent k-mers when the hopeless check is on)
  */
@@ -239,9 +239,6 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
       if (cur == EMPTY_KEY) {
         if (my_occ) atomicOr(&a.table[h].pay, my_occ);
         claimed = true;
-        uint32_t fw, fb;   // first arrival of the k-mer: its two filter bits (a fire-and-forget reduction into an L2-resident array)
-        geom_filter(a.geom, hk, fw, fb);
-        atomicOr(a.filter + fw, fb);
         break;
       }
       if (cur == key) {
@@ -527,6 +524,20 @@ __global__ void k_first_occ(const Slot *__restrict__ table, uint64_t n_slots, co
   if (!pay_is_list(sl.pay)) { atomicAdd(&hist[occ_str(sl.pay)], 1u); return; }
   const uint32_t n = pay_len(sl.pay);
   if (n) atomicAdd(&hist[occ_str(occ[pay_start(sl.pay) + n - 1])], 1u);
+}
+
+// Bloom filter of the finished slices [slot_lo, slot_hi): one thread per slot, coalesced read of the table, one reduction per
+// k-mer into the filter.  Run on its own (not from inside k_insert, where the table lines stream through L2 and every filter
+// update missed it: measured 27 ms instead of 10 for the build) the 64 MB filter stays L2-resident while it is filled.
+__global__ void __launch_bounds__(256) k_filter_build(const Slot *__restrict__ table, uint64_t slot_lo, uint64_t slot_hi, TableGeom geom,
+                                                      uint32_t *filter) {
+  const uint64_t i = slot_lo + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= slot_hi) return;
+  const unsigned long long key = __ldg(&table[i].key);
+  if (key == EMPTY_KEY) return;
+  uint32_t fw, fb;
+  geom_filter(geom, hash_key(key), fw, fb);
+  atomicOr(filter + fw, fb);
 }
 
 // Mark_Skip_Kmers: one thread per (k-mer, orientation) key.

@@ -132,7 +132,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
     const int limit = side == 0 ? err_limit : err_limit - right_errors;
     int a_end = 0, b_end = 0, lo = 0, to_end = 1, dl = 0, errs;
     ws.n_mode = (S == a.rc) ? (s_is_a ? 1 : 2) : 0;
-    if (LSW) {
+    if constexpr (LSW != 0) {
       // the lean loop only walks forward: the leftward run compares the same bases on the reverse-complement streams
       // (base i of a read is base len-1-i of its reverse complement, stored at the same stream offset)
       const uint64_t *Ax = A, *Bx = B;
@@ -143,7 +143,7 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
         Ax = s_is_a ? So : To; Bx = s_is_a ? To : So;
         ax = s_is_a ? s0 : t0; bx = s_is_a ? t0 : s0;
       }
-      errs = dp_run_lean<LSW ? LSW : 32>(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, Ax, ax, m, Bx, bx, n, limit, a_end, b_end, lo, to_end, dl);
+      errs = dp_run_lean<LSW>(side == 0 ? 1 : -1, a, ws, fs.row0, fs.row1, Ax, ax, m, Bx, bx, n, limit, a_end, b_end, lo, to_end, dl);
     } else errs = dp_run_fast(side == 0 ? 1 : -1, a, ws, fs, A, a0, m, B, b0, n, limit, a_end, b_end, lo, to_end, dl);
     if (errs < 0) return errs;   // -1 history overflow, -2 (lean only) row wider than the shared-memory staging
     if (side == 0) {

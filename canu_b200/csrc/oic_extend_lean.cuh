@@ -4,7 +4,8 @@
  * dp_run_fast (oic_extend_fast.cuh; LIBO/prefixEditDistance-forward.C:110-285, -reverse.C:130-300) -- the results are
  * bit-identical -- but written for instruction count: no generic pointers, two chunks of 32 diagonals per iteration with
  * branch-free bookkeeping (selects on ballot words instead of warp-uniform branches), one uniform branch per chunk pair for
- * the rare "a cell reached the end of a string" exit, direction words gathered in registers and stored once per row.
+ * the rare "a cell reached the end of a string" exit; no direction bits are stored (the traceback recomputes the
+ * predecessors from the stored rows, traceback_vals), the band is trimmed by scanning the finished row from both ends.
  * Returns -1 when the rows do not fit the warp's history, -2 when a row is wider than LSW (the caller reruns the
  * extension with dp_run_fast).
  */
@@ -49,18 +50,76 @@ __device__ __forceinline__ void stg_s32(int32_t *p, int32_t v) {
 }
 __device__ __forceinline__ uint32_t lean_ext16(const uint32_t *Wp, int p) {
   const uint32_t *q = Wp + (p >> 4);
-  return __funnelshift_r(ldg_nc(q), ldg_nc(q + 1), (p & 15) * 2);
+  uint32_t r;
+  const uint32_t lo = ldg_nc(q), hi = ldg_nc(q + 1);
+  asm("shf.r.wrap.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(p + p));   // the shifter takes 2p mod 32 = 2 (p mod 16)
+  return r;
 }
 __device__ __forceinline__ int lean_step(const uint32_t *Ap, int pa, const uint32_t *Tp, int pt) {
   const uint32_t x = lean_ext16(Ap, pa) ^ lean_ext16(Tp, pt);
-  return __clz((int)__brev(x)) >> 1;   // clz(0) = 32 -> 16
+  uint32_t y = x - 1u;
+  asm("" : "+r"(y));                   // (hides the idiom: the compiler would turn it back into a count-trailing-zeros with a zero test)
+  return __popc(~x & y) >> 1;          // trailing zero bits / 2; x == 0 gives 32 -> 16 without a special case
+}
+
+/* Traceback of the lean loop: the predecessor of every cell on the path is recomputed from the STORED rows with the rule of
+ * the forward pass (forward.C:60-78 / 163-170: prefer d, then d-1 if strictly greater, then d+1 if strictly greater), reading
+ * -2 for every cell outside the trimmed band of the row above, which is what the -2 sentinels of forward.C:155-161 make the
+ * forward pass see.  The forward pass therefore stores no direction bits at all.  32 rows per batch: lane j fetches a window
+ * of TB_WIN cells of row k-j-1 around the current diagonal into shared memory (the path drifts by at most one diagonal per
+ * row), then the batch is walked serially -- a few instructions per row, all lanes in step -- and re-centred early when the
+ * path leaves a window.  Leaves the events in ws.stack[0 .. nev), same encoding as traceback_fast. */
+constexpr int TB_HALF = 6, TB_WIN = 2 * TB_HALF + 1;
+__device__ __forceinline__ int traceback_vals(const WarpScratch &ws, int32_t *win, int fin_e, int fin_d, int from0) {
+  const int l = lane_id();
+  int nev = 0, dcur = fin_d, k = fin_e;
+  while (k >= 1) {
+    const int kj = k - l;                    // this lane's row of the batch
+    const int centre = dcur;
+    __syncwarp();
+    if (kj >= 1) {
+      const int4 mp = ws.meta[kj - 1];       // row above: {lo, trimmed lo, trimmed hi, offset}
+      const int32_t *row = ws.vals + mp.w - mp.x;
+#pragma unroll
+      for (int w = 0; w < TB_WIN; w++) {
+        const int x = centre - TB_HALF + w;
+        win[l * TB_WIN + w] = (x >= mp.y && x <= mp.z) ? row[x] : -2;
+      }
+    }
+    __syncwarp();
+    const int steps = k < 32 ? k : 32;
+    int j = 0;
+#pragma unroll 1
+    for (; j < steps; j++) {
+      const int rel = dcur - centre + TB_HALF;
+      if (rel < 1 || rel > TB_WIN - 2) break;            // the path left this row's window: fetch again around it
+      const int32_t *wj = win + j * TB_WIN + rel;
+      const int g0 = wj[0], gm = wj[-1], gp = wj[1];
+      int x = 1 + g0, f = 0;
+      if (gm > x) { x = gm; f = -1; }
+      if (1 + gp > x) f = 1;
+      if (from0 != FROM_NONE && k - j == fin_e) f = from0;
+      if (f != 0) {
+        const int pv = f < 0 ? gm : gp;
+        if (l == 0) ws.stack[nev] = (pv + 4) * 4 + (f + 1);
+        nev++;
+      }
+      dcur += f;
+    }
+    k -= j;
+  }
+  __syncwarp();
+  return nev;
 }
 
 template <int LSW>
 __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, WarpScratch &ws, int32_t *srow0, int32_t *srow1,
                                            const uint64_t *__restrict__ A, int64_t a0, int m, const uint64_t *__restrict__ T, int64_t t0,
                                            int n, int error_limit, int &a_end, int &t_end, int &leftover, int &to_end, int &delta_len) {
-  const int l = lane_id();
+  static_assert(LSW <= 1024, "the best-cell key packs the cell index into 10 bits");
+  static_assert(LSW + 8 + 32 * LU >= 32 * TB_WIN, "the traceback windows reuse a live row");
+  int l = lane_id();
+  asm volatile("" : "+r"(l));                          // keep the lane in a register (S2R inside the row loop otherwise)
   const uint32_t *Ap = reinterpret_cast<const uint32_t *>(A) + (a0 >> 4);
   const uint32_t *Tp = reinterpret_cast<const uint32_t *>(T) + (t0 >> 4);
   asm volatile("" : "+l"(Ap));   // keep the two string bases as plain 64-bit registers: one IMAD.WIDE per window address
@@ -72,8 +131,8 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   if (l == 0) {
     ws.cells += 1;
     ws.words += (unsigned)(row0 + 1 + 15) / 16;
-    ws.meta[0] = make_int4(0, 0, 0, 2);
-    ws.vals[2] = row0;
+    ws.meta[0] = make_int4(0, 0, 0, 0);
+    ws.vals[0] = row0;
   }
   delta_len = 0;
   leftover = 0;
@@ -88,7 +147,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   int max_score_len = 0, max_score_best_d = 0, max_score_best_e = 0;
   int best_d = 0, best_e = 0, longest = 0;
   int plo = 0;
-  int next_off = 5;
+  int next_off = 1;     // history of the warp: the rows back to back, values only (meta[e] = {lo, trimmed lo, trimmed hi, offset})
   int fin_e = -1, fin_d = 0, fin_val = 0, from0 = FROM_NONE;
   int errors = 0;
   unsigned wsum = 0;    // per-lane count of 16-base compare words (W), without the first word of the cells that ncell counts
@@ -106,11 +165,10 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     const int width = right - left + 1;
     const int nch = (width + 31) >> 5;
     if (width > LSW) { errors = LEAN_WIDE; break; }
-    if (e > max_e || next_off + width + 4 + 2 * nch > rowcap) { errors = -1; break; }
-    const int off = next_off + 2;
-    next_off += width + 4 + 2 * nch;
-    int32_t *hp = ws.vals + off + l;                     // this lane's cells of the row in the history
-    asm volatile("" : "+l"(hp));
+    if (e > max_e || next_off + width > rowcap) { errors = -1; break; }
+    const int off = next_off;
+    next_off += width;
+    unsigned hidx = (unsigned)(off + l);                 // this lane's cell of chunk 0 in the history
     const int lim = lim_next;
     lim_next = ws.match_limit[imin(e + 1, max_e)];
     const int32_t *pp = prev + (left - plo) + l;         // this lane's cell of chunk 0 in the previous row
@@ -118,22 +176,18 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
 
     bool ended = false;
     int d_end = 0, r_end = 0;
-    // lane c keeps the ballot words of chunk c; they are folded into band / best cell once per row
-    unsigned my_bm = 0, my_bp = 0, my_ok = 0, my_pm = 0;
-    int my_mx = -1;
+    int key_mx = -1;                                     // this lane's best cell: (value << 10) | (1023 - index), see below
+    int koff = 1023 - l;
 
 #pragma unroll 1
     for (int c0 = 0; c0 < nch; c0 += LU) {
       int r[LU], r0[LU], cap[LU], dd[LU];
+      int32_t *hp = ws.vals + hidx;
 #pragma unroll
       for (int u = 0; u < LU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
-        const int c = c0 + u, i = 32 * c + l, d = left + i;
-        const int g0 = pp[32 * c] + 1, gm = pp[32 * c - 1], gp = pp[32 * c + 1] + 1;
-        const int x = imax(g0, gm);
-        const unsigned bp = __ballot_sync(FULL, gp > x);
-        const unsigned bm = __ballot_sync(FULL, gm > g0) & ~bp;
-        if (l == c) { my_bm = bm; my_bp = bp; }
-        r0[u] = imax(x, gp);
+        const int i = 32 * (c0 + u) + l, d = left + i;
+        const int g0 = pp[32 * u] + 1, gm = pp[32 * u - 1], gp = pp[32 * u + 1] + 1;
+        r0[u] = imax(imax(g0, gm), gp);
         dd[u] = d;
         cap[u] = (i < width) ? imin(m, n - d) : LEAN_IDLE;
       }
@@ -167,24 +221,24 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         r[1] = s1 ? rr : r[1];
         more &= (has && stop) ? (s1 ? ~2 : ~1) : ~0;
       }
-      unsigned em[LU], any_em = 0;
+      bool endp = false;
 #pragma unroll
       for (int u = 0; u < LU; u++) {
-        const int c = c0 + u, i = 32 * c + l;
-        const bool act = i < width;
+        const bool act = cap[u] != LEAN_IDLE;
         r[u] = imin(r[u], cap[u]);
-        if (act) { cp[32 * c] = r[u]; stg_s32(hp + 32 * c, r[u]); }
-        em[u] = __ballot_sync(FULL, act && r[u] == cap[u]);            // reached the end of A (r == m) or of T (r + d == n)
-        any_em |= em[u];
-        const unsigned ok = __ballot_sync(FULL, r[u] >= lim - imax(dd[u], 0));   // idle lanes hold INT_MIN
-        if (l == c) my_ok = ok;
-        if (r[u] > my_mx) { my_mx = r[u]; my_pm = (unsigned)i; }   // this lane's highest cell, lowest chunk on ties
+        if (act) { cp[32 * u] = r[u]; stg_s32(hp + 32 * u, r[u]); }
+        endp = endp || (act && r[u] == cap[u]);          // reached the end of A (r == m) or of T (r + d == n)
+        // best cell of the lane: highest value, lowest index on ties, as ONE integer (idle lanes: INT_MIN << 10 = 0, never above a real cell)
+        key_mx = imax(key_mx, r[u] * 1024 + (koff - 32 * u));
       }
-      if (any_em) {                                      // a cell reached the end of A or T: the row stops at the first one
+      if (__any_sync(FULL, endp)) {                      // a cell reached the end of A or T: the row stops at the first one
+        unsigned em[LU];
+#pragma unroll
+        for (int u = 0; u < LU; u++) em[u] = __ballot_sync(FULL, cap[u] != LEAN_IDLE && r[u] == cap[u]);
         // W of this chunk group from the slide lengths: ceil((run + 1) / 16) compare words per cell
         unsigned wc[LU];
 #pragma unroll
-        for (int u = 0; u < LU; u++) wc[u] = (32 * (c0 + u) + l < width) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
+        for (int u = 0; u < LU; u++) wc[u] = (cap[u] != LEAN_IDLE) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         int uu = 0;
 #pragma unroll
         for (int u = LU - 1; u >= 0; u--) if (em[u]) uu = u;
@@ -207,12 +261,9 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       // no cell of the group reached the end of a string: a cell slid 16 * (its continuation steps) + less than 16 bases, i.e.
       // it cost 1 + steps compare words; the "1" of every cell is added once per run from the cell count (below)
       wsum += nst;
+      pp += 32 * LU; cp += 32 * LU; hidx += 32 * LU; koff -= 32 * LU;
     }
     int32_t *hist = ws.vals + off;
-    {   // direction words of the row: two per chunk, right behind the values (and their 2-int margin)
-      uint32_t *dirs = reinterpret_cast<uint32_t *>(hist + width + 2);
-      if (l < nch) { dirs[2 * l] = my_bm; dirs[2 * l + 1] = my_bp; }
-    }
     __syncwarp();
 
     if (ended) {
@@ -250,24 +301,33 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     }
     ncell += width;
 
-    // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches Edit_Match_Limit[e]
-    const unsigned has = __ballot_sync(FULL, my_ok != 0);
-    if (has == 0) {
+    // band trimming (forward.C:235-254): [nl, nr] = first / last cell whose progress reaches Edit_Match_Limit[e].  The row is
+    // complete in shared memory: scan it from both ends, one chunk per step (the ends move by a few cells per row, so the
+    // first step almost always decides) instead of a ballot per chunk in the loop above.
+    int nl = right + 1, nr = left - 1;
+#pragma unroll 1
+    for (int c = 0; c < nch; c++) {
+      const int i = 32 * c + l, d = left + i;
+      const unsigned b = __ballot_sync(FULL, i < width && cur[i] + imax(d, 0) >= lim);
+      if (b) { nl = left + 32 * c + __ffs(b) - 1; break; }
+    }
+    if (nl > right) {
       if (l == 0) ws.meta[e] = make_int4(left, right + 1, right, off);
       break;
     }
-    const int cf = __ffs(has) - 1, cl = 31 - __clz(has);
-    const int nl = left + 32 * cf + __ffs(__shfl_sync(FULL, my_ok, cf)) - 1;
-    const int nr = left + 32 * cl + 31 - __clz(__shfl_sync(FULL, my_ok, cl));
-    if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
-    int gmax = __reduce_max_sync(FULL, my_mx);           // highest cell of the row, lowest diagonal on ties
-    int gpos = 0;
-    if (gmax > longest) {
-      gpos = left + (int)__reduce_min_sync(FULL, (my_mx == gmax) ? my_pm : 0x7fffffffu);
+#pragma unroll 1
+    for (int c = nch - 1; c >= 0; c--) {
+      const int i = 32 * c + l, d = left + i;
+      const unsigned b = __ballot_sync(FULL, i < width && cur[i] + imax(d, 0) >= lim);
+      if (b) { nr = left + 32 * c + 31 - __clz(b); break; }
     }
+    if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
+    const int gkey = __reduce_max_sync(FULL, key_mx);    // highest cell of the row, lowest diagonal on ties
+    int gmax = gkey >> 10;
 
     // best cell of the trimmed band: highest row, lowest diagonal on ties; only if it beats `longest`
     if (gmax > longest) {
+      int gpos = left + 1023 - (gkey & 1023);
       if (gpos < nl || gpos > nr) {   // rare: the row's top cell was trimmed away -> exact search inside the band
         gmax = -1;
         for (int c = (nl - left) >> 5; c <= ((nr - left) >> 5); c++) {
@@ -300,7 +360,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   ws.words += wsum + ((l == 0) ? ncell - w_adj : 0u);
   if (errors < 0) return errors;
   return dp_finish(DIR, ws, n, row0, fin_e, fin_d, fin_val, from0, errors, max_score_len, max_score_best_d, max_score_best_e, a_end, t_end,
-                   leftover, to_end, delta_len);
+                   leftover, to_end, delta_len, srow0);
 }
 
 }  // namespace oic
