@@ -175,15 +175,16 @@ __device__ __forceinline__ int extend_alignment(const ExtArgs &a, WarpScratch &w
 }
 
 constexpr int EXT_WARPS = 4;
-// Two instances of the lean task kernel: staging width x resident blocks per SM.  Measured on B200 (c3 job): 1024 x 4 (128
-// registers) 91.6 ms; 768 x 6 (80 registers, small spills outside the row loop, more L1 left) 88.3 ms; 512 x 8 86.4 ms but 105
-// tasks meet a wider row and are rerun by the generic kernel (+3.1 ms); 1024 x 5/6 99 ms (L1 squeezed).  Low error rates keep
-// the band narrow (no row beyond 640 diagonals at --maxerate 0.06 on 5-15 kb reads); at high rates the wide instance runs.
+// Two instances of the lean task kernel: staging width x resident blocks per SM.  Measured on B200 (c3 job, round-2 row loop):
+// 768 x 6 (80 registers) 64.6 ms; 640 x 7 (72 registers) 61.7 ms; 512 x 8 (64 registers) 65.0 ms plus 3.3 ms of generic reruns
+// (105 tasks meet a row wider than 512); 768 x 5 (96 registers, hardly any spill) 74.8 ms; 1024 x 4 69.2 ms.  What is left of
+// the 256 KB L1/shared memory for the sequence windows matters as much as the resident warps.  Low error rates keep the band
+// narrow (no row beyond 640 diagonals at --maxerate 0.06 on 5-15 kb reads); at high rates the wide instance runs.
 #ifndef OIC_SW_NARROW
-#define OIC_SW_NARROW 768
+#define OIC_SW_NARROW 640
 #endif
 #ifndef OIC_TASK_BLOCKS
-#define OIC_TASK_BLOCKS 6
+#define OIC_TASK_BLOCKS 7
 #endif
 constexpr int LSW_NARROW = OIC_SW_NARROW, LSW_WIDE = SW;
 constexpr int TASK_BLOCKS_NARROW = OIC_TASK_BLOCKS, TASK_BLOCKS_WIDE = 4;

@@ -133,14 +133,14 @@ __device__ __forceinline__ int traceback_fast(const WarpScratch &ws, int fin_e, 
   return nev;
 }
 
-__device__ __forceinline__ int traceback_vals(const WarpScratch &ws, int32_t *win, int fin_e, int fin_d, int from0);   // oic_extend_lean.cuh
+__device__ __forceinline__ int traceback_vals(const WarpScratch &ws, int fin_e, int fin_d, int from0);   // oic_extend_lean.cuh
 
 /* After the row loop of one direction: pick the exit cell (or fall back to the best cell seen), trace back, build the
  * delta list (Set_Right_Delta / Set_Left_Delta).  Shared by the generic and the lean row loops. */
 __device__ __forceinline__ int dp_finish(const int DIR, WarpScratch &ws, int n, int row0, int fin_e, int fin_d, int fin_val, int from0, int errors,
                                          int max_score_len, int max_score_best_d, int max_score_best_e, int &a_end, int &t_end,
-                                         int &leftover, int &to_end, int &delta_len, int32_t *lean_win = nullptr) {
-  // lean_win != nullptr: the history was written by the lean loop (values only) -> traceback_vals with this shared-memory scratch
+                                         int &leftover, int &to_end, int &delta_len, bool lean_history = false) {
+  // lean_history: the history was written by the lean loop (values only, no direction words) -> traceback_vals
   const int l = lane_id();
 
   if (fin_e < 0) {   // ran out of errors / band, or branch-point abort: back to the best cell seen
@@ -154,7 +154,7 @@ __device__ __forceinline__ int dp_finish(const int DIR, WarpScratch &ws, int n, 
   }
   __syncwarp();
   const long long tb0 = OIC_CLOCK();
-  const int ns = lean_win ? traceback_vals(ws, lean_win, fin_e, fin_d, from0) : traceback_fast(ws, fin_e, fin_d, from0);
+  const int ns = lean_history ? traceback_vals(ws, fin_e, fin_d, from0) : traceback_fast(ws, fin_e, fin_d, from0);
   const int last = ns ? ((ws.stack[ns - 1] >> 2) - 4) : fin_val;
   if (DIR > 0) {
     // Set_Right_Delta: st = entries, then last + 1; delta[x] = |st[ns - x]| * sign(st[ns - x - 1])

@@ -12,6 +12,11 @@
 #ifndef OIC_EXTEND_LEAN_CUH
 #define OIC_EXTEND_LEAN_CUH
 
+#include <type_traits>
+
+#ifndef OIC_TAIL_PASS
+#define OIC_TAIL_PASS 1   /* an odd last chunk of a row runs a single-chunk copy of the pass (0: always pairs) */
+#endif
 #ifndef LEAN_U
 #define LEAN_U 2   /* chunks of 32 diagonals in flight together */
 #endif
@@ -65,47 +70,57 @@ __device__ __forceinline__ int lean_step(const uint32_t *Ap, int pa, const uint3
 /* Traceback of the lean loop: the predecessor of every cell on the path is recomputed from the STORED rows with the rule of
  * the forward pass (forward.C:60-78 / 163-170: prefer d, then d-1 if strictly greater, then d+1 if strictly greater), reading
  * -2 for every cell outside the trimmed band of the row above, which is what the -2 sentinels of forward.C:155-161 make the
- * forward pass see.  The forward pass therefore stores no direction bits at all.  32 rows per batch: lane j fetches a window
- * of TB_WIN cells of row k-j-1 around the current diagonal into shared memory (the path drifts by at most one diagonal per
- * row), then the batch is walked serially -- a few instructions per row, all lanes in step -- and re-centred early when the
- * path leaves a window.  Leaves the events in ws.stack[0 .. nev), same encoding as traceback_fast. */
-constexpr int TB_HALF = 6, TB_WIN = 2 * TB_HALF + 1;
-__device__ __forceinline__ int traceback_vals(const WarpScratch &ws, int32_t *win, int fin_e, int fin_d, int from0) {
+ * forward pass see.  The forward pass therefore stores no direction bits at all.  32 rows per batch, one row per lane: the
+ * lane fetches a window of TB_WIN cells of the row above around the current diagonal (the path drifts by at most one diagonal
+ * per row) and works out the direction of EVERY cell of the window (2 bits each, one word); the path is then a chain of 32
+ * shuffles through those words, and the batch is re-centred early when the path leaves a window.  Leaves the events in
+ * ws.stack[0 .. nev), same encoding as traceback_fast. */
+constexpr int TB_HALF = 7, TB_WIN = 2 * TB_HALF + 1;   // 13 interior cells x 2 bits = 26 bits of a word
+__device__ __forceinline__ int traceback_vals(const WarpScratch &ws, int fin_e, int fin_d, int from0) {
   const int l = lane_id();
   int nev = 0, dcur = fin_d, k = fin_e;
   while (k >= 1) {
     const int kj = k - l;                    // this lane's row of the batch
     const int centre = dcur;
-    __syncwarp();
+    uint32_t fw = 0;                         // direction of the cell at window index rel: bits [2 rel, 2 rel + 2): 0 = d, 1 = d-1, 2 = d+1
+    const int32_t *row = ws.vals;
     if (kj >= 1) {
       const int4 mp = ws.meta[kj - 1];       // row above: {lo, trimmed lo, trimmed hi, offset}
-      const int32_t *row = ws.vals + mp.w - mp.x;
+      row = ws.vals + mp.w - mp.x;
+      int v[TB_WIN];
 #pragma unroll
       for (int w = 0; w < TB_WIN; w++) {
         const int x = centre - TB_HALF + w;
-        win[l * TB_WIN + w] = (x >= mp.y && x <= mp.z) ? row[x] : -2;
+        v[w] = (x >= mp.y && x <= mp.z) ? row[x] : -2;
       }
+#pragma unroll
+      for (int rel = 1; rel < TB_WIN - 1; rel++) {
+        const int x = 1 + v[rel];
+        const uint32_t c = (1 + v[rel + 1] > imax(x, v[rel - 1])) ? 2u : ((v[rel - 1] > x) ? 1u : 0u);
+        fw |= c << (2 * rel);
+      }
+      if (from0 != FROM_NONE && kj == fin_e) fw = (from0 < 0 ? 0x55555555u : (from0 > 0 ? 0xaaaaaaaau : 0u));
     }
-    __syncwarp();
     const int steps = k < 32 ? k : 32;
-    int j = 0;
+    int rel = TB_HALF, myrel = TB_HALF, j = 0;
 #pragma unroll 1
     for (; j < steps; j++) {
-      const int rel = dcur - centre + TB_HALF;
-      if (rel < 1 || rel > TB_WIN - 2) break;            // the path left this row's window: fetch again around it
-      const int32_t *wj = win + j * TB_WIN + rel;
-      const int g0 = wj[0], gm = wj[-1], gp = wj[1];
-      int x = 1 + g0, f = 0;
-      if (gm > x) { x = gm; f = -1; }
-      if (1 + gp > x) f = 1;
-      if (from0 != FROM_NONE && k - j == fin_e) f = from0;
-      if (f != 0) {
-        const int pv = f < 0 ? gm : gp;
-        if (l == 0) ws.stack[nev] = (pv + 4) * 4 + (f + 1);
-        nev++;
-      }
-      dcur += f;
+      if (rel < 1 || rel > TB_WIN - 2) break;            // the path left the windows: fetch again around it
+      const uint32_t w = __shfl_sync(FULL, fw, j);
+      myrel = (l == j) ? rel : myrel;
+      const uint32_t c = (w >> (2 * rel)) & 3u;
+      rel += (int)(c >> 1) - (int)(c & 1u);
     }
+    // rows 0 .. j-1 of the batch are decided: an event for every row whose predecessor is on another diagonal
+    const uint32_t c = (l < j) ? (fw >> (2 * myrel)) & 3u : 0u;
+    const int f = (int)(c >> 1) - (int)(c & 1u);
+    const unsigned em = __ballot_sync(FULL, c != 0);
+    if (c != 0) {
+      const int pv = row[centre - TB_HALF + myrel + f];  // the predecessor itself (never a sentinel: it won the comparison)
+      ws.stack[nev + __popc(em & ((1u << l) - 1))] = (pv + 4) * 4 + (f + 1);
+    }
+    nev += __popc(em);
+    dcur = centre + rel - TB_HALF;
     k -= j;
   }
   __syncwarp();
@@ -117,7 +132,6 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
                                            const uint64_t *__restrict__ A, int64_t a0, int m, const uint64_t *__restrict__ T, int64_t t0,
                                            int n, int error_limit, int &a_end, int &t_end, int &leftover, int &to_end, int &delta_len) {
   static_assert(LSW <= 1024, "the best-cell key packs the cell index into 10 bits");
-  static_assert(LSW + 8 + 32 * LU >= 32 * TB_WIN, "the traceback windows reuse a live row");
   int l = lane_id();
   asm volatile("" : "+r"(l));                          // keep the lane in a register (S2R inside the row loop otherwise)
   const uint32_t *Ap = reinterpret_cast<const uint32_t *>(A) + (a0 >> 4);
@@ -179,12 +193,16 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     int key_mx = -1;                                     // this lane's best cell: (value << 10) | (1023 - index), see below
     int koff = 1023 - l;
 
-#pragma unroll 1
-    for (int c0 = 0; c0 < nch; c0 += LU) {
-      int r[LU], r0[LU], cap[LU], dd[LU];
+    // One pass over NU chunks of 32 diagonals starting at chunk c0; returns true when the row ended in it.  Two chunks per
+    // pass keep two independent dependency chains in flight; an odd last chunk takes the single-chunk copy of the pass instead
+    // of dragging 32 idle lanes through a pair (rows average 3.8 chunks).
+    int c0 = 0;
+    auto pass = [&](auto nu_tag) -> bool {
+      constexpr int NU = decltype(nu_tag)::value;
+      int r[NU], r0[NU], cap[NU], dd[NU];
       int32_t *hp = ws.vals + hidx;
 #pragma unroll
-      for (int u = 0; u < LU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
+      for (int u = 0; u < NU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
         const int i = 32 * (c0 + u) + l, d = left + i;
         const int g0 = pp[32 * u] + 1, gm = pp[32 * u - 1], gp = pp[32 * u + 1] + 1;
         r0[u] = imax(imax(g0, gm), gp);
@@ -193,9 +211,9 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       }
       int more = 0;                                      // bit u: the slide of chunk u goes on
       // Branch-free: a cell that does not slide (idle lane, or already at the end of a string) compares the first windows
-      // of the two strings instead and discards the result, so the 4*LU loads of a chunk group issue back to back.
+      // of the two strings instead and discards the result, so the 4*NU loads of a pass issue back to back.
 #pragma unroll
-      for (int u = 0; u < LU; u++) {
+      for (int u = 0; u < NU; u++) {
         const bool go = r0[u] < cap[u];
         const int p = go ? r0[u] : 0, q = go ? r0[u] + dd[u] : 0;
         int adv = lean_step(Ap, aph + p, Tp, tph + q);
@@ -204,26 +222,26 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         more |= ((adv == 16) && (r[u] < cap[u])) ? (1 << u) : 0;
       }
       // Slides longer than 16 bases (the cells on the alignment path): few lanes, seldom both chunks of a lane, so every
-      // pass advances ONE chunk per lane (the lowest one still sliding) through a single copy of the compare.
-      unsigned nst = 0;                                  // continuation steps of this lane in this chunk group
+      // step advances ONE chunk per lane (the lowest one still sliding) through a single copy of the compare.
+      unsigned nst = 0;                                  // continuation steps of this lane in this pass
       while (__any_sync(FULL, more != 0)) {
-        static_assert(LU == 2, "the merged continuation loop is written for two chunks in flight");
-        const bool has = more != 0, s1 = (more == 2);
+        static_assert(NU <= 2, "the merged continuation loop is written for at most two chunks in flight");
+        const bool has = more != 0, s1 = (NU == 2) && (more == 2);
         nst += has ? 1u : 0u;
-        int rr = s1 ? r[1] : r[0];
-        const int ds = s1 ? dd[1] : dd[0], cs = s1 ? cap[1] : cap[0];
+        int rr = s1 ? r[NU - 1] : r[0];
+        const int ds = s1 ? dd[NU - 1] : dd[0], cs = s1 ? cap[NU - 1] : cap[0];
         const int p = has ? rr : 0, q = has ? rr + ds : 0;
         int adv = lean_step(Ap, aph + p, Tp, tph + q);
         adv = has ? adv : 0;
         rr += adv;
         const bool stop = !((adv == 16) && (rr < cs));
         r[0] = (has && !s1) ? rr : r[0];
-        r[1] = s1 ? rr : r[1];
+        if (NU == 2) r[NU - 1] = s1 ? rr : r[NU - 1];
         more &= (has && stop) ? (s1 ? ~2 : ~1) : ~0;
       }
       bool endp = false;
 #pragma unroll
-      for (int u = 0; u < LU; u++) {
+      for (int u = 0; u < NU; u++) {
         const bool act = cap[u] != LEAN_IDLE;
         r[u] = imin(r[u], cap[u]);
         if (act) { cp[32 * u] = r[u]; stg_s32(hp + 32 * u, r[u]); }
@@ -232,37 +250,49 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         key_mx = imax(key_mx, r[u] * 1024 + (koff - 32 * u));
       }
       if (__any_sync(FULL, endp)) {                      // a cell reached the end of A or T: the row stops at the first one
-        unsigned em[LU];
+        unsigned em[NU];
 #pragma unroll
-        for (int u = 0; u < LU; u++) em[u] = __ballot_sync(FULL, cap[u] != LEAN_IDLE && r[u] == cap[u]);
-        // W of this chunk group from the slide lengths: ceil((run + 1) / 16) compare words per cell
-        unsigned wc[LU];
+        for (int u = 0; u < NU; u++) em[u] = __ballot_sync(FULL, cap[u] != LEAN_IDLE && r[u] == cap[u]);
+        // W of this pass from the slide lengths: ceil((run + 1) / 16) compare words per cell
+        unsigned wc[NU];
 #pragma unroll
-        for (int u = 0; u < LU; u++) wc[u] = (cap[u] != LEAN_IDLE) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
+        for (int u = 0; u < NU; u++) wc[u] = (cap[u] != LEAN_IDLE) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         int uu = 0;
 #pragma unroll
-        for (int u = LU - 1; u >= 0; u--) if (em[u]) uu = u;
+        for (int u = NU - 1; u >= 0; u--) if (em[u]) uu = u;
         unsigned emu = 0, wcu = 0;
         int ru = 0;
 #pragma unroll
-        for (int u = 0; u < LU; u++) {
+        for (int u = 0; u < NU; u++) {
           if (u < uu) wsum += wc[u];
           if (u == uu) { emu = em[u]; wcu = wc[u]; ru = r[u]; }
         }
         const int first = __ffs(emu) - 1;
         if (l <= first) wsum += wcu;
         ncell += 32 * (c0 + uu) + first + 1;
-        w_adj = 32 * uu + first + 1;                     // the cells of this chunk group are counted by wc above, not by ncell
+        w_adj = 32 * uu + first + 1;                     // the cells of this pass are counted by wc above, not by ncell
         d_end = left + 32 * (c0 + uu) + first;
         r_end = __shfl_sync(FULL, ru, first);
-        ended = true;
-        break;
+        return true;
       }
-      // no cell of the group reached the end of a string: a cell slid 16 * (its continuation steps) + less than 16 bases, i.e.
+      // no cell of the pass reached the end of a string: a cell slid 16 * (its continuation steps) + less than 16 bases, i.e.
       // it cost 1 + steps compare words; the "1" of every cell is added once per run from the cell count (below)
       wsum += nst;
-      pp += 32 * LU; cp += 32 * LU; hidx += 32 * LU; koff -= 32 * LU;
+      pp += 32 * NU; cp += 32 * NU; hidx += 32 * NU; koff -= 32 * NU; c0 += NU;
+      return false;
+    };
+#if OIC_TAIL_PASS
+#pragma unroll 1
+    while (c0 + 1 < nch) {
+      if (pass(std::integral_constant<int, 2>{})) { ended = true; break; }
     }
+    if (!ended && c0 < nch) ended = pass(std::integral_constant<int, 1>{});
+#else
+#pragma unroll 1
+    while (c0 < nch) {
+      if (pass(std::integral_constant<int, 2>{})) { ended = true; break; }
+    }
+#endif
     int32_t *hist = ws.vals + off;
     __syncwarp();
 
@@ -305,21 +335,29 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     // complete in shared memory: scan it from both ends, one chunk per step (the ends move by a few cells per row, so the
     // first step almost always decides) instead of a ballot per chunk in the loop above.
     int nl = right + 1, nr = left - 1;
-#pragma unroll 1
-    for (int c = 0; c < nch; c++) {
-      const int i = 32 * c + l, d = left + i;
-      const unsigned b = __ballot_sync(FULL, i < width && cur[i] + imax(d, 0) >= lim);
-      if (b) { nl = left + 32 * c + __ffs(b) - 1; break; }
+    {
+      unsigned b = __ballot_sync(FULL, l < width && cur[l] + imax(left + l, 0) >= lim);
+      int c = 0;
+      while (b == 0 && ++c < nch) {   // rare: the whole first chunk fell below the limit
+        const int i = 32 * c + l;
+        b = __ballot_sync(FULL, i < width && cur[i] + imax(left + i, 0) >= lim);
+      }
+      if (b) nl = left + 32 * c + __ffs(b) - 1;
     }
     if (nl > right) {
       if (l == 0) ws.meta[e] = make_int4(left, right + 1, right, off);
       break;
     }
-#pragma unroll 1
-    for (int c = nch - 1; c >= 0; c--) {
-      const int i = 32 * c + l, d = left + i;
-      const unsigned b = __ballot_sync(FULL, i < width && cur[i] + imax(d, 0) >= lim);
-      if (b) { nr = left + 32 * c + 31 - __clz(b); break; }
+    {
+      int c = nch - 1;
+      const int i0 = 32 * c + l;
+      unsigned b = __ballot_sync(FULL, i0 < width && cur[i0] + imax(left + i0, 0) >= lim);
+      while (b == 0) {                // rare; ends at the chunk that holds nl at the latest
+        c--;
+        const int i = 32 * c + l;
+        b = __ballot_sync(FULL, i < width && cur[i] + imax(left + i, 0) >= lim);
+      }
+      nr = left + 32 * c + 31 - __clz(b);
     }
     if (l == 0) ws.meta[e] = make_int4(left, nl, nr, off);
     const int gkey = __reduce_max_sync(FULL, key_mx);    // highest cell of the row, lowest diagonal on ties
@@ -360,7 +398,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
   ws.words += wsum + ((l == 0) ? ncell - w_adj : 0u);
   if (errors < 0) return errors;
   return dp_finish(DIR, ws, n, row0, fin_e, fin_d, fin_val, from0, errors, max_score_len, max_score_best_d, max_score_best_e, a_end, t_end,
-                   leftover, to_end, delta_len, srow0);
+                   leftover, to_end, delta_len, true);
 }
 
 }  // namespace oic

@@ -25,7 +25,8 @@ if [ ! -d "$REF" ]; then
   exit 0
 fi
 if [ -x "$OUT/overlapInCore" ] && [ -x "$OUT/gatekeeperCreate" ] && [ -x "$OUT/overlapConvert" ] \
-   && [ -x "$OUT/overlapInCorePartition" ] && [ -x "$OUT/meryl" ] && [ "$1" != "-f" ]; then
+   && [ -x "$OUT/overlapInCorePartition" ] && [ -x "$OUT/meryl" ] && [ -x "$OUT/ovStoreBuild" ] && [ -x "$OUT/ovStoreDump" ] \
+   && [ "$1" != "-f" ]; then
   exit 0
 fi
 
@@ -88,7 +89,9 @@ meryl/libleaff/seqStore.C meryl/libleaff/seqStream.C meryl/libleaff/sffFile.C
 INC="$INC -I$REF/meryl"
 
 pids=""; LIB_OBJS=""
-for s in $LIB_SRCS $OIC_SRCS $MERYL_SRCS stores/gatekeeperCreate.C overlapInCore/overlapConvert.C overlapInCore/overlapInCorePartition.C; do
+# ovStoreBuild / ovStoreDump: the step downstream of overlapInCore -- oracle of the overlap-store writer
+for s in $LIB_SRCS $OIC_SRCS $MERYL_SRCS stores/gatekeeperCreate.C overlapInCore/overlapConvert.C overlapInCore/overlapInCorePartition.C \
+         stores/ovStoreBuild.C stores/ovStoreDump.C; do
   ( compile "$s" >/dev/null ) &
   pids="$pids $!"
   # bound parallelism to 8
@@ -103,6 +106,8 @@ $CXX -o "$OUT/overlapInCore"          $OIC_OBJS $LIB_OBJS $LD
 $CXX -o "$OUT/gatekeeperCreate"       "$(compile stores/gatekeeperCreate.C)" $LIB_OBJS $LD
 $CXX -o "$OUT/overlapConvert"         "$(compile overlapInCore/overlapConvert.C)" $LIB_OBJS $LD
 $CXX -o "$OUT/overlapInCorePartition" "$(compile overlapInCore/overlapInCorePartition.C)" $LIB_OBJS $LD
+$CXX -o "$OUT/ovStoreBuild"           "$(compile stores/ovStoreBuild.C)" $LIB_OBJS $LD
+$CXX -o "$OUT/ovStoreDump"            "$(compile stores/ovStoreDump.C)" $LIB_OBJS $LD
 MERYL_OBJS=""; for s in $MERYL_SRCS; do MERYL_OBJS="$MERYL_OBJS $(compile $s)"; done
 $CXX -o "$OUT/meryl"                  $MERYL_OBJS $LIB_OBJS $LD
 echo "build_ref.sh: built reference tools in $OUT" >&2
