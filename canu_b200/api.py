@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
     "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
     "oic_copy_kmer_histogram", "oic_comm_unique_id", "oic_comm_init_rank", "oic_comm_init_all", "oic_comm_info",
-    "oic_hash_block_replicate", "oic_build_hash_index_sharded",
+    "oic_hash_block_replicate", "oic_build_hash_index_sharded", "oic_ovlstore_sort",
 ]
 
 
@@ -118,6 +118,7 @@ def load_library():
     lib.oic_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.oic_hash_block_replicate.argtypes = [vp, vp, C.c_int]
     lib.oic_build_hash_index_sharded.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+    lib.oic_ovlstore_sort.argtypes = [vp, vp, C.c_uint64, C.c_uint32, vp, vp, vp, C.c_uint32, vp, C.POINTER(C.c_uint64), vp, C.POINTER(C.c_double)]
     lib.oic_dump_index.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp, vp, vp]
     lib.oic_set_debug.argtypes = [vp, C.c_uint32]
     lib.oic_dump_pairs.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp]
@@ -359,6 +360,23 @@ class Overlapper:
         last = C.c_uint32(0)
         self._check(self.lib.oic_build_hash_index_sharded(self._h, comm, bgn_id, end_id, C.byref(last)), "oic_build_hash_index_sharded")
         return last.value
+
+    # ---- overlap store construction (ovStoreBuild's filter + mirror + sort on the GPU)
+    def ovlstore_sort(self, recs, read_len, skip_dup, library, max_evalue=4095):
+        """(n, 6) uint32 .ovb records -> (m, 6) records of the store in ovOverlap::operator< order, filter tallies, device ms.
+        read_len / skip_dup / library are indexed by read ID (entry 0 unused)."""
+        recs = np.ascontiguousarray(recs, dtype=np.uint32).reshape(-1, 6)
+        read_len = np.ascontiguousarray(read_len, dtype=np.uint32)
+        skip_dup = np.ascontiguousarray(skip_dup, dtype=np.uint8)
+        library = np.ascontiguousarray(library, dtype=np.uint8)
+        assert len(read_len) == len(skip_dup) == len(library)
+        out = np.zeros((2 * len(recs), 6), dtype=np.uint32)
+        m, ms = C.c_uint64(0), C.c_double(0.0)
+        counts = np.zeros(9, dtype=np.uint64)
+        self._check(self.lib.oic_ovlstore_sort(self._h, recs.ctypes.data, len(recs), len(read_len), read_len.ctypes.data, skip_dup.ctypes.data,
+                                               library.ctypes.data, max_evalue, out.ctypes.data, C.byref(m), counts.ctypes.data, C.byref(ms)),
+                    "oic_ovlstore_sort")
+        return out[:m.value], counts, ms.value
 
     # ---- stage dumps (tests)
     def set_debug(self, mask):

@@ -17,6 +17,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -24,6 +25,7 @@
 #include "../../include/oic_b200.h"
 #include "oic_extend.cuh"
 #include "oic_count.cuh"
+#include "oic_store.cuh"
 
 using namespace oic;
 
@@ -331,16 +333,27 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   a.ctr = c->d_ctr.as<DevCounters>();
 
   // no host round trip between the kernels: the list kernels take their sizes from the device counters
+  static const bool trace = getenv("OIC_PHASE_CLOCKS") != nullptr;
+  auto tick = [&]() { if (trace) cudaStreamSynchronize(c->stream); return std::chrono::steady_clock::now(); };
+  const auto tb0 = tick();
   k_insert<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
+  const auto tb1 = tick();
   k_multi_prep<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_count<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_alloc<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_fill<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_sort<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_sort_mid<<<MULTI_GRID, 256, 0, c->stream>>>(a);
+  const auto tb2 = tick();
   {
     const uint64_t per = slots / n_parts;   // the filter regions of this share follow its slices
     k_filter_build<<<nblocks(per, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), per * part, per * (part + 1), geom, c->d_filter.as<uint32_t>());
+  }
+  if (trace) {
+    const auto tb3 = tick();
+    auto ms = [](auto x, auto y) { return std::chrono::duration<double, std::milli>(y - x).count(); };
+    fprintf(stderr, "[oic] build_block share %u/%u: insert %.2f ms | lists %.2f ms | filter %.2f ms (%llu windows, %llu slots)\n", part, n_parts,
+            ms(tb0, tb1), ms(tb1, tb2), ms(tb2, tb3), (unsigned long long)n_windows, (unsigned long long)slots);
   }
   c->tm.launches += 9;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
@@ -507,8 +520,11 @@ int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t 
   }
   if (n_ranks > 1 && !root_path) {
     // ---- every rank builds the slices it owns, then the slices / list segments / filter regions are exchanged
+    static const bool trace = getenv("OIC_PHASE_CLOCKS") != nullptr;
+    const auto tp0 = std::chrono::steady_clock::now();
     int rcode = build_block(c, ri_bgn, n_strings, use, hc, (uint32_t)rank, (uint32_t)n_ranks);
     if (rcode) return rcode;
+    const auto tp1 = std::chrono::steady_clock::now();
     CK(c->d_xchg.ensure(sizeof(ShardCounts) * (size_t)n_ranks + 256));
     std::vector<ShardCounts> cnt(n_ranks);
     ShardCounts mine = {hc.n_inserts, hc.n_distinct, c->hb.n_occ, 0};
@@ -531,15 +547,36 @@ int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t 
       CK(c->d_occ_tmp.ensure((my_occ + 32) * 8));
       if (my_occ) CK(cudaMemcpyAsync(c->d_occ_tmp.p, c->d_occ.p, my_occ * 8, cudaMemcpyDeviceToDevice, c->stream));
       if (base) k_rebase_lists<<<nblocks(per, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), per * rank, per * (rank + 1), (uint32_t)base);
-      NK(api->GroupStart());
-      NK(api->AllGather(c->d_table.as<Slot>() + per * rank, c->d_table.p, per * sizeof(Slot), ncclChar, comm, c->stream));
+      static const char *xm = getenv("OIC_EXCHANGE");   // experiment knob: "bcast" = per-rank broadcasts instead of ncclAllGather
+      const bool use_bcast = xm && strcmp(xm, "bcast") == 0;
+      auto tsync = [&]() { if (trace) cudaStreamSynchronize(c->stream); return std::chrono::steady_clock::now(); };
+      const auto tx0 = tsync();
+      if (!trace) NK(api->GroupStart());
+      if (use_bcast) {
+        for (int q = 0; q < n_ranks; q++) NK(api->Broadcast(c->d_table.as<Slot>() + per * q, c->d_table.as<Slot>() + per * q, per * sizeof(Slot), ncclChar, q, comm, c->stream));
+      } else NK(api->AllGather(c->d_table.as<Slot>() + per * rank, c->d_table.p, per * sizeof(Slot), ncclChar, comm, c->stream));
+      const auto tx1 = tsync();
       NK(api->AllGather(c->d_filter.as<uint32_t>() + fper * rank, c->d_filter.p, fper * 4, ncclChar, comm, c->stream));
+      const auto tx2 = tsync();
       unsigned long long off = 0;
       for (int q = 0; q < n_ranks; q++) {
         if (cnt[q].n_occ) NK(api->Broadcast(c->d_occ_tmp.p, c->d_occ.as<uint64_t>() + off, cnt[q].n_occ * 8, ncclChar, q, comm, c->stream));
         off += cnt[q].n_occ;
       }
-      NK(api->GroupEnd());
+      if (!trace) NK(api->GroupEnd());
+      if (trace) {
+        const auto tx3 = tsync();
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[oic rank %d] exchange (ungrouped, synchronised for the trace): table %.2f ms | filter %.2f ms | lists %.2f ms\n", rank, ms(tx0, tx1), ms(tx1, tx2), ms(tx2, tx3));
+      }
+      if (trace) {
+        const auto tp2 = std::chrono::steady_clock::now();
+        cudaStreamSynchronize(c->stream);
+        const auto tp3 = std::chrono::steady_clock::now();
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[oic rank %d] sharded build: own slices %.2f ms | counts + rebase + enqueue %.2f ms | exchange %.2f ms (table %.0f MB, lists %.0f MB)\n",
+                rank, ms(tp0, tp1), ms(tp1, tp2), ms(tp2, tp3), slots * 16.0 / 1e6, tot_occ * 8.0 / 1e6);
+      }
       c->tm.launches += 1;
       c->hb.n_occ = tot_occ;
       c->hb.n_distinct = tot_distinct;
@@ -1574,6 +1611,85 @@ int oic_copy_kmer_histogram(oic_ctx_t *c, uint64_t *hist, uint64_t capacity, uin
   if (!c) return OIC_ERR_ARG;
   if (length) *length = c->kc_hist.size();
   if (hist) for (uint64_t i = 0; i < capacity && i < c->kc_hist.size(); i++) hist[i] = c->kc_hist[i];
+  return OIC_OK;
+}
+
+/* Overlap store construction on the GPU: filter + mirror, radix sort by (a_iid, b_iid), ties by the data words (oic_store.cuh). */
+int oic_ovlstore_sort(oic_ctx_t *c, const oic_ovb_record_t *recs, uint64_t n, uint32_t max_id, const uint32_t *read_len, const uint8_t *skip_dup,
+                      const uint8_t *library, uint32_t max_evalue, oic_ovb_record_t *sorted, uint64_t *n_sorted, uint64_t counts[9], double *device_ms) {
+  if (!c) return OIC_ERR_ARG;
+  if ((n && (!recs || !sorted)) || !read_len || !skip_dup || !library || max_id == 0) return c->fail(OIC_ERR_ARG, "oic_ovlstore_sort: bad argument");
+  if (2 * n >= (1ull << 32)) return c->fail(OIC_ERR_CAPACITY, "oic_ovlstore_sort: more than 2^31 overlaps in one call");
+  cudaSetDevice(c->device);
+  if (n_sorted) *n_sorted = 0;
+  if (device_ms) *device_ms = 0.0;
+  if (counts) memset(counts, 0, 9 * sizeof(uint64_t));
+  if (n == 0) return OIC_OK;
+  DevBuf d_in, d_mir, d_out, d_len, d_skip, d_lib, d_cnt, d_keys[2], d_idx[2], d_hist;
+  struct Release {
+    std::vector<DevBuf *> v;
+    ~Release() { for (DevBuf *b : v) b->release(); }
+  } rel{{&d_in, &d_mir, &d_out, &d_len, &d_skip, &d_lib, &d_cnt, &d_keys[0], &d_keys[1], &d_idx[0], &d_idx[1], &d_hist}};
+  CK(d_in.ensure(n * sizeof(StoreRec)));
+  CK(d_mir.ensure(2 * n * sizeof(StoreRec)));
+  CK(d_len.ensure((size_t)max_id * 4));
+  CK(d_skip.ensure(max_id));
+  CK(d_lib.ensure(max_id));
+  CK(d_cnt.ensure(16 * 8));
+  CK(cudaMemsetAsync(d_cnt.p, 0, 16 * 8, c->stream));
+  CK(cudaMemcpyAsync(d_in.p, recs, n * sizeof(StoreRec), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d_len.p, read_len, (size_t)max_id * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d_skip.p, skip_dup, max_id, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d_lib.p, library, max_id, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += n * sizeof(StoreRec) + (uint64_t)max_id * 6;
+  cudaEventRecord(c->ev_call[0], c->stream);
+  MirrorArgs ma;
+  ma.in = d_in.as<StoreRec>(); ma.n = n; ma.max_id = max_id; ma.rd_len = d_len.as<uint32_t>(); ma.skip_dup = d_skip.as<uint8_t>();
+  ma.lib = d_lib.as<uint8_t>(); ma.max_evalue = max_evalue; ma.out = d_mir.as<StoreRec>();
+  ma.n_out = d_cnt.as<unsigned long long>() + 15; ma.counts = d_cnt.as<unsigned long long>();
+  k_store_mirror<<<nblocks(n, 256), 256, 0, c->stream>>>(ma);
+  unsigned long long hcnt[16];
+  CK(cudaMemcpyAsync(hcnt, d_cnt.p, sizeof(hcnt), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  c->tm.launches += 1;
+  if (counts) for (int i = 0; i < 9; i++) counts[i] = hcnt[i];
+  const uint64_t m = hcnt[15];
+  if (hcnt[0]) return c->fail(OIC_ERR_ARG, "oic_ovlstore_sort: %llu overlaps have IDs out of range (maxID %u), possibly corrupt input data", hcnt[0], max_id);
+  if (m) {
+    for (int i = 0; i < 2; i++) { CK(d_keys[i].ensure(m * 8)); CK(d_idx[i].ensure(m * 4)); }
+    CK(d_out.ensure(m * sizeof(StoreRec)));
+    const uint32_t nb = nblocks(m, RADIX_TILE);
+    CK(d_hist.ensure((size_t)2 * 256 * nb * 4 + 16));   // digit histogram, then its exclusive scan
+    const uint64_t hn = (uint64_t)256 * nb, hb = (hn + SCAN_ITEMS - 1) / SCAN_ITEMS;
+    CK(c->d_blk.ensure((hb + 2) * 4));
+    k_store_keys<<<nblocks(m, 256), 256, 0, c->stream>>>(d_mir.as<StoreRec>(), m, d_keys[0].as<unsigned long long>(), d_idx[0].as<uint32_t>());
+    int id_bits = 1;
+    while ((1ull << id_bits) < max_id) id_bits++;
+    int cur = 0;
+    for (int half = 0; half < 2; half++)                       // b_iid digits first (low word), then a_iid
+      for (int shift = 32 * half; shift < 32 * half + id_bits; shift += 8) {
+        k_radix_hist<<<nb, RADIX_THREADS, 0, c->stream>>>(d_keys[cur].as<unsigned long long>(), m, shift, d_hist.as<uint32_t>(), nb);
+        k_scan_u32_reduce<<<(unsigned)hb, SCAN_THREADS, 0, c->stream>>>(d_hist.as<uint32_t>(), hn, c->d_blk.as<uint32_t>());
+        k_scan_u32_single<<<1, SCAN_THREADS, 0, c->stream>>>(c->d_blk.as<uint32_t>(), (uint32_t)hb);
+        k_scan_u32_apply<<<(unsigned)hb, SCAN_THREADS, 0, c->stream>>>(d_hist.as<uint32_t>(), d_hist.as<uint32_t>() + hn, hn, c->d_blk.as<uint32_t>());
+        k_radix_scatter<<<nb, RADIX_THREADS, 0, c->stream>>>(d_keys[cur].as<unsigned long long>(), d_idx[cur].as<uint32_t>(), m, shift, d_hist.as<uint32_t>() + hn, nb,
+                                                             d_keys[cur ^ 1].as<unsigned long long>(), d_idx[cur ^ 1].as<uint32_t>());
+        c->tm.launches += 5;
+        cur ^= 1;
+      }
+    k_store_tiefix<<<nblocks(m, 256), 256, 0, c->stream>>>(d_keys[cur].as<unsigned long long>(), d_idx[cur].as<uint32_t>(), d_mir.as<StoreRec>(), m);
+    k_store_gather<<<nblocks(m, 256), 256, 0, c->stream>>>(d_mir.as<StoreRec>(), d_idx[cur].as<uint32_t>(), m, d_out.as<StoreRec>());
+    c->tm.launches += 3;
+    cudaEventRecord(c->ev_call[1], c->stream);
+    CK(cudaMemcpyAsync(sorted, d_out.p, m * sizeof(StoreRec), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    c->tm.d2h_bytes += m * sizeof(StoreRec);
+    float ms = 0;
+    if (device_ms && cudaEventElapsedTime(&ms, c->ev_call[0], c->ev_call[1]) == cudaSuccess) *device_ms = ms;
+  }
+  if (n_sorted) *n_sorted = m;
   return OIC_OK;
 }
 

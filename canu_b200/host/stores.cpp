@@ -1,6 +1,8 @@
 // stores.cpp -- gkpStore reader and .ovb / .counts writer (see stores.h for the reference citations).
 #include "stores.h"
 
+#include "snappy_lite.h"
+
 #include <errno.h>
 #include <fcntl.h>
 #include <stdlib.h>
@@ -134,21 +136,10 @@ OvbWriter::OvbWriter(const std::string &name) : name_(name) {
 
 void OvbWriter::flush() {
   if (buf_.empty()) return;
-  // snappy raw format, literal only: varint(uncompressed bytes), then one literal element with a 3-byte length
+  // one snappy raw block per buffer (ST/ovStoreFile.C:157-185): size_t compressed length, then the block
   const size_t n = buf_.size() * sizeof(uint32_t);
-  std::vector<unsigned char> out;
-  out.reserve(n + 16);
-  size_t v = n;
-  while (v >= 0x80) { out.push_back((unsigned char)(v | 0x80)); v >>= 7; }
-  out.push_back((unsigned char)v);
-  const size_t l1 = n - 1;
-  if (l1 < 60) out.push_back((unsigned char)(l1 << 2));
-  else if (l1 < (1u << 8)) { out.push_back(60 << 2); out.push_back((unsigned char)l1); }
-  else if (l1 < (1u << 16)) { out.push_back(61 << 2); out.push_back((unsigned char)l1); out.push_back((unsigned char)(l1 >> 8)); }
-  else { out.push_back(62 << 2); out.push_back((unsigned char)l1); out.push_back((unsigned char)(l1 >> 8)); out.push_back((unsigned char)(l1 >> 16)); }
-  const unsigned char *src = reinterpret_cast<const unsigned char *>(buf_.data());
-  out.insert(out.end(), src, src + n);
-  size_t bl = out.size();
+  std::vector<unsigned char> out(snappy_max_compressed(n));
+  const size_t bl = snappy_compress(reinterpret_cast<const unsigned char *>(buf_.data()), n, out.data());
   if (fwrite(&bl, sizeof(size_t), 1, f_) != 1 || fwrite(out.data(), 1, bl, f_) != bl) die("ERROR: write to '%s' failed: %s", name_, strerror(errno));
   buf_.clear();
 }

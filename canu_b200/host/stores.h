@@ -47,8 +47,8 @@ class GkStore {
 };
 
 /* ovFile in ovFileFullWrite mode: blocks of <= 262080 uint32 (whole 6-word records), each written as
- * size_t compressedLength + a snappy raw block.  Blocks are emitted as snappy LITERAL-ONLY streams (valid snappy,
- * no compression); ovStoreBuild / overlapConvert read them with the stock snappy decoder. */
+ * size_t compressedLength + a snappy raw block (snappy_lite.h: a greedy LZ77 compressor of the raw format; ovStoreBuild /
+ * overlapConvert read the blocks with the stock snappy decoder). */
 class OvbWriter {
  public:
   explicit OvbWriter(const std::string &name);   // exits on failure

@@ -224,6 +224,21 @@ int oic_copy_frequent_kmers(oic_ctx_t *ctx, uint64_t *keys, uint32_t *counts, ui
  * total = sum i * hist[i]. */
 int oic_copy_kmer_histogram(oic_ctx_t *ctx, uint64_t *hist, uint64_t capacity, uint64_t *length);
 
+/* ---- overlap store construction: the step downstream of overlapInCore -------------------------------
+ * Replaces the compute of ovStoreBuild's in-core path (ST/ovStoreBuild.C:500-645): every overlap of the input is filtered and
+ * mirrored (ovStoreFilter::filterOverlap, ST/ovStoreFilter.C:118-260; ovOverlap::swapIDs, ST/ovOverlap.C:114-144), and the
+ * records that still carry a forUTG / forOBT / forDUP flag are sorted by ovOverlap::operator< (ST/ovOverlap.H:327-339: a_iid,
+ * b_iid, then the two 64-bit data words) on the GPU.  recs: n overlaps in .ovb word order (host memory); read_len / skip_dup /
+ * library: per read ID, max_id = numReads + 1 entries (skip_dup[i] = 1 when the read's library does not ask for
+ * deduplication, ST/ovStoreFilter.C:62-65); max_evalue = AS_OVS_encodeEvalue(-e).  sorted must hold 2 n records; *n_sorted
+ * receives the number written.  counts (may be NULL) receives 9 tallies of the filter: records with an ID out of range (the
+ * reference exits on the first one: the caller must treat a non-zero count as fatal), skipERATE, skipOBTbad, skipOBTshort,
+ * skipDUP, skipDUPlib, saveUTG, saveOBT, saveDUP.  The store files themselves (info, index, data, evalueLen, overlapScores)
+ * are host work: canu_b200/host/ovstore.cpp, tool canu_b200/bin/ovStoreBuild. */
+int oic_ovlstore_sort(oic_ctx_t *ctx, const oic_ovb_record_t *recs, uint64_t n, uint32_t max_id, const uint32_t *read_len,
+                      const uint8_t *skip_dup, const uint8_t *library, uint32_t max_evalue, oic_ovb_record_t *sorted,
+                      uint64_t *n_sorted, uint64_t counts[9], double *device_ms);
+
 /* Roofline denominator of the extension stage: INT32 issue rates of `device`, measured (thread Gop/s).  alu = chains of
  * LOP3 + IADD3 (the pipe the edit-distance rows live on; reference code measured against: LIBO/prefixEditDistance-forward.C
  * inner loop), imad = chains of IMAD.  Takes a few milliseconds. */

@@ -178,3 +178,86 @@ def test_frequent_mers_tool_vs_meryl(name, K, T, tmp_path):
     gold = gzip.open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
     assert got == gold
     assert got == H.run_meryl(store, K, T, str(tmp_path))
+
+
+# ------------------------------------------------------------------------------------------------ overlap store
+OVSB = os.path.join(os.path.dirname(BIN), "ovStoreBuild")
+needs_store_tools = pytest.mark.skipif(not (H.have_ref() and os.access(OVSB, os.X_OK) and os.access(os.path.join(H.REF_DIR, "ovStoreBuild"), os.X_OK)),
+                                       reason="ovStoreBuild (ours or the reference's) not built")
+STORE_FILES = ["info", "index", "0001", "evalueLen", "overlapScores"]
+
+
+@needs_store_tools
+@pytest.mark.parametrize("name,extra", [("c1_small", []), ("c4_short", []), ("quirk_m", []), ("c2_noisy", ["-e", "0.1"])])
+def test_ovStoreBuild_equals_reference(name, extra, tmp_path):
+    """canu_b200/bin/ovStoreBuild (filter + mirror + sort on the GPU, oic_ovlstore_sort) on the .ovb our overlapInCore wrote vs the
+    reference's ovStoreBuild on the reference overlapInCore's .ovb of the same job: every file of the two stores is identical,
+    and so is the reference's own `ovStoreDump -d` of them."""
+    wd = str(tmp_path)
+    store, ovb, _ = run_case(name, wd)
+    reads, P, erate, threads, skip = cases.build_case(name)
+    args = H.oic_args(P, erate)
+    if skip:
+        args += ["-k", os.path.join(wd, "skip.fasta")]
+    ref_ovb, _ = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref"), args, threads)
+    mine, ref = os.path.join(wd, "mine.ovlStore"), os.path.join(wd, "ref.ovlStore")
+    subprocess.check_call([OVSB, "-O", mine, "-G", store] + extra + [ovb], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    subprocess.check_call([os.path.join(H.REF_DIR, "ovStoreBuild"), "-O", ref, "-G", store] + extra + [ref_ovb],
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    assert sorted(os.listdir(mine)) == sorted(os.listdir(ref)) == sorted(STORE_FILES)
+    for f in STORE_FILES:
+        assert open(os.path.join(mine, f), "rb").read() == open(os.path.join(ref, f), "rb").read(), f
+    dump = [subprocess.check_output([os.path.join(H.REF_DIR, "ovStoreDump"), "-G", store, "-O", s, "-d", "-raw"], stderr=subprocess.DEVNULL)
+            for s in (mine, ref)]
+    assert dump[0] == dump[1] and dump[0].count(b"\n") > 100
+    # ... and our tool reads the reference's snappy-compressed .ovb as well as its own
+    mine2 = os.path.join(wd, "mine2.ovlStore")
+    subprocess.check_call([OVSB, "-O", mine2, "-G", store] + extra + [ref_ovb], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    for f in STORE_FILES:
+        assert open(os.path.join(mine2, f), "rb").read() == open(os.path.join(ref, f), "rb").read(), f
+
+
+def test_ovlstore_sort_vs_numpy_restatement():
+    """oic_ovlstore_sort through the C ABI on synthetic records that exercise every filter branch (flipped / unflipped, OBT and DUP
+    flags, short and near-identical overlaps, two libraries, evalue cut, duplicate (a, b) pairs whose order the data words decide)"""
+    import numpy as np
+    from canu_b200 import api
+    from test_host_stores import mirror_filter_sort, pack_records
+    rng = np.random.default_rng(2024)
+    n, n_reads = 200000, 3000
+    length = np.zeros(n_reads + 1, dtype=np.uint32)
+    length[1:] = rng.integers(150, 4000, n_reads)
+    library = np.zeros(n_reads + 1, dtype=np.uint8)
+    library[1:] = rng.integers(1, 3, n_reads)
+    skip_dup = np.zeros(n_reads + 1, dtype=np.uint8)
+    skip_dup[library == 2] = 1
+    ov = np.zeros(n, dtype=H.OVERLAP_DT)
+    ov["a_iid"] = rng.integers(1, n_reads + 1, n)
+    ov["b_iid"] = rng.integers(1, 40, n) + (ov["a_iid"] % 7)       # many equal (a, b) pairs
+    ov["b_iid"] = np.clip(ov["b_iid"], 1, n_reads)
+    la, lb = length[ov["a_iid"]], length[ov["b_iid"]]
+    ov["ahg5"] = rng.integers(0, 120, n) % la
+    ov["ahg3"] = rng.integers(0, 60, n) % (la - ov["ahg5"])
+    ov["bhg5"] = rng.integers(0, 120, n) % lb
+    ov["bhg3"] = rng.integers(0, 60, n) % (lb - ov["bhg5"])
+    ov["span"] = rng.integers(0, 4000, n)
+    ov["evalue"] = rng.integers(0, 1500, n)
+    ov["flipped"] = rng.integers(0, 2, n)
+    ov["for_obt"] = rng.integers(0, 2, n)
+    ov["for_dup"] = rng.integers(0, 2, n)
+    ov["for_utg"] = rng.integers(0, 2, n)
+    rec = pack_records(ov)
+    rec[-500:] = rec[:500]                                          # exact duplicates too
+    ovl = api.Overlapper(api.default_params(min_olap_len=500))
+    for max_evalue in (4095, 1000):
+        got, counts, ms = ovl.ovlstore_sort(rec, length, skip_dup, library, max_evalue)
+        want = mirror_filter_sort(rec, length, skip_dup, library, max_evalue)
+        assert len(got) == len(want) > n
+        assert np.array_equal(got, want)
+        assert counts[0] == 0 and (counts[1] > 0) == (max_evalue < 1499)
+    # an ID out of range is fatal, as in the reference (ST/ovStoreBuild.C:594-603)
+    bad = rec[:10].copy()
+    bad[3, 1] = n_reads + 5
+    with pytest.raises(api.OicError):
+        ovl.ovlstore_sort(bad, length, skip_dup, library)
+    ovl.close()
