@@ -143,6 +143,8 @@ struct oic_ctx {
   bool hash_ready = false;
   oic_hash_meta_t hb = {};
   TableGeom geom = {};
+  DevBuf d_word_read;           // read index per stream word (k_word_read, once per load)
+  DevBuf d_parts, d_part_ctr;   // build: the block's windows as partitioned {key, occurrence} records
   DevBuf d_table, d_occ, d_str_flags, d_str_use, d_filter, d_ovf_slot, d_ovf_occ, d_multi_list, d_first_occ, d_cnt, d_mid_list, d_blk, d_big_list, d_occ_tmp, d_hist;
   // identity of the block in the table (oic_set_job sweeps reuse it): requested range + the two load limits
   uint32_t hbk_bgn = 0, hbk_end = 0, hbk_strings = 0; uint64_t hbk_datalen = 0;
@@ -151,6 +153,7 @@ struct oic_ctx {
   bool have_filter = false;      // Bloom filter of the current hash block is valid
 
   // search buffers
+  DevBuf d_q_order;
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
       d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool, d_wide;
   DevBuf d_ctr, d_flag;
@@ -300,8 +303,11 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   CK(c->d_occ.ensure((n_windows + 32) * sizeof(uint64_t)));
 
   if (zero_counters(c)) return OIC_ERR_CUDA;
-  k_table_init<<<nblocks(slots, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>(), slots);
-  CK(cudaMemsetAsync(c->d_filter.p, 0, fwords * 4, c->stream));
+  {   // (a rank of a group only clears the slices / filter regions it fills: the others arrive by the exchange)
+    const uint64_t per = slots / n_parts, fper = fwords / n_parts;
+    k_table_init<<<nblocks(per, 256), 256, 0, c->stream>>>(c->d_table.as<Slot>() + per * part, per);
+    CK(cudaMemsetAsync(c->d_filter.as<uint32_t>() + fper * part, 0, fper * 4, c->stream));
+  }
   CK(cudaMemsetAsync(c->d_str_flags.p, 0, ((size_t)n_strings + 8) & ~(size_t)3, c->stream));
   CK(cudaMemcpyAsync(c->d_str_use.p, use.data(), n_strings, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += n_strings;
@@ -311,6 +317,7 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   a.n_off = c->n_off;
   a.rd_pos = c->d_pos.as<int64_t>();
   a.rd_len = c->d_len.as<uint32_t>();
+  a.word_read = c->d_word_read.as<uint32_t>();
   a.str_use = c->d_str_use.as<uint8_t>();
   a.ri_bgn = ri_bgn;
   a.n_strings = n_strings;
@@ -336,7 +343,15 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   static const bool trace = getenv("OIC_PHASE_CLOCKS") != nullptr;
   auto tick = [&]() { if (trace) cudaStreamSynchronize(c->stream); return std::chrono::steady_clock::now(); };
   const auto tb0 = tick();
-  k_insert<<<nblocks(region_words * 32, 256), 256, 0, c->stream>>>(a);
+  if (n_parts > 1) {
+    // a rank of a group owns 1/N of the windows: pack them first, then a dense insert (oic_build.cuh)
+    CK(c->d_parts.ensure((n_windows + 32) * sizeof(PartRec)));   // worst case: every window hashes into this rank's slices
+    CK(c->d_part_ctr.ensure(16));
+    CK(cudaMemsetAsync(c->d_part_ctr.p, 0, 16, c->stream));
+    const uint64_t cap = n_windows;
+    k_compact_windows<<<nblocks(region_words * 32, INS_TILE), INS_THREADS, 0, c->stream>>>(a, c->d_parts.as<PartRec>(), c->d_part_ctr.as<uint32_t>());
+    k_insert<true><<<nblocks(cap, INS_TILE), INS_THREADS, 0, c->stream>>>(a, c->d_parts.as<PartRec>(), c->d_part_ctr.as<uint32_t>());
+  } else k_insert<false><<<nblocks(region_words * 32, INS_TILE), INS_THREADS, 0, c->stream>>>(a, nullptr, nullptr);
   const auto tb1 = tick();
   k_multi_prep<<<MULTI_GRID, 256, 0, c->stream>>>(a);
   k_multi_count<<<MULTI_GRID, 256, 0, c->stream>>>(a);
@@ -352,10 +367,10 @@ int build_block(oic_ctx *c, uint32_t ri_bgn, uint32_t n_strings, const std::vect
   if (trace) {
     const auto tb3 = tick();
     auto ms = [](auto x, auto y) { return std::chrono::duration<double, std::milli>(y - x).count(); };
-    fprintf(stderr, "[oic] build_block share %u/%u: insert %.2f ms | lists %.2f ms | filter %.2f ms (%llu windows, %llu slots)\n", part, n_parts,
+    fprintf(stderr, "[oic] build_block share %u/%u: partition + insert %.2f ms | lists %.2f ms | filter %.2f ms (%llu windows, %llu slots)\n", part, n_parts,
             ms(tb0, tb1), ms(tb1, tb2), ms(tb2, tb3), (unsigned long long)n_windows, (unsigned long long)slots);
   }
-  c->tm.launches += 9;
+  c->tm.launches += 11;
   if (read_counters(c, hc)) return OIC_ERR_CUDA;
   if (n_parts == 1 && (c->n_off ? hc.n_inserts > n_windows : hc.n_inserts != n_windows))
     return c->fail(OIC_ERR_STATE, "internal: %llu windows inserted, %llu expected", (unsigned long long)hc.n_inserts, (unsigned long long)n_windows);
@@ -551,7 +566,8 @@ int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t 
       const bool use_bcast = xm && strcmp(xm, "bcast") == 0;
       auto tsync = [&]() { if (trace) cudaStreamSynchronize(c->stream); return std::chrono::steady_clock::now(); };
       const auto tx0 = tsync();
-      if (!trace) NK(api->GroupStart());
+      static const bool grouped = getenv("OIC_NCCL_GROUP") != nullptr;   // (measured: one group of the four collectives is slower than issuing them back to back)
+      if (!trace && grouped) NK(api->GroupStart());
       if (use_bcast) {
         for (int q = 0; q < n_ranks; q++) NK(api->Broadcast(c->d_table.as<Slot>() + per * q, c->d_table.as<Slot>() + per * q, per * sizeof(Slot), ncclChar, q, comm, c->stream));
       } else NK(api->AllGather(c->d_table.as<Slot>() + per * rank, c->d_table.p, per * sizeof(Slot), ncclChar, comm, c->stream));
@@ -563,7 +579,7 @@ int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t 
         if (cnt[q].n_occ) NK(api->Broadcast(c->d_occ_tmp.p, c->d_occ.as<uint64_t>() + off, cnt[q].n_occ * 8, ncclChar, q, comm, c->stream));
         off += cnt[q].n_occ;
       }
-      if (!trace) NK(api->GroupEnd());
+      if (!trace && grouped) NK(api->GroupEnd());
       if (trace) {
         const auto tx3 = tsync();
         auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
@@ -710,7 +726,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read};
   if (c->comm && nccl_api()) nccl_api()->CommDestroy(c->comm);
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -803,6 +819,9 @@ static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const ui
     CK(cudaGetLastError());
     c->n_off = n_off;
   }
+  CK(c->d_word_read.ensure(c->stream_words * 4));
+  k_word_read<<<nblocks(c->stream_words, 256), 256, 0, c->stream>>>(c->d_pos.as<int64_t>(), n, c->stream_words, c->d_word_read.as<uint32_t>());
+  c->tm.launches += 1;
   t.stop();
 
   // Edit_Match_Limit for every row an extension can reach: error limit <= ceil(erate * longest read)
@@ -888,9 +907,8 @@ int replicate_impl(oic_ctx *c, ncclComm_t comm, int n, int rank, int root) {
   oic_dev_buffer_t b[OIC_HASH_BLOCK_NBUF];
   oic_hash_block_buffers(c, b);
   c->hb = keep;
-  NK(api->GroupStart());
+  // (back to back, not as one NCCL group: measured on 2 B200, a group of these collectives runs ~5 ms slower than the same calls in sequence)
   for (int i = 0; i < OIC_HASH_BLOCK_NBUF; i++) NK(api->Broadcast(b[i].ptr, b[i].ptr, b[i].bytes, ncclChar, root, comm, c->stream));
-  NK(api->GroupEnd());
   c->tm.launches += 1;
   if (rank != root) {
     const int rc = oic_hash_block_commit(c, &meta);
@@ -916,7 +934,16 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
 
   CK(c->d_qs_read.ensure((size_t)nq * 4));
   CK(cudaMemcpyAsync(c->d_qs_read.p, qs_read.data(), (size_t)nq * 4, cudaMemcpyHostToDevice, c->stream));
-  c->tm.h2d_bytes += (uint64_t)nq * 4;
+  // longest-first order of the scan (skipped reads last)
+  std::vector<uint32_t> q_order(nq);
+  for (uint32_t q = 0; q < nq; q++) q_order[q] = q;
+  std::stable_sort(q_order.begin(), q_order.end(), [&](uint32_t x, uint32_t y) {
+    const uint32_t lx = qs_read[x] == 0xffffffffu ? 0 : c->h_len[qs_read[x]], ly = qs_read[y] == 0xffffffffu ? 0 : c->h_len[qs_read[y]];
+    return lx > ly;
+  });
+  CK(c->d_q_order.ensure((size_t)nq * 4));
+  CK(cudaMemcpyAsync(c->d_q_order.p, q_order.data(), (size_t)nq * 4, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += (uint64_t)nq * 8;
   CK(c->d_recs.ensure((size_t)max_chunks * CHUNK * sizeof(Seed)));
   CK(c->d_chunk_next.ensure((size_t)max_chunks * 4));
   CK(c->d_chunk_cnt.ensure((size_t)max_chunks * 4));
@@ -945,7 +972,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   ScanArgs sa;
   sa.fwd = c->d_fwd.as<uint64_t>(); sa.rc = c->d_rc.as<uint64_t>(); sa.n_off = c->n_off;
   sa.rd_pos = c->d_pos.as<int64_t>(); sa.rd_len = c->d_len.as<uint32_t>();
-  sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.n_queries = nq;
+  sa.qs_read = c->d_qs_read.as<uint32_t>(); sa.q_order = c->d_q_order.as<uint32_t>(); sa.n_queries = nq;
   sa.first_id = c->first_id; sa.hash_bgn_id = c->hb.bgn_id; sa.K = P.kmer_len;
   sa.table = c->d_table.as<Slot>(); sa.geom = c->geom; sa.occ = c->d_occ.as<uint64_t>();
   sa.filter = (c->have_filter && use_filter()) ? c->d_filter.as<uint32_t>() : nullptr;

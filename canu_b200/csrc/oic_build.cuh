@@ -8,13 +8,14 @@
  * the screened-end flags, (d) the hash-load cut-off (which read is the last one loaded).
  *
  *   k_pack_reads   ASCII -> 2-bit words, forward and reverse-complement streams
- *   k_insert       one warp per 32-base word of the block: 32 windows, one per lane; one CAS on the key per probe, the
- *                  occurrence ORed into the slot (k-mers seen once stay inline in the slot); repeats go to an overflow list; 
+ *   k_insert       one window per lane: one CAS on the key per probe, the occurrence ORed into the slot (k-mers seen once stay
+ *                  inline in the slot); repeats go to an overflow list; a sharded build first packs the rank's windows
+ *                  (k_compact_windows) so that every lane of an insert warp has work
+ *   k_filter_build Bloom filter of the block's k-mers (L2-resident while filled), tested by the seed scan before the table
  *   k_multi_prep / _count / _alloc / _fill   per repeated k-mer: count its overflow entries, reserve its run of the
  *                  occurrence array (bump allocator), scatter the entries into it
  *   k_multi_sort   runs of 2..6 entries: one thread each (sorting network in registers, descending);
  *   k_sort_mid     7..32 entries: one warp per run (bitonic);  k_sort_big: longer runs, one block each (LSD radix)
- *   k_filter_build Bloom filter of the block's k-mers (L2-resident), tested by the seed scan before it touches the table
  *   k_first_occ    histogram of "read in which a k-mer first appears" -> hash-load cut-off on the host
  *   k_mark_skip    Empty bit + screened ends for the -k skip list (and absent k-mers when the hopeless check is on)
  */
@@ -134,6 +135,7 @@ struct BuildArgs {
   uint64_t n_off;            // word offset of the N-mask stream behind the base stream (0: no read holds an N)
   const int64_t *rd_pos;     // per read index (0-based within the loaded set)
   const uint32_t *rd_len;
+  const uint32_t *word_read; // per stream word: index of the read it belongs to (k_word_read)
   const uint8_t *str_use;    // per string slot of this block: 1 = read is loaded into the hash
   uint32_t ri_bgn;           // read index of string 0
   uint32_t n_strings;
@@ -154,13 +156,22 @@ struct BuildArgs {
   DevCounters *ctr;
 };
 
-__device__ __forceinline__ uint32_t find_string(const BuildArgs &a, int64_t p0) {
-  uint32_t lo = 0, hi = a.n_strings;
+// read that owns every 64-bit word of the stream (the last read that starts at or before it), filled once per load: the build
+// kernels look the string of a word up instead of searching the read table (14 dependent loads per warp on a 10 k-read block)
+__global__ void __launch_bounds__(256) k_word_read(const int64_t *__restrict__ rd_pos, uint32_t n_reads, uint64_t n_words, uint32_t *word_read) {
+  const uint64_t gw = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gw >= n_words) return;
+  const int64_t p0 = (int64_t)gw * 32;
+  uint32_t lo = 0, hi = n_reads;
   while (hi - lo > 1) {
-    uint32_t mid = (lo + hi) >> 1;
-    if (a.rd_pos[a.ri_bgn + mid] <= p0) lo = mid; else hi = mid;
+    const uint32_t mid = (lo + hi) >> 1;
+    if (rd_pos[mid] <= p0) lo = mid; else hi = mid;
   }
-  return lo;
+  word_read[gw] = lo;
+}
+__device__ __forceinline__ uint32_t find_string(const BuildArgs &a, int64_t p0) {
+  const uint32_t r = a.word_read[p0 >> 5];
+  return r > a.ri_bgn ? (r - a.ri_bgn < a.n_strings ? r - a.ri_bgn : a.n_strings - 1) : 0;
 }
 
 /* 16-byte compare-and-swap on a slot: returns the slot's previous content */
@@ -189,19 +200,10 @@ __device__ __forceinline__ bool table_find(const Slot *__restrict__ table, const
   }
 }
 
-/*
- * One warp per 32-base word of the hash block's stream region, one window per lane.  Per probe one 8-byte CAS on the key:
- *   - the slot was free: the window owns the k-mer and ORs its occurrence word into the payload (first occurrence of a
- *     k-mer: ~90 % of the windows of a 1x block never need anything else);
- *   - the key is already there: the window ORs the list mark into the payload and appends {slot, occurrence} to the
- *     overflow list; the arrival that finds the mark clear also queues the slot for the list kernels.
- * Both payload updates are ORs into disjoint bits, so they commute: no arrival ever waits for another one.
- * Hash_Insert's chained bucket (Build_Hash_Index.C:296-350) appears as: slot = k-mer, list = chain.
- */
-__global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
-  uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (gw >= a.region_words) return;
-  const int l = lane_id();
+/* The k-mer window of lane l of stream word gw of the block: its key, its occurrence word (string, offset, previous base) and
+ * the hash of the key.  false: no window starts there (read end, string not loaded, a window with an N: Char_Is_Bad,
+ * Build_Hash_Index.C:376-393). */
+__device__ __forceinline__ bool block_window(const BuildArgs &a, uint64_t gw, int l, unsigned long long &key, unsigned long long &occ, uint64_t &hk) {
   const int64_t p0 = a.region_pos + (int64_t)gw * 32;
   const uint32_t s = find_string(a, p0);
   const int64_t spos = a.rd_pos[a.ri_bgn + s];
@@ -209,67 +211,24 @@ __global__ void __launch_bounds__(256) k_insert(BuildArgs a) {
   const int64_t o = p0 - spos + l;
   bool valid_n = true;
   const uint64_t W0 = a.fwd[p0 >> 5], W1 = a.fwd[(p0 >> 5) + 1];
-  uint64_t key = l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0;
+  key = l ? ((W0 >> (2 * l)) | (W1 << (64 - 2 * l))) : W0;
   key &= (a.K == 32) ? ~0ULL : ((1ULL << (2 * a.K)) - 1);
   bool prev_n = false;
-  if (a.n_off) {   // a window with an N is not inserted (Char_Is_Bad, Build_Hash_Index.C:376-393)
+  if (a.n_off) {
     const uint64_t M0 = a.fwd[(p0 >> 5) + a.n_off], M1 = a.fwd[(p0 >> 5) + 1 + a.n_off];
     uint64_t mk = l ? ((M0 >> (2 * l)) | (M1 << (64 - 2 * l))) : M0;
     mk &= (a.K == 32) ? ~0ULL : ((1ULL << (2 * a.K)) - 1);
     if (mk) valid_n = false;
     prev_n = l ? ((M0 >> (2 * (l - 1))) & 3u) != 0 : (o > 0 && ((a.fwd[(p0 >> 5) - 1 + a.n_off] >> 62) & 3u) != 0);
   }
-  bool claimed = false, conv = false, later = false, mine = false;
-  unsigned long long my_occ = 0;
-  uint32_t my_slot = 0;
   const bool valid = valid_n && a.str_use[s] && o >= 0 && o + a.K <= (int64_t)len;
-  if (valid) {
-    const uint32_t pv = o > 0 && !prev_n;   // the window one base earlier holds an N: it is not in the table, a run starts here
-    const uint32_t pb = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : (pv ? (uint32_t)(a.fwd[(p0 >> 5) - 1] >> 62) & 3u : 0u);
-    my_occ = occ_pack(s, (uint32_t)o, pv, pb);
-    const uint64_t hk = hash_key(key);
-    const uint32_t slice = geom_slice(a.geom, hk);
-    mine = slice >= a.slice_lo && slice < a.slice_hi;
-    uint64_t h = geom_home(a.geom, hk);
-    // a plain load first: it brings the line into L2 with the memory-level parallelism of loads; an atomic that misses
-    // L2 is several times slower (measured on B200: CAS-first insert 25 ms, load-first 6 ms for 99 M windows)
-    unsigned long long cur = mine ? ld_key(a.table + h) : 0ULL;
-    while (mine) {
-      if (cur == EMPTY_KEY) cur = atomicCAS(&a.table[h].key, EMPTY_KEY, key);
-      if (cur == EMPTY_KEY) {
-        if (my_occ) atomicOr(&a.table[h].pay, my_occ);
-        claimed = true;
-        break;
-      }
-      if (cur == key) {
-        my_slot = (uint32_t)h;
-        conv = !pay_is_list(atomicOr(&a.table[h].pay, PAY_MULTI));
-        later = true;
-        break;
-      }
-      h = geom_next(a.geom, h);
-      cur = ld_key(a.table + h);
-    }
-  }
-  // overflow list entries of the warp: one allocation
-  const unsigned lm = __ballot_sync(FULL, later), cm = __ballot_sync(FULL, conv);
-  if (lm) {
-    uint32_t base = 0, mbase = 0;
-    if (l == 0) {
-      base = atomicAdd(&a.ctr->n_ovf, (unsigned)__popc(lm));
-      if (cm) mbase = atomicAdd(&a.ctr->n_multi, (unsigned)__popc(cm));
-    }
-    base = __shfl_sync(FULL, base, 0);
-    mbase = __shfl_sync(FULL, mbase, 0);
-    const unsigned below = (1u << l) - 1;
-    if (later) { const uint32_t w = base + __popc(lm & below); a.ovf_slot[w] = my_slot; a.ovf_occ[w] = my_occ; }
-    if (conv) a.multi_list[mbase + __popc(cm & below)] = my_slot;
-  }
-  const uint32_t nv = __popc(__ballot_sync(FULL, valid && mine)), nc = __popc(__ballot_sync(FULL, claimed));
-  if (l == 0) {
-    if (nv) atomicAdd(&a.ctr->n_inserts, (unsigned long long)nv);
-    if (nc) atomicAdd(&a.ctr->n_distinct, (unsigned long long)nc);
-  }
+  if (!valid) return false;
+  const uint32_t pv = o > 0 && !prev_n;   // the window one base earlier holds an N: it is not in the table, a run starts here
+  const uint32_t pb = l ? (uint32_t)(W0 >> (2 * (l - 1))) & 3u : (pv ? (uint32_t)(a.fwd[(p0 >> 5) - 1] >> 62) & 3u : 0u);
+  occ = occ_pack(s, (uint32_t)o, pv, pb);
+  hk = hash_key(key);
+  const uint32_t slice = geom_slice(a.geom, hk);
+  return slice >= a.slice_lo && slice < a.slice_hi;   // (a sharded build only takes the k-mers of this rank's slices)
 }
 
 // block-wide exclusive scan helper + exclusive scan of a uint32 array (per-query-strand run counts), 3 phases
@@ -341,6 +300,131 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_apply(const uint32_t 
   for (int i = 0; i < SCAN_PER_THREAD; i++) {
     if (base + i < n) out[base + i] = ex;
     ex += c[i];
+  }
+}
+
+/*
+ * The insert (Hash_Insert's chained bucket, Build_Hash_Index.C:296-350, appears as: slot = k-mer, list = chain).  Per probe: a
+ * plain load of the key (a load that misses is much cheaper than an atomic that misses), then one 8-byte CAS;
+ *   - the slot was free: the window owns the k-mer and ORs its occurrence word into the payload (first occurrence of a k-mer:
+ *     ~90 % of the windows of a 1x block never need anything else);
+ *   - the key is already there: the window ORs the list mark into the payload and appends {slot, occurrence} to the overflow
+ *     list; the arrival that finds the mark clear also queues the slot for the list kernels.
+ * Both payload updates are ORs into disjoint bits, so they commute: no arrival waits for another, and the result does not
+ * depend on the order of the windows.
+ *
+ * INS_R windows per thread, INS_THREADS threads per block: the block's appends to the overflow list / the list-of-lists and its
+ * contributions to the two counters are aggregated in shared memory, so a block does FOUR atomics on the context's counters
+ * (one atomic per warp on those few addresses -- 10 M same-line atomics for a 100 Mbp block -- serialise in one L2 slice).
+ *
+ * FROM_RECS = false: the windows are taken straight from the stream (one warp per 32-base word).  FROM_RECS = true: from a
+ * compacted record array (k_compact_windows) -- the sharded build of a GPU group, where a rank owns 1/N of the windows and
+ * would otherwise run warps with 1/N of their lanes busy: the insert is a chain of dependent memory operations per warp, so
+ * its time follows the number of WARPS, not of inserts (measured: half the inserts in 81 % of the time).
+ *
+ * Measured and dropped in round 2: ordering the records by table region so that the lines being filled stay in L2 (256
+ * partitions, contiguous or hashed by line).  DRAM traffic fell as planned, the insert time did not (7.1 ms either way): what
+ * bounds it on this GPU is the ~200 M 64-bit atomics themselves, not where their lines come from.
+ */
+struct PartRec { unsigned long long key, occ; };
+constexpr int INS_THREADS = 256, INS_R = 4, INS_TILE = INS_THREADS * INS_R;
+
+// the windows a rank owns, packed: block-aggregated append of {key, occurrence} records (one atomic per block)
+__global__ void __launch_bounds__(INS_THREADS) k_compact_windows(BuildArgs a, PartRec *recs, uint32_t *n_recs) {
+  __shared__ uint32_t s_cnt[INS_THREADS / 32], s_base;
+  const int l = lane_id(), w = threadIdx.x >> 5;
+  unsigned long long key[INS_R], occ[INS_R];
+  uint32_t have = 0, n = 0;
+#pragma unroll
+  for (int r = 0; r < INS_R; r++) {
+    const uint64_t gw = ((uint64_t)blockIdx.x * INS_TILE + (uint64_t)r * INS_THREADS + threadIdx.x) >> 5;
+    uint64_t hk;
+    if (gw < a.region_words && block_window(a, gw, l, key[r], occ[r], hk)) { have |= 1u << r; n++; }
+  }
+  const uint32_t incl = warp_incl_scan(n);
+  if (l == 31) s_cnt[w] = incl;
+  __syncthreads();
+  uint32_t off = incl - n;
+  for (int ww = 0; ww < w; ww++) off += s_cnt[ww];
+  if (threadIdx.x == INS_THREADS - 1) s_base = (off + n) ? atomicAdd(n_recs, off + n) : 0;
+  __syncthreads();
+  uint32_t wpos = s_base + off;
+#pragma unroll
+  for (int r = 0; r < INS_R; r++)
+    if ((have >> r) & 1) recs[wpos++] = PartRec{key[r], occ[r]};
+}
+
+template <bool FROM_RECS>
+__global__ void __launch_bounds__(INS_THREADS) k_insert(BuildArgs a, const PartRec *__restrict__ recs, const uint32_t *__restrict__ n_recs_p) {
+  __shared__ uint32_t s_later[INS_THREADS / 32], s_conv[INS_THREADS / 32], s_base[2], s_tot[4];
+  const uint32_t n_recs = FROM_RECS ? *n_recs_p : 0u;
+  const int l = lane_id(), w = threadIdx.x >> 5;
+  unsigned long long occ_l[INS_R];
+  uint32_t slot_l[INS_R];
+  uint32_t n_later = 0, n_conv = 0, conv_mask = 0, later_mask = 0, n_valid = 0, n_claimed = 0;
+#pragma unroll
+  for (int r = 0; r < INS_R; r++) {
+    const uint64_t i = (uint64_t)blockIdx.x * INS_TILE + (uint64_t)r * INS_THREADS + threadIdx.x;
+    unsigned long long key, my_occ;
+    uint64_t hk;
+    if constexpr (FROM_RECS) {
+      if (i >= n_recs) continue;
+      const uint4 rv = __ldcs(reinterpret_cast<const uint4 *>(recs + i));   // read once
+      key = ((unsigned long long)rv.y << 32) | rv.x;
+      my_occ = ((unsigned long long)rv.w << 32) | rv.z;
+      hk = hash_key(key);
+    } else {
+      if ((i >> 5) >= a.region_words || !block_window(a, i >> 5, l, key, my_occ, hk)) continue;
+    }
+    n_valid++;
+    uint64_t h = geom_home(a.geom, hk);
+    unsigned long long cur = ld_key(a.table + h);
+    while (true) {
+      if (cur == EMPTY_KEY) cur = atomicCAS(&a.table[h].key, EMPTY_KEY, key);
+      if (cur == EMPTY_KEY) {
+        if (my_occ) atomicOr(&a.table[h].pay, my_occ);
+        n_claimed++;
+        break;
+      }
+      if (cur == key) {
+        if (!pay_is_list(atomicOr(&a.table[h].pay, PAY_MULTI))) { conv_mask |= 1u << r; n_conv++; }
+        slot_l[r] = (uint32_t)h;
+        occ_l[r] = my_occ;
+        later_mask |= 1u << r;
+        n_later++;
+        break;
+      }
+      h = geom_next(a.geom, h);
+      cur = ld_key(a.table + h);
+    }
+  }
+  // block-wide exclusive ranks of this thread's list entries: warp scan, then the warp totals through shared memory
+  const uint32_t il = warp_incl_scan(n_later), ic = warp_incl_scan(n_conv);
+  if (l == 31) { s_later[w] = il; s_conv[w] = ic; }
+  const uint32_t bv = warp_sum(n_valid), bc = warp_sum(n_claimed);
+  if (threadIdx.x < 4) s_tot[threadIdx.x] = 0;
+  __syncthreads();
+  if (l == 0) { if (bv) atomicAdd(&s_tot[0], bv); if (bc) atomicAdd(&s_tot[1], bc); }
+  uint32_t off_l = il - n_later, off_c = ic - n_conv;
+  for (int ww = 0; ww < w; ww++) { off_l += s_later[ww]; off_c += s_conv[ww]; }
+  __syncthreads();
+  if (threadIdx.x == INS_THREADS - 1) {
+    const uint32_t tl = off_l + n_later, tc = off_c + n_conv;
+    s_base[0] = tl ? atomicAdd(&a.ctr->n_ovf, tl) : 0;
+    s_base[1] = tc ? atomicAdd(&a.ctr->n_multi, tc) : 0;
+    if (s_tot[0]) atomicAdd(&a.ctr->n_inserts, (unsigned long long)s_tot[0]);
+    if (s_tot[1]) atomicAdd(&a.ctr->n_distinct, (unsigned long long)s_tot[1]);
+  }
+  __syncthreads();
+  uint32_t wl = s_base[0] + off_l, wc = s_base[1] + off_c;
+#pragma unroll
+  for (int r = 0; r < INS_R; r++) {
+    if ((later_mask >> r) & 1) {
+      a.ovf_slot[wl] = slot_l[r];
+      a.ovf_occ[wl] = occ_l[r];
+      wl++;
+      if ((conv_mask >> r) & 1) a.multi_list[wc++] = slot_l[r];
+    }
   }
 }
 
@@ -527,8 +611,8 @@ __global__ void k_first_occ(const Slot *__restrict__ table, uint64_t n_slots, co
 }
 
 // Bloom filter of the finished slices [slot_lo, slot_hi): one thread per slot, coalesced read of the table, one reduction per
-// k-mer into the filter.  Run on its own (not from inside k_insert, where the table lines stream through L2 and every filter
-// update missed it: measured 27 ms instead of 10 for the build) the 64 MB filter stays L2-resident while it is filled.
+// k-mer into the filter.  On its own (not from inside the insert, where the filter competes with the table lines for L2) the
+// 64 MB filter stays L2-resident while it is filled.
 __global__ void __launch_bounds__(256) k_filter_build(const Slot *__restrict__ table, uint64_t slot_lo, uint64_t slot_hi, TableGeom geom,
                                                       uint32_t *filter) {
   const uint64_t i = slot_lo + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -40,6 +40,8 @@ struct ScanArgs {
   const int64_t *rd_pos;
   const uint32_t *rd_len;
   const uint32_t *qs_read;        // per query in batch: read index, or 0xffffffff if the read is skipped
+  const uint32_t *q_order;        // queries of the batch, longest first: the order the warps take them in (the scan of a strand is one
+                                  // serial chain of dependent loads, so a long strand started last would be the tail of the kernel)
   uint32_t n_queries;             // reads in the batch (strands = 2x)
   uint32_t first_id;              // read ID of read index 0
   uint32_t hash_bgn_id;           // read ID of string 0
@@ -62,16 +64,20 @@ struct ScanArgs {
 
 constexpr int SCAN_WARPS = 4;
 
+// resident blocks per SM the register allocation aims at.  The scan is a chain of dependent loads per warp (filter word -> table
+// line -> occurrence list), so throughput comes from resident warps: measured on B200 (c3 job) 1 (69 registers, 28 warps per SM)
+// 5.47 ms, 8 (56 registers) 4.52 ms, 10 (48) 4.28 ms, 12 (40 registers, 16 bytes of spills, 48 warps) 4.02 ms.
 #ifndef OIC_SCAN_BLOCKS
-#define OIC_SCAN_BLOCKS 1
+#define OIC_SCAN_BLOCKS 12
 #endif
 __global__ void __launch_bounds__(SCAN_WARPS * 32, OIC_SCAN_BLOCKS) k_seed_scan(ScanArgs a) {
   __shared__ uint32_t s_pref[SCAN_WARPS][33];
   __shared__ unsigned long long s_pay[SCAN_WARPS][32];
   const int wib = threadIdx.x >> 5, l = lane_id();
-  const uint32_t qs = blockIdx.x * SCAN_WARPS + wib;
-  if (qs >= 2 * a.n_queries) return;
-  const uint32_t q = qs >> 1, strand = qs & 1;
+  const uint32_t slot = blockIdx.x * SCAN_WARPS + wib;
+  if (slot >= 2 * a.n_queries) return;
+  const uint32_t q = a.q_order[slot >> 1], strand = slot & 1;
+  const uint32_t qs = 2 * q + strand;
   const uint32_t ri = a.qs_read[q];
   if (l == 0) { a.qs_first_chunk[qs] = NO_CHUNK; a.qs_nrec[qs] = 0; a.qs_screen[qs] = 0; }
   if (ri == 0xffffffffu) return;

@@ -252,7 +252,7 @@ def test_ovlstore_sort_vs_numpy_restatement():
     for max_evalue in (4095, 1000):
         got, counts, ms = ovl.ovlstore_sort(rec, length, skip_dup, library, max_evalue)
         want = mirror_filter_sort(rec, length, skip_dup, library, max_evalue)
-        assert len(got) == len(want) > n
+        assert len(got) == len(want) > n // 2
         assert np.array_equal(got, want)
         assert counts[0] == 0 and (counts[1] > 0) == (max_evalue < 1499)
     # an ID out of range is fatal, as in the reference (ST/ovStoreBuild.C:594-603)
