@@ -23,8 +23,12 @@ ABI_SYMBOLS = [
     "oic_hash_block_reserve", "oic_hash_block_buffers", "oic_hash_block_commit", "oic_dump_index", "oic_set_debug",
     "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
     "oic_copy_kmer_histogram", "oic_comm_unique_id", "oic_comm_init_rank", "oic_comm_init_all", "oic_comm_info",
-    "oic_hash_block_replicate", "oic_build_hash_index_sharded", "oic_ovlstore_sort",
+    "oic_hash_block_replicate", "oic_build_hash_index_sharded", "oic_ovlstore_sort", "oic_ovlstore_sort_noalloc",
+    "oic_ovlstore_sort_noalloc_max",
 ]
+
+# status codes of include/oic_b200.h
+OIC_OK, OIC_ERR_CUDA, OIC_ERR_ARG, OIC_ERR_UNSUPPORTED, OIC_ERR_BASES, OIC_ERR_CAPACITY, OIC_ERR_STATE = 0, -1, -2, -3, -4, -5, -6
 
 
 class OicError(RuntimeError):
@@ -119,6 +123,10 @@ def load_library():
     lib.oic_hash_block_replicate.argtypes = [vp, vp, C.c_int]
     lib.oic_build_hash_index_sharded.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
     lib.oic_ovlstore_sort.argtypes = [vp, vp, C.c_uint64, C.c_uint32, vp, vp, vp, C.c_uint32, vp, C.POINTER(C.c_uint64), vp, C.POINTER(C.c_double)]
+    # allocation-free variant of the store sort: DEVICE pointers in and out, scratch in a static __device__ array of the library
+    lib.oic_ovlstore_sort_noalloc.argtypes = [C.c_int, vp, C.c_uint64, C.c_uint32, vp, vp, vp, C.c_uint32, vp, C.POINTER(C.c_uint64), vp]
+    lib.oic_ovlstore_sort_noalloc_max.restype = C.c_uint64
+    lib.oic_ovlstore_sort_noalloc_max.argtypes = []
     lib.oic_dump_index.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp, vp, vp]
     lib.oic_set_debug.argtypes = [vp, C.c_uint32]
     lib.oic_dump_pairs.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), vp, vp]

@@ -1720,6 +1720,116 @@ int oic_ovlstore_sort(oic_ctx_t *c, const oic_ovb_record_t *recs, uint64_t n, ui
   return OIC_OK;
 }
 
+/* ---- allocation-free variant of oic_ovlstore_sort (no counterpart in the reference)
+ * All intermediate buffers of the sort in one static device array.  Layout (bytes, every piece 256-aligned), for at most
+ * NOALLOC_MAX_N input overlaps = NOALLOC_MAX_M mirrored records:
+ *   counters 256 | mirrored records M x 24 | keys[2] M x 8 each | idx[2] M x 4 each | digit histogram + its scan 2 x 256 x blocks x 4 | block sums 256 */
+constexpr uint64_t NOALLOC_MAX_N = 65536, NOALLOC_MAX_M = 2 * NOALLOC_MAX_N;
+constexpr uint64_t NOALLOC_MAX_NB = (NOALLOC_MAX_M + RADIX_TILE - 1) / RADIX_TILE;
+constexpr size_t NA_OFF_CNT = 0;
+constexpr size_t NA_OFF_MIR = NA_OFF_CNT + 256;
+constexpr size_t NA_OFF_KEY0 = NA_OFF_MIR + NOALLOC_MAX_M * sizeof(StoreRec);
+constexpr size_t NA_OFF_KEY1 = NA_OFF_KEY0 + NOALLOC_MAX_M * 8;
+constexpr size_t NA_OFF_IDX0 = NA_OFF_KEY1 + NOALLOC_MAX_M * 8;
+constexpr size_t NA_OFF_IDX1 = NA_OFF_IDX0 + NOALLOC_MAX_M * 4;
+constexpr size_t NA_OFF_HIST = NA_OFF_IDX1 + NOALLOC_MAX_M * 4;
+constexpr size_t NA_OFF_BLK = NA_OFF_HIST + 2 * 256 * NOALLOC_MAX_NB * 4;
+constexpr size_t NOALLOC_BYTES = NA_OFF_BLK + 256;
+static_assert(NOALLOC_BYTES == 6357504, "the size stated in include/oic_b200.h, DESIGN.md and INTEGRATION.md");
+static_assert(NA_OFF_MIR % 256 == 0 && NA_OFF_KEY0 % 256 == 0 && NA_OFF_KEY1 % 256 == 0 && NA_OFF_IDX0 % 256 == 0 && NA_OFF_IDX1 % 256 == 0 &&
+              NA_OFF_HIST % 256 == 0 && NA_OFF_BLK % 256 == 0, "every piece of the scratch is 256-byte aligned");
+static_assert((256 * NOALLOC_MAX_NB + SCAN_ITEMS - 1) / SCAN_ITEMS + 2 <= 64, "block sums fit their 256 bytes");
+
+// In HOST code this name is a host-side stand-in, not a device address: a kernel given it faults (or, where the GPU can reach
+// host memory, silently uses the wrong memory).  Host code takes the address from cudaGetSymbolAddress, per device (below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+static std::mutex g_noalloc_mutex;
+static unsigned char *g_noalloc_ptr[64];   // device address of g_noalloc_scratch on device i (nullptr: not looked up yet)
+
+uint64_t oic_ovlstore_sort_noalloc_max(void) { return NOALLOC_MAX_N; }
+
+int oic_ovlstore_sort_noalloc(int device, const oic_ovb_record_t *d_recs, uint64_t n, uint32_t max_id, const uint32_t *d_read_len,
+                              const uint8_t *d_skip_dup, const uint8_t *d_library, uint32_t max_evalue, oic_ovb_record_t *d_sorted,
+                              uint64_t *n_sorted, uint64_t counts[9]) {
+  auto fail = [](int code, const char *fmt, auto... args) {
+    char buf[512];
+    snprintf(buf, sizeof(buf), fmt, args...);
+    g_create_error = buf;   // read back with oic_last_error(NULL) on this thread
+    return code;
+  };
+  if (n_sorted) *n_sorted = 0;
+  if (counts) memset(counts, 0, 9 * sizeof(uint64_t));
+  if (n > NOALLOC_MAX_N)
+    return fail(OIC_ERR_CAPACITY, "oic_ovlstore_sort_noalloc: %llu overlaps exceed the static scratch (at most %llu per call: split the input or use oic_ovlstore_sort)",
+                (unsigned long long)n, (unsigned long long)NOALLOC_MAX_N);
+  if (device < 0 || device >= 64 || max_id == 0 || !d_read_len || !d_skip_dup || !d_library || (n && (!d_recs || !d_sorted)))
+    return fail(OIC_ERR_ARG, "oic_ovlstore_sort_noalloc: bad argument");
+  if (n == 0) return OIC_OK;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return fail(OIC_ERR_CUDA, "oic_ovlstore_sort_noalloc: cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  unsigned char *base = nullptr;
+  {   // set-up, once per device, with that device current
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+      void *p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (e != cudaSuccess || !p) return fail(OIC_ERR_CUDA, "oic_ovlstore_sort_noalloc: cudaGetSymbolAddress on device %d: %s", device, cudaGetErrorString(e));
+      g_noalloc_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    base = g_noalloc_ptr[device];
+  }
+#define NK_CUDA(call)                                                                                                     \
+  do {                                                                                                                    \
+    cudaError_t e_ = (call);                                                                                              \
+    if (e_ != cudaSuccess) return fail(OIC_ERR_CUDA, "oic_ovlstore_sort_noalloc: %s: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+  unsigned long long *cnt = reinterpret_cast<unsigned long long *>(base + NA_OFF_CNT);
+  StoreRec *mir = reinterpret_cast<StoreRec *>(base + NA_OFF_MIR);
+  unsigned long long *keys[2] = {reinterpret_cast<unsigned long long *>(base + NA_OFF_KEY0), reinterpret_cast<unsigned long long *>(base + NA_OFF_KEY1)};
+  uint32_t *idx[2] = {reinterpret_cast<uint32_t *>(base + NA_OFF_IDX0), reinterpret_cast<uint32_t *>(base + NA_OFF_IDX1)};
+  uint32_t *hist = reinterpret_cast<uint32_t *>(base + NA_OFF_HIST), *blk = reinterpret_cast<uint32_t *>(base + NA_OFF_BLK);
+  const cudaStream_t st = 0;   // legacy default stream: creating a stream would allocate
+  // the array keeps the last call's contents: the counters must start at zero, everything else is written before it is read
+  NK_CUDA(cudaMemsetAsync(cnt, 0, 256, st));
+  MirrorArgs ma;
+  ma.in = reinterpret_cast<const StoreRec *>(d_recs); ma.n = n; ma.max_id = max_id; ma.rd_len = d_read_len; ma.skip_dup = d_skip_dup;
+  ma.lib = d_library; ma.max_evalue = max_evalue; ma.out = mir; ma.n_out = cnt + 15; ma.counts = cnt;
+  k_store_mirror<<<nblocks(n, 256), 256, 0, st>>>(ma);
+  unsigned long long hcnt[16];
+  NK_CUDA(cudaMemcpyAsync(hcnt, cnt, sizeof(hcnt), cudaMemcpyDeviceToHost, st));
+  NK_CUDA(cudaStreamSynchronize(st));
+  NK_CUDA(cudaGetLastError());
+  if (counts) for (int i = 0; i < 9; i++) counts[i] = hcnt[i];
+  const uint64_t m = hcnt[15];
+  if (hcnt[0]) return fail(OIC_ERR_ARG, "oic_ovlstore_sort_noalloc: %llu overlaps have IDs out of range (maxID %u), possibly corrupt input data", hcnt[0], max_id);
+  if (m > NOALLOC_MAX_M) return fail(OIC_ERR_STATE, "oic_ovlstore_sort_noalloc: internal: %llu records from %llu overlaps", (unsigned long long)m, (unsigned long long)n);
+  if (m) {
+    const uint32_t nb = nblocks(m, RADIX_TILE);
+    const uint64_t hn = (uint64_t)256 * nb, hb = (hn + SCAN_ITEMS - 1) / SCAN_ITEMS;
+    k_store_keys<<<nblocks(m, 256), 256, 0, st>>>(mir, m, keys[0], idx[0]);
+    int id_bits = 1;
+    while ((1ull << id_bits) < max_id) id_bits++;
+    int cur = 0;
+    for (int half = 0; half < 2; half++)                       // b_iid digits first (low word), then a_iid
+      for (int shift = 32 * half; shift < 32 * half + id_bits; shift += 8) {
+        k_radix_hist<<<nb, RADIX_THREADS, 0, st>>>(keys[cur], m, shift, hist, nb);
+        k_scan_u32_reduce<<<(unsigned)hb, SCAN_THREADS, 0, st>>>(hist, hn, blk);
+        k_scan_u32_single<<<1, SCAN_THREADS, 0, st>>>(blk, (uint32_t)hb);
+        k_scan_u32_apply<<<(unsigned)hb, SCAN_THREADS, 0, st>>>(hist, hist + hn, hn, blk);
+        k_radix_scatter<<<nb, RADIX_THREADS, 0, st>>>(keys[cur], idx[cur], m, shift, hist + hn, nb, keys[cur ^ 1], idx[cur ^ 1]);
+        cur ^= 1;
+      }
+    k_store_tiefix<<<nblocks(m, 256), 256, 0, st>>>(keys[cur], idx[cur], mir, m);
+    k_store_gather<<<nblocks(m, 256), 256, 0, st>>>(mir, idx[cur], m, reinterpret_cast<StoreRec *>(d_sorted));   // straight into the caller's buffer
+    NK_CUDA(cudaStreamSynchronize(st));
+    NK_CUDA(cudaGetLastError());
+  }
+#undef NK_CUDA
+  if (n_sorted) *n_sorted = m;
+  return OIC_OK;
+}
+
 /* Measured INT32 issue rates of this GPU in Gop/s (thread operations): alu = LOP3/IADD3 chains, imad = IMAD chains. */
 int oic_measure_int32_peak(int device, double *alu_gops, double *imad_gops) {
   if (cudaSetDevice(device) != cudaSuccess) return OIC_ERR_CUDA;

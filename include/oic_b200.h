@@ -239,6 +239,30 @@ int oic_ovlstore_sort(oic_ctx_t *ctx, const oic_ovb_record_t *recs, uint64_t n, 
                       const uint8_t *skip_dup, const uint8_t *library, uint32_t max_evalue, oic_ovb_record_t *sorted,
                       uint64_t *n_sorted, uint64_t counts[9], double *device_ms);
 
+/* ---- allocation-free variant of oic_ovlstore_sort ---------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same filter + mirror + sort, same kernels and
+ * bit-identical output as oic_ovlstore_sort, but every intermediate buffer (mirrored records, two key and two index arrays of
+ * the radix sort, digit histograms, counters) lives in ONE file-scope `static __device__` array of the library, and the call
+ * makes no cudaMalloc / cudaFree and uses no allocating library routine.  It needs no context.
+ *
+ * Limit: at most oic_ovlstore_sort_noalloc_max() = 65 536 input overlaps per call (131 072 store records).  The array is
+ * 6 357 504 bytes (6.06 MiB) and every GPU that loads the library holds it until the process exits.  A larger n is refused with
+ * OIC_ERR_CAPACITY before anything runs (split the input by a_iid range, or use oic_ovlstore_sort).
+ *
+ * d_recs / d_read_len / d_skip_dup / d_library / d_sorted are DEVICE pointers on `device`, owned by the caller, with the
+ * meaning and sizes of the host arrays of oic_ovlstore_sort (d_sorted holds 2 n records).  n_sorted and counts[9] (may be NULL)
+ * are HOST pointers.  Work is issued on the legacy default stream of `device`; the call returns after the result is complete.
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress, once per device).
+ *
+ * Every call shares the array, which keeps the last call's contents (the counters are cleared at the start of each call;
+ * nothing else is read before it is written).  Calls that overlap on the GPU -- from two threads, or two processes' worth of
+ * streams on one device -- RACE on it: serialise them. */
+uint64_t oic_ovlstore_sort_noalloc_max(void);
+int oic_ovlstore_sort_noalloc(int device, const oic_ovb_record_t *d_recs, uint64_t n, uint32_t max_id, const uint32_t *d_read_len,
+                              const uint8_t *d_skip_dup, const uint8_t *d_library, uint32_t max_evalue, oic_ovb_record_t *d_sorted,
+                              uint64_t *n_sorted, uint64_t counts[9]);
+
 /* Roofline denominator of the extension stage: INT32 issue rates of `device`, measured (thread Gop/s).  alu = chains of
  * LOP3 + IADD3 (the pipe the edit-distance rows live on; reference code measured against: LIBO/prefixEditDistance-forward.C
  * inner loop), imad = chains of IMAD.  Takes a few milliseconds. */
