@@ -478,6 +478,8 @@ def main():
 
     def ncu_of(name):
         k = ncu_k.get(name)
+        if not k:   # template instances: "k_insert" finds "k_insert<0>"
+            k = next((v for n, v in sorted(ncu_k.items()) if n.startswith(name + "<")), None)
         if not k:
             return None
         return {x: k.get(x) for x in ("ms", "dram_bytes_per_launch", "dram_GBps", "issue_active_pct", "alu_pipe_pct", "lsu_pipe_pct",

@@ -5,7 +5,7 @@ set -u
 TAG=$1
 OUT=gpurun_out
 mkdir -p $OUT
-python bench.py --steps 5 --warmup 3 --no-cpu > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err || { tail -30 $OUT/bench_$TAG.err; exit 2; }
+python bench.py --steps 5 --warmup 3 --no-cpu > $OUT/bench_${TAG}_nocpu.json 2> $OUT/bench_${TAG}_nocpu.err || { tail -30 $OUT/bench_${TAG}_nocpu.err; exit 2; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_$TAG.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu > $OUT/ncu_launches_$TAG.log 2>&1 || { tail -5 $OUT/ncu_launches_$TAG.log; exit 3; }
 ncu --set full --clock-control none --import-source on -k regex:'k_insert|k_filter_build|k_seed_scan|k_process_pairs|k_extend_tasks|k_commit_pairs|k_table_init' \
