@@ -154,6 +154,7 @@ struct oic_ctx {
 
   // search buffers
   DevBuf d_q_order;
+  DevBuf d_strand;              // -l path: per-pair ordering scratch (k_process_strands)
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
       d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool, d_wide;
   DevBuf d_ctr, d_flag;
@@ -680,7 +681,6 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   if (!p || !out) { g_create_error = "null argument"; return OIC_ERR_ARG; }
   *out = nullptr;
   if (p->kmer_len < 2 || p->kmer_len > 31) { g_create_error = "k-mer length must be 2..31 in this build"; return OIC_ERR_UNSUPPORTED; }
-  if (p->frag_olap_limit != UINT64_MAX) { g_create_error = "-l (per-end overlap limit) is not supported in this build"; return OIC_ERR_UNSUPPORTED; }
   if (!(p->max_erate > 0.0) || p->max_erate >= 1.0) { g_create_error = "bad --maxerate"; return OIC_ERR_ARG; }
   if (p->max_hash_strings == 0 || p->num_threads == 0) { g_create_error = "bad --hashstrings / -t"; return OIC_ERR_ARG; }
   int ndev = 0;
@@ -726,7 +726,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read, &c->d_strand};
   if (c->comm && nccl_api()) nccl_api()->CommDestroy(c->comm);
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -921,6 +921,35 @@ int ensure_pair_scratch(oic_ctx *c, unsigned n_warps, unsigned long long rowcap)
   CK(c->d_vals.ensure((size_t)n_warps * rowcap * 4));
   CK(c->d_rowmeta.ensure((size_t)n_warps * c->max_rows * sizeof(int4)));
   CK(c->d_deltas.ensure((size_t)n_warps * (4ull * c->max_rows + 8) * 4));
+  return 0;
+}
+
+// The -l path of the pair stage (oic_extend.cuh k_process_strands): one warp per query strand walks its partners in the
+// reference's order.  A partner cannot be deferred to a retry pass (the next one depends on it), so every warp gets worst-case
+// edit-row scratch and the grid is sized by what that costs.
+int run_pairs_limited(oic_ctx *c, ExtArgs &ea, const Seed *runs, uint32_t n_pairs, unsigned long long vals_bytes, DevCounters &hc) {
+  const unsigned sms = (unsigned)c->sm_count;
+  const unsigned long long big = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
+  const unsigned grid2 = (unsigned)std::max<unsigned long long>(8, std::min<unsigned long long>(sms * 4, std::max<unsigned long long>(24ull << 30, vals_bytes) / 4 / big / EXT_WARPS));
+  if (ensure_pair_scratch(c, grid2 * EXT_WARPS, big)) return OIC_ERR_CUDA;
+  ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = big; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
+  ea.task_list = nullptr; ea.n_tasks = 0; ea.handoff = 0;
+  const size_t np = (size_t)n_pairs + 8;
+  CK(c->d_strand.ensure(np * 40));   // per pair: creation key + mean diagonal (8 bytes each), six 4-byte arrays
+  unsigned char *b = c->d_strand.as<unsigned char>();
+  StrandArgs st;
+  st.src = runs;
+  st.ckey = reinterpret_cast<unsigned long long *>(b);
+  st.mean = reinterpret_cast<double *>(b + np * 8);
+  uint32_t *w = reinterpret_cast<uint32_t *>(b + np * 16);
+  st.slot = w; st.rank = w + np; st.by_creation = w + 2 * np; st.order = w + 3 * np; st.strand_first = w + 4 * np; st.strand_n = w + 5 * np;
+  st.limit = c->P.frag_olap_limit;
+  k_strand_ranges<<<nblocks(n_pairs, 256), 256, 0, c->stream>>>(ea.pairs, n_pairs, st, ea.ctr);
+  k_process_strands<<<grid2, EXT_WARPS * 32, 0, c->stream>>>(ea, st);
+  c->tm.launches += 2;
+  if (read_counters(c, hc)) return OIC_ERR_CUDA;
+  CK(cudaGetLastError());
+  if (hc.n_retry) return c->fail(OIC_ERR_CAPACITY, "edit rows exceed worst-case scratch in the -l path (internal)");
   return 0;
 }
 
@@ -1123,6 +1152,10 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
+      if (P.frag_olap_limit != UINT64_MAX) {   // -l: partners of a strand depend on each other -> serial walk per strand
+        const int rl = run_pairs_limited(c, ea, rp.src, n_pairs, vals_bytes, hc);
+        if (rl) return rl;
+      } else {
       // speculative second round (oic_extend.cuh): state per pair, one result slot per seed, a pool for the delta lists
       unsigned long long dpool_cap = std::min<unsigned long long>(std::max<unsigned long long>(1ull << 28, avail * 15 / 100 / 4),
                                                                   (unsigned long long)n_runs * 512 + (16ull << 20));
@@ -1196,6 +1229,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       if (getenv("OIC_PHASE_CLOCKS"))
         fprintf(stderr, "[oic] pair stage: pairs %u | handed over %u | speculative tasks %u used %u | delta pool %llu of %llu | retried %u | wide tasks %u\n",
                 n_pairs, hc_first.n_pend, hc_first.n_spec_tasks, hc_first.n_spec_used, (unsigned long long)hc_first.dpool_used, dpool_cap, hc_first.n_retry, hc_first.n_wide_tasks);
+      }   // (default path)
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         size_t old = c->overlaps.size();

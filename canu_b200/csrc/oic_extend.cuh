@@ -261,7 +261,9 @@ __device__ __forceinline__ void accept_overlap(const ExtArgs &a, int kind, int s
 
 /* end of Process_Matches for one pair: merge / choose the distinct overlaps, write the records, bump the -s counters
  * (Process_String_Overlaps.C:540-600, Output.C).  Lane 0 only. */
-__device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct) {
+__device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct, int *a_inc = nullptr,
+                                              int *b_inc = nullptr) {
+  // a_inc / b_inc (-l only): overlaps output that reach the 5' / the 3' end of the query strand (Process_String_Overlaps.C:631-635)
   int overlaps_output = 0;
   if (distinct_ct > 0) {
     int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
@@ -281,6 +283,8 @@ __device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x
       }
       ob++;
       overlaps_output++;
+      if (a_inc && distinct[i].s_lo == 0) (*a_inc)++;
+      if (b_inc && distinct[i].s_hi >= x.s_len - 1) (*b_inc)++;
     }
     atomicAdd(&a.ctr->total_overlaps, (unsigned long long)overlaps_output);
   }
@@ -300,6 +304,137 @@ __device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x
  *   each, by k_extend_tasks, and k_commit_pairs then replays the loop over the stored results.  This removes the serial
  *   chain of a pair (up to ~100 extensions of the same 15 kb overlap) from the critical path of the stage.
  */
+constexpr int PP_DONE = 0, PP_OVERFLOW = 1, PP_HANDED = 2;
+
+/* Process_Matches for pair pi by one warp (filters, the extension loop, seed pruning, output).  LIMIT = false: the default path
+ * (a.handoff decides whether the pair is parked after its first extension).  LIMIT = true: the -l path (Process_String_Overlaps.C:
+ * 482-490): a_full / b_full say that the 5' / 3' end of the query strand already has its -l overlaps; a seed whose extension
+ * would add to a full end is not extended -- it only removes itself, because Kind_Of_Olap and the alignment bounds keep the
+ * values of the previous iteration (:415) and re-applying that alignment's pruning removes nothing new.  (With -G a skipped FIRST
+ * seed makes the reference read uninitialised bounds; here, as in the oracle, they are zero and nothing else is pruned.) */
+template <bool LIMIT>
+__device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, uint32_t pi, unsigned long long &ext_calls,
+                                            bool a_full, bool b_full, int &a_inc, int &b_inc) {
+  const int l = lane_id();
+  a_inc = b_inc = 0;
+  const Pair pr = a.pairs[pi];
+  const PairInfo inf = a.info[pi];
+  const PairCtx x = pair_ctx(a, pr);
+  Seed *seeds = a.seeds + pr.first;
+  int n = (int)pr.n;
+
+  // --minkmers filter: computeMinimumKmers (Process_String_Overlaps.C:75-86,725)
+  if (a.filter_by_kmer_count != 0) {
+    double ovl = (double)(inf.diag_end - inf.diag_bgn);
+    if (ovl < 0) ovl = -ovl;
+    unsigned long long expected = 0;
+    if (!(ovl < (double)a.K)) expected = (unsigned long long)(int)floor(OIC_DMUL(a.minkmer_factor, ovl - a.K + 1));
+    unsigned long long need = a.filter_by_kmer_count > expected ? a.filter_by_kmer_count : expected;
+    if (need > (unsigned long long)inf.diag_ct) {
+      if (l == 0) atomicAdd(&a.ctr->kmer_hits_skipped, 1ull);
+      return PP_DONE;
+    }
+  }
+  // hopeless check for a singleton seed far from both ends (Process_String_Overlaps.C:433-464)
+  if (a.use_hopeless && n == 1 && !a.partial) {
+    const Seed m = seeds[0];
+    const unsigned qsc = a.qs_screen[pr.qs], hsc = a.str_flags[pr.str];
+    bool hopeless = false;
+    const int s_head = m.start, t_head = m.offset;
+    if (s_head <= t_head) { if (s_head > HOPELESS_MATCH && !(qsc & 1)) hopeless = true; }
+    else { if (t_head > HOPELESS_MATCH && !(hsc & 1)) hopeless = true; }
+    const int s_tail = x.s_len - s_head - m.len + 1, t_tail = x.t_len - t_head - m.len + 1;
+    if (s_tail <= t_tail) { if (s_tail > HOPELESS_MATCH && !(qsc & 2)) hopeless = true; }
+    else { if (t_tail > HOPELESS_MATCH && !(hsc & 2)) hopeless = true; }
+    if (hopeless) {
+      if (l == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
+      return PP_DONE;
+    }
+  }
+
+  // a pair with an N in either read stays here for its whole loop: only this kernel's generic row loop knows the N masks
+  bool pair_n = false;
+  if (a.n_off) {
+    uint64_t acc = 0;
+    const int64_t sw = (x.sp >> 5) + (int64_t)a.n_off, tw = (x.tp >> 5) + (int64_t)a.n_off;
+    for (int w = l; w * 32 < x.s_len; w += 32) acc |= x.S[sw + w];
+    for (int w = l; w * 32 < x.t_len; w += 32) acc |= x.T[tw + w];
+    pair_n = __any_sync(FULL, acc != 0);
+  }
+
+  OlapInfo distinct[MAX_DISTINCT_OLAPS];
+  int distinct_ct = 0;
+  bool overflow = false, handed = false;
+  const unsigned long long snap_cells = ws.cells, snap_words = ws.words, snap_calls = ext_calls;
+  int kind = 0, s_lo = 0, s_hi = 0, t_lo = 0, t_hi = 0, errors = 0, dlen = 0;   // (LIMIT: a skipped seed sees the previous iteration's)
+
+  while (n > 0) {
+    const int li = longest_seed(seeds, nullptr, n);
+    const Seed lg = seeds[li];
+    bool skip = false;
+    if (LIMIT) {
+      const int a_hang = lg.start - lg.offset, b_hang = a_hang + x.s_len - x.t_len;
+      skip = (a_full && a_hang <= 0) || (b_full && b_hang <= 0);
+    }
+    if (!skip) {
+      ext_calls++;
+      kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi, errors, dlen);
+      if (kind < 0) { overflow = true; break; }
+      accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
+    }
+    if (inf.consistent) break;
+
+    // drop the extended seed and every seed that lies on this alignment (Process_String_Overlaps.C:514-531)
+    int newn = 0;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+      const int i = i0 + l;
+      bool keep = false;
+      Seed nd;
+      if (i < n) {
+        nd = seeds[i];
+        bool remove = (i == li) ||
+                      ((kind == 3 || a.partial) && s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= s_hi + SHIFT_SLACK &&
+                       lies_on_alignment(nd.start, nd.offset, s_lo, t_lo, ws.ldelta, dlen));
+        keep = !remove;
+      }
+      const unsigned km = __ballot_sync(FULL, keep);
+      __syncwarp();
+      if (keep) seeds[newn + __popc(km & ((1u << l) - 1))] = nd;
+      newn += __popc(km);
+      __syncwarp();
+    }
+    n = newn;
+    if (!LIMIT && a.handoff && n > 0 && !pair_n) { handed = true; break; }
+  }
+
+  if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
+    ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
+    return PP_OVERFLOW;
+  }
+  if (handed) {
+    // park the pair: its first extension is counted when (and if) k_commit_pairs finalises it
+    const unsigned long long cw = warp_sum64(ws.words - snap_words);
+    PairState *ps = a.pstate + pi;
+    if (l == 0) {
+      for (int i = 0; i < distinct_ct; i++) ps->distinct[i] = distinct[i];
+      ps->distinct_ct = distinct_ct;
+      ps->n_rem = (uint32_t)n;
+      ps->cells = ws.cells - snap_cells;
+      ps->words = cw;
+      a.pend_list[atomicAdd(&a.ctr->n_pend, 1u)] = pi;
+    }
+    uint32_t tb = 0;
+    if (l == 0) tb = atomicAdd(&a.ctr->n_spec_tasks, (unsigned)n);
+    tb = __shfl_sync(FULL, tb, 0);
+    for (int i = l; i < n; i += 32) a.tasks[tb + i] = make_uint2(pi, (uint32_t)i);
+    ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
+    return PP_HANDED;
+  }
+  if (l == 0) finalize_pair(a, x, distinct, distinct_ct, LIMIT ? &a_inc : nullptr, LIMIT ? &b_inc : nullptr);
+  if (LIMIT) { a_inc = __shfl_sync(FULL, a_inc, 0); b_inc = __shfl_sync(FULL, b_inc, 0); }
+  return PP_DONE;
+}
+
 __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) {
   const int l = lane_id();
   const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -316,115 +451,138 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
     ti = __shfl_sync(FULL, ti, 0);
     if (ti >= a.n_tasks) break;
     const uint32_t pi = a.task_list ? a.task_list[ti] : ti;
-    const Pair pr = a.pairs[pi];
-    const PairInfo inf = a.info[pi];
-    const PairCtx x = pair_ctx(a, pr);
-    Seed *seeds = a.seeds + pr.first;
-    int n = (int)pr.n;
+    int a_inc, b_inc;
+    if (process_pair<false>(a, ws, fs, pi, ext_calls, false, false, a_inc, b_inc) == PP_OVERFLOW && l == 0)
+      a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
+  }
 
-    // --minkmers filter: computeMinimumKmers (Process_String_Overlaps.C:75-86,725)
-    if (a.filter_by_kmer_count != 0) {
-      double ovl = (double)(inf.diag_end - inf.diag_bgn);
-      if (ovl < 0) ovl = -ovl;
-      unsigned long long expected = 0;
-      if (!(ovl < (double)a.K)) expected = (unsigned long long)(int)floor(OIC_DMUL(a.minkmer_factor, ovl - a.K + 1));
-      unsigned long long need = a.filter_by_kmer_count > expected ? a.filter_by_kmer_count : expected;
-      if (need > (unsigned long long)inf.diag_ct) {
-        if (l == 0) atomicAdd(&a.ctr->kmer_hits_skipped, 1ull);
-        continue;
+  unsigned long long c = warp_sum64(ws.cells), w = warp_sum64(ws.words);
+  if (l == 0) {
+    if (c) atomicAdd(&a.ctr->ext_cells, c);
+    if (w) atomicAdd(&a.ctr->ext_words, w);
+    if (ext_calls) atomicAdd(&a.ctr->ext_calls, ext_calls);
+  }
+}
+
+/* ---- the -l path: a per-end cap on the overlaps of a query strand (OIC/overlapInCore.C:345-347, Process_String_Overlaps.C:743-797)
+ * With -l the partners of a strand are no longer independent: whether a partner is processed at all, and which of its seeds
+ * are extended, depends on how many overlaps the partners BEFORE it have put on each end of the read.  So this path gives a
+ * strand to ONE warp, which walks the partners in the reference's order with the two counters in registers; the extensions of a
+ * partner run serially (process_pair<true>).  Strands are still independent of each other, which is where the parallelism is.
+ *
+ * The order (Process_String_Olaps): the String_Olap array is compacted in index order -- the 256 primary slots
+ * (StrNum ^ StrNum >> 8) & 255, first come first served, then the overflow nodes in creation order (Find_Overlaps.C:163-187) -- and,
+ * when there are more partners than the limit, sorted by mean diagonal with qsort(By_Diag_Sum): glibc's qsort is a merge sort,
+ * so partners on the same mean diagonal keep their array order (pinned against the reference binary on this image, glibc 2.39).
+ * Then: from diagonal zero upward while the 5' end has room, then from just below zero downward while the 3' end has room.
+ * Creation order of a strand's partners = arrival order of their first k-mer hit = (query offset ascending, hash string
+ * descending: the chain order of one k-mer's occurrences), read off the first run of every pair.
+ * Ranks are found by counting (O(partners^2 / 32) per strand): fine for the tens to hundreds of partners of a read, slow for a
+ * read with many thousands -- this is the -l path only, which the pipeline never takes. */
+struct StrandArgs {
+  const Seed *src;                    // runs in arrival order, grouped by pair (output of k_group_runs)
+  uint32_t *strand_first, *strand_n;  // per listed strand: its pair range (pairs of a strand are contiguous)
+  unsigned long long *ckey;           // [n_pairs] creation key
+  double *mean;                       // [n_pairs] mean diagonal
+  uint32_t *slot, *rank, *by_creation, *order;   // [n_pairs]
+  unsigned long long limit;           // G.Frag_Olap_Limit
+};
+
+__global__ void __launch_bounds__(256) k_strand_ranges(const Pair *__restrict__ pairs, uint32_t n_pairs, StrandArgs sa, DevCounters *ctr) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pairs) return;
+  const uint32_t qs = pairs[i].qs;
+  if (i > 0 && pairs[i - 1].qs == qs) return;
+  uint32_t n = 1;
+  while (i + n < n_pairs && pairs[i + n].qs == qs) n++;
+  const uint32_t w = atomicAdd(&ctr->n_strands, 1u);
+  sa.strand_first[w] = i;
+  sa.strand_n[w] = n;
+}
+
+__global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_strands(ExtArgs a, StrandArgs sa) {
+  const int l = lane_id();
+  const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  WarpScratch ws = warp_scratch(a, gw);
+  unsigned long long ext_calls = 0;
+  __shared__ int32_t s_rows[EXT_WARPS][2][SW + 4];
+  FastScratch fs;
+  fs.row0 = s_rows[threadIdx.x >> 5][0];
+  fs.row1 = s_rows[threadIdx.x >> 5][1];
+  const uint32_t n_strands = a.ctr->n_strands;
+
+  while (true) {
+    uint32_t si = 0;
+    if (l == 0) si = atomicAdd(&a.ctr->pair_cursor, 1u);
+    si = __shfl_sync(FULL, si, 0);
+    if (si >= n_strands) break;
+    const uint32_t p0 = sa.strand_first[si], np = sa.strand_n[si];
+    // mean diagonal and creation key of every partner
+    for (uint32_t i = l; i < np; i += 32) {
+      const Pair pr = a.pairs[p0 + i];
+      const Seed *runs = sa.src + pr.first;
+      long long sum = 0;                                   // sum of (hash offset - query offset) over the k-mer hits: exact
+      for (uint32_t j = 0; j < pr.n; j++) sum += (long long)(runs[j].offset - runs[j].start) * (long long)(runs[j].len - a.K + 1);
+      sa.mean[p0 + i] = OIC_DDIV((double)sum, (double)a.info[p0 + i].diag_ct);
+      sa.ckey[p0 + i] = ((unsigned long long)(uint32_t)runs[0].start << 32) | (0xffffffffu - pr.str);
+    }
+    __syncwarp();
+    for (uint32_t i = l; i < np; i += 32) {
+      const unsigned long long k = sa.ckey[p0 + i];
+      uint32_t r = 0;
+      for (uint32_t j = 0; j < np; j++) r += sa.ckey[p0 + j] < k;
+      sa.by_creation[p0 + r] = i;
+    }
+    __syncwarp();
+    if (l == 0) {   // String_Olap slots, in creation order
+      uint32_t used[8] = {0, 0, 0, 0, 0, 0, 0, 0}, n_over = 0;
+      for (uint32_t r = 0; r < np; r++) {
+        const uint32_t i = sa.by_creation[p0 + r], str = a.pairs[p0 + i].str, sub = (str ^ (str >> 8)) & 255u;
+        if (!((used[sub >> 5] >> (sub & 31)) & 1u)) { used[sub >> 5] |= 1u << (sub & 31); sa.slot[p0 + i] = sub; }
+        else sa.slot[p0 + i] = 256u + n_over++;
       }
     }
-    // hopeless check for a singleton seed far from both ends (Process_String_Overlaps.C:433-464)
-    if (a.use_hopeless && n == 1 && !a.partial) {
-      const Seed m = seeds[0];
-      const unsigned qsc = a.qs_screen[pr.qs], hsc = a.str_flags[pr.str];
-      bool hopeless = false;
-      const int s_head = m.start, t_head = m.offset;
-      if (s_head <= t_head) { if (s_head > HOPELESS_MATCH && !(qsc & 1)) hopeless = true; }
-      else { if (t_head > HOPELESS_MATCH && !(hsc & 1)) hopeless = true; }
-      const int s_tail = x.s_len - s_head - m.len + 1, t_tail = x.t_len - t_head - m.len + 1;
-      if (s_tail <= t_tail) { if (s_tail > HOPELESS_MATCH && !(qsc & 2)) hopeless = true; }
-      else { if (t_tail > HOPELESS_MATCH && !(hsc & 2)) hopeless = true; }
-      if (hopeless) {
-        if (l == 0) atomicAdd(&a.ctr->kmer_hits_without_olap, 1ull);
-        continue;
-      }
+    __syncwarp();
+    for (uint32_t i = l; i < np; i += 32) {   // position in the compacted array
+      const uint32_t k = sa.slot[p0 + i];
+      uint32_t r = 0;
+      for (uint32_t j = 0; j < np; j++) r += sa.slot[p0 + j] < k;
+      sa.rank[p0 + i] = r;
     }
-
-    // a pair with an N in either read stays here for its whole loop: only this kernel's generic row loop knows the N masks
-    bool pair_n = false;
-    if (a.n_off) {
-      uint64_t acc = 0;
-      const int64_t sw = (x.sp >> 5) + (int64_t)a.n_off, tw = (x.tp >> 5) + (int64_t)a.n_off;
-      for (int w = l; w * 32 < x.s_len; w += 32) acc |= x.S[sw + w];
-      for (int w = l; w * 32 < x.t_len; w += 32) acc |= x.T[tw + w];
-      pair_n = __any_sync(FULL, acc != 0);
-    }
-
-    OlapInfo distinct[MAX_DISTINCT_OLAPS];
-    int distinct_ct = 0;
-    bool overflow = false, handed = false;
-    const unsigned long long snap_cells = ws.cells, snap_words = ws.words, snap_calls = ext_calls;
-
-    while (n > 0) {
-      const int li = longest_seed(seeds, nullptr, n);
-      const Seed lg = seeds[li];
-      int s_lo, s_hi, t_lo, t_hi, errors, dlen;
-      ext_calls++;
-      const int kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi,
-                                        errors, dlen);
-      if (kind < 0) { overflow = true; break; }
-      accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
-      if (inf.consistent) break;
-
-      // drop the extended seed and every seed that lies on this alignment (Process_String_Overlaps.C:514-531)
-      int newn = 0;
-      for (int i0 = 0; i0 < n; i0 += 32) {
-        const int i = i0 + l;
-        bool keep = false;
-        Seed nd;
-        if (i < n) {
-          nd = seeds[i];
-          bool remove = (i == li) ||
-                        ((kind == 3 || a.partial) && s_lo - SHIFT_SLACK <= nd.start && nd.start + nd.len <= s_hi + SHIFT_SLACK &&
-                         lies_on_alignment(nd.start, nd.offset, s_lo, t_lo, ws.ldelta, dlen));
-          keep = !remove;
+    __syncwarp();
+    const bool all = (unsigned long long)np <= sa.limit;   // few partners: all of them, in array order (:722-741)
+    uint32_t n_neg = 0;
+    for (uint32_t i = l; i < np; i += 32) {
+      uint32_t r = sa.rank[p0 + i];
+      if (!all) {                                          // stable order by mean diagonal
+        const double m = sa.mean[p0 + i];
+        const uint32_t mine = r;
+        r = 0;
+        for (uint32_t j = 0; j < np; j++) {
+          const double mj = sa.mean[p0 + j];
+          r += (mj < m) || (mj == m && sa.rank[p0 + j] < mine);
         }
-        const unsigned km = __ballot_sync(FULL, keep);
-        __syncwarp();
-        if (keep) seeds[newn + __popc(km & ((1u << l) - 1))] = nd;
-        newn += __popc(km);
-        __syncwarp();
+        n_neg += m < 0.0;
       }
-      n = newn;
-      if (a.handoff && n > 0 && !pair_n) { handed = true; break; }
+      sa.order[p0 + r] = i;
     }
+    n_neg = warp_sum(n_neg);
+    __syncwarp();
 
-    if (overflow) {   // the retry pass redoes this pair from scratch: forget its partial work counters
-      ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
-      if (l == 0) a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
-      continue;
+    int A = 0, B = 0;
+    bool failed = false;
+    auto one = [&](uint32_t r) {
+      int a_inc, b_inc;
+      const uint32_t pi = p0 + sa.order[p0 + r];
+      if (process_pair<true>(a, ws, fs, pi, ext_calls, (unsigned long long)A >= sa.limit, (unsigned long long)B >= sa.limit, a_inc, b_inc) != PP_DONE) failed = true;
+      A += a_inc; B += b_inc;
+    };
+    if (all) for (uint32_t r = 0; r < np && !failed; r++) one(r);
+    else {
+      for (uint32_t r = n_neg; r < np && (unsigned long long)A < sa.limit && !failed; r++) one(r);
+      for (uint32_t r = n_neg; r > 0 && (unsigned long long)B < sa.limit && !failed; r--) one(r - 1);
     }
-    if (handed) {
-      // park the pair: its first extension is counted when (and if) k_commit_pairs finalises it
-      const unsigned long long cw = warp_sum64(ws.words - snap_words);
-      PairState *ps = a.pstate + pi;
-      if (l == 0) {
-        for (int i = 0; i < distinct_ct; i++) ps->distinct[i] = distinct[i];
-        ps->distinct_ct = distinct_ct;
-        ps->n_rem = (uint32_t)n;
-        ps->cells = ws.cells - snap_cells;
-        ps->words = cw;
-        a.pend_list[atomicAdd(&a.ctr->n_pend, 1u)] = pi;
-      }
-      uint32_t tb = 0;
-      if (l == 0) tb = atomicAdd(&a.ctr->n_spec_tasks, (unsigned)n);
-      tb = __shfl_sync(FULL, tb, 0);
-      for (int i = l; i < n; i += 32) a.tasks[tb + i] = make_uint2(pi, (uint32_t)i);
-      ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
-      continue;
-    }
-    if (l == 0) finalize_pair(a, x, distinct, distinct_ct);
+    if (failed && l == 0) atomicAdd(&a.ctr->n_retry, 1u);   // cannot happen with worst-case scratch; the host reports it
   }
 
   unsigned long long c = warp_sum64(ws.cells), w = warp_sum64(ws.words);

@@ -55,6 +55,7 @@ void usage(const char *argv0) {
   fprintf(stderr, "-G          do partial overlaps\n");
   fprintf(stderr, "-h <range>  to specify fragments to put in hash table\n");
   fprintf(stderr, "-H <range>  libraries to put in the hash table\n");
+  fprintf(stderr, "-l <n>      at most <n> overlaps off each end of a read (default: no limit)\n");
   fprintf(stderr, "-k          if one or two digits, the length of a kmer, otherwise\n");
   fprintf(stderr, "            the filename containing a list of kmers to ignore in the hash table\n");
   fprintf(stderr, "-m          allow multiple overlaps per oriented fragment pair\n");

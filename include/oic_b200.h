@@ -24,7 +24,7 @@ extern "C" {
 #define OIC_OK                0
 #define OIC_ERR_CUDA        (-1)   /* CUDA runtime error / no device                          */
 #define OIC_ERR_ARG         (-2)   /* bad argument                                            */
-#define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31, -l, -w ...)  */
+#define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31, -w ...)      */
 #define OIC_ERR_BASES       (-4)   /* a loaded read holds a letter other than ACGTN           */
 #define OIC_ERR_CAPACITY    (-5)   /* an internal device buffer could not be sized            */
 #define OIC_ERR_STATE       (-6)   /* call order violated (e.g. search before build)          */
@@ -42,7 +42,7 @@ typedef struct {
   double   hash_load;            /* --hashload        G.Max_Hash_Load                                 */
   uint32_t max_hash_strings;     /* --hashstrings     G.Max_Hash_Strings                              */
   uint64_t max_hash_data_len;    /* --hashdatalen     G.Max_Hash_Data_Len                             */
-  uint64_t frag_olap_limit;      /* -l                must be UINT64_MAX (unlimited) in this build    */
+  uint64_t frag_olap_limit;      /* -l                G.Frag_Olap_Limit (UINT64_MAX = unlimited)      */
   uint64_t filter_by_kmer_count; /* --minkmers        G.Filter_By_Kmer_Count (0 = off)                */
   uint32_t num_threads;          /* -t                only feeds the scheduler quirk (see driver)     */
   uint32_t bgn_hash_id, end_hash_id;  /* -h a-b                                                       */

@@ -608,7 +608,7 @@ void oracle_ctx::find_overlaps(const char *frag, int32_t frag_len, uint32_t frag
   memset(slot_used, 0, sizeof(slot_used));
   n_overflow = 0;
   left_end_screened = right_end_screened = false;
-  a_olaps_for_frag = b_olaps_for_frag = 0;
+  a_olaps_for_frag = b_olaps_for_frag = 0;   // Find_Overlaps.C:306-307
 
   // The scan is NUL-driven: the first K characters are taken unconditionally (:309-311), then `while (*P != 0)` (:341) stops
   // at the first NUL at index >= K.  Only the reverse strand can hold NULs (RC turns non-ACGT into NUL).
@@ -647,9 +647,10 @@ void oracle_ctx::find_overlaps(const char *frag, int32_t frag_len, uint32_t frag
   process_string_olaps(frag, frag_len, frag_num, dir);
 }
 
-// Process_String_Olaps: OIC/overlapInCore-Process_String_Overlaps.C:687-800 (default path; -l is not restated)
+// Process_String_Olaps: OIC/overlapInCore-Process_String_Overlaps.C:687-800, the -l path (:743-797) included
 void oracle_ctx::process_string_olaps(const char *S, int32_t len, uint32_t id, int dir) {
   if (pairs.empty()) return;
+  // compaction of String_Olap_Space (:701-718): array index order = the 256 primary slots, then the overflow nodes in creation order
   std::vector<uint32_t> order(pairs.size());
   for (uint32_t i = 0; i < pairs.size(); i++) order[i] = i;
   std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return pairs[a].slot < pairs[b].slot; });
@@ -665,7 +666,9 @@ void oracle_ctx::process_string_olaps(const char *S, int32_t len, uint32_t id, i
       for (const MatchNode &m : pa.list) d_matches.push_back(oracle_match_t{m.offset, m.len, m.start});
       d_pairs.push_back(dp);
     }
-    // --minkmers filter: computeMinimumKmers (:75-86,725)
+  }
+  // one partner: the --minkmers filter (computeMinimumKmers :75-86,725), then Process_Matches
+  auto one = [&](PairAcc &pa) {
     if (P.filter_by_kmer_count != 0) {
       double ovl = (double)(pa.diag_end - pa.diag_bgn);
       if (ovl < 0) ovl = -ovl;
@@ -673,10 +676,22 @@ void oracle_ctx::process_string_olaps(const char *S, int32_t len, uint32_t id, i
       if (!(ovl < (double)P.kmer_len))
         expected = (uint64_t)(int)floor(exp(-1.0 * (double)P.kmer_len * P.max_erate) * (ovl - P.kmer_len + 1));
       uint64_t need = std::max(P.filter_by_kmer_count, expected);
-      if (need > (uint64_t)pa.diag_ct) { stats.kmer_hits_skipped++; continue; }
+      if (need > (uint64_t)pa.diag_ct) { stats.kmer_hits_skipped++; return; }
     }
     process_matches(pa, S, len, id, dir);
+  };
+  const uint64_t ct = order.size();
+  if (ct <= P.frag_olap_limit) {   // :722-741 (always, without -l)
+    for (uint32_t oi : order) one(pairs[oi]);
+    return;
   }
+  // more partners than the limit (:743-797): by mean diagonal -- qsort(By_Diag_Sum), which on glibc is a merge sort, so partners on
+  // the same mean diagonal keep their array order -- then outward from diagonal zero, each side until its end of the read is full
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return pairs[a].diag_sum < pairs[b].diag_sum; });
+  uint64_t start = 0;
+  while (start < ct && pairs[order[start]].diag_sum < 0) start++;
+  for (uint64_t i = start; i < ct && (uint64_t)a_olaps_for_frag < P.frag_olap_limit; i++) one(pairs[order[i]]);
+  for (int64_t i = (int64_t)start - 1; i >= 0 && (uint64_t)b_olaps_for_frag < P.frag_olap_limit; i--) one(pairs[order[i]]);
 }
 
 namespace {
@@ -817,15 +832,35 @@ void oracle_ctx::process_matches(PairAcc &pa, const char *S, int32_t s_len, uint
   int distinct_ct = 0;
   int overlaps_output = 0;
 
+  // Kind_Of_Olap starts as NONE and, like S_Lo .. T_Hi, keeps its value through an iteration that -l skips (:415,484-490): such a
+  // seed only removes itself (re-applying the previous alignment's pruning removes nothing new).  In -G mode a skipped FIRST seed
+  // makes the reference read uninitialised bounds; here they are zero (documented in DESIGN.md).
+  int32_t kind = 0, s_lo = 0, s_hi = 0, t_lo = 0, t_hi = 0, errors = 0;
   while (!list.empty()) {
     size_t li = 0;
     for (size_t i = 1; i < list.size(); i++)
       if (list[i].len > list[li].len) li = i;     // first of the longest, in list order (:473-480)
     MatchNode longest = list[li];
 
-    int32_t s_lo, s_hi, t_lo, t_hi, errors;
+    const int32_t a_hang = longest.start - longest.offset, b_hang = a_hang + s_len - t_len;
+    const bool hit_limit = ((uint64_t)a_olaps_for_frag >= P.frag_olap_limit && a_hang <= 0) ||
+                           ((uint64_t)b_olaps_for_frag >= P.frag_olap_limit && b_hang <= 0);   // :482-490
+    if (hit_limit) {
+      if (pa.consistent) { list.clear(); break; }
+      std::vector<MatchNode> keep;
+      for (size_t i = 0; i < list.size(); i++) {
+        const MatchNode &nd = list[i];
+        bool remove = (i == li) ||
+                      ((kind == 3 || partial) && s_lo - SHIFT_SLACK <= nd.start &&
+                       nd.start + nd.len <= (s_hi + 1) + SHIFT_SLACK - 1 &&
+                       lies_on_alignment(nd.start, nd.offset, s_lo, t_lo, ed->left_delta));
+        if (!remove) keep.push_back(nd);
+      }
+      list.swap(keep);
+      continue;
+    }
     stats.ext_calls++;
-    int32_t kind = ed->extend(S, s_len, T, t_len, longest.start, longest.offset, longest.len, s_lo, s_hi, t_lo, t_hi, errors);
+    kind = ed->extend(S, s_len, T, t_len, longest.start, longest.offset, longest.len, s_lo, s_hi, t_lo, t_hi, errors);
 
     if (dump_mask & 2) {
       oracle_ext_t x;
@@ -871,6 +906,8 @@ void oracle_ctx::process_matches(PairAcc &pa, const char *S, int32_t s_len, uint
       if (partial) output_partial(s_id, t_id, dir, distinct[i], s_len, t_len);
       else output_overlap(s_id, s_len, dir, t_id, t_len, distinct[i]);
       overlaps_output++;
+      if (distinct[i].s_lo == 0) a_olaps_for_frag++;               // :631-635
+      if (distinct[i].s_hi >= s_len - 1) b_olaps_for_frag++;
     }
   }
   if (overlaps_output == 0) stats.kmer_hits_without_olap++;

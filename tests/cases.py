@@ -62,6 +62,18 @@ CASES = {
     "n_bases_partial": dict(gen=dict(genome_len=12000, coverage=25, len_min=150, len_max=150, err=0.005, seed=1044, sub_only=True),
                             erate="0.06", params=dict(hash_bits=15, hash_load=0.75, partial=1, min_olap_len=40), threads=2,
                             inject_n=dict(rate=0.003, runs=10, seed=5)),
+    # -l: per-end cap on the overlaps of a query strand (Process_String_Overlaps.C:482-490,743-797): partners sorted by mean diagonal
+    # (ties in array order: glibc's qsort is a merge sort), walked outward from diagonal zero until each end is full; seeds that would
+    # add to a full end are skipped.  Deep coverage so that most strands have more partners than the limit.
+    "olap_limit": dict(gen=dict(genome_len=30000, coverage=28, len_min=900, len_max=2600, err=0.02, seed=4101),
+                       erate="0.06", params=dict(hash_bits=17, hash_load=0.75, frag_olap_limit=2), threads=3),
+    # -l 1 with -m (several overlaps of one pair count separately towards the ends)
+    "olap_limit_m": dict(gen=dict(genome_len=24000, coverage=24, len_min=800, len_max=2200, err=0.025, seed=4102),
+                         erate="0.06", params=dict(hash_bits=16, hash_load=0.75, frag_olap_limit=1, unique_olap=0), threads=2),
+    # a limit that only some strands reach (both branches of Process_String_Olaps in one job), hash sub-blocks, -z
+    "olap_limit_blocks": dict(gen=dict(genome_len=36000, coverage=18, len_min=700, len_max=3000, err=0.015, seed=4103),
+                              erate="0.045", params=dict(hash_bits=17, hash_load=0.75, frag_olap_limit=7, max_hash_strings=120,
+                                                         use_hopeless_check=0), threads=4),
     # empty output: sparse reads of a large genome share no k-mer runs worth an overlap
     "no_overlaps": dict(gen=dict(genome_len=2000000, coverage=0.02, len_min=900, len_max=1500, err=0.02, seed=12),
                         erate="0.06", params=dict(hash_bits=14, hash_load=0.75), threads=2),
@@ -139,12 +151,12 @@ KMER_CASES = [("repeats_skip", 22, 40), ("repeats_skip", 17, 14), ("c1_small", 3
 
 # ----------------------------------------------------------------------------- seeded random cases
 ERATES = ["0.03", "0.045", "0.06", "0.1", "0.15"]
-N_FUZZ = 64
+N_FUZZ = 80    # jobs 64.. also draw a -l limit (the first 64 are the round-1 set, unchanged)
 
 
 def fuzz_case(i):
     """Seeded random job i -> (reads, params, erate string, threads, None): random read shape / error rate, K, --maxerate, -G,
-    -m/-u, -z, --minlength, hash sub-blocks (--hashstrings, tiny tables that trip the load cut-off), -h/-r sub-ranges,
+    -m/-u, -z, -l (jobs 64..), --minlength, hash sub-blocks (--hashstrings, tiny tables that trip the load cut-off), -h/-r sub-ranges,
     thread count (scheduler quirk) and N bases.  The oracle is held to the LIVE reference binary on these (test_oracle.py,
     where the reference is built) and the CUDA path to the oracle (test_gpu_parity.py)."""
     import numpy as np
@@ -181,5 +193,7 @@ def fuzz_case(i):
     else:
         over["end_ref_id"] = n
     threads = int(rng.choice([1, 2, 3, 4, 7]))
+    if i >= 64 and not over["partial"]:   # (-G with -l makes the reference read uninitialised alignment bounds: not testable)
+        over["frag_olap_limit"] = int(rng.choice([1, 2, 3, 5, 9]))
     P = H.default_params(max_erate=H.strtof(erate), num_threads=threads, **over)
     return reads, P, erate, threads, None

@@ -396,6 +396,8 @@ def oic_args(params, erate_str):
           "--hashload", repr(params["hash_load"]), "--maxerate", erate_str,
           "--minlength", str(params["min_olap_len"])] + (["--minkmers"] if params.get("filter_by_kmer_count") else []) + [
           "--hashstrings", str(params["max_hash_strings"]), "--hashdatalen", str(params["max_hash_data_len"])]
+    if params.get("frag_olap_limit", 2 ** 64 - 1) != 2 ** 64 - 1:
+        a += ["-l", str(params["frag_olap_limit"])]
     if params["end_hash_id"] != 2 ** 32 - 1 or params["bgn_hash_id"] != 1:
         a += ["-h", "%d-%d" % (params["bgn_hash_id"], params["end_hash_id"])]
     if params["end_ref_id"] != 2 ** 32 - 1 or params["bgn_ref_id"] != 1:

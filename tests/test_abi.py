@@ -50,8 +50,6 @@ def test_unsupported_options_fail_loudly():
     from canu_b200 import api
     with pytest.raises(api.OicError):
         api.Overlapper(api.default_params(kmer_len=32))
-    with pytest.raises(api.OicError):
-        api.Overlapper(api.default_params(frag_olap_limit=5))
 
 
 def test_tools_fail_without_device(tmp_path):
