@@ -24,7 +24,7 @@ ABI_SYMBOLS = [
     "oic_dump_pairs", "oic_measure_int32_peak", "oic_set_job", "oic_reset_stats", "oic_count_kmers", "oic_copy_frequent_kmers",
     "oic_copy_kmer_histogram", "oic_comm_unique_id", "oic_comm_init_rank", "oic_comm_init_all", "oic_comm_info",
     "oic_hash_block_replicate", "oic_build_hash_index_sharded", "oic_ovlstore_sort", "oic_ovlstore_sort_noalloc",
-    "oic_ovlstore_sort_noalloc_max",
+    "oic_ovlstore_sort_noalloc_max", "oic_load_qualities",
 ]
 
 # status codes of include/oic_b200.h
@@ -42,7 +42,7 @@ class Params(C.Structure):
                 ("max_hash_data_len", C.c_uint64), ("frag_olap_limit", C.c_uint64),
                 ("filter_by_kmer_count", C.c_uint64), ("num_threads", C.c_uint32),
                 ("bgn_hash_id", C.c_uint32), ("end_hash_id", C.c_uint32),
-                ("bgn_ref_id", C.c_uint32), ("end_ref_id", C.c_uint32)]
+                ("bgn_ref_id", C.c_uint32), ("end_ref_id", C.c_uint32), ("use_window_filter", C.c_int32)]
 
 
 STATS_FIELDS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skipped", "multi_overlap",
@@ -52,7 +52,8 @@ STATS_FIELDS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skip
 
 
 class Stats(C.Structure):
-    _fields_ = [(n, C.c_uint64) for n in STATS_FIELDS] + [("n_hash_blocks", C.c_uint32), ("last_end_hash_id", C.c_uint32)]
+    _fields_ = ([(n, C.c_uint64) for n in STATS_FIELDS] + [("n_hash_blocks", C.c_uint32), ("last_end_hash_id", C.c_uint32)] +
+                [("bad_short_window", C.c_uint64), ("bad_long_window", C.c_uint64)])
 
 
 class Timings(C.Structure):
@@ -94,6 +95,7 @@ def load_library():
     lib.oic_last_error.argtypes = [vp]
     lib.oic_load_reads.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.oic_load_reads_2bit.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
+    lib.oic_load_qualities.argtypes = [vp, vp, vp]
     lib.oic_set_skip_kmers.argtypes = [vp, C.c_uint64, C.c_char_p]
     lib.oic_set_job.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
     lib.oic_reset_stats.argtypes = [vp]
@@ -144,10 +146,11 @@ def default_params(**kw):
     d = dict(kmer_len=22, max_erate=strtof("0.06"), min_olap_len=0, partial=0, unique_olap=1,
              use_hopeless_check=1, hash_bits=22, hash_load=0.6, max_hash_strings=10000,
              max_hash_data_len=100000000, frag_olap_limit=2 ** 64 - 1, filter_by_kmer_count=0,
-             num_threads=1, bgn_hash_id=1, end_hash_id=2 ** 32 - 1, bgn_ref_id=1, end_ref_id=2 ** 32 - 1)
+             num_threads=1, bgn_hash_id=1, end_hash_id=2 ** 32 - 1, bgn_ref_id=1, end_ref_id=2 ** 32 - 1, use_window_filter=0)
     d.update(kw)
     if d["max_erate"] > 0.06:
         d["use_hopeless_check"] = 0
+        d["use_window_filter"] = 0
     return d
 
 
@@ -266,6 +269,12 @@ class Overlapper:
         self.n_reads = len(lengths)
         self.first_id = first_id
 
+    def load_qualities(self, quals, offsets):
+        """-w: one quality value per base of the loaded reads (read i at quals[offsets[i] ..])"""
+        quals = np.ascontiguousarray(quals, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self._check(self.lib.oic_load_qualities(self._h, offsets.ctypes.data, quals.ctypes.data), "oic_load_qualities")
+
     def set_job(self, bgn_hash_id, end_hash_id, bgn_ref_id, end_ref_id, max_hash_strings, max_hash_data_len):
         """New -h / -r / --hashstrings / --hashdatalen for the resident reads (one job of overlapInCorePartition)."""
         self._check(self.lib.oic_set_job(self._h, bgn_hash_id, end_hash_id, bgn_ref_id, end_ref_id, max_hash_strings,
@@ -323,7 +332,7 @@ class Overlapper:
     def stats(self):
         s = Stats()
         self._check(self.lib.oic_get_stats(self._h, C.byref(s)), "oic_get_stats")
-        return {n: getattr(s, n) for n in STATS_FIELDS + ["n_hash_blocks", "last_end_hash_id"]}
+        return {n: getattr(s, n) for n in STATS_FIELDS + ["n_hash_blocks", "last_end_hash_id", "bad_short_window", "bad_long_window"]}
 
     def timings(self):
         t = Timings()

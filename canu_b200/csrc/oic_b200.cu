@@ -155,6 +155,8 @@ struct oic_ctx {
   // search buffers
   DevBuf d_q_order;
   DevBuf d_strand;              // -l path: per-pair ordering scratch (k_process_strands)
+  DevBuf d_quals;               // -w: one quality byte per base at the base's stream position
+  bool have_quals = false;
   DevBuf d_qs_read, d_qs_tile_base, d_tile_empty, d_recs, d_chunk_next, d_chunk_cnt, d_chunk_qs, d_qs_first, d_qs_nrec,
       d_qs_base, d_qs_screen, d_bufA, d_bufB, d_scratch, d_pairs, d_info, d_out, d_retry, d_vals, d_rowmeta, d_deltas, d_dirs, d_order, d_hist2, d_pstate, d_pend, d_tasks, d_results, d_alive, d_dpool, d_wide;
   DevBuf d_ctr, d_flag;
@@ -693,7 +695,7 @@ int oic_create(const oic_params_t *p, int device, oic_ctx_t **out) {
   if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OIC_ERR_CUDA; }
   oic_ctx *c = new oic_ctx();
   c->P = *p;
-  if (c->P.max_erate > 0.06) c->P.use_hopeless_check = 0;   // OIC/overlapInCore.C:416-421
+  if (c->P.max_erate > 0.06) { c->P.use_hopeless_check = 0; c->P.use_window_filter = 0; }   // OIC/overlapInCore.C:416-421
   c->device = device;
   {
     int sms = 0;
@@ -726,7 +728,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_qs_read, &c->d_qs_tile_base, &c->d_tile_empty, &c->d_recs, &c->d_chunk_next, &c->d_chunk_cnt,
                     &c->d_chunk_qs, &c->d_qs_first, &c->d_qs_nrec, &c->d_qs_base, &c->d_qs_screen, &c->d_bufA, &c->d_bufB,
                     &c->d_scratch, &c->d_pairs, &c->d_info, &c->d_out, &c->d_retry, &c->d_vals, &c->d_rowmeta, &c->d_deltas, &c->d_dirs, &c->d_order, &c->d_hist2, &c->d_pstate, &c->d_pend, &c->d_tasks, &c->d_results, &c->d_alive, &c->d_dpool, &c->d_wide,
-                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read, &c->d_strand};
+                    &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read, &c->d_strand, &c->d_quals};
   if (c->comm && nccl_api()) nccl_api()->CommDestroy(c->comm);
   for (DevBuf *b : bufs) b->release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -747,6 +749,7 @@ static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const ui
   if (!c || (n && (!offsets || !lengths || !bases)) || first_id < 1) return c ? c->fail(OIC_ERR_ARG, "oic_load_reads: bad argument") : OIC_ERR_ARG;
   cudaSetDevice(c->device);
   c->hash_ready = false;
+  c->have_quals = false;
   c->mem_avail = 0;
   c->first_id = first_id;
   c->n_reads = n;
@@ -846,6 +849,23 @@ int oic_load_reads(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *
 int oic_load_reads_2bit(oic_ctx_t *c, uint32_t first_id, uint32_t n, const uint64_t *byte_offsets, const uint32_t *lengths,
                         const uint8_t *packed, const uint8_t *hash_ok, const uint8_t *ref_ok) {
   return load_reads_impl(c, first_id, n, byte_offsets, lengths, packed, hash_ok, ref_ok, true);
+}
+
+int oic_load_qualities(oic_ctx_t *c, const uint64_t *offsets, const uint8_t *quals) {
+  if (!c || !offsets || !quals) return c ? c->fail(OIC_ERR_ARG, "oic_load_qualities: bad argument") : OIC_ERR_ARG;
+  if (c->n_reads == 0) return c->fail(OIC_ERR_STATE, "oic_load_qualities before oic_load_reads");
+  cudaSetDevice(c->device);
+  // laid out like the base stream: quality of base i of read r at [h_pos[r] + i], zero elsewhere
+  const size_t bytes = (size_t)c->stream_words * 32;
+  std::vector<uint8_t> q(bytes, 0);
+  for (uint32_t r = 0; r < c->n_reads; r++) memcpy(q.data() + c->h_pos[r], quals + offsets[r], c->h_len[r]);
+  CK(c->d_quals.ensure(bytes));
+  CK(cudaMemcpyAsync(c->d_quals.p, q.data(), bytes, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->tm.h2d_bytes += bytes;
+  c->have_quals = true;
+  c->mem_avail = 0;
+  return OIC_OK;
 }
 
 int oic_set_skip_kmers(oic_ctx_t *c, uint64_t n, const char *kmers) {
@@ -1152,6 +1172,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.vals = c->d_vals.as<int32_t>(); ea.rowcap = rowcap; ea.rowmeta = c->d_rowmeta.as<int4>(); ea.deltas = c->d_deltas.as<int32_t>();
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
+      ea.quals = P.use_window_filter ? c->d_quals.as<uint8_t>() : nullptr;
       if (P.frag_olap_limit != UINT64_MAX) {   // -l: partners of a strand depend on each other -> serial walk per strand
         const int rl = run_pairs_limited(c, ea, rp.src, n_pairs, vals_bytes, hc);
         if (rl) return rl;
@@ -1172,7 +1193,8 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         dpool_cap /= 2;
       }
       // (pairs with an N in either read are never handed over: the lean loop of pass 2 knows no wildcards)
-      ea.handoff = getenv("OIC_NO_SPECULATION") ? 0 : 1;
+      // (-w walks the delta list of every overlap it outputs, which the speculative path does not keep: serial path)
+      ea.handoff = (getenv("OIC_NO_SPECULATION") || ea.quals) ? 0 : 1;
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
       ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;
@@ -1249,6 +1271,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   s.kmer_hits_without_olap += hc.kmer_hits_without_olap; s.kmer_hits_with_olap += hc.kmer_hits_with_olap;
   s.kmer_hits_skipped += hc.kmer_hits_skipped; s.multi_overlap += hc.multi_overlap;
   s.total_overlaps += hc.total_overlaps; s.contained += hc.contained; s.dovetail += hc.dovetail;
+  s.bad_short_window += hc.bad_short_window; s.bad_long_window += hc.bad_long_window;
   return 0;
 }
 
@@ -1282,6 +1305,7 @@ int oic_process_overlaps(oic_ctx_t *c, uint32_t bgn_ref_id, uint32_t end_ref_id)
   if (!c) return OIC_ERR_ARG;
   cudaSetDevice(c->device);
   if (!c->hash_ready) return c->fail(OIC_ERR_STATE, "oic_process_overlaps before oic_build_hash_index");
+  if (c->P.use_window_filter && !c->have_quals) return c->fail(OIC_ERR_STATE, "-w (window filter) needs the reads' quality values: call oic_load_qualities first");
   c->dbg_pairs.clear();
   c->dbg_matches.clear();
   if (end_ref_id < bgn_ref_id) return OIC_OK;

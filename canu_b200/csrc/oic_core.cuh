@@ -181,8 +181,10 @@ struct OlapInfo {   // Olap_Info_t, OIC/overlapInCore.H:258-267 (without the 8 M
   int32_t min_diag, max_diag;
 };
 
-OIC_HD void add_overlap(int partial, int s_lo, int s_hi, int t_lo, int t_hi, double qual, int delta_ct,
-                        OlapInfo *olap, int &ct) {
+/* returns the slot whose alignment -- and with it the delta list the reference copies into Olap_Info_t.delta
+ * (Process_String_Overlaps.C:253-256,278-282; read only by the -w window filter) -- was set, or -1 */
+OIC_HD int add_overlap(int partial, int s_lo, int s_hi, int t_lo, int t_hi, double qual, int delta_ct,
+                       OlapInfo *olap, int &ct) {
   if (!partial) {
     int new_diag = t_lo - s_lo;
     for (int i = 0; i < ct; i++) {
@@ -200,12 +202,13 @@ OIC_HD void add_overlap(int partial, int s_lo, int s_hi, int t_lo, int t_hi, dou
           o.s_lo = s_lo; o.s_hi = s_hi; o.t_lo = t_lo; o.t_hi = t_hi;
           o.quality = qual;
           o.delta_ct = delta_ct;
+          return i;
         }
-        return;
+        return -1;
       }
     }
   }
-  if (ct >= MAX_DISTINCT_OLAPS) return;
+  if (ct >= MAX_DISTINCT_OLAPS) return -1;
   OlapInfo &o = olap[ct];
   o.s_lo = o.s_left_boundary = s_lo;
   o.s_hi = o.s_right_boundary = s_hi;
@@ -215,7 +218,30 @@ OIC_HD void add_overlap(int partial, int s_lo, int s_hi, int t_lo, int t_hi, dou
   o.delta_ct = delta_ct;
   o.min_diag = o.max_diag = t_lo - s_lo;
   ct++;
+  return ct - 1;
 }
+
+constexpr int QUALITY_CUTOFF = 20;                          // OIC/overlapInCore.H:190
+constexpr int BAD_WINDOW_LEN = 50, BAD_WINDOW_VALUE = 8 * QUALITY_CUTOFF;     // OIC/overlapInCore.H:80-84
+constexpr int BAD_LONG_WINDOW_LEN = 100, BAD_LONG_WINDOW_VALUE = 240;         // Process_String_Overlaps.C:616
+
+/* Has_Bad_Window (Process_String_Overlaps.C:365-388) for BOTH windows in one streaming pass: feed the q_diff values in order;
+ * `bad` gets bit 0 when some 50-long stretch sums to >= 160 and bit 1 when some 100-long stretch sums to >= 240.  ring[] holds
+ * the last 100 values. */
+struct WindowScan {
+  int n, sum_s, sum_l, bad;
+  OIC_HD void reset() { n = sum_s = sum_l = bad = 0; }
+  OIC_HD void push(signed char *ring, int d) {
+    const int at = n % BAD_LONG_WINDOW_LEN;
+    if (n >= BAD_LONG_WINDOW_LEN) sum_l -= ring[at];
+    if (n >= BAD_WINDOW_LEN) sum_s -= ring[(n - BAD_WINDOW_LEN) % BAD_LONG_WINDOW_LEN];
+    ring[at] = (signed char)d;
+    sum_s += d; sum_l += d;
+    n++;
+    if (n >= BAD_WINDOW_LEN && sum_s >= BAD_WINDOW_VALUE) bad |= 1;
+    if (n >= BAD_LONG_WINDOW_LEN && sum_l >= BAD_LONG_WINDOW_VALUE) bad |= 2;
+  }
+};
 
 OIC_HD void combine_into_one(OlapInfo *olap, int ct, int *deleted) {
   int best = 0;

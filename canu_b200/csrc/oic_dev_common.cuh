@@ -158,6 +158,7 @@ struct DevCounters {
   unsigned int occ_cursor;     // hash build: bump allocator of `occ`
   unsigned int n_mid_lists;    // hash build: lists of 7..32 occurrences (sorted by a warp each)
   unsigned int n_strands;      // -l path: query strands that have partners
+  unsigned long long bad_short_window, bad_long_window;   // -w: overlaps rejected by the 50- / the 100-base window
   unsigned long long dpool_used;           // ints of the delta pool handed out
   // phase clocks of the pair kernel (SM cycles summed over warps; t_warp_max = busiest warp)
   unsigned long long t_dp, t_tb, t_prune, t_warp_sum, t_warp_max, t_pair_max;

@@ -61,6 +61,8 @@ struct ExtArgs {
   uint8_t *alive;                             // per seed, scratch of the commit pass
   uint32_t *wide_list;                        // tasks the lean kernel could not run (a row wider than SW)
   int32_t *dpool; unsigned long long dpool_cap;   // delta lists of the speculative results
+  // -w (window filter): one quality value per base at the base's stream position (quals[rd_pos[read] + i]); nullptr = filter off
+  const uint8_t *quals;
   DevCounters *ctr;
 };
 
@@ -247,31 +249,37 @@ __device__ __forceinline__ int longest_seed(const Seed *seeds, const uint8_t *al
 }
 
 /* the accept test of Process_Matches (Process_String_Overlaps.C:488-512) */
-__device__ __forceinline__ void accept_overlap(const ExtArgs &a, int kind, int s_lo, int s_hi, int t_lo, int t_hi, int errors, int dlen,
-                                               OlapInfo *distinct, int &distinct_ct) {
+/* returns the slot of `distinct` whose alignment this extension became, or -1 */
+__device__ __forceinline__ int accept_overlap(const ExtArgs &a, int kind, int s_lo, int s_hi, int t_lo, int t_hi, int errors, int dlen,
+                                              OlapInfo *distinct, int &distinct_ct) {
   if (kind == 3 || a.partial) {
     if (1 + s_hi - s_lo >= a.min_olap_len && 1 + t_hi - t_lo >= a.min_olap_len) {
       const int olap_len = 1 + imin(s_hi - s_lo, t_hi - t_lo);
       const double quality = OIC_DDIV((double)errors, (double)olap_len);
       if (errors <= (int)ceil(OIC_DMUL((double)olap_len, a.erate)))
-        add_overlap(a.partial, s_lo, s_hi, t_lo, t_hi, quality, dlen, distinct, distinct_ct);
+        return add_overlap(a.partial, s_lo, s_hi, t_lo, t_hi, quality, dlen, distinct, distinct_ct);
     }
   }
+  return -1;
 }
 
-/* end of Process_Matches for one pair: merge / choose the distinct overlaps, write the records, bump the -s counters
- * (Process_String_Overlaps.C:540-600, Output.C).  Lane 0 only. */
-__device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct, int *a_inc = nullptr,
-                                              int *b_inc = nullptr) {
-  // a_inc / b_inc (-l only): overlaps output that reach the 5' / the 3' end of the query strand (Process_String_Overlaps.C:631-635)
+/* Combine_Into_One_Olap / Merge_Intersecting_Olaps / Choose_Best_Partial (Process_String_Overlaps.C:540-556): which of the
+ * distinct overlaps survive.  Scalar, the same on every lane that calls it. */
+__device__ __forceinline__ void reduce_olaps(const ExtArgs &a, OlapInfo *distinct, int distinct_ct, int *deleted) {
+  if (a.partial) { if (a.unique_olap) choose_best_partial(distinct, distinct_ct, deleted); }
+  else { if (a.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
+}
+
+/* end of Process_Matches for one pair: write the records of the overlaps that are not deleted, bump the -s counters
+ * (Process_String_Overlaps.C:558-650, Output.C).  Lane 0 only.
+ * a_inc / b_inc (-l only): overlaps output that reach the 5' / the 3' end of the query strand (:631-635). */
+__device__ __forceinline__ void emit_olaps(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct, const int *deleted, int *a_inc,
+                                           int *b_inc) {
   int overlaps_output = 0;
   if (distinct_ct > 0) {
-    int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
-    if (a.partial) { if (a.unique_olap) choose_best_partial(distinct, distinct_ct, deleted); }
-    else { if (a.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
     int nout = 0;
     for (int i = 0; i < distinct_ct; i++) nout += !deleted[i];
-    uint32_t ob = atomicAdd(&a.ctr->n_out, (unsigned)nout);
+    uint32_t ob = nout ? atomicAdd(&a.ctr->n_out, (unsigned)nout) : 0u;
     for (int i = 0; i < distinct_ct; i++) {
       if (deleted[i]) continue;
       if (ob >= a.out_cap) { atomicOr(&a.ctr->out_overflow, 1u); break; }
@@ -293,6 +301,54 @@ __device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x
     atomicAdd(&a.ctr->kmer_hits_with_olap, 1ull);
     if (overlaps_output > 1) atomicAdd(&a.ctr->multi_overlap, 1ull);
   }
+}
+
+__device__ __forceinline__ void finalize_pair(const ExtArgs &a, const PairCtx &x, OlapInfo *distinct, int distinct_ct, int *a_inc = nullptr,
+                                              int *b_inc = nullptr) {
+  int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
+  if (distinct_ct > 0) reduce_olaps(a, distinct, distinct_ct, deleted);
+  emit_olaps(a, x, distinct, distinct_ct, deleted, a_inc, b_inc);
+}
+
+/* ---- -w, the window filter (OIC/overlapInCore.C:398,417-419; Process_String_Overlaps.C:560-620, Has_Bad_Window :365-388)
+ * An overlap about to be output is walked along its alignment: every mismatch contributes min(query quality, hash-read quality,
+ * 20), every indel min(quality of the extra base, 20); the overlap is rejected when some 50 consecutive positions sum to 160 or
+ * more ("short window"), else when some 100 sum to 240 or more ("long window").
+ * The alignment is the delta list of the extension that set the overlap's slot.  The reference copies that list into the slot;
+ * here the slot remembers the SEED of that extension and the extension is run again when the overlap is output (deterministic, one
+ * more extension per output overlap, -w only) -- no delta lists are kept.  The walk itself is serial (lane 0). */
+__device__ __forceinline__ bool base_same(const PairCtx &x, uint64_t n_off, int i, int j) {
+  const int64_t ps = x.sp + i, pt = x.tp + j;
+  if (n_off) {
+    const bool sn = ((x.S[(ps >> 5) + n_off] >> ((ps & 31) * 2)) & 3u) != 0, tn = ((x.T[(pt >> 5) + n_off] >> ((pt & 31) * 2)) & 3u) != 0;
+    if (tn) return true;                 // T[j] == 'n' matches anything (:578)
+    if (sn) return x.dir == 0;           // S[i] == 'n' on the forward strand; on the reverse strand the reference holds NUL there, which equals nothing
+  }
+  return (((x.S[ps >> 5] >> ((ps & 31) * 2)) ^ (x.T[pt >> 5] >> ((pt & 31) * 2))) & 3u) == 0;
+}
+/* 0 = keep, 1 = rejected by the short window, 2 = by the long window.  delta[0 .. delta_ct) = the alignment's delta list. */
+__device__ __forceinline__ int window_filter(const ExtArgs &a, const PairCtx &x, const OlapInfo &p, const int32_t *delta, int delta_ct, signed char *ring) {
+  // query qualities are reversed with the bases on the reverse strand (reverseComplement(bases, quals, len), Process_Overlaps.C:139)
+  const uint8_t *sq = a.quals + x.sp, *tq = a.quals + x.tp;
+  auto s_q = [&](int i) { return (int)sq[x.dir ? x.s_len - 1 - i : i]; };
+  WindowScan ws;
+  ws.reset();
+  int i = p.s_lo, j = p.t_lo;
+  for (int k = 0; k < delta_ct; k++) {
+    const int dl = delta[k], len = iabs(dl);
+    for (int n = 1; n < len; n++) {
+      ws.push(ring, base_same(x, a.n_off, i, j) ? 0 : imin(imin(s_q(i), (int)tq[j]), QUALITY_CUTOFF));
+      i++; j++;
+    }
+    int d;
+    if (dl > 0) { d = s_q(i); i++; } else { d = (int)tq[j]; j++; }
+    ws.push(ring, imin(d, QUALITY_CUTOFF));
+  }
+  while (i <= p.s_hi) {
+    ws.push(ring, base_same(x, a.n_off, i, j) ? 0 : imin(imin(s_q(i), (int)tq[j]), QUALITY_CUTOFF));
+    i++; j++;
+  }
+  return (ws.bad & 1) ? 1 : ((ws.bad & 2) ? 2 : 0);
 }
 
 /*
@@ -363,6 +419,7 @@ __device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, c
   }
 
   OlapInfo distinct[MAX_DISTINCT_OLAPS];
+  Seed olap_seed[MAX_DISTINCT_OLAPS];   // -w only
   int distinct_ct = 0;
   bool overflow = false, handed = false;
   const unsigned long long snap_cells = ws.cells, snap_words = ws.words, snap_calls = ext_calls;
@@ -380,7 +437,8 @@ __device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, c
       ext_calls++;
       kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi, errors, dlen);
       if (kind < 0) { overflow = true; break; }
-      accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
+      const int slot = accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
+      if (a.quals && slot >= 0) olap_seed[slot] = lg;   // -w: the slot's alignment (and delta list) is this seed's extension
     }
     if (inf.consistent) break;
 
@@ -430,7 +488,31 @@ __device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, c
     ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
     return PP_HANDED;
   }
-  if (l == 0) finalize_pair(a, x, distinct, distinct_ct, LIMIT ? &a_inc : nullptr, LIMIT ? &b_inc : nullptr);
+  if (a.quals && distinct_ct > 0) {
+    // -w: the survivors of the reduction go through the window filter before they are output (:558-620)
+    int deleted[MAX_DISTINCT_OLAPS] = {0, 0, 0};
+    reduce_olaps(a, distinct, distinct_ct, deleted);   // (every lane holds the same `distinct`)
+    const unsigned long long keep_cells = ws.cells, keep_words = ws.words;   // the re-extensions below are not the reference's work
+    for (int i = 0; i < distinct_ct; i++) {
+      if (deleted[i]) continue;
+      const Seed sd = olap_seed[i];
+      int s_lo2, s_hi2, t_lo2, t_hi2, errors2, dlen2;
+      if (extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, sd.start, sd.offset, sd.len, s_lo2, s_hi2, t_lo2, t_hi2, errors2, dlen2) < 0) {
+        ws.cells = snap_cells; ws.words = snap_words; ext_calls = snap_calls;
+        return PP_OVERFLOW;   // (it fitted the first time: cannot happen)
+      }
+      int rej = 0;
+      if (l == 0) {
+        signed char ring[BAD_LONG_WINDOW_LEN];
+        rej = window_filter(a, x, distinct[i], ws.ldelta, dlen2, ring);
+        if (rej) atomicAdd(rej == 1 ? &a.ctr->bad_short_window : &a.ctr->bad_long_window, 1ull);
+      }
+      rej = __shfl_sync(FULL, rej, 0);
+      if (rej) deleted[i] = 1;
+    }
+    ws.cells = keep_cells; ws.words = keep_words;
+    if (l == 0) emit_olaps(a, x, distinct, distinct_ct, deleted, LIMIT ? &a_inc : nullptr, LIMIT ? &b_inc : nullptr);
+  } else if (l == 0) finalize_pair(a, x, distinct, distinct_ct, LIMIT ? &a_inc : nullptr, LIMIT ? &b_inc : nullptr);
   if (LIMIT) { a_inc = __shfl_sync(FULL, a_inc, 0); b_inc = __shfl_sync(FULL, b_inc, 0); }
   return PP_DONE;
 }

@@ -65,6 +65,7 @@ void usage(const char *argv0) {
   fprintf(stderr, "-s          specify statistics file name\n");
   fprintf(stderr, "-t <n>      use <n> parallel threads (only decides which reads the reference's scheduler would process)\n");
   fprintf(stderr, "-u          allow only 1 overlap per oriented fragment pair\n");
+  fprintf(stderr, "-w          filter out overlaps with too many errors in a window\n");
   fprintf(stderr, "-z          skip the hopeless check\n\n");
   fprintf(stderr, "--maxerate <n>     only output overlaps with fraction <n> or less error (e.g., 0.06 == 6%%)\n");
   fprintf(stderr, "--minlength <n>    only output overlaps of <n> or more bases\n");
@@ -183,7 +184,7 @@ int main(int argc, char **argv) {
   if (P.max_hash_strings > max_string_num) fprintf(stderr, "Too many strings (--hashstrings), must be less than %llu\n", (unsigned long long)max_string_num), err++;
   if (out_name == nullptr && sweep_prefix == nullptr) fprintf(stderr, "ERROR:  No output file name specified\n"), err++;
   if (err || store_path == nullptr) { usage(argv[0]); return 1; }
-  if (window_filter) { fprintf(stderr, "ERROR: -w (window filter) is not supported by this build\n"); return 1; }
+  P.use_window_filter = window_filter ? 1 : 0;
   if (P.num_threads == 0) P.num_threads = 1;
   if (n_gpus < 1) n_gpus = 1;
 
@@ -251,6 +252,17 @@ int main(int argc, char **argv) {
   }
   fprintf(stderr, "Loaded reads %u-%u (%llu bases) from '%s'  [%.2f s]\n", first_id, last_id, (unsigned long long)total, store_path, elapsed());
 
+  // -w: the reads' quality values (QVAL constants / UQLT bytes), one byte per base, in read order
+  std::vector<uint8_t> quals;
+  std::vector<uint64_t> qual_off;
+  if (window_filter) {
+    qual_off.resize(n);
+    uint64_t at = 0;
+    for (uint32_t i = 0; i < n; i++) { qual_off[i] = at; at += lengths[i]; }
+    quals.resize(at + 1);
+    for (uint32_t i = 0; i < n; i++) store.load_qualities(first_id + i, quals.data() + qual_off[i]);
+  }
+
   std::vector<char> skip;   // Mark_Skip_Kmers input: '>' header line, then exactly K bases (Build_Hash_Index.C:233-286)
   uint64_t n_skip = 0;
   if (skip_file) {
@@ -294,6 +306,7 @@ int main(int argc, char **argv) {
     if (rc) { sh[g].err = oic_last_error(nullptr); return rc; }
     rc = two_bit ? oic_load_reads_2bit(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), (const uint8_t *)bases.data(), hash_ok.data(), ref_ok.data())
                  : oic_load_reads(sh[g].ctx, first_id, n, offsets.data(), lengths.data(), bases.data(), hash_ok.data(), ref_ok.data());
+    if (!rc && window_filter) rc = oic_load_qualities(sh[g].ctx, qual_off.data(), quals.data());
     if (!rc && n_skip) rc = oic_set_skip_kmers(sh[g].ctx, n_skip, skip.data());
     if (rc) sh[g].err = oic_last_error(sh[g].ctx);
     fprintf(stderr, "GPU %d: context up, reads resident  [%.2f s]\n", device0 + g, elapsed());
@@ -377,6 +390,7 @@ int main(int argc, char **argv) {
       tot.kmer_hits_without_olap += s.kmer_hits_without_olap; tot.kmer_hits_with_olap += s.kmer_hits_with_olap;
       tot.multi_overlap += s.multi_overlap; tot.total_overlaps += s.total_overlaps;
       tot.contained += s.contained; tot.dovetail += s.dovetail;
+      tot.bad_short_window += s.bad_short_window; tot.bad_long_window += s.bad_long_window;
     }
     FILE *stats = stderr;
     if (job_stat) {
@@ -389,8 +403,8 @@ int main(int argc, char **argv) {
     fprintf(stats, " Total overlaps produced = %lld\n", (long long)tot.total_overlaps);
     fprintf(stats, "      Contained overlaps = %lld\n", (long long)tot.contained);
     fprintf(stats, "       Dovetail overlaps = %lld\n", (long long)tot.dovetail);
-    fprintf(stats, "Rejected by short window = %lld\n", 0LL);
-    fprintf(stats, " Rejected by long window = %lld\n", 0LL);
+    fprintf(stats, "Rejected by short window = %lld\n", (long long)tot.bad_short_window);
+    fprintf(stats, " Rejected by long window = %lld\n", (long long)tot.bad_long_window);
     if (stats != stderr) fclose(stats);
     return 0;
   };

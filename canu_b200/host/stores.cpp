@@ -117,6 +117,29 @@ const uint8_t *GkStore::sequence_2bit(uint32_t id) const {
   return nullptr;
 }
 
+void GkStore::load_qualities(uint32_t id, uint8_t *out) const {
+  const GkRead &r = reads_[id];
+  const uint32_t len = r.seq_len();
+  const uint64_t at = r.m_ptr();
+  memset(out, 0, len);
+  if (at + 8 > blobs_bytes_ || memcmp(blobs_ + at, "BLOB", 4) != 0) {
+    fprintf(stderr, "gkStore: read %u: no BLOB at offset %llu of '%s/blobs'\n", id, (unsigned long long)at, path_.c_str());
+    exit(1);
+  }
+  const uint8_t *b = blobs_ + at + 8;
+  while (memcmp(b, "STOP", 4) != 0) {
+    uint32_t clen;
+    memcpy(&clen, b + 4, 4);
+    if (memcmp(b, "QVAL", 4) == 0 && clen >= 4) {
+      uint32_t qv;
+      memcpy(&qv, b + 8, 4);
+      memset(out, (int)(uint8_t)qv, len);
+    } else if (memcmp(b, "UQLT", 4) == 0 && clen >= len) memcpy(out, b + 8, len);
+    b += 8 + clen;
+    if ((size_t)(b - blobs_) + 4 > blobs_bytes_) { fprintf(stderr, "gkStore: read %u: blob runs past the end of the file\n", id); exit(1); }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 std::string counts_name_for(const std::string &name) {
   // AS_UTL_findBaseFileName: cut at the first '.' after the last '/', then add ".counts"

@@ -36,6 +36,9 @@ class GkStore {
   // the read's `2SEQ` chunk as stored (4 bases per byte, first base in bits 7-6; ceil(seq_len/4) bytes), or nullptr when the
   // read is kept unencoded (`USEQ`: it contains non-ACGT bases) -- fed to oic_load_reads_2bit without decoding
   const uint8_t *sequence_2bit(uint32_t id) const;
+  // quality values of read `id` into out[0 .. seq_len), as gkReadData_getQualities returns them (ST/gkStore.C:117-145): the `QVAL`
+  // constant for every base, or the `UQLT` bytes; a read with neither gets zeros (what the reference's untouched buffer holds)
+  void load_qualities(uint32_t id, uint8_t *out) const;
 
  private:
   std::string path_;

@@ -24,7 +24,7 @@ extern "C" {
 #define OIC_OK                0
 #define OIC_ERR_CUDA        (-1)   /* CUDA runtime error / no device                          */
 #define OIC_ERR_ARG         (-2)   /* bad argument                                            */
-#define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31, -w ...)      */
+#define OIC_ERR_UNSUPPORTED (-3)   /* option outside this build's scope (K > 31 ...)          */
 #define OIC_ERR_BASES       (-4)   /* a loaded read holds a letter other than ACGTN           */
 #define OIC_ERR_CAPACITY    (-5)   /* an internal device buffer could not be sized            */
 #define OIC_ERR_STATE       (-6)   /* call order violated (e.g. search before build)          */
@@ -47,6 +47,7 @@ typedef struct {
   uint32_t num_threads;          /* -t                only feeds the scheduler quirk (see driver)     */
   uint32_t bgn_hash_id, end_hash_id;  /* -h a-b                                                       */
   uint32_t bgn_ref_id,  end_ref_id;   /* -r a-b                                                       */
+  int32_t  use_window_filter;    /* -w                G.Use_Window_Filter (forced 0 if erate > 0.06); needs oic_load_qualities */
 } oic_params_t;
 
 /* The 8 counters of the -s stats file (OIC/overlapInCore.C:569-588) plus the work counters the
@@ -59,6 +60,7 @@ typedef struct {
   uint64_t n_runs, n_pairs;                                   /* exact-match runs / read pairs    */
   uint64_t ext_calls, ext_cells, ext_words;                   /* C and W of I_ext = 6C + 4W       */
   uint32_t n_hash_blocks, last_end_hash_id;
+  uint64_t bad_short_window, bad_long_window;                 /* -w: "Rejected by short / long window"  */
 } oic_stats_t;
 
 /* Accumulated device time per stage, CUDA events on the library's stream (milliseconds) and launch counts. */
@@ -97,6 +99,14 @@ int oic_load_reads(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const ui
  * non-ACGT bases and go through oic_load_reads.) */
 int oic_load_reads_2bit(oic_ctx_t *ctx, uint32_t first_id, uint32_t n_reads, const uint64_t *byte_offsets,
                         const uint32_t *lengths, const uint8_t *packed, const uint8_t *hash_ok, const uint8_t *ref_ok);
+
+/* -w, the window filter (OIC/overlapInCore.C:398,417-419; OIC/overlapInCore-Process_String_Overlaps.C:365-388,560-620): the
+ * quality values of the reads loaded by the last oic_load_reads / oic_load_reads_2bit -- what gkReadData_getQualities gives the
+ * reference (ST/gkStore.C:117-145: the read's QVAL constant for every base, or its UQLT bytes), one byte per base, read i at
+ * quals[offsets[i] .. + lengths[i]).  Needed before oic_process_overlaps when params.use_window_filter is set; loading new reads
+ * drops them.  With the filter on, the pair stage runs its serial path (one warp per read pair for the whole Process_Matches
+ * loop): every overlap about to be output is re-aligned and walked along its delta list, which the speculative path does not keep. */
+int oic_load_qualities(oic_ctx_t *ctx, const uint64_t *offsets, const uint8_t *quals);
 
 /* In-process sweep over the jobs of overlapInCorePartition (OIC/overlapInCorePartition.C, OverlapInCore.pm:184-233): the
  * pipeline starts one overlapInCore process per (hash range, query range) job, each re-opening the store and rebuilding its

@@ -30,6 +30,9 @@ const int32_t HOPELESS_MATCH = 90;           // OIC/overlapInCore.H:122
 const int32_t MAX_DISTINCT_OLAPS = 3;        // OIC/overlapInCore.H:151
 const int32_t MIN_INTERSECTION = 10;         // OIC/overlapInCore.H:171
 const int32_t SHIFT_SLACK = 1;               // OIC/overlapInCore.H:197
+const int32_t QUALITY_CUTOFF = 20;           // OIC/overlapInCore.H:190
+const int32_t BAD_WINDOW_LEN = 50;           // OIC/overlapInCore.H:80
+const int32_t BAD_WINDOW_VALUE = 8 * QUALITY_CUTOFF;   // OIC/overlapInCore.H:84 (the long window: 100 / 240, Process_String_Overlaps.C:616)
 const int32_t MIN_BRANCH_END_DIST = 20;      // LIBO/prefixEditDistance.C:40
 
 // ---------------------------------------------------------------------------------------
@@ -423,6 +426,10 @@ struct oracle_ctx {
   uint32_t n_overflow;
   bool left_end_screened, right_end_screened;
   int64_t a_olaps_for_frag, b_olaps_for_frag;
+  // -w
+  std::vector<uint8_t> quals;          // per base, same offsets as the bases
+  bool use_window_filter = false;
+  const uint8_t *s_quality = nullptr;  // qualities of the current query strand (reversed on the reverse strand)
 
   EditDist *ed = nullptr;
 
@@ -697,8 +704,9 @@ void oracle_ctx::process_string_olaps(const char *S, int32_t len, uint32_t id, i
 namespace {
 
 // Add_Overlap: OIC/overlapInCore-Process_String_Overlaps.C:220-289
-void add_overlap(bool partial, int32_t s_lo, int32_t s_hi, int32_t t_lo, int32_t t_hi, double qual, int32_t delta_ct,
-                 OlapInfo *olap, int &ct) {
+// returns the slot whose alignment -- and therefore delta list (:253-256,278-282) -- was set, or -1
+int add_overlap(bool partial, int32_t s_lo, int32_t s_hi, int32_t t_lo, int32_t t_hi, double qual, int32_t delta_ct,
+                OlapInfo *olap, int &ct) {
   if (!partial) {
     int32_t new_diag = t_lo - s_lo;
     for (int i = 0; i < ct; i++) {
@@ -716,12 +724,13 @@ void add_overlap(bool partial, int32_t s_lo, int32_t s_hi, int32_t t_lo, int32_t
           o.s_lo = s_lo; o.s_hi = s_hi; o.t_lo = t_lo; o.t_hi = t_hi;
           o.quality = qual;
           o.delta_ct = delta_ct;
+          return i;
         }
-        return;
+        return -1;
       }
     }
   }
-  if (ct >= MAX_DISTINCT_OLAPS) return;
+  if (ct >= MAX_DISTINCT_OLAPS) return -1;
   OlapInfo &o = olap[ct];
   o.s_lo = o.s_left_boundary = s_lo;
   o.s_hi = o.s_right_boundary = s_hi;
@@ -731,6 +740,23 @@ void add_overlap(bool partial, int32_t s_lo, int32_t s_hi, int32_t t_lo, int32_t
   o.delta_ct = delta_ct;
   o.min_diag = o.max_diag = t_lo - s_lo;
   ct++;
+  return ct - 1;
+}
+
+// Has_Bad_Window (Process_String_Overlaps.C:365-388): does any window_len-long stretch of a[0 .. n) sum to threshold or more
+bool has_bad_window(const std::vector<int8_t> &a, int window_len, int threshold) {
+  const int n = (int)a.size();
+  if (n < window_len) return false;
+  int32_t sum = 0;
+  int i = 0, j = 0;
+  for (i = 0; i < window_len; i++) sum += a[i];
+  if (sum >= threshold) return true;
+  while (i < n) {
+    sum -= a[j++];
+    sum += a[i++];
+    if (sum >= threshold) return true;
+  }
+  return false;
 }
 
 // Lies_On_Alignment: :305-326
@@ -829,6 +855,7 @@ void oracle_ctx::process_matches(PairAcc &pa, const char *S, int32_t s_len, uint
   }
 
   OlapInfo distinct[MAX_DISTINCT_OLAPS];
+  std::vector<int32_t> olap_delta[MAX_DISTINCT_OLAPS];   // Olap_Info_t.delta: the delta list of the alignment each slot holds
   int distinct_ct = 0;
   int overlaps_output = 0;
 
@@ -878,8 +905,10 @@ void oracle_ctx::process_matches(PairAcc &pa, const char *S, int32_t s_len, uint
       if (1 + s_hi - s_lo >= P.min_olap_len && 1 + t_hi - t_lo >= P.min_olap_len) {
         int32_t olap_len = 1 + std::min(s_hi - s_lo, t_hi - t_lo);
         double quality = (double)errors / olap_len;
-        if (errors <= error_bound(P.max_erate, olap_len))
-          add_overlap(partial, s_lo, s_hi, t_lo, t_hi, quality, (int32_t)ed->left_delta.size(), distinct, distinct_ct);
+        if (errors <= error_bound(P.max_erate, olap_len)) {
+          const int slot = add_overlap(partial, s_lo, s_hi, t_lo, t_hi, quality, (int32_t)ed->left_delta.size(), distinct, distinct_ct);
+          if (slot >= 0) olap_delta[slot] = ed->left_delta;
+        }
       }
     }
 
@@ -903,6 +932,31 @@ void oracle_ctx::process_matches(PairAcc &pa, const char *S, int32_t s_len, uint
     else { if (P.unique_olap) combine_into_one(distinct, distinct_ct, deleted); else merge_intersecting(distinct, distinct_ct, deleted); }
     for (int i = 0; i < distinct_ct; i++) {
       if (deleted[i]) continue;
+      if (use_window_filter) {   // :562-620: quality-weighted differences along the alignment, then two sliding windows
+        const OlapInfo &p = distinct[i];
+        const uint8_t *tq = quals.data() + offsets[t_id - 1];
+        std::vector<int8_t> q_diff;
+        int32_t si = p.s_lo, tj = p.t_lo;
+        auto same = [&](int32_t a_, int32_t b_) { return S[a_] == T[b_] || S[a_] == 'n' || T[b_] == 'n'; };
+        for (int32_t dl : olap_delta[i]) {
+          const int32_t len = dl < 0 ? -dl : dl;
+          for (int32_t n = 1; n < len; n++) {
+            int32_t d = same(si, tj) ? 0 : std::min((int32_t)std::min(s_quality[si], tq[tj]), (int32_t)QUALITY_CUTOFF);
+            q_diff.push_back((int8_t)d);
+            si++; tj++;
+          }
+          int32_t d;
+          if (dl > 0) { d = s_quality[si]; si++; } else { d = tq[tj]; tj++; }
+          q_diff.push_back((int8_t)std::min(d, (int32_t)QUALITY_CUTOFF));
+        }
+        while (si <= p.s_hi) {
+          int32_t d = same(si, tj) ? 0 : std::min((int32_t)std::min(s_quality[si], tq[tj]), (int32_t)QUALITY_CUTOFF);
+          q_diff.push_back((int8_t)d);
+          si++; tj++;
+        }
+        if (has_bad_window(q_diff, BAD_WINDOW_LEN, BAD_WINDOW_VALUE)) { stats.bad_short_window++; continue; }
+        if (has_bad_window(q_diff, 100, 240)) { stats.bad_long_window++; continue; }
+      }
       if (partial) output_partial(s_id, t_id, dir, distinct[i], s_len, t_len);
       else output_overlap(s_id, s_len, dir, t_id, t_len, distinct[i]);
       overlaps_output++;
@@ -998,6 +1052,14 @@ oracle_ctx_t *oracle_create(const oracle_params_t *p, uint32_t n_reads, const ui
   return c;
 }
 
+void oracle_set_qualities(oracle_ctx_t *c, const uint64_t *offsets, const uint8_t *quals) {
+  // same layout as the bases (oracle_create): read i at c->offsets[i], one spare byte behind every read
+  c->quals.assign(c->bases.size(), 0);
+  for (uint32_t i = 0; i < c->n_reads; i++)
+    for (uint32_t j = 0; j < c->lengths[i]; j++) c->quals[c->offsets[i] + j] = quals[offsets[i] + j];
+  c->use_window_filter = !(c->P.max_erate > 0.06);   // OIC/overlapInCore.C:416-421
+}
+
 void oracle_set_skip_kmers(oracle_ctx_t *c, uint64_t n, const char *kmers) {
   c->skip_kmers.clear();
   for (uint64_t i = 0; i < n; i++) c->skip_kmers.push_back(std::string(kmers + i * c->P.kmer_len, c->P.kmer_len));
@@ -1038,14 +1100,21 @@ int oracle_run(oracle_ctx_t *c) {
     if (end_ref < bgn_ref) last_processed = 0;
 
     std::string rc;
+    std::vector<uint8_t> qrev;
     for (uint32_t fi = bgn_ref; fi <= last_processed && fi >= 1; fi++) {
       if (!c->ref_ok[fi - 1]) continue;
       uint32_t len = c->lengths[fi - 1];
       if ((int64_t)len < (int64_t)P.min_olap_len) continue;
       const char *seq = c->read_seq(fi);
+      if (c->use_window_filter) c->s_quality = c->quals.data() + c->offsets[fi - 1];
       c->find_overlaps(seq, (int32_t)len, fi, 0);
       rc.assign(len, 0);
       for (uint32_t i = 0; i < len; i++) rc[i] = rc_char(seq[len - 1 - i]);
+      if (c->use_window_filter) {   // reverseComplement(seq, qlt, len) reverses the qualities with the bases (AS_UTL_reverseComplement.C:114-143)
+        qrev.assign(len, 0);
+        for (uint32_t i = 0; i < len; i++) qrev[i] = c->s_quality[len - 1 - i];
+        c->s_quality = qrev.data();
+      }
       c->find_overlaps(rc.c_str(), (int32_t)len, fi, 1);
     }
 

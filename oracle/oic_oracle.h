@@ -76,6 +76,7 @@ typedef struct {
   uint64_t ext_calls, ext_cells, ext_words; /* C and W of I_ext = 6C + 4W */
   uint32_t n_hash_blocks;
   uint32_t last_end_hash_id;
+  uint64_t bad_short_window, bad_long_window;   /* -w: overlaps rejected by the 50- / 100-base window (appended: older fields keep their offsets) */
 } oracle_stats_t;
 
 typedef struct oracle_ctx oracle_ctx_t;
@@ -87,6 +88,10 @@ oracle_ctx_t *oracle_create(const oracle_params_t *p, uint32_t n_reads, const ui
                             const uint8_t *hash_ok, const uint8_t *ref_ok);
 /* skip k-mers: n strings of exactly kmer_len chars, concatenated (OIC/...Build_Hash_Index.C:233-286) */
 void oracle_set_skip_kmers(oracle_ctx_t *c, uint64_t n, const char *kmers);
+/* -w, the window filter (OIC/overlapInCore.C:398,417-419; Process_String_Overlaps.C:365-388,560-620): quals holds one quality value per
+ * base (0..93, what gkReadData_getQualities returns: a QVAL constant or the UQLT bytes), read i at quals[offsets[i-1] ..] (the offsets
+ * given to oracle_create).  Calling this turns the filter on (it stays off when --maxerate > 0.06, as in main()). */
+void oracle_set_qualities(oracle_ctx_t *c, const uint64_t *offsets, const uint8_t *quals);
 /* which stage dumps to keep (bit 0 pairs+matches, bit 1 extensions, bit 2 k-mer index of the LAST hash block) */
 void oracle_set_dump(oracle_ctx_t *c, uint32_t mask);
 /* run the whole OverlapDriver loop (OIC/overlapInCore.C:190-300); returns 0 */

@@ -74,6 +74,19 @@ CASES = {
     "olap_limit_blocks": dict(gen=dict(genome_len=36000, coverage=18, len_min=700, len_max=3000, err=0.015, seed=4103),
                               erate="0.045", params=dict(hash_bits=17, hash_load=0.75, frag_olap_limit=7, max_hash_strings=120,
                                                          use_hopeless_check=0), threads=4),
+    # -w: window filter (Process_String_Overlaps.C:365-388,560-620).  Reads at 3 % error so that a good share of the overlaps has a
+    # 50-base window with >= 8 errors.  The reference's gatekeeperCreate stores one quality per read (its library's default QV, 20);
+    # one thread: the two "Rejected by ... window" counters are unsynchronised globals in the reference
+    "window_filter": dict(gen=dict(genome_len=30000, coverage=14, len_min=800, len_max=2500, err=0.03, seed=4201),
+                          erate="0.06", params=dict(hash_bits=17, hash_load=0.75, use_window_filter=1), threads=1),
+    # four libraries with default QVs 12 / 31 / 17 / 25 (min(query, hash read) and the cap at 20 both matter), -m
+    "window_libs": dict(gen=dict(genome_len=30000, coverage=16, len_min=800, len_max=2500, err=0.035, seed=4202),
+                        erate="0.06", params=dict(hash_bits=17, hash_load=0.75, use_window_filter=1, unique_olap=0), threads=1,
+                        lib_qv=[12, 31, 17, 25]),
+    # -w together with -l, on reads with N (the filter's base comparison has the same wildcard / NUL rules as the aligner)
+    "window_limit_n": dict(gen=dict(genome_len=26000, coverage=18, len_min=900, len_max=2400, err=0.03, seed=4203),
+                           erate="0.06", params=dict(hash_bits=16, hash_load=0.75, use_window_filter=1, frag_olap_limit=4), threads=1,
+                           lib_qv=[25, 15], inject_n=dict(rate=0.001, runs=12, seed=7)),
     # empty output: sparse reads of a large genome share no k-mer runs worth an overlap
     "no_overlaps": dict(gen=dict(genome_len=2000000, coverage=0.02, len_min=900, len_max=1500, err=0.02, seed=12),
                         erate="0.06", params=dict(hash_bits=14, hash_load=0.75), threads=2),
@@ -86,6 +99,10 @@ def build_case(name):
     reads = H.gen_reads(**c["gen"])
     if c.get("inject_n"):
         inject_n(reads, **c["inject_n"])
+    if c.get("lib_qv"):   # consecutive libraries of (almost) equal read count, each with its own default QV
+        import numpy as np
+        k = len(c["lib_qv"])
+        reads.read_qv = np.array([c["lib_qv"][min(k - 1, i * k // reads.n)] for i in range(reads.n)], dtype=np.uint8)
     over = dict(c["params"])
     if over.pop("minkmers", False):
         import math

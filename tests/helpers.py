@@ -53,17 +53,28 @@ class GenParams(C.Structure):
 class Reads:
     """Reads in memory: ASCII bases concatenated (uint8), offsets[n+1], lengths[n]. IDs are 1-based."""
 
-    def __init__(self, bases, offsets, lengths):
+    def __init__(self, bases, offsets, lengths, read_qv=None):
         self.bases, self.offsets, self.lengths = bases, offsets, lengths
         self.n = len(lengths)
+        # optional: one quality value per READ.  The reference's gatekeeperCreate is built with DO_NOT_STORE_QVs (ST/gatekeeperCreate.C:
+        # 49-54): it stores no per-base qualities, every read gets a QVAL chunk = its library's default QV (`qv N` in the .gkp file,
+        # :663-664; 20 unless set).  make_store writes one library per run of equal values.
+        self.read_qv = read_qv
+
+    def qualities(self, default_qv=20):
+        """what gkReadData_getQualities gives the overlapper (ST/gkStore.C:140-145): the read's QVAL constant for every base"""
+        q = np.full(int(self.offsets[-1]), default_qv, dtype=np.uint8)
+        if self.read_qv is not None:
+            q[:] = np.repeat(np.asarray(self.read_qv, dtype=np.uint8), np.asarray(self.lengths, dtype=np.int64))
+        return q
 
     def seq(self, rid):
         o = int(self.offsets[rid - 1])
         return self.bases[o:o + int(self.lengths[rid - 1])].tobytes().decode()
 
-    def write_fasta(self, path):
+    def write_fasta(self, path, first=0, last=None):
         with open(path, "wb") as f:
-            for i in range(self.n):
+            for i in range(first, self.n if last is None else last):
                 f.write(b">read%d\n" % (i + 1))
                 o = int(self.offsets[i])
                 f.write(self.bases[o:o + int(self.lengths[i])].tobytes())
@@ -209,11 +220,24 @@ def run_meryl(store, K, threshold, workdir, threads=4):
 def make_store(reads, workdir, minlength=0):
     """reads -> FASTA -> reference gatekeeperCreate -> <workdir>/t.gkpStore"""
     os.makedirs(workdir, exist_ok=True)
-    fa = os.path.join(workdir, "reads.fasta")
-    reads.write_fasta(fa)
     gkp = os.path.join(workdir, "in.gkp")
-    with open(gkp, "w") as f:
-        f.write("name reads\npreset pacbio-corrected\n%s\n" % fa)
+    qv = getattr(reads, "read_qv", None)
+    if qv is None:
+        fa = os.path.join(workdir, "reads.fasta")
+        reads.write_fasta(fa)
+        with open(gkp, "w") as f:
+            f.write("name reads\npreset pacbio-corrected\n%s\n" % fa)
+    else:   # one library (with its own default QV) per run of reads with the same value; read IDs stay in order
+        with open(gkp, "w") as f:
+            i = 0
+            while i < reads.n:
+                j = i
+                while j < reads.n and qv[j] == qv[i]:
+                    j += 1
+                fa = os.path.join(workdir, "reads_%d.fasta" % i)
+                reads.write_fasta(fa, i, j)
+                f.write("name lib%d\npreset pacbio-corrected\nqv %d\n%s\n" % (i, int(qv[i]), fa))
+                i = j
     store = os.path.join(workdir, "t.gkpStore")
     subprocess.check_call(["rm", "-rf", store])
     subprocess.check_call([os.path.join(REF_DIR, "gatekeeperCreate"), "-minlength", str(minlength), "-o", store, gkp],
@@ -286,6 +310,7 @@ EXT_DT = np.dtype([("q_id", np.uint32), ("h_id", np.uint32), ("strand", np.uint3
                    ("m_offset", np.int32), ("m_len", np.int32), ("m_start", np.int32),
                    ("s_lo", np.int32), ("s_hi", np.int32), ("t_lo", np.int32), ("t_hi", np.int32),
                    ("errors", np.int32), ("kind", np.int32), ("delta_len", np.int32), ("delta_hash", np.int32)])
+WINDOW_FIELDS = ["bad_short_window", "bad_long_window"]
 STATS_FIELDS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skipped", "multi_overlap",
                 "total_overlaps", "contained", "dovetail", "n_hash_bases", "n_inserts", "n_distinct",
                 "n_query_bases", "n_windows", "n_found", "n_refs", "n_add_ref", "ext_calls", "ext_cells",
@@ -293,7 +318,8 @@ STATS_FIELDS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skip
 
 
 class OracleStats(C.Structure):
-    _fields_ = [(n, C.c_uint64) for n in STATS_FIELDS] + [("n_hash_blocks", C.c_uint32), ("last_end_hash_id", C.c_uint32)]
+    _fields_ = ([(n, C.c_uint64) for n in STATS_FIELDS] + [("n_hash_blocks", C.c_uint32), ("last_end_hash_id", C.c_uint32)] +
+                [(n, C.c_uint64) for n in WINDOW_FIELDS])
 
 
 def strtof(s):
@@ -309,6 +335,7 @@ def oracle_lib():
                                   C.c_void_p, C.c_void_p]
     lib.oracle_set_skip_kmers.argtypes = [C.c_void_p, C.c_uint64, C.c_char_p]
     lib.oracle_set_dump.argtypes = [C.c_void_p, C.c_uint32]
+    lib.oracle_set_qualities.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.oracle_run.argtypes = [C.c_void_p]
     for name in ("overlaps", "pairs", "matches", "exts"):
         getattr(lib, "oracle_num_" + name).restype = C.c_uint64
@@ -346,29 +373,34 @@ def default_params(**kw):
     d = dict(kmer_len=22, max_erate=strtof("0.06"), min_olap_len=500, partial=0, unique_olap=1,
              use_hopeless_check=1, hash_bits=22, hash_load=0.6, max_hash_strings=10000,
              max_hash_data_len=100000000, frag_olap_limit=2 ** 64 - 1, filter_by_kmer_count=0,
-             num_threads=1, bgn_hash_id=1, end_hash_id=2 ** 32 - 1, bgn_ref_id=1, end_ref_id=2 ** 32 - 1)
+             num_threads=1, bgn_hash_id=1, end_hash_id=2 ** 32 - 1, bgn_ref_id=1, end_ref_id=2 ** 32 - 1, use_window_filter=0)
     d.update(kw)
     if d["max_erate"] > 0.06:
         d["use_hopeless_check"] = 0
+        d["use_window_filter"] = 0   # OIC/overlapInCore.C:416-421
     return d
 
 
 def run_oracle(reads, params, dump=0, skip_kmers=None):
-    """Run the CPU restatement. Returns dict(overlaps, stats, pairs, matches, exts, index)."""
+    """Run the CPU restatement. Returns dict(overlaps, stats, pairs, matches, exts, index).  params["use_window_filter"]: -w, with the
+    qualities of `reads` (Reads.qualities())."""
     lib = oracle_lib()
-    p = OracleParams(**params)
+    p = OracleParams(**{k: v for k, v in params.items() if k != "use_window_filter"})
     offs = np.ascontiguousarray(reads.offsets[:-1], dtype=np.uint64)
     lens = np.ascontiguousarray(reads.lengths, dtype=np.uint32)
     bases = np.ascontiguousarray(reads.bases)
     ctx = lib.oracle_create(C.byref(p), reads.n, offs.ctypes.data, lens.ctypes.data, bases.ctypes.data, None, None)
     if skip_kmers:
         lib.oracle_set_skip_kmers(ctx, len(skip_kmers), "".join(skip_kmers).encode())
+    if params.get("use_window_filter"):
+        q = reads.qualities()
+        lib.oracle_set_qualities(ctx, offs.ctypes.data, q.ctypes.data)
     lib.oracle_set_dump(ctx, dump)
     lib.oracle_run(ctx)
     res = {}
     res["overlaps"] = _copy(lib.oracle_overlaps(ctx), lib.oracle_num_overlaps(ctx), OVERLAP_DT)
     st = lib.oracle_stats(ctx).contents
-    res["stats"] = {n: getattr(st, n) for n in STATS_FIELDS + ["n_hash_blocks", "last_end_hash_id"]}
+    res["stats"] = {n: getattr(st, n) for n in STATS_FIELDS + ["n_hash_blocks", "last_end_hash_id"] + WINDOW_FIELDS}
     res["pairs"] = _copy(lib.oracle_pairs(ctx), lib.oracle_num_pairs(ctx), PAIR_DT)
     res["matches"] = _copy(lib.oracle_matches(ctx), lib.oracle_num_matches(ctx), MATCH_DT)
     res["exts"] = _copy(lib.oracle_exts(ctx), lib.oracle_num_exts(ctx), EXT_DT)
@@ -392,6 +424,8 @@ def oic_args(params, erate_str):
         a.append("-m")
     if not params["use_hopeless_check"] and float(erate_str) <= 0.06:
         a.append("-z")
+    if params.get("use_window_filter"):
+        a.append("-w")
     a += ["-k", str(params["kmer_len"]), "--hashbits", str(params["hash_bits"]),
           "--hashload", repr(params["hash_load"]), "--maxerate", erate_str,
           "--minlength", str(params["min_olap_len"])] + (["--minkmers"] if params.get("filter_by_kmer_count") else []) + [

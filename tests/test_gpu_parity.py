@@ -20,7 +20,8 @@ import helpers as H
 pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-STAT_KEYS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skipped", "multi_overlap", "contained", "dovetail"]
+STAT_KEYS = ["kmer_hits_without_olap", "kmer_hits_with_olap", "kmer_hits_skipped", "multi_overlap", "contained", "dovetail",
+             "bad_short_window", "bad_long_window"]
 WORK_KEYS = ["n_hash_bases", "n_inserts", "n_distinct", "n_query_bases", "n_windows", "n_found", "n_refs", "n_add_ref",
              "ext_calls", "ext_cells", "ext_words", "n_hash_blocks", "last_end_hash_id"]
 
@@ -29,6 +30,8 @@ def make_overlapper(reads, P, skip=None, debug=0):
     from canu_b200 import api
     ov = api.Overlapper(P)
     ov.load_reads(reads.bases, reads.offsets[:-1], reads.lengths)
+    if P.get("use_window_filter"):
+        ov.load_qualities(reads.qualities(), reads.offsets[:-1])
     if skip:
         ov.set_skip_kmers(skip)
     ov.set_debug(debug)
@@ -62,6 +65,9 @@ def test_overlaps_vs_golden_and_oracle(name):
         assert st[k] == res["stats"][k], k
     ref_map = {"Kmer hits without olaps": "kmer_hits_without_olap", "Kmer hits with olaps": "kmer_hits_with_olap",
                "Multiple overlaps/pair": "multi_overlap", "Contained overlaps": "contained", "Dovetail overlaps": "dovetail"}
+    if P.get("use_window_filter"):   # (these cases run the reference with one thread: its two window counters are racy otherwise)
+        ref_map.update({"Rejected by short window": "bad_short_window", "Rejected by long window": "bad_long_window"})
+        assert st["bad_short_window"] + st["bad_long_window"] > 0, "the case is meant to reject something"
     for k, v in ref_map.items():
         assert meta["stats"][k] == st[v], k
 
