@@ -228,6 +228,12 @@ def main():
                     help="N > 1: every rank builds 1/N of the hash table and the slices are exchanged by ncclAllGather (default); rank 0 "
                          "builds and ncclBroadcasts the block; or every rank builds its own copy (no collective)")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json shape; c3 is the bench line")
+    ap.add_argument("--shard", default="blocks", choices=["interleaved", "blocks"],
+                    help="N > 1: how the N query blocks are dealt to the ranks: one contiguous block per rank (the reference's own partition, "
+                         "default) or read by read (every rank gets the same mix; measured no faster, see DESIGN.md section 6)")
+    ap.add_argument("--as-rank", default=None, metavar="R/W",
+                    help="diagnostic: ONE GPU runs the job that rank R of a W-rank run would run (its query block, the same hash block; no "
+                         "collective) -- separates the spread between the ranks' query blocks from anything the box does to a multi-GPU run")
     ap.add_argument("--check", action="store_true",
                     help="after the timed runs: gather every rank's records on the host of rank 0 and compare the multiset (all stored fields) "
                          "with the reference binary run on the same job (exit 1 on any difference)")
@@ -235,6 +241,10 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    as_rank = None
+    if a.as_rank:
+        assert world == 1, "--as-rank is a single-GPU diagnostic"
+        as_rank = tuple(int(x) for x in a.as_rank.split("/"))
 
     wl = set_workload(a.workload)
     if MODE == "self" and world > 1:
@@ -244,8 +254,9 @@ def main():
         metric = "overlapInCore query Mbp/sec (+overlaps/sec), workload %s" % a.workload
     config = {"workload": wl["desc"],
               "hash_block_mbp": BLOCK_BASES * a.scale / 1e6, "query_block_mbp_per_gpu": BLOCK_BASES * a.scale / 1e6,
-              "parallelism": "query blocks sharded over %d GPU(s), hash block replicated%s" % (
-                  world, "" if world == 1 else {"sharded": " by NCCL: every rank builds 1/N of the table, ncclAllGather of the slices (oic_build_hash_index_sharded)",
+              "parallelism": "query blocks sharded over %d GPU(s)%s, hash block replicated%s" % (
+                  world, "" if world == 1 else (" read by read (rank r takes every N-th query read)" if a.shard == "interleaved" else " one block per rank"),
+                  "" if world == 1 else {"sharded": " by NCCL: every rank builds 1/N of the table, ncclAllGather of the slices (oic_build_hash_index_sharded)",
                                                 "broadcast": " by ncclBroadcast from rank 0 (oic_hash_block_replicate)",
                                                 "rebuild": " by rebuilding it on every rank (no collective)"}[a.replicate]),
               "l2": "inputs larger than L2 (k-mer table + occurrence array > 1 GB per block); no flush needed",
@@ -302,12 +313,15 @@ def main():
         hash_range, query_range = (1, reads.n), (1, reads.n)
     else:
         # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
-        reads = gen_blocks(genome, world + 1, block, SEED)
-        blocks = shard.split_blocks(reads.n, world + 1)
-        rj = shard.RankJob(blocks, rank)
+        gen_world, gen_rank = (as_rank[1], as_rank[0]) if as_rank else (world, rank)
+        reads = gen_blocks(genome, gen_world + 1, block, SEED)
+        blocks = shard.split_blocks(reads.n, gen_world + 1)
+        rj = shard.RankJob(blocks, gen_rank, interleave=(a.shard == "interleaved"))
         hb, he, qb, qe, n_q, n_h = rj.hb, rj.he, rj.qb, rj.qe, rj.n_q, rj.n_h
-        q_bases_rank = int(reads.lengths[qb - 1:qe].sum())
-        q_bases_all = int(reads.lengths[:hb - 1].sum())
+        q_bases_rank = int(reads.lengths[rj.q_ids - 1].sum())
+        q_bases_all = q_bases_rank if as_rank else int(reads.lengths[:hb - 1].sum())
+        if as_rank:
+            config["as_rank"] = "the job of rank %d of a %d-rank run, alone on one GPU (diagnostic)" % as_rank
         P = params_for(he - hb + 1, reads.n)
         # this rank needs its query block and the hash block, gathered into one pinned host buffer in a local ID space
         # (queries 1..n_q, hash n_q+1..n_q+n_h: query ID < hash ID, as in the sweep); canu_b200/shard.py maps records back

@@ -28,12 +28,12 @@ def _pack(ov):
     return pack_records(ov)
 
 
-def _worker(rank, world, port, outdir):
+def _worker(rank, world, port, outdir, interleave=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     reads = H.gen_reads(30000, 3 * 6, 800, 2000, 0.02, 808)
     blocks = shard.split_blocks(reads.n, world + 1)
-    job = shard.RankJob(blocks, rank)
+    job = shard.RankJob(blocks, rank, interleave=interleave)
     bases, offs, lens = job.select(reads.bases, reads.offsets[:-1], reads.lengths)
     P = H.default_params(hash_bits=16, hash_load=0.75, end_hash_id=reads.n, end_ref_id=reads.n, max_hash_strings=reads.n)
     LP = job.local_params(P)
@@ -46,9 +46,10 @@ def _worker(rank, world, port, outdir):
     dist.destroy_process_group()
 
 
-def test_two_rank_split_equals_unsharded(tmp_path):
+@pytest.mark.parametrize("interleave", [False, True], ids=["blocks", "interleaved"])
+def test_two_rank_split_equals_unsharded(tmp_path, interleave):
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), interleave), nprocs=world, join=True)
     got = np.load(str(tmp_path / "gathered.npy"))
     reads = H.gen_reads(30000, 3 * 6, 800, 2000, 0.02, 808)
     blocks = shard.split_blocks(reads.n, world + 1)
@@ -73,3 +74,27 @@ def test_split_blocks_and_id_mapping():
     assert g[:, :2].tolist() == [[251, 751], [500, 1003]]
     LP = job.local_params(dict(max_hash_strings=1))
     assert (LP["bgn_ref_id"], LP["end_ref_id"], LP["bgn_hash_id"], LP["end_hash_id"]) == (1, 250, 251, 503)
+
+
+def test_interleaved_id_mapping():
+    """rank r of N takes query reads r+1, r+1+N, ... of ALL query blocks; local IDs map back to those store IDs"""
+    blocks = shard.split_blocks(1003, 4)            # hash block 751-1003, query reads 1-750
+    jobs = [shard.RankJob(blocks, r, interleave=True) for r in range(3)]
+    assert sorted(int(i) for j in jobs for i in j.q_ids) == list(range(1, 751))
+    assert [j.n_q for j in jobs] == [250, 250, 250]
+    job = jobs[1]
+    assert job.q_ids[:3].tolist() == [2, 5, 8] and not job.contiguous
+    rec = np.zeros((3, 6), dtype=np.uint32)
+    rec[0, :2] = (1, 251)        # first query of the rank, first hash read
+    rec[1, :2] = (503, 250)      # last hash read (local 250 + 253), last query of the rank -- either column may hold either
+    rec[2, :2] = (3, 252)
+    g = job.to_global(rec)
+    assert g[:, :2].tolist() == [[2, 751], [1003, 749], [8, 752]]
+    # select() lays the strided reads out back to back, in rank order
+    lengths = np.arange(1, 1004, dtype=np.uint32)
+    offsets = np.zeros(1003, dtype=np.uint64)
+    np.cumsum(lengths[:-1], out=offsets[1:])
+    bases = np.repeat((np.arange(1003) % 251).astype(np.uint8), lengths)
+    out, offs, lens = job.select(bases, offsets, lengths)
+    assert lens[:3].tolist() == [2, 5, 8] and lens[250] == 751
+    assert out[int(offs[1])] == (5 - 1) % 251 and out[int(offs[250])] == 750 % 251
