@@ -99,32 +99,94 @@ def gen_blocks(genome_len, n_blocks, block_bases, seed):
     return H.gen_reads(genome_len, cov, LEN_MIN, LEN_MAX, READ_ERR, seed, sub_only=SUB_ONLY, **rep)
 
 
+def gen_job(genome_len, world, block_bases, seed):
+    """(reads, blocks) of the step at `world` GPUs: `world` query blocks + the hash block, IDs laid out [Q0 .. Q(world-1) | H] (every
+    query ID below every hash ID).  The generator makes read i from (seed, i) alone, so the job is the SAME at every N where it can
+    be: H = generated reads [0, per), Q_r = generated reads [(r+1) per, (r+2) per), per = the reads of one block -- rank 0 of any
+    run searches the job of the 1-GPU run, rank r the same block at every N > r.  (Until r2p the hash block was the LAST block of an
+    (N+1)-block set: a different hash block and a different block 0 at every N, 12.8 to 13.6 G DP cells on rank 0, which the
+    driver's N x (1-GPU rate) comparison booked as scaling loss or gain.)"""
+    from canu_b200 import shard
+    g = gen_blocks(genome_len, world + 1, block_bases, seed)
+    per = int(block_bases / (0.5 * (LEN_MIN + LEN_MAX)) + 0.5)
+    n = min(g.n, per * (world + 1))
+    cut, end = int(g.offsets[per]), int(g.offsets[n])
+    import helpers as H
+    lengths = np.concatenate([g.lengths[per:n], g.lengths[:per]])
+    offsets = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum(lengths, out=offsets[1:])
+    bases = np.empty(end, dtype=np.uint8)
+    bases[:end - cut] = g.bases[cut:end]
+    bases[end - cut:] = g.bases[:cut]
+    blocks = [(r * per + 1, min((r + 1) * per, n - per)) for r in range(world)] + [(n - per + 1, n)]
+    return H.Reads(bases, offsets, lengths), blocks
+
+
 class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons of one GPU DURING the timed region (the recipe's clocks line).  Read through NVML inside this
+    process (nvidia_ml_py: one nvmlInit, then two cheap queries per sample): forking `nvidia-smi` 5x a second attaches a new NVML
+    client to every GPU of the box each time, and the step of a run next to it showed gaps of 5-35 ms between kernels (r2q: extend
+    stage 75.6 / 100.4 ms around the same 65.9 ms of kernels).  OIC_CLOCK_SAMPLER=smi|nvml|off selects; `smi` is the fallback
+    when NVML cannot be loaded."""
+
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
     def __init__(self, gpu_index):
         super().__init__(daemon=True)
         self.gpu = gpu_index
         self.stop_flag = False
-        self.rows = []
+        self.rows = []          # (sm MHz, max MHz, [hw_slowdown, hw_thermal, sw_thermal, sw_power_cap])
+        self.mode = os.environ.get("OIC_CLOCK_SAMPLER", "nvml")
+        self.nv, self.h = None, None
+        if self.mode == "nvml":
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                # NVML indexes the physical GPUs: follow CUDA_VISIBLE_DEVICES when it is a plain list of indices
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                phys = gpu_index
+                if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                    phys = int(vis.split(",")[gpu_index])
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+                self.nv = pynvml
+                self.gpu = phys
+            except Exception:
+                self.mode = "smi"
 
-    def run(self):
+    def sample_nvml(self):
+        nv = self.nv
+        sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+        mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        bits = [nv.nvmlClocksEventReasonHwSlowdown, nv.nvmlClocksEventReasonHwThermalSlowdown, nv.nvmlClocksEventReasonSwThermalSlowdown,
+                nv.nvmlClocksEventReasonSwPowerCap]
+        self.rows.append((float(sm), float(mx), [bool(r & b) for b in bits]))
+
+    def sample_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        out = subprocess.check_output(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                      stderr=subprocess.DEVNULL, timeout=5).decode().strip()
+        r = [x.strip() for x in out.split(",")]
+        self.rows.append((float(r[0]), float(r[1]), [x.lower().startswith("active") for x in r[2:6]]))
+
+    def run(self):
+        if self.mode == "off":
+            return
         while not self.stop_flag:
             try:
-                out = subprocess.check_output(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                              stderr=subprocess.DEVNULL, timeout=5).decode().strip()
-                self.rows.append([x.strip() for x in out.split(",")])
+                self.sample_nvml() if self.mode == "nvml" else self.sample_smi()
             except Exception:
-                pass
-            time.sleep(0.2)
+                if self.mode == "nvml" and not self.rows:
+                    self.mode = "smi"    # an NVML build without these queries: fall back to the command-line tool
+            time.sleep(0.05 if self.mode == "nvml" else 0.2)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = sorted({self.NAMES[i] for r in self.rows for i in range(4) if r[2][i]})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+                "samples": len(sm), "source": {"nvml": "NVML in-process, 20 Hz", "smi": "nvidia-smi, 5 Hz", "off": "disabled"}[self.mode]}
 
 
 def reference_records(store, ovb):
@@ -158,8 +220,7 @@ def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=No
                   % (cores, "the full job of the step" if full else "genome %.1f Mbp at the same coverage, same read model/flags" % (g / 1e6),
                      reads.n, qbases / 1e6))
     else:
-        reads = gen_blocks(g, world + 1, blk, seed)
-        blocks = shard.split_blocks(reads.n, world + 1)
+        reads, blocks = gen_job(g, world, blk, seed)
         hb, he = blocks[-1]
         qbases = int(reads.lengths[:hb - 1].sum())
         P = params_for(he - hb + 1, reads.n, threads=cores)
@@ -314,8 +375,7 @@ def main():
     else:
         # reads: `world` query blocks + 1 hash block, all sampled from the same genome (every rank generates the same set)
         gen_world, gen_rank = (as_rank[1], as_rank[0]) if as_rank else (world, rank)
-        reads = gen_blocks(genome, gen_world + 1, block, SEED)
-        blocks = shard.split_blocks(reads.n, gen_world + 1)
+        reads, blocks = gen_job(genome, gen_world, block, SEED)
         rj = shard.RankJob(blocks, gen_rank, interleave=(a.shard == "interleaved"))
         hb, he, qb, qe, n_q, n_h = rj.hb, rj.he, rj.qb, rj.qe, rj.n_q, rj.n_h
         q_bases_rank = int(reads.lengths[rj.q_ids - 1].sum())

@@ -17,6 +17,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <mutex>
 #include <string>
@@ -33,11 +34,17 @@ namespace {
 
 thread_local std::string g_create_error;   // error text of the last failed context-less call on THIS thread (oic_last_error(NULL))
 
+// Bumped by every cudaMalloc / cudaFree of this library: what cudaMemGetInfo last said stays true while it stands still.  The
+// steady state of a job stream (same block sizes, buffers grown to size) then makes NO call that enters the kernel-mode driver
+// -- cudaMalloc, cudaFree and cudaMemGetInfo do, and on a box whose other GPUs are busy they were seen to take 5-100 ms at random.
+std::atomic<uint64_t> g_alloc_epoch{1};
+
 struct DevBuf {
   void *p = nullptr;
   size_t cap = 0;
   cudaError_t ensure(size_t bytes) {
     if (bytes <= cap) return cudaSuccess;
+    g_alloc_epoch.fetch_add(1, std::memory_order_relaxed);
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
     size_t want = bytes + bytes / 8 + 256;
@@ -46,7 +53,7 @@ struct DevBuf {
     if (e == cudaSuccess) cap = want;
     return e;
   }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  void release() { if (p) { cudaFree(p); g_alloc_epoch.fetch_add(1, std::memory_order_relaxed); } p = nullptr; cap = 0; }
   template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
@@ -150,6 +157,7 @@ struct oic_ctx {
   uint32_t hbk_bgn = 0, hbk_end = 0, hbk_strings = 0; uint64_t hbk_datalen = 0;
   bool job_mode = false;   // set by oic_set_job: only a job sweep reuses a block; a plain oic_build_hash_index always builds
   unsigned long long mem_avail = 0;   // device memory the pair stage may plan with (free + what it already holds)
+  uint64_t mem_avail_epoch = 0;       // g_alloc_epoch when it was asked: any allocation since makes it stale
   bool have_filter = false;      // Bloom filter of the current hash block is valid
 
   // search buffers
@@ -667,7 +675,6 @@ int build_hash_index_impl(oic_ctx *c, void *comm_arg, uint32_t bgn_id, uint32_t 
   c->stats.n_distinct += tot_distinct;
   c->stats.n_hash_blocks++;
   c->stats.last_end_hash_id = c->hb.last_id;
-  c->mem_avail = 0;   // the pair stage re-plans its scratch against what is free now
   if (last_id) *last_id = c->hb.last_id;
   return OIC_OK;
 }
@@ -750,7 +757,6 @@ static int load_reads_impl(oic_ctx_t *c, uint32_t first_id, uint32_t n, const ui
   cudaSetDevice(c->device);
   c->hash_ready = false;
   c->have_quals = false;
-  c->mem_avail = 0;
   c->first_id = first_id;
   c->n_reads = n;
   c->h_pos.resize(n + 1);
@@ -864,7 +870,6 @@ int oic_load_qualities(oic_ctx_t *c, const uint64_t *offsets, const uint8_t *qua
   CK(cudaStreamSynchronize(c->stream));
   c->tm.h2d_bytes += bytes;
   c->have_quals = true;
-  c->mem_avail = 0;
   return OIC_OK;
 }
 
@@ -1112,6 +1117,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
     // ---- K3 pairs
     if (n_pairs) {
       StageTimer t3(c, &c->tm.ms_extend);
+      const bool phase_trace = getenv("OIC_PHASE_CLOCKS") != nullptr;
+      const auto h0 = std::chrono::steady_clock::now();
+      auto h1 = h0, h2 = h0;
       // lean task kernel: the narrow-staging instance (more resident warps) unless the error rate makes wide bands the rule
       const bool narrow = !(P.max_erate > 0.06) && getenv("OIC_LEAN_WIDE") == nullptr;
       const unsigned sms = (unsigned)c->sm_count;
@@ -1121,12 +1129,14 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       // (pairs that overflow are rerun below with worst-case scratch on fewer warps)
       const unsigned long long worst = ((unsigned long long)c->max_rows + 2) * ((unsigned long long)c->max_rows + 2) * 17 / 16 + 8ull * c->max_rows + 1024;
       // memory budgets follow the device: a B200 has 180 GB, the c3 job needs 8 GB of history, the wide-band c2 job 51 GB.
-      // mem_avail = what is free now + what the two big scratch buffers already hold; it is asked again whenever the loaded
-      // reads or the hash block changed (they zero it) and after a failed allocation (cudaMemGetInfo costs about a millisecond).
-      if (c->mem_avail == 0) {
+      // mem_avail = what is free now + what the two big scratch buffers already hold; it is asked again whenever this library
+      // allocated or freed anything since (g_alloc_epoch) and after a failed allocation -- not per call: cudaMemGetInfo enters
+      // the kernel-mode driver (a millisecond alone, tens of milliseconds at random next to busy GPUs).
+      if (c->mem_avail == 0 || c->mem_avail_epoch != g_alloc_epoch.load(std::memory_order_relaxed) || getenv("OIC_MEMINFO_ALWAYS")) {
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
         c->mem_avail = (unsigned long long)free_b + c->d_vals.cap + c->d_dpool.cap;
+        c->mem_avail_epoch = g_alloc_epoch.load(std::memory_order_relaxed);
       }
       unsigned long long avail = c->mem_avail;
       unsigned long long vals_bytes = std::min<unsigned long long>(96ull << 30, std::min<unsigned long long>(std::max<unsigned long long>(12ull << 30, avail * 45 / 100), avail * 60 / 100));
@@ -1198,6 +1208,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.pstate = c->d_pstate.as<PairState>(); ea.pend_list = c->d_pend.as<uint32_t>(); ea.tasks = c->d_tasks.as<uint2>();
       ea.results = c->d_results.as<TaskResult>(); ea.alive = c->d_alive.as<uint8_t>(); ea.wide_list = c->d_wide.as<uint32_t>();
       ea.dpool = c->d_dpool.as<int32_t>(); ea.dpool_cap = dpool_cap;
+      h1 = std::chrono::steady_clock::now();
       cudaEventRecord(c->ev_k[0], c->stream);
       k_process_pairs<<<grid, EXT_WARPS * 32, 0, c->stream>>>(ea);
       cudaEventRecord(c->ev_k[1], c->stream);
@@ -1212,6 +1223,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         c->tm.launches += 3;
       }
       if (read_counters(c, hc)) return OIC_ERR_CUDA;
+      h2 = std::chrono::steady_clock::now();
       CK(cudaGetLastError());
       {
         float ms = 0;
@@ -1261,6 +1273,12 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
         c->tm.d2h_bytes += (uint64_t)hc.n_out * 24;
       }
       t3.stop();
+      if (phase_trace) {
+        const auto h3 = std::chrono::steady_clock::now();
+        auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[oic] pair stage host clock: plan + order %.2f ms | kernels until the counters are back %.2f ms | records to the host %.2f ms\n",
+                ms(h0, h1), ms(h1, h2), ms(h2, h3));
+      }
     }
   }
 
@@ -1454,7 +1472,6 @@ int oic_hash_block_commit(oic_ctx_t *c, const oic_hash_meta_t *m) {
   c->hbk_bgn = c->hbk_end = 0;   // a block that arrived from another rank is never mistaken for a local build
   c->stats.n_hash_blocks++;
   c->stats.last_end_hash_id = m->last_id;
-  c->mem_avail = 0;
   return OIC_OK;
 }
 
@@ -1569,8 +1586,7 @@ int oic_count_kmers(oic_ctx_t *c, uint32_t K, uint32_t min_count, uint64_t *n_fo
   if (c) {
     cudaSetDevice(c->device);
     c->d_kc_table.release(); c->d_kc_out_keys.release(); c->d_kc_out_cnt.release(); c->d_kc_big.release(); c->d_kc_hist.release();
-    c->mem_avail = 0;
-    if (rc != OIC_OK) { c->freq.clear(); c->kc_hist.clear(); if (n_found) *n_found = 0; }
+      if (rc != OIC_OK) { c->freq.clear(); c->kc_hist.clear(); if (n_found) *n_found = 0; }
   }
   return rc;
 }

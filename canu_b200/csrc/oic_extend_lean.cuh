@@ -44,6 +44,26 @@ __device__ __forceinline__ uint32_t ldg_nc(const uint32_t *p) {   // the bases a
 #ifndef OIC_HIST_ST
 #define OIC_HIST_ST 2   /* cache operator of the row-history stores: 0 default, 1 .cg (L2 only), 2 .cs (streaming: written once, read once by the traceback); measured 88.37 / 88.34 / 88.03 ms */
 #endif
+/* history store under a predicate (no branch around the store: an asm volatile inside an `if` keeps the compiler from predicating it) */
+__device__ __forceinline__ void stg_s32_if(int32_t *p, int32_t v, bool on) {
+#if OIC_HIST_ST == 2
+  asm volatile("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q st.global.cs.s32 [%0], %1; }" ::"l"(p), "r"(v), "r"((int)on) : "memory");
+#elif OIC_HIST_ST == 1
+  asm volatile("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q st.global.cg.s32 [%0], %1; }" ::"l"(p), "r"(v), "r"((int)on) : "memory");
+#else
+  asm volatile("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q st.global.s32 [%0], %1; }" ::"l"(p), "r"(v), "r"((int)on) : "memory");
+#endif
+}
+/* both history stores of a chunk pair from ONE address operand (p and p + 32 ints) */
+__device__ __forceinline__ void stg_s32_if2(int32_t *p, int32_t v0, bool on0, int32_t v1, bool on1) {
+#if OIC_HIST_ST == 2
+  asm volatile("{ .reg .pred q0, q1; setp.ne.s32 q0, %2, 0; setp.ne.s32 q1, %4, 0; @q0 st.global.cs.s32 [%0], %1; @q1 st.global.cs.s32 [%0+128], %3; }"
+               ::"l"(p), "r"(v0), "r"((int)on0), "r"(v1), "r"((int)on1) : "memory");
+#else
+  stg_s32_if(p, v0, on0);
+  stg_s32_if(p + 32, v1, on1);
+#endif
+}
 __device__ __forceinline__ void stg_s32(int32_t *p, int32_t v) {
 #if OIC_HIST_ST == 1
   asm volatile("st.global.cg.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -182,7 +202,10 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     if (e > max_e || next_off + width > rowcap) { errors = -1; break; }
     const int off = next_off;
     next_off += width;
-    unsigned hidx = (unsigned)(off + l);                 // this lane's cell of chunk 0 in the history
+    int32_t *hp = ws.vals + (off + l);                   // this lane's cell of chunk 0 in the history
+#ifndef OIC_HP_NOPIN
+    asm volatile("" : "+l"(hp));                         // (one 64-bit register advanced per pass, not an index re-scaled per store)
+#endif
     const int lim = lim_next;
     lim_next = ws.match_limit[imin(e + 1, max_e)];
     const int32_t *pp = prev + (left - plo) + l;         // this lane's cell of chunk 0 in the previous row
@@ -200,7 +223,6 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     auto pass = [&](auto nu_tag) -> bool {
       constexpr int NU = decltype(nu_tag)::value;
       int r[NU], r0[NU], cap[NU], dd[NU];
-      int32_t *hp = ws.vals + hidx;
 #pragma unroll
       for (int u = 0; u < NU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
         const int i = 32 * (c0 + u) + l, d = left + i;
@@ -244,11 +266,13 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       for (int u = 0; u < NU; u++) {
         const bool act = cap[u] != LEAN_IDLE;
         r[u] = imin(r[u], cap[u]);
-        if (act) { cp[32 * u] = r[u]; stg_s32(hp + 32 * u, r[u]); }
+        if (act) cp[32 * u] = r[u];
+        if (NU == 1) stg_s32_if(hp, r[u], act);
         endp = endp || (act && r[u] == cap[u]);          // reached the end of A (r == m) or of T (r + d == n)
         // best cell of the lane: highest value, lowest index on ties, as ONE integer (idle lanes: INT_MIN << 10 = 0, never above a real cell)
         key_mx = imax(key_mx, r[u] * 1024 + (koff - 32 * u));
       }
+      if (NU == 2) stg_s32_if2(hp, r[0], cap[0] != LEAN_IDLE, r[NU - 1], cap[NU - 1] != LEAN_IDLE);
       if (__any_sync(FULL, endp)) {                      // a cell reached the end of A or T: the row stops at the first one
         unsigned em[NU];
 #pragma unroll
@@ -278,15 +302,17 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       // no cell of the pass reached the end of a string: a cell slid 16 * (its continuation steps) + less than 16 bases, i.e.
       // it cost 1 + steps compare words; the "1" of every cell is added once per run from the cell count (below)
       wsum += nst;
-      pp += 32 * NU; cp += 32 * NU; hidx += 32 * NU; koff -= 32 * NU; c0 += NU;
+      pp += 32 * NU; cp += 32 * NU; hp += 32 * NU; koff -= 32 * NU; c0 += NU;
       return false;
     };
 #if OIC_TAIL_PASS
+    int npair = nch >> 1;
+    asm volatile("" : "+r"(npair));                      // (a countdown in a register: the compiler would re-derive nch from the width every pass)
 #pragma unroll 1
-    while (c0 + 1 < nch) {
+    for (; npair > 0; npair--) {
       if (pass(std::integral_constant<int, 2>{})) { ended = true; break; }
     }
-    if (!ended && c0 < nch) ended = pass(std::integral_constant<int, 1>{});
+    if (!ended && (nch & 1)) ended = pass(std::integral_constant<int, 1>{});
 #else
 #pragma unroll 1
     while (c0 < nch) {

@@ -1,7 +1,7 @@
 """Full-size properties of the CUDA path on BASELINE.json's bench shape (c3: 100 Mbp hash block x 100 Mbp query block).
 
-The CPU oracle needs ~25 core-minutes for this job, so parity at this size is checked through properties that do not
-depend on size (the small seeded cases of test_gpu_parity.py pin the records themselves):
+The records of this job are compared with the reference binary's in test_gpu_fullsize_ref.py (about 20 s on 16 host cores).  The
+properties below do not depend on size and need no checker at all; they cover what a comparison of one run cannot:
 
 * determinism: two runs of the same job give the same record multiset and the same work counters (the kernels use
   atomics, work queues and speculative extension; none of it may leak into the result);
@@ -32,8 +32,7 @@ def sorted_records(rec):
 def test_c3_full_size_properties():
     import bench
     from canu_b200 import api, shard
-    reads = bench.gen_blocks(bench.GENOME, 2, bench.BLOCK_BASES, bench.SEED)
-    (qb, qe), (hb, he) = shard.split_blocks(reads.n, 2)
+    reads, ((qb, qe), (hb, he)) = bench.gen_job(bench.GENOME, 1, bench.BLOCK_BASES, bench.SEED)
     P = bench.params_for(he - hb + 1, reads.n)
     n_q = qe - qb + 1
     ov = api.Overlapper(P)

@@ -4,7 +4,7 @@ TAG=$1; shift
 mkdir -p gpurun_out
 i=0
 for envs in "$@"; do
-  env $envs python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/q_${TAG}_$i.json 2> gpurun_out/q_${TAG}_$i.err || tail -20 gpurun_out/q_${TAG}_$i.err
+  env $envs python bench.py --steps ${STEPS:-3} --warmup 3 --no-cpu > gpurun_out/q_${TAG}_$i.json 2> gpurun_out/q_${TAG}_$i.err || tail -20 gpurun_out/q_${TAG}_$i.err
   python - <<PY
 import json
 d = json.loads(open("gpurun_out/q_${TAG}_$i.json").read().strip().splitlines()[-1])
