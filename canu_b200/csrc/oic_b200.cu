@@ -989,12 +989,18 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
   CK(c->d_qs_read.ensure((size_t)nq * 4));
   CK(cudaMemcpyAsync(c->d_qs_read.p, qs_read.data(), (size_t)nq * 4, cudaMemcpyHostToDevice, c->stream));
   // longest-first order of the scan (skipped reads last)
+  // (a stable counting sort on length / 32: linear in the reads -- a comparison sort cost 21 ms per call on the 667 k reads of a
+  // short-read block, where every read has the same length anyway)
   std::vector<uint32_t> q_order(nq);
-  for (uint32_t q = 0; q < nq; q++) q_order[q] = q;
-  std::stable_sort(q_order.begin(), q_order.end(), [&](uint32_t x, uint32_t y) {
-    const uint32_t lx = qs_read[x] == 0xffffffffu ? 0 : c->h_len[qs_read[x]], ly = qs_read[y] == 0xffffffffu ? 0 : c->h_len[qs_read[y]];
-    return lx > ly;
-  });
+  {
+    constexpr uint32_t QB = (uint32_t)(MAX_READLEN >> 5) + 2;
+    std::vector<uint32_t> bin(QB + 1, 0);
+    auto key = [&](uint32_t q) { return qs_read[q] == 0xffffffffu ? 0u : 1u + (c->h_len[qs_read[q]] >> 5); };
+    for (uint32_t q = 0; q < nq; q++) bin[QB - key(q)]++;          // descending length = ascending QB - key
+    uint32_t run = 0;
+    for (uint32_t b = 0; b <= QB; b++) { const uint32_t n_b = bin[b]; bin[b] = run; run += n_b; }
+    for (uint32_t q = 0; q < nq; q++) q_order[bin[QB - key(q)]++] = q;
+  }
   CK(c->d_q_order.ensure((size_t)nq * 4));
   CK(cudaMemcpyAsync(c->d_q_order.p, q_order.data(), (size_t)nq * 4, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += (uint64_t)nq * 8;

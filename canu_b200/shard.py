@@ -68,6 +68,19 @@ class RankJob:
 
     def to_global(self, rec):
         """(n, 6) uint32 .ovb words with local IDs -> store IDs (words 0 and 1 are a_iid, b_iid: ST/ovStoreFile.C:196-221)"""
+        if self.contiguous:
+            # one offset per side, applied in place (`rec` is the caller's fresh copy from Overlapper.overlaps()): a short-read block
+            # returns a million records per step and this runs inside the end-to-end timing
+            rec = np.asarray(rec, dtype=np.uint32).reshape(-1, 6)
+            dq = np.uint32(int(self.q_ids[0]) - 1 if self.n_q else 0)
+            dh = np.uint32(self.hb - self.n_q - 1)
+            if dq or dh:
+                if not rec.flags.writeable:
+                    rec = rec.copy()
+                for col in (0, 1):
+                    v = rec[:, col]
+                    v += np.where(v <= np.uint32(self.n_q), dq, dh).astype(np.uint32)
+            return rec
         rec = np.array(rec, dtype=np.uint32).reshape(-1, 6)
         for col in (0, 1):
             v = rec[:, col].astype(np.int64)
