@@ -57,6 +57,31 @@ struct DevBuf {
   template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// The overlap records on the host: a growable PINNED buffer (the device-to-host copy of a short-read block's million records
+// ran at 4 GB/s into a pageable std::vector, 25 GB/s into this).  Grows by doubling; never shrinks until the context closes.
+struct HostRecs {
+  oic_ovb_record_t *p = nullptr;
+  size_t n = 0, cap = 0;
+  size_t size() const { return n; }
+  const oic_ovb_record_t *data() const { return p; }
+  void clear() { n = 0; }
+  // room for `more` records behind the current ones; returns where they go, or nullptr when the host has no memory for them
+  oic_ovb_record_t *grow(size_t more) {
+    if (n + more > cap) {
+      size_t want = std::max<size_t>(2 * cap, n + more + 4096);
+      oic_ovb_record_t *q = nullptr;
+      if (cudaMallocHost(reinterpret_cast<void **>(&q), want * sizeof(oic_ovb_record_t)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+      if (n) memcpy(q, p, n * sizeof(oic_ovb_record_t));
+      if (p) cudaFreeHost(p);
+      p = q; cap = want;
+    }
+    oic_ovb_record_t *at = p + n;
+    n += more;
+    return at;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; n = cap = 0; }
+};
+
 // ---- host tables: Edit_Match_Limit (LIBO/Binomial_Bound.C:47-107,119-194, BITS == 21 slope) ------------------
 // Smallest n >= start such that more than e errors in n bases at rate p is not "improbable" (1e-4).
 int binomial_bound(int e, double p, int start) {
@@ -179,7 +204,7 @@ struct oic_ctx {
   std::vector<std::pair<uint64_t, uint32_t>> freq;   // {key (first base high), count}, ascending
   float kc_ms = 0;
 
-  std::vector<oic_ovb_record_t> overlaps;
+  HostRecs overlaps;
   oic_stats_t stats = {};
   oic_timings_t tm = {};
   cudaEvent_t ev[2] = {nullptr, nullptr};
@@ -738,6 +763,7 @@ void oic_destroy(oic_ctx_t *c) {
                     &c->d_ctr, &c->d_flag, &c->d_kc_table, &c->d_kc_out_keys, &c->d_kc_out_cnt, &c->d_kc_n, &c->d_kc_hist, &c->d_kc_big, &c->d_xchg, &c->d_parts, &c->d_part_ctr, &c->d_q_order, &c->d_word_read, &c->d_strand, &c->d_quals};
   if (c->comm && nccl_api()) nccl_api()->CommDestroy(c->comm);
   for (DevBuf *b : bufs) b->release();
+  c->overlaps.release();
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
   if (c->ev_call[0]) cudaEventDestroy(c->ev_call[0]);
@@ -1272,9 +1298,9 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       }   // (default path)
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
-        size_t old = c->overlaps.size();
-        c->overlaps.resize(old + hc.n_out);
-        CK(cudaMemcpyAsync(c->overlaps.data() + old, c->d_out.p, (size_t)hc.n_out * 24, cudaMemcpyDeviceToHost, c->stream));
+        oic_ovb_record_t *at = c->overlaps.grow(hc.n_out);
+        if (!at) return c->fail(OIC_ERR_CUDA, "no pinned host memory for %llu overlap records", (unsigned long long)(c->overlaps.size() + hc.n_out));
+        CK(cudaMemcpyAsync(at, c->d_out.p, (size_t)hc.n_out * 24, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaStreamSynchronize(c->stream));
         c->tm.d2h_bytes += (uint64_t)hc.n_out * 24;
       }
