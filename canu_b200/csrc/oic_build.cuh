@@ -188,6 +188,23 @@ __device__ __forceinline__ unsigned long long ld_key(const Slot *sl) {
   asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(&sl->key) : "memory");
   return v;
 }
+#ifndef OIC_CAS128
+#define OIC_CAS128 1   /* claim a free slot with ONE 16-byte compare-and-swap {EMPTY, 0} -> {key, occurrence} instead of a CAS on the key + an OR into the payload */
+#endif
+// returns the key the slot held before (EMPTY_KEY: the claim succeeded and the payload is in place)
+__device__ __forceinline__ unsigned long long slot_claim(Slot *sl, unsigned long long key, unsigned long long occ) {
+#if OIC_CAS128
+  unsigned long long ok, op;
+  asm volatile("{\n\t.reg .b128 c, n, d;\n\tmov.b128 c, {%3, %4};\n\tmov.b128 n, {%5, %6};\n\t"
+               "atom.global.relaxed.gpu.cas.b128 d, [%2], c, n;\n\tmov.b128 {%0, %1}, d;\n\t}"
+               : "=l"(ok), "=l"(op) : "l"(sl), "l"(EMPTY_KEY), "l"(0ULL), "l"(key), "l"(occ) : "memory");
+  return ok;
+#else
+  const unsigned long long cur = atomicCAS(&sl->key, EMPTY_KEY, key);
+  if (cur == EMPTY_KEY && occ) atomicOr(&sl->pay, occ);
+  return cur;
+#endif
+}
 __device__ __forceinline__ bool table_find(const Slot *__restrict__ table, const TableGeom &g, uint64_t hk, unsigned long long key, uint32_t &slot,
                                            unsigned long long &pay) {
   uint64_t h = geom_home(g, hk);
@@ -305,8 +322,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_apply(const uint32_t 
 
 /*
  * The insert (Hash_Insert's chained bucket, Build_Hash_Index.C:296-350, appears as: slot = k-mer, list = chain).  Per probe: a
- * plain load of the key (a load that misses is much cheaper than an atomic that misses), then one 8-byte CAS;
- *   - the slot was free: the window owns the k-mer and ORs its occurrence word into the payload (first occurrence of a k-mer:
+ * plain load of the key (a load that misses is much cheaper than an atomic that misses), then one 16-byte CAS;
+ *   - the slot was free: the window owns the k-mer, its occurrence word went in with the same CAS (first occurrence of a k-mer:
  *     ~90 % of the windows of a 1x block never need anything else);
  *   - the key is already there: the window ORs the list mark into the payload and appends {slot, occurrence} to the overflow
  *     list; the arrival that finds the mark clear also queues the slot for the list kernels.
@@ -324,7 +341,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_u32_apply(const uint32_t 
  *
  * Measured and dropped in round 2: ordering the records by table region so that the lines being filled stay in L2 (256
  * partitions, contiguous or hashed by line).  DRAM traffic fell as planned, the insert time did not (7.1 ms either way): what
- * bounds it on this GPU is the ~200 M 64-bit atomics themselves, not where their lines come from.
+ * bounds it on this GPU is the ~200 M 64-bit atomics themselves, not where their lines come from.  Hence slot_claim: a free slot is
+ * taken with ONE 16-byte compare-and-swap {EMPTY, 0} -> {key, occurrence} (atom.cas.b128) instead of a CAS on the key followed
+ * by an OR into the payload -- 90 % of the windows of a 1x block are first occurrences: 190 M atomics become 100 M, the build
+ * 10.0 -> 8.9 ms.
  */
 struct PartRec { unsigned long long key, occ; };
 constexpr int INS_THREADS = 256, INS_R = 4, INS_TILE = INS_THREADS * INS_R;
@@ -380,9 +400,8 @@ __global__ void __launch_bounds__(INS_THREADS) k_insert(BuildArgs a, const PartR
     uint64_t h = geom_home(a.geom, hk);
     unsigned long long cur = ld_key(a.table + h);
     while (true) {
-      if (cur == EMPTY_KEY) cur = atomicCAS(&a.table[h].key, EMPTY_KEY, key);
+      if (cur == EMPTY_KEY) cur = slot_claim(a.table + h, key, my_occ);
       if (cur == EMPTY_KEY) {
-        if (my_occ) atomicOr(&a.table[h].pay, my_occ);
         n_claimed++;
         break;
       }

@@ -15,6 +15,8 @@
 
 #include <chrono>
 #include <string>
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "../../include/oic_b200.h"
@@ -94,9 +96,24 @@ int main(int argc, char **argv) {
   OvlStoreWriter store(ovl_name, gkp);
   std::vector<uint32_t> rec;
   fprintf(stderr, "\n-- LOADING --\n\n");
-  for (const std::string &f : files) {
-    fprintf(stderr, "-  Loading '%s'\n", f.c_str());
-    read_ovb_file(f, rec);
+  {   // the files are independent (framed, snappy blocks): decompress them on all host cores, then concatenate in command-line order
+    std::vector<std::vector<uint32_t>> part(files.size());
+    std::atomic<size_t> next{0};
+    const unsigned nt = std::max(1u, std::min<unsigned>((unsigned)files.size(), std::thread::hardware_concurrency()));
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++)
+      th.emplace_back([&]() { for (size_t i; (i = next.fetch_add(1)) < files.size();) read_ovb_file(files[i], part[i]); });
+    for (std::thread &t : th) t.join();
+    size_t total = 0;
+    for (const auto &v : part) total += v.size();
+    rec.resize(total);
+    size_t at = 0;
+    for (size_t i = 0; i < files.size(); i++) {
+      fprintf(stderr, "-  Loading '%s'\n", files[i].c_str());
+      if (!part[i].empty()) memcpy(rec.data() + at, part[i].data(), part[i].size() * 4);
+      at += part[i].size();
+      std::vector<uint32_t>().swap(part[i]);
+    }
   }
   const uint64_t n = rec.size() / 6;
   fprintf(stderr, "-  %llu overlaps loaded  [%.2f s]\n\n-- FILTERING AND SORTING (GPU) --\n\n", (unsigned long long)n, secs());

@@ -133,7 +133,7 @@ void OvlStoreWriter::write(const uint32_t *rec, uint64_t n) {
     const uint32_t a = w[0], b = w[1];
     if (offt_.a_iid > a) { fprintf(stderr, "LAST:  a:%u\nTHIS:  a:%u b:%u\novStoreWriter: overlaps are not sorted\n", offt_.a_iid, a, b); exit(1); }
     // a new data file when there is none yet or the current one is full (1 GiB of 20-byte records)
-    if (data_ && this_file_ >= this_file_max_) { fclose(data_); data_ = nullptr; this_file_ = this_file_max_ = 0; }
+    if (data_ && this_file_ >= this_file_max_) { flush_data(); fclose(data_); data_ = nullptr; this_file_ = this_file_max_ = 0; }
     if (!data_) {
       char nm[32];
       snprintf(nm, sizeof(nm), "/%04d", (int)++file_index_);
@@ -154,7 +154,8 @@ void OvlStoreWriter::write(const uint32_t *rec, uint64_t n) {
       offt_.num_olaps = 0;
     }
     if (offt_.num_olaps == 0) { offt_.a_iid = a; offt_.fileno = file_index_; offt_.offset = (uint32_t)this_file_; offt_.overlap_id = info_[5]; }
-    fwrite(w + 1, 4, 5, data_);   // ovFileNormalWrite: b_iid + the four data words, uncompressed (ST/ovStoreFile.C:101-106,196-221)
+    dbuf_.insert(dbuf_.end(), w + 1, w + 6);   // ovFileNormalWrite: b_iid + the four data words, uncompressed (ST/ovStoreFile.C:101-106,196-221)
+    if (dbuf_.size() >= (1u << 20)) flush_data();
     offt_.num_olaps++;
     if (info_[3] > a) info_[3] = a;
     if (info_[4] < a) info_[4] = a;
@@ -195,7 +196,7 @@ void OvlStoreWriter::finish() {
   fclose(index_);
   index_ = nullptr;
   save_info(true);
-  if (data_) { fclose(data_); data_ = nullptr; }
+  if (data_) { flush_data(); fclose(data_); data_ = nullptr; }
   {   // evalueLen (ST/ovStoreHistogram.C:345-376)
     FILE *f = fopen((path_ + "/evalueLen").c_str(), "w");
     if (!f) die2("failed to open evalueLen file '%s/evalueLen' for writing: %s", path_, strerror(errno));

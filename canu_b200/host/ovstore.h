@@ -46,6 +46,8 @@ class OvlStoreWriter {
   const GkStore &gkp_;
   uint64_t info_[8];               // magic, version, unused, smallestIID, largestIID, numOverlapsTotal, highestFileIndex, maxReadLenInBits
   FILE *index_ = nullptr, *data_ = nullptr;
+  std::vector<uint32_t> dbuf_;     // 20-byte records of the current data file not yet written (one fwrite per 4 MB, not per record)
+  void flush_data() { if (data_ && !dbuf_.empty()) fwrite(dbuf_.data(), 4, dbuf_.size(), data_); dbuf_.clear(); }
   Offt offt_, offm_;
   uint64_t this_file_ = 0, this_file_max_ = 0;
   uint32_t file_index_ = 0;
