@@ -220,8 +220,9 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
     // pass keep two independent dependency chains in flight; an odd last chunk takes the single-chunk copy of the pass instead
     // of dragging 32 idle lanes through a pair (rows average 3.8 chunks).
     int c0 = 0;
-    auto pass = [&](auto nu_tag) -> bool {
+    auto pass = [&](auto nu_tag, auto full_tag) -> bool {
       constexpr int NU = decltype(nu_tag)::value;
+      constexpr bool FULLP = decltype(full_tag)::value;   // every cell of the pass lies inside the row: no idle lanes, no predicates for them
       int r[NU], r0[NU], cap[NU], dd[NU];
 #pragma unroll
       for (int u = 0; u < NU; u++) {                     // predecessor rule (forward.C:163-170), out-of-band = -2 sentinel
@@ -229,7 +230,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         const int g0 = pp[32 * u] + 1, gm = pp[32 * u - 1], gp = pp[32 * u + 1] + 1;
         r0[u] = imax(imax(g0, gm), gp);
         dd[u] = d;
-        cap[u] = (i < width) ? imin(m, n - d) : LEAN_IDLE;
+        cap[u] = (FULLP || i < width) ? imin(m, n - d) : LEAN_IDLE;
       }
       int more = 0;                                      // bit u: the slide of chunk u goes on
       // Branch-free: a cell that does not slide (idle lane, or already at the end of a string) compares the first windows
@@ -264,7 +265,7 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       bool endp = false;
 #pragma unroll
       for (int u = 0; u < NU; u++) {
-        const bool act = cap[u] != LEAN_IDLE;
+        const bool act = FULLP || cap[u] != LEAN_IDLE;
         r[u] = imin(r[u], cap[u]);
         if (act) cp[32 * u] = r[u];
         if (NU == 1) stg_s32_if(hp, r[u], act);
@@ -272,15 +273,18 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
         // best cell of the lane: highest value, lowest index on ties, as ONE integer (idle lanes: INT_MIN << 10 = 0, never above a real cell)
         key_mx = imax(key_mx, r[u] * 1024 + (koff - 32 * u));
       }
-      if (NU == 2) stg_s32_if2(hp, r[0], cap[0] != LEAN_IDLE, r[NU - 1], cap[NU - 1] != LEAN_IDLE);
+      if (NU == 2) {
+        if (FULLP) { stg_s32(hp, r[0]); stg_s32(hp + 32, r[NU - 1]); }
+        else stg_s32_if2(hp, r[0], cap[0] != LEAN_IDLE, r[NU - 1], cap[NU - 1] != LEAN_IDLE);
+      }
       if (__any_sync(FULL, endp)) {                      // a cell reached the end of A or T: the row stops at the first one
         unsigned em[NU];
 #pragma unroll
-        for (int u = 0; u < NU; u++) em[u] = __ballot_sync(FULL, cap[u] != LEAN_IDLE && r[u] == cap[u]);
+        for (int u = 0; u < NU; u++) em[u] = __ballot_sync(FULL, (FULLP || cap[u] != LEAN_IDLE) && r[u] == cap[u]);
         // W of this pass from the slide lengths: ceil((run + 1) / 16) compare words per cell
         unsigned wc[NU];
 #pragma unroll
-        for (int u = 0; u < NU; u++) wc[u] = (cap[u] != LEAN_IDLE) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
+        for (int u = 0; u < NU; u++) wc[u] = (FULLP || cap[u] != LEAN_IDLE) ? (unsigned)(r[u] - r0[u] + 16) >> 4 : 0u;
         int uu = 0;
 #pragma unroll
         for (int u = NU - 1; u >= 0; u--) if (em[u]) uu = u;
@@ -306,17 +310,18 @@ __device__ __forceinline__ int dp_run_lean(const int DIR, const ExtArgs &a, Warp
       return false;
     };
 #if OIC_TAIL_PASS
-    int npair = nch >> 1;
-    asm volatile("" : "+r"(npair));                      // (a countdown in a register: the compiler would re-derive nch from the width every pass)
+    int nfull = width >> 6;                              // chunk pairs that lie entirely inside the row
+    asm volatile("" : "+r"(nfull));                      // (a countdown in a register: the compiler would re-derive it from the width every pass)
 #pragma unroll 1
-    for (; npair > 0; npair--) {
-      if (pass(std::integral_constant<int, 2>{})) { ended = true; break; }
+    for (; nfull > 0; nfull--) {
+      if (pass(std::integral_constant<int, 2>{}, std::true_type{})) { ended = true; break; }
     }
-    if (!ended && (nch & 1)) ended = pass(std::integral_constant<int, 1>{});
+    if (!ended && c0 + 1 < nch) ended = pass(std::integral_constant<int, 2>{}, std::false_type{});   // at most one partial pair
+    if (!ended && c0 < nch) ended = pass(std::integral_constant<int, 1>{}, std::false_type{});
 #else
 #pragma unroll 1
     while (c0 < nch) {
-      if (pass(std::integral_constant<int, 2>{})) { ended = true; break; }
+      if (pass(std::integral_constant<int, 2>{}, std::false_type{})) { ended = true; break; }
     }
 #endif
     int32_t *hist = ws.vals + off;
