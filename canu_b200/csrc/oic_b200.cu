@@ -1215,6 +1215,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       ea.out = c->d_out.as<uint32_t>(); ea.out_cap = out_cap; ea.retry_list = c->d_retry.as<uint32_t>();
       ea.ctr = sa.ctr;
       ea.quals = P.use_window_filter ? c->d_quals.as<uint8_t>() : nullptr;
+      ea.first_lean = getenv("OIC_NO_FIRST_LEAN") ? 0 : 1;
       if (P.frag_olap_limit != UINT64_MAX) {   // -l: partners of a strand depend on each other -> serial walk per strand
         const int rl = run_pairs_limited(c, ea, rp.src, n_pairs, vals_bytes, hc);
         if (rl) return rl;

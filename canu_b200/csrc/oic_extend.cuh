@@ -54,6 +54,7 @@ struct ExtArgs {
   uint32_t *retry_list;
   // speculative round: pairs that still have seeds after their first extension (see k_extend_tasks / k_commit_pairs)
   int handoff;                                // k_process_pairs: 1 = stop after the first extension and hand the pair over
+  int first_lean;   // k_process_pairs tries the lean row loop first (0: generic loop only)
   struct PairState *pstate;                   // per pair
   uint32_t *pend_list;                        // pairs handed over
   uint2 *tasks;                               // {pair, seed index}
@@ -368,7 +369,10 @@ constexpr int PP_DONE = 0, PP_OVERFLOW = 1, PP_HANDED = 2;
  * would add to a full end is not extended -- it only removes itself, because Kind_Of_Olap and the alignment bounds keep the
  * values of the previous iteration (:415) and re-applying that alignment's pruning removes nothing new.  (With -G a skipped FIRST
  * seed makes the reference read uninitialised bounds; here, as in the oracle, they are zero and nothing else is pruned.) */
-template <bool LIMIT>
+#ifndef OIC_FIRST_LEAN
+#define OIC_FIRST_LEAN 896   /* staging width of the lean row loop inside k_process_pairs (0: first extensions run the generic loop) */
+#endif
+template <bool LIMIT, int LSWF = 0>
 __device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, const FastScratch &fs, uint32_t pi, unsigned long long &ext_calls,
                                             bool a_full, bool b_full, int &a_inc, int &b_inc) {
   const int l = lane_id();
@@ -435,7 +439,18 @@ __device__ __forceinline__ int process_pair(const ExtArgs &a, WarpScratch &ws, c
     }
     if (!skip) {
       ext_calls++;
-      kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi, errors, dlen);
+      bool done = false;
+      if constexpr (LSWF != 0) {
+        // the lean row loop first (same results, about two thirds of the instructions); it knows no N masks and no row wider
+        // than its staging: those extensions run again in the generic loop, counters rewound
+        if (!pair_n && a.first_lean) {
+          const unsigned long long c0 = ws.cells, w0 = ws.words;
+          kind = extend_alignment<LSWF>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi, errors, dlen);
+          done = kind != LEAN_WIDE;
+          if (!done) { ws.cells = c0; ws.words = w0; }
+        }
+      }
+      if (!done) kind = extend_alignment<0>(a, ws, fs, x.S, x.sp, x.s_len, x.T, x.tp, x.t_len, lg.start, lg.offset, lg.len, s_lo, s_hi, t_lo, t_hi, errors, dlen);
       if (kind < 0) { overflow = true; break; }
       const int slot = accept_overlap(a, kind, s_lo, s_hi, t_lo, t_hi, errors, dlen, distinct, distinct_ct);
       if (a.quals && slot >= 0) olap_seed[slot] = lg;   // -w: the slot's alignment (and delta list) is this seed's extension
@@ -534,7 +549,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32, 4) k_process_pairs(ExtArgs a) 
     if (ti >= a.n_tasks) break;
     const uint32_t pi = a.task_list ? a.task_list[ti] : ti;
     int a_inc, b_inc;
-    if (process_pair<false>(a, ws, fs, pi, ext_calls, false, false, a_inc, b_inc) == PP_OVERFLOW && l == 0)
+    if (process_pair<false, (OIC_FIRST_LEAN + 8 + 32 * LU <= SW + 4) ? OIC_FIRST_LEAN : 0>(a, ws, fs, pi, ext_calls, false, false, a_inc, b_inc) == PP_OVERFLOW && l == 0)
       a.retry_list[atomicAdd(&a.ctr->n_retry, 1u)] = pi;
   }
 
