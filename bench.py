@@ -195,7 +195,25 @@ def reference_records(store, ovb):
     return H.dump_ovb_sorted(store, ovb)
 
 
-def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=None):
+def executable_leg(exe, store, wd, args, cores, qbases, runs=2):
+    """SURVEY.md 8(d)'s own definition of the metric, through the DROP-IN EXECUTABLE: wall time of one `overlapInCore` process from
+    opening the gkpStore to `.ovb` / `.counts` / `.stats` closed (CUDA start-up, store read, 2-bit reads to the GPU, build, search,
+    snappy-framed output), on the store the reference leg just wrote.  The first run also pays the cold start of the driver; both
+    are reported, the rate is of the last."""
+    import helpers as H
+    walls, ovb, st = [], None, None
+    for i in range(runs):
+        t0 = time.time()
+        ovb, st = H.run_overlapper(exe, store, os.path.join(wd, "exe%d" % i), args, cores)
+        walls.append(time.time() - t0)
+    n = int(H.parse_stats(st).get("Total overlaps produced", 0))
+    w = walls[-1]
+    return {"what": "canu_b200/bin/overlapInCore, one process, gkpStore in -> .ovb/.counts/.stats closed (wall)", "wall_s": w,
+            "wall_s_all_runs": walls, "overlaps": n, "overlaps_per_sec": n / w, "query_mbp_per_sec": qbases / 1e6 / w,
+            "ovb_bytes": os.path.getsize(ovb), "ovb": ovb}
+
+
+def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=None, exe=None):
     """The reference's own CPU overlapInCore (oracle/_ref, built from /root/reference/src by oracle/build_ref.sh) on the SAME job
     the GPU arm times at `world` GPUs: same generator seed, the full hash block, and the same `world` query blocks searched
     by ONE reference process (-h <hash block> -r 1-<hash block - 1>), -t <all host cores>; wall time of the process (store open
@@ -258,6 +276,14 @@ def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=No
                 n_warm, times = 1, times[1:]
             times = times[:max(1, steps)]
             n_ovl = H.parse_stats(st).get("Total overlaps produced", 0)
+            exe_res = None
+            if exe and os.access(exe, os.X_OK):
+                try:
+                    exe_res = executable_leg(exe, store, wd, args, cores, qbases)
+                    # its records against the reference's, every stored field (the files are small next to the search)
+                    exe_res["equals_reference_ovb"] = H.dump_ovb_sorted(store, exe_res.pop("ovb")) == H.dump_ovb_sorted(store, ovb)
+                except Exception as ex:   # the line must not fail because of the extra leg
+                    exe_res = {"error": "%s: %s" % (type(ex).__name__, ex)}
             if keep is not None:
                 keep.update(store=store, ovb=ovb, stats=st, workdir=wd)
         else:
@@ -272,7 +298,8 @@ def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=No
     t = float(np.mean(times))
     sample += "; %d timed run(s) after %d warm-up, %.1f s each (store written in %.1f s, not timed)" % (len(times), n_warm, t, prep_s)
     return dict(value=qbases / 1e6 / t, unit="query Mbp/s", cores=cores, kind=kind, sample=sample, full_job=full,
-                seconds_per_step=t, overlaps_per_sec=n_ovl / t, overlaps=int(n_ovl), steps=len(times), warmup=n_warm)
+                seconds_per_step=t, overlaps_per_sec=n_ovl / t, overlaps=int(n_ovl), steps=len(times), warmup=n_warm,
+                executable=exe_res if kind == "reference" else None)
 
 
 def main():
@@ -599,7 +626,11 @@ def main():
     if (world == 1 and not a.no_cpu) or a.check:
         if a.scale != 1.0:
             globals().update(GENOME=genome, BLOCK_BASES=block)
-        r = reference_leg(world, 1, 0, keep=keep)   # the same job, one run of the reference binary on this box's host cores
+        # the same job, one run of the reference binary on this box's host cores; at one GPU the drop-in executable then runs on the same store
+        exe = os.environ.get("OIC_BENCH_EXE", os.path.join(ROOT, "canu_b200", "bin", "overlapInCore")) if world == 1 else None
+        r = reference_leg(world, 1, 0, keep=keep, exe=exe)
+        if r.get("executable"):
+            line["executable"] = r["executable"]
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         line["cpu_baseline"]["overlaps_per_sec"] = r["overlaps_per_sec"]
         line["cpu_baseline"]["overlaps"] = r["overlaps"]
