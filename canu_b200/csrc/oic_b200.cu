@@ -62,24 +62,33 @@ struct DevBuf {
 struct HostRecs {
   oic_ovb_record_t *p = nullptr;
   size_t n = 0, cap = 0;
+  bool pinned = true;   // false: the host refused to pin that much (ulimit -l, fragmentation): plain memory, slower copies, same results
   size_t size() const { return n; }
   const oic_ovb_record_t *data() const { return p; }
   void clear() { n = 0; }
+  void drop() { if (p) { if (pinned) cudaFreeHost(p); else free(p); } p = nullptr; }
   // room for `more` records behind the current ones; returns where they go, or nullptr when the host has no memory for them
   oic_ovb_record_t *grow(size_t more) {
     if (n + more > cap) {
       size_t want = std::max<size_t>(2 * cap, n + more + 4096);
       oic_ovb_record_t *q = nullptr;
-      if (cudaMallocHost(reinterpret_cast<void **>(&q), want * sizeof(oic_ovb_record_t)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+      bool q_pinned = true;
+      if (cudaMallocHost(reinterpret_cast<void **>(&q), want * sizeof(oic_ovb_record_t)) != cudaSuccess) {
+        cudaGetLastError();
+        want = n + more + 4096;
+        q = static_cast<oic_ovb_record_t *>(malloc(want * sizeof(oic_ovb_record_t)));
+        q_pinned = false;
+        if (!q) return nullptr;
+      }
       if (n) memcpy(q, p, n * sizeof(oic_ovb_record_t));
-      if (p) cudaFreeHost(p);
-      p = q; cap = want;
+      drop();
+      p = q; cap = want; pinned = q_pinned;
     }
     oic_ovb_record_t *at = p + n;
     n += more;
     return at;
   }
-  void release() { if (p) cudaFreeHost(p); p = nullptr; n = cap = 0; }
+  void release() { drop(); n = cap = 0; pinned = true; }
 };
 
 // ---- host tables: Edit_Match_Limit (LIBO/Binomial_Bound.C:47-107,119-194, BITS == 21 slope) ------------------
@@ -1300,7 +1309,7 @@ int run_batch(oic_ctx *c, const std::vector<uint32_t> &qs_read /* read index or 
       if (hc.out_overflow) return c->fail(OIC_ERR_CAPACITY, "overlap output buffer overflow (internal)");
       if (hc.n_out) {
         oic_ovb_record_t *at = c->overlaps.grow(hc.n_out);
-        if (!at) return c->fail(OIC_ERR_CUDA, "no pinned host memory for %llu overlap records", (unsigned long long)(c->overlaps.size() + hc.n_out));
+        if (!at) return c->fail(OIC_ERR_CUDA, "no host memory for %llu overlap records", (unsigned long long)(c->overlaps.size() + hc.n_out));
         CK(cudaMemcpyAsync(at, c->d_out.p, (size_t)hc.n_out * 24, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaStreamSynchronize(c->stream));
         c->tm.d2h_bytes += (uint64_t)hc.n_out * 24;
