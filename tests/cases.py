@@ -214,3 +214,41 @@ def fuzz_case(i):
         over["frag_olap_limit"] = int(rng.choice([1, 2, 3, 5, 9]))
     P = H.default_params(max_erate=H.strtof(erate), num_threads=threads, **over)
     return reads, P, erate, threads, None
+
+
+N_FUZZ_W = 24
+
+
+def fuzz_case_w(i):
+    """Seeded random -w job i (CPU only: the oracle against the live reference binary, tests/test_oracle.py): long reads at 2-4 % error
+    so that 50-base windows with many errors occur, --maxerate <= 0.06 (above it the reference turns -w off), one thread (the two
+    window counters are unsynchronised globals in the reference), 1-4 libraries with their own default QV (the window score uses
+    min(quality, 20) of both reads), sometimes -m, -l, N bases, hash sub-blocks and -h / -r sub-ranges."""
+    import numpy as np
+    rng = np.random.default_rng(7700 + i)
+    lmin = int(rng.integers(500, 1400)); lmax = lmin + int(rng.integers(200, 2000))
+    glen = int(rng.integers(12000, 30000)); cov = float(rng.uniform(8, 16))
+    err = float(rng.choice([0.02, 0.03, 0.035, 0.04]))
+    reads = H.gen_reads(genome_len=glen, coverage=cov, len_min=lmin, len_max=lmax, err=err, seed=int(9700 + i), sub_only=bool(rng.random() < 0.2))
+    if rng.random() < 0.3:
+        inject_n(reads, rate=float(rng.choice([0.0005, 0.002])), runs=int(rng.integers(0, 10)), seed=int(i))
+    k = int(rng.integers(1, 5))
+    qv = [int(x) for x in rng.choice([5, 10, 12, 15, 17, 19, 20, 21, 25, 31, 40], size=k)]
+    reads.read_qv = np.array([qv[min(k - 1, j * k // reads.n)] for j in range(reads.n)], dtype=np.uint8)
+    erate = str(rng.choice(["0.045", "0.06"]))
+    over = dict(kmer_len=int(rng.choice([14, 16, 17, 20, 22])), hash_bits=int(rng.choice([12, 14, 16])), hash_load=float(rng.choice([0.6, 0.75])),
+                partial=0, unique_olap=int(rng.random() < 0.6), use_hopeless_check=int(rng.random() < 0.7),
+                min_olap_len=int(rng.choice([100, 250, 500])), use_window_filter=1)
+    n = reads.n
+    over["max_hash_strings"] = int(rng.choice([n, max(2, n // 2), max(2, n // 4)]))
+    over["end_hash_id"] = n
+    if rng.random() < 0.3:
+        a, b = sorted(int(x) for x in rng.integers(1, n + 1, size=2))
+        over["bgn_ref_id"], over["end_ref_id"] = a, b
+    else:
+        over["end_ref_id"] = n
+    if rng.random() < 0.35:
+        over["frag_olap_limit"] = int(rng.choice([2, 3, 5, 9]))
+    P = H.default_params(max_erate=H.strtof(erate), num_threads=1, **over)
+    return reads, P, erate, 1, None
+

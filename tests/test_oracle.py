@@ -75,6 +75,24 @@ def test_oracle_vs_live_reference_fuzz(i):
     check_stats(ref_stats, res["stats"], P["partial"])
 
 
+@pytest.mark.skipif(not H.have_ref(), reason="reference binary not built (oracle/build_ref.sh)")
+@pytest.mark.parametrize("i", list(range(cases.N_FUZZ_W)))
+def test_oracle_vs_live_reference_fuzz_window_filter(i):
+    """Seeded random -w jobs (tests/cases.py fuzz_case_w): records and all -s counters, the two window rejections included."""
+    reads, P, erate, threads, _ = cases.fuzz_case_w(i)
+    with tempfile.TemporaryDirectory() as wd:
+        store = H.make_store(reads, wd)
+        ovb, st = H.run_overlapper(os.path.join(H.REF_DIR, "overlapInCore"), store, os.path.join(wd, "ref"),
+                                   H.oic_args(P, erate), threads)
+        ref = H.dump_ovb_sorted(store, ovb)
+        ref_stats = H.parse_stats(st)
+    res = H.run_oracle(reads, P)
+    assert sorted(H.format_raw(o) for o in res["overlaps"]) == ref
+    check_stats(ref_stats, res["stats"], P["partial"])
+    for k, v in {"Rejected by short window": "bad_short_window", "Rejected by long window": "bad_long_window"}.items():
+        assert ref_stats[k] == res["stats"][v], k
+
+
 def _kmer_golden(name, K, T):
     return gzip.open(os.path.join(GOLDEN, "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
 
