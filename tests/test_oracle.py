@@ -93,6 +93,16 @@ def test_oracle_vs_live_reference_fuzz_window_filter(i):
         assert ref_stats[k] == res["stats"][v], k
 
 
+_EXTRA = int(os.environ.get("OIC_FUZZ_EXTRA", "0"))
+
+
+@pytest.mark.skipif(not (H.have_ref() and _EXTRA), reason="set OIC_FUZZ_EXTRA=<n> to hold the oracle to the reference on n more random jobs")
+@pytest.mark.parametrize("i", list(range(cases.N_FUZZ, cases.N_FUZZ + _EXTRA)))
+def test_oracle_vs_live_reference_fuzz_extra(i):
+    """More of the same sweep on demand (jobs N_FUZZ .. N_FUZZ + n - 1; run with n = 240 at the end of round 2: all equal)."""
+    test_oracle_vs_live_reference_fuzz(i)
+
+
 def _kmer_golden(name, K, T):
     return gzip.open(os.path.join(GOLDEN, "kmers_%s_%d_%d.txt.gz" % (name, K, T))).read().decode()
 
