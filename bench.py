@@ -218,12 +218,12 @@ def reference_leg(world=1, steps=2, warmup=1, cores=None, budget_s=None, keep=No
     the GPU arm times at `world` GPUs: same generator seed, the full hash block, and the same `world` query blocks searched
     by ONE reference process (-h <hash block> -r 1-<hash block - 1>), -t <all host cores>; wall time of the process (store open
     + hash build + search + .ovb/.counts written).  The steps/warm-ups actually run are bounded by `budget_s` of host time
-    (default 420 s, OIC_REF_BUDGET_S) and REPORTED: the first run always counts unless two more fit the budget, in which case it
+    (default 300 s, OIC_REF_BUDGET_S) and REPORTED: the first run always counts unless two more fit the budget, in which case it
     is the warm-up.  Workloads with REF_FULL = False (c2) run a REF_SCALE_MBP-genome sample of the same read model instead.
     keep: optional dict that receives store / ovb paths of the last run (bench.py --check); the work directory then stays."""
     import helpers as H
     cores = cores or os.cpu_count()
-    budget_s = float(os.environ.get("OIC_REF_BUDGET_S", "420")) if budget_s is None else budget_s
+    budget_s = float(os.environ.get("OIC_REF_BUDGET_S", "300")) if budget_s is None else budget_s
     from canu_b200 import shard
     t_start = time.time()
     full = bool(REF_FULL)
