@@ -51,7 +51,7 @@ WORKLOADS = {
                GENOME=4_600_000, BLOCK_BASES=138_000_000, ERATE="0.15", READ_ERR=0.06, SEED=1002, MODE="self", REF_SCALE_MBP=0.1,
                REF_FULL=False),   # the full c2 job takes the reference ~20 min on 16 cores
     "c3": dict(desc="c3: synthetic 100 Mbp genome, 30x corrected reads 5-15 kb, 2% error, k=22, --maxerate 0.06, "
-                    "100 Mbp hash block (1x) broadcast, one 100 Mbp query block per GPU"),
+                    "100 Mbp hash block (1x) replicated, one 100 Mbp query block per GPU"),
     "c4": dict(desc="c4: synthetic 100 Mbp genome, 150 bp reads (substitutions only, 0.5%), -G --minlength 40, k=22, --maxerate 0.06, "
                     "100 Mbp hash block (667 k reads, 1x) vs one 100 Mbp query block per GPU",
                LEN_MIN=150, LEN_MAX=150, READ_ERR=0.005, SUB_ONLY=True, PARTIAL=1, MIN_OLAP=40, HASH_BITS=24, SEED=1004, REF_SCALE_MBP=5),
